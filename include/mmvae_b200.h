@@ -1,0 +1,148 @@
+/* mmvae_b200.h — C ABI of libmmvae_b200.so: the B200 (sm_100a) kernels behind bivae's multimodal-ELBO hot path.
+ *
+ * The reference (clementchadebec/mmvae, package `bivae`) has no FFI: its "plugin boundary" for this path is a
+ * duck-typed Python API.  Each entry point below replaces one group of eager-PyTorch ops the
+ * reference issues; the reference file:line it replaces is cited beside it (paths relative to
+ * /root/reference/src/bivae).  The ctypes binding a maintainer would add is shown in INTEGRATION.md and is what
+ * mmvae_b200/_lib.py does.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer to contiguous fp32 unless stated; nothing is owned or freed here;
+ *  - `stream` is a cudaStream_t passed as void* (0 = legacy default stream); all work is enqueued on it, no call
+ *    synchronises, so every call is CUDA-graph capturable;
+ *  - return value: 0 = ok, 1 = invalid argument, 1000+e = cudaError_t e.  mmvae_last_error() gives a message;
+ *  - layouts: K-major sample stacking as in the reference: element (k,b) of a (K,B,...) tensor is row k*B+b
+ *    (mmvae.py:41-54); evaluators use (B,K,...) (mmvae.py:133).
+ */
+#ifndef MMVAE_B200_H
+#define MMVAE_B200_H
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MMVAE_ABI_VERSION 1
+
+/* posterior / prior family of the latent (params.dist; multi_vaes.py:25) */
+#define MMVAE_DIST_NORMAL   0
+#define MMVAE_DIST_LAPLACE  1
+/* decoder likelihood (params.recon_losses; multi_vaes.py:45-46) */
+#define MMVAE_LIK_NORMAL    0
+#define MMVAE_LIK_LAPLACE   1
+#define MMVAE_LIK_BERNOULLI 2
+/* how the second encoder head becomes a scale */
+#define MMVAE_XFORM_EXP_HALF      0  /* std = exp(0.5*raw)            vae_model_adapted.py:84 */
+#define MMVAE_XFORM_SOFTMAX       1  /* std = softmax(raw)*L + 1e-6   laplace_vae.py:69 */
+#define MMVAE_XFORM_EXP_HALF_EPS  2  /* std = exp(0.5*raw) + 1e-6     joint_encoders.py:81-82 */
+/* objective modes of the mixture-of-experts log-weight kernel */
+#define MMVAE_OBJ_IWAE         0  /* objectives.py:117-131,333-340 */
+#define MMVAE_OBJ_IWAE_LOOSER  1  /* objectives.py:343-369 */
+#define MMVAE_OBJ_DREG         2  /* objectives.py:372-403 */
+#define MMVAE_OBJ_DREG_LOOSER  3  /* objectives.py:406-438 */
+/* GEMM epilogue activations */
+#define MMVAE_ACT_NONE    0
+#define MMVAE_ACT_RELU    1
+#define MMVAE_ACT_SIGMOID 2
+
+int         mmvae_abi_version(void);
+const char* mmvae_last_error(void);
+/* 1 if the library was compiled with the tcgen05/TMA GEMM and the device is sm_100; 0 otherwise */
+int         mmvae_has_tcgen05(void);
+
+/* ---- kernel (1): fused reparameterised rsample, all modalities and all K in one launch ---------------------
+ * replaces laplace_vae.py:69-71, vae_model_adapted.py:84-86,133-137 on the K-tiled batch of mmvae.py:41-47.
+ * mu,raw: [M,B,L]; noise: [M,K,B,L] (u~U(eps-1,1) for Laplace, eps~N(0,1) for Normal); out z: [M,K,B,L],
+ * std: [M,B,L].  If bk_layout != 0 noise and z are [M,B,K,L] (evaluator layout). */
+int mmvae_rsample_fwd(const float* mu, const float* raw, const float* noise, float* z, float* std,
+                      int M, int K, int B, int L, int dist, int xform, int bk_layout, void* stream);
+/* grad_z: [M,K,B,L]; grad_std_direct: [M,B,L] or NULL (gradient reaching std other than through z);
+ * out grad_mu, grad_raw: [M,B,L]. */
+int mmvae_rsample_bwd(const float* grad_z, const float* grad_std_direct, const float* noise, const float* raw,
+                      const float* std, float* grad_mu, float* grad_raw,
+                      int M, int K, int B, int L, int dist, int xform, int bk_layout, void* stream);
+
+/* ---- kernel (2): decoder log-likelihood reduced over pixels ------------------------------------------------
+ * replaces px_z(recon, 1).log_prob(x).view(K,B,-1).mul(lik_scaling).sum(-1) (objectives.py:381-385,416-419;
+ * mmvae.py:154-156).  recon: [R,D]; x: [B,D]; row r uses x row (r / x_div) % B  (training: x_div=1; evaluator
+ * (B,K) layout: x_div=K).  out lp: [R].  D % 4 == 0. */
+int mmvae_loglik_fwd(const float* recon, const float* x, float* lp, int R, int B, int D, int x_div,
+                     int lik, float lik_scaling, void* stream);
+/* grad_lp: [R]; out grad: [R,D].  If through_sigmoid != 0, `recon` is sigmoid(h) and the output is the gradient
+ * w.r.t. the pre-activation h (fuses the decoder's final Sigmoid backward, encoders.py:128, pythae Decoder_AE_MLP). */
+int mmvae_loglik_bwd(const float* grad_lp, const float* recon, const float* x, float* grad, int R, int B, int D,
+                     int x_div, int lik, float lik_scaling, int through_sigmoid, void* stream);
+
+/* ---- kernel (3): cross-modal log q mixture, two-level logsumexp, objective and stop-gradient weights --------
+ * replaces objectives.py:117-131 / 343-359 / 372-403 / 406-438 after model(x,K).
+ * z: [M,K,B,L]; mu,std: [M,B,L]; lpx: [M(expert),M(decoder),K,B] (already lik-scaled); pz_loc,pz_scale: [L].
+ * out lw: [M,K,B]; wt: [M,K,B] = d loss / d lw (softmax weights incl. the 1/M of `looser`);
+ * loss: [1] = objective (sum over datapoints); loss_per: [B] = each datapoint's term. */
+int mmvae_moe_logw_fwd(const float* z, const float* mu, const float* std, const float* lpx,
+                       const float* pz_loc, const float* pz_scale, float* lw, float* wt, float* loss,
+                       float* loss_per, int M, int K, int B, int L, int dist, int mode, void* stream);
+/* grad_loss: [1] (device scalar).  out grad_z [M,K,B,L], grad_lpx [M,M,K,B]; grad_mu, grad_std [M,B,L] are the
+ * gradients through log q only (zero in the DReG modes: params detached, objectives.py:376,411). */
+int mmvae_moe_logw_bwd(const float* grad_loss, const float* z, const float* mu, const float* std, const float* wt,
+                       const float* pz_loc, const float* pz_scale, float* grad_z, float* grad_mu, float* grad_std,
+                       float* grad_lpx, int M, int K, int B, int L, int dist, int mode, void* stream);
+
+/* m_elbo (objectives.py:87-111): closed-form KL + importance ratio on the diagonal decoders.
+ * lpx_diag: [M,K,B]; out loss [1], loss_per [B] (as above), terms [M*M] (sum over k,b of w*lpx for (r,d), the `details` dict). */
+int mmvae_elbo_fwd(const float* z, const float* mu, const float* std, const float* lpx_diag,
+                   const float* pz_loc, const float* pz_scale, float* loss, float* loss_per, float* terms,
+                   int M, int K, int B, int L, int dist, void* stream);
+int mmvae_elbo_bwd(const float* grad_loss, const float* z, const float* mu, const float* std,
+                   const float* lpx_diag, const float* pz_loc, const float* pz_scale,
+                   float* grad_mu, float* grad_std, float* grad_lpx_diag,
+                   int M, int K, int B, int L, int dist, void* stream);
+
+/* importance-sampled log-likelihood combine (mmvae.py:139-175, multi_vaes.py:290-316, jmvae_nf.py:231-268):
+ * a: [B,Kc] log-weights of one K-shard -> per-datapoint running (max, sum exp(a-max)): mx,se: [B].
+ * If accumulate != 0 the shard is merged into the existing (mx,se).  finish: ll[b] = mx + log(se) - log(K_total). */
+int mmvae_lse_partial(const float* a, float* mx, float* se, int B, int Kc, int accumulate, void* stream);
+int mmvae_lse_finish(const float* mx, const float* se, float* ll, int B, float log_K_total, void* stream);
+/* evaluator log-weights: a[b,k] = sum_d lpx[d,b,k] + log p(z) - mixture term.  z: [B,K,L]; mu,std: [E,B,L]
+ * (E experts in the proposal); qmode 0: -logsumexp_e(lq)/2 (mmvae.py:166 quirk), 1: -(logsumexp_e - log E),
+ * 2: -lq_0 (single proposal), 3: no q term (z from the prior), 4: minus the given lq_ext[B,K]. */
+int mmvae_eval_logw(const float* z, const float* mu, const float* std, const float* lpx, const float* lq_ext,
+                    const float* pz_loc, const float* pz_scale, float* a,
+                    int E, int D, int B, int K, int L, int dist, int qmode, void* stream);
+
+/* ---- kernel (4): dense contractions ------------------------------------------------------------------------
+ * C[M,N] = act( A * B + bias ), fp32 in/out, fp32 accumulate.  a_kmajor: A stored [M,K] (k contiguous) else
+ * [K,M]; b_kmajor: B stored [N,K] (k contiguous, nn.Linear weight layout) else [K,N].  bias: [N] or NULL.
+ * workspace: NULL or >= mmvae_gemm_workspace_bytes() bytes (split-K partials).  replaces torch.nn.Linear /
+ * F.linear calls of pythae Encoder_VAE_MLP/Decoder_AE_MLP, joint_encoders.py:61-82, encoders.py:181-210 and,
+ * through the lowering below, Conv2d/ConvTranspose2d of encoders.py:80-136; and their autograd backward. */
+int mmvae_gemm(const float* A, const float* B, const float* bias, float* C, int M, int N, int K,
+               int a_kmajor, int b_kmajor, int act, float* workspace, long workspace_bytes, int allow_tc,
+               void* stream);
+long mmvae_gemm_workspace_bytes(int M, int N, int K);
+/* column sums: out[n] = sum_m A[m,n]  (bias gradients); workspace >= mmvae_colsum_workspace_bytes(M,N) */
+int  mmvae_colsum(const float* A, float* out, float* workspace, int M, int N, void* stream);
+long mmvae_colsum_workspace_bytes(int M, int N);
+/* activation backward: out = g * act'(y)  (relu: y>0; sigmoid: y(1-y)); out may alias g */
+int mmvae_act_bwd(const float* g, const float* y, float* out, long n, int act, void* stream);
+
+/* conv lowering.  Activations are NHWC internally; generic element strides (sn,sc,sy,sx) describe the tensor at
+ * the boundary.  Weights are used in permuted form: conv Wp[Cout,(ky,kx,ci)], convT Wp[Cin,(ky,kx,co)]. */
+int mmvae_permute_weight(const float* w, float* wp, int C0, int C1, int kk, int to_permuted, void* stream);
+/* im2col: x (N,C,H,W by strides) -> col[N*Ho*Wo, k*k*C]; Ho=(H+2p-k)/s+1 */
+int mmvae_im2col(const float* x, float* col, int N, int C, int H, int W, int k, int s, int p,
+                 long sn, long sc, long sy, long sx, void* stream);
+/* col2im (gather form, deterministic): col[N*H*W, k*k*C] -> y (N,C,Ho,Wo by strides), Ho=(H-1)s-2p+k; adds
+ * bias[C] (or NULL) and applies act. */
+int mmvae_col2im(const float* col, const float* bias, float* y, int N, int C, int H, int W, int k, int s, int p,
+                 long sn, long sc, long sy, long sx, int act, void* stream);
+
+/* MADE / MAF / IAF elementwise pieces (maf_model.py:62-74,91-104; iaf_model.py:60-78,94-100) */
+int mmvae_mask_weight(const float* w, const float* mask, float* out, long n, void* stream);
+
+/* fused multi-tensor Adam(amsgrad) over one flat buffer (main.py:114-115).  step_dev: device fp32 scalar holding
+ * the number of steps taken so far; this call increments it first (so the update is CUDA-graph replayable). */
+int mmvae_adam_amsgrad(float* p, const float* g, float* m, float* v, float* vmax, long n, float lr, float beta1,
+                       float beta2, float eps, float* step_dev, int amsgrad, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

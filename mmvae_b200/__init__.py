@@ -1,0 +1,12 @@
+"""mmvae_b200 — B200-native (sm_100a) implementation of bivae's multimodal-ELBO hot path behind the reference's
+model / objective API.  Importing the package loads libmmvae_b200.so and fails loudly when it is missing."""
+from . import _lib
+
+_lib.load()
+
+from . import objectives, ops  # noqa: E402
+from .models import (MMVAE, MNIST_SVHN, CIRCLES_SQUARES, MNIST_SVHN_FASHION, Multi_VAES, VAE_circles_squares,  # noqa: E402
+                     VAE_mmvae_msf, VAE_mnist_svhn)
+
+__all__ = ["objectives", "ops", "MMVAE", "Multi_VAES", "MNIST_SVHN", "CIRCLES_SQUARES", "MNIST_SVHN_FASHION",
+           "VAE_mnist_svhn", "VAE_circles_squares", "VAE_mmvae_msf"]

@@ -1,0 +1,226 @@
+// Kernel (4), exact-fp32 path: tiled SIMT GEMM with fused bias + activation epilogue and deterministic split-K.
+// C[M,N] = act(A*B + bias).  Used for every shape the tcgen05 path does not take (skinny K = latent dim, tiny M,
+// unaligned sizes) and as the bit-honest fp32 cross-check of the tensor-core path.
+// Reference ops replaced: torch.nn.Linear / F.linear (pythae Encoder_VAE_MLP / Decoder_AE_MLP; joint_encoders.py:61-82;
+// encoders.py:181-210; layers.py:24-25) and, through conv_lower.cu, Conv2d / ConvTranspose2d (encoders.py:80-136),
+// plus their autograd backward (dgrad: a_kmajor=1,b_kmajor=0; wgrad: a_kmajor=0,b_kmajor=0).
+#include "common.cuh"
+
+#define G_BM 128
+#define G_BK 16
+#define G_PAD 4
+#define G_THREADS 256
+
+__device__ __forceinline__ float apply_act(float v, int act) {
+    if (act == MMVAE_ACT_RELU) return fmaxf(v, 0.f);
+    if (act == MMVAE_ACT_SIGMOID) return 1.f / (1.f + expf(-v));
+    return v;
+}
+
+// Load one (ROWS x G_BK) operand tile into registers.  KMAJOR: src[row*ld + k] ; else src[k*ld + row].
+// Each thread owns NV float4 (vector path) — zero-filled outside [0,rows_total) x [k_begin,k_end).
+template <int ROWS, bool KMAJOR>
+struct TileLoader {
+    static constexpr int NV = ROWS * G_BK / 4 / G_THREADS;      // float4 per thread
+    float4 v[NV];
+    __device__ __forceinline__ void load(const float* __restrict__ src, int ld, int row0, int rows_total, int k0,
+                                         int k_end, bool vec_ok) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int f = threadIdx.x + i * G_THREADS;
+            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (KMAJOR) {
+                const int row = f / (G_BK / 4), kq = (f % (G_BK / 4)) * 4;
+                const int gr = row0 + row, gk = k0 + kq;
+                if (gr < rows_total) {
+                    const float* p = src + (long)gr * ld + gk;
+                    if (vec_ok && gk + 3 < k_end) t = *reinterpret_cast<const float4*>(p);
+                    else {
+                        if (gk < k_end) t.x = p[0];
+                        if (gk + 1 < k_end) t.y = p[1];
+                        if (gk + 2 < k_end) t.z = p[2];
+                        if (gk + 3 < k_end) t.w = p[3];
+                    }
+                }
+            } else {
+                const int k = f / (ROWS / 4), rq = (f % (ROWS / 4)) * 4;
+                const int gk = k0 + k, gr = row0 + rq;
+                if (gk < k_end) {
+                    const float* p = src + (long)gk * ld + gr;
+                    if (vec_ok && gr + 3 < rows_total) t = *reinterpret_cast<const float4*>(p);
+                    else {
+                        if (gr < rows_total) t.x = p[0];
+                        if (gr + 1 < rows_total) t.y = p[1];
+                        if (gr + 2 < rows_total) t.z = p[2];
+                        if (gr + 3 < rows_total) t.w = p[3];
+                    }
+                }
+            }
+            v[i] = t;
+        }
+    }
+    // smem tile layout: s[k][row], row stride ROWS + G_PAD
+    __device__ __forceinline__ void store(float* __restrict__ s) const {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int f = threadIdx.x + i * G_THREADS;
+            if (KMAJOR) {
+                const int row = f / (G_BK / 4), kq = (f % (G_BK / 4)) * 4;
+                s[(kq + 0) * (ROWS + G_PAD) + row] = v[i].x;
+                s[(kq + 1) * (ROWS + G_PAD) + row] = v[i].y;
+                s[(kq + 2) * (ROWS + G_PAD) + row] = v[i].z;
+                s[(kq + 3) * (ROWS + G_PAD) + row] = v[i].w;
+            } else {
+                const int k = f / (ROWS / 4), rq = (f % (ROWS / 4)) * 4;
+                *reinterpret_cast<float4*>(&s[k * (ROWS + G_PAD) + rq]) = v[i];
+            }
+        }
+    }
+};
+
+// grid: (ceil(N/BN), ceil(M/BM), S).  S == 1: writes act(acc+bias) to C; S > 1: raw partials to ws[z][M][N].
+template <int BN, bool A_KMAJOR, bool B_KMAJOR>
+__global__ void __launch_bounds__(G_THREADS, 2)
+gemm_simt_kernel(const float* __restrict__ A, const float* __restrict__ Bm, const float* __restrict__ bias,
+                 float* __restrict__ C, float* __restrict__ ws, int M, int N, int K, int act, int tiles_per_split) {
+    constexpr int TN = BN / 16;                                   // columns per thread (8 or 4)
+    __shared__ __align__(16) float As[2][G_BK][G_BM + G_PAD];
+    __shared__ __align__(16) float Bs[2][G_BK][BN + G_PAD];
+    const int m0 = blockIdx.y * G_BM, n0 = blockIdx.x * BN;
+    const int kt_begin = blockIdx.z * tiles_per_split;
+    const int nk_total = (K + G_BK - 1) / G_BK;
+    const int kt_end = min(nk_total, kt_begin + tiles_per_split);
+    const int lda = A_KMAJOR ? K : M, ldb = B_KMAJOR ? K : N;
+    const bool a_vec = (((uintptr_t)A & 15) == 0) && (lda % 4 == 0);
+    const bool b_vec = (((uintptr_t)Bm & 15) == 0) && (ldb % 4 == 0);
+    const int ty = threadIdx.x / 16, tx = threadIdx.x % 16;
+
+    float acc[8][TN];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+
+    TileLoader<G_BM, A_KMAJOR> la;
+    TileLoader<BN, B_KMAJOR> lb;
+    if (kt_begin < kt_end) {
+        la.load(A, lda, m0, M, kt_begin * G_BK, K, a_vec);
+        lb.load(Bm, ldb, n0, N, kt_begin * G_BK, K, b_vec);
+        la.store(&As[0][0][0]);
+        lb.store(&Bs[0][0][0]);
+    }
+    __syncthreads();
+    int cur = 0;
+    for (int kt = kt_begin; kt < kt_end; ++kt) {
+        const bool more = (kt + 1 < kt_end);
+        if (more) {
+            la.load(A, lda, m0, M, (kt + 1) * G_BK, K, a_vec);
+            lb.load(Bm, ldb, n0, N, (kt + 1) * G_BK, K, b_vec);
+        }
+#pragma unroll
+        for (int kk = 0; kk < G_BK; ++kk) {
+            const float4 a0 = *reinterpret_cast<const float4*>(&As[cur][kk][ty * 4]);
+            const float4 a1 = *reinterpret_cast<const float4*>(&As[cur][kk][64 + ty * 4]);
+            const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            float bv[TN];
+            const float4 b0 = *reinterpret_cast<const float4*>(&Bs[cur][kk][tx * 4]);
+            bv[0] = b0.x; bv[1] = b0.y; bv[2] = b0.z; bv[3] = b0.w;
+            if (TN == 8) {
+                const float4 b1 = *reinterpret_cast<const float4*>(&Bs[cur][kk][BN / 2 + tx * 4]);
+                bv[TN - 4] = b1.x; bv[TN - 3] = b1.y; bv[TN - 2] = b1.z; bv[TN - 1] = b1.w;
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+        if (more) {
+            la.store(&As[cur ^ 1][0][0]);
+            lb.store(&Bs[cur ^ 1][0][0]);
+        }
+        __syncthreads();
+        cur ^= 1;
+    }
+
+    const bool split = (gridDim.z > 1);
+    float* out = split ? ws + (long)blockIdx.z * M * N : C;
+    const bool c_vec = (((uintptr_t)out & 15) == 0) && (N % 4 == 0);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int gm = m0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
+        if (gm >= M) continue;
+#pragma unroll
+        for (int h = 0; h < TN / 4; ++h) {
+            const int gn = n0 + (h == 0 ? tx * 4 : BN / 2 + tx * 4);
+            float r[4] = {acc[i][h * 4 + 0], acc[i][h * 4 + 1], acc[i][h * 4 + 2], acc[i][h * 4 + 3]};
+            if (!split) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (gn + j < N) r[j] = apply_act(r[j] + (bias ? bias[gn + j] : 0.f), act);
+            }
+            float* p = out + (long)gm * N + gn;
+            if (c_vec && gn + 3 < N) *reinterpret_cast<float4*>(p) = make_float4(r[0], r[1], r[2], r[3]);
+            else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (gn + j < N) p[j] = r[j];
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+splitk_reduce_kernel(const float* __restrict__ ws, const float* __restrict__ bias, float* __restrict__ C, long MN,
+                     int N, int S, int act) {
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < MN; i += (long)gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int z = 0; z < S; ++z) s += ws[(long)z * MN + i];
+        if (bias) s += bias[i % N];
+        C[i] = apply_act(s, act);
+    }
+}
+
+static int pick_splits(int M, int N, int K, int BN) {
+    const long tiles = (long)((M + G_BM - 1) / G_BM) * ((N + BN - 1) / BN);
+    const int nk = (K + G_BK - 1) / G_BK;
+    if (tiles >= MMVAE_NUM_SMS || nk < 8) return 1;
+    long s = (2L * MMVAE_NUM_SMS + tiles - 1) / tiles;
+    if (s > nk / 4) s = nk / 4;
+    if (s > 64) s = 64;
+    return s < 1 ? 1 : (int)s;
+}
+
+extern "C" long mmvae_gemm_workspace_bytes(int M, int N, int K) {
+    const int BN = (N <= 64) ? 64 : 128;
+    const int S = pick_splits(M, N, K, BN);
+    return S > 1 ? (long)S * M * N * (long)sizeof(float) : 0;
+}
+
+template <int BN>
+static void launch_simt(const float* A, const float* B, const float* bias, float* C, float* ws, int M, int N, int K,
+                        int a_k, int b_k, int act, int S, cudaStream_t st) {
+    const int nk = (K + G_BK - 1) / G_BK;
+    const int tps = (nk + S - 1) / S;
+    dim3 grid((N + BN - 1) / BN, (M + G_BM - 1) / G_BM, S);
+    if (a_k && b_k) gemm_simt_kernel<BN, true, true><<<grid, G_THREADS, 0, st>>>(A, B, bias, C, ws, M, N, K, act, tps);
+    else if (a_k && !b_k) gemm_simt_kernel<BN, true, false><<<grid, G_THREADS, 0, st>>>(A, B, bias, C, ws, M, N, K, act, tps);
+    else if (!a_k && b_k) gemm_simt_kernel<BN, false, true><<<grid, G_THREADS, 0, st>>>(A, B, bias, C, ws, M, N, K, act, tps);
+    else gemm_simt_kernel<BN, false, false><<<grid, G_THREADS, 0, st>>>(A, B, bias, C, ws, M, N, K, act, tps);
+}
+
+int mmvae_gemm_simt(const float* A, const float* B, const float* bias, float* C, int M, int N, int K, int a_kmajor,
+                    int b_kmajor, int act, float* workspace, long workspace_bytes, cudaStream_t st) {
+    const int BN = (N <= 64) ? 64 : 128;
+    int S = pick_splits(M, N, K, BN);
+    if (S > 1 && (!workspace || workspace_bytes < (long)S * M * N * (long)sizeof(float))) S = 1;
+    if (BN == 64) launch_simt<64>(A, B, bias, C, workspace, M, N, K, a_kmajor, b_kmajor, act, S, st);
+    else launch_simt<128>(A, B, bias, C, workspace, M, N, K, a_kmajor, b_kmajor, act, S, st);
+    MMVAE_LAUNCH_CHECK("gemm_simt");
+    if (S > 1) {
+        const long MN = (long)M * N;
+        const int grid = (int)min((long)MMVAE_NUM_SMS * 4, (MN + 255) / 256);
+        splitk_reduce_kernel<<<grid, 256, 0, st>>>(workspace, bias, C, MN, N, S, act);
+        MMVAE_LAUNCH_CHECK("splitk_reduce");
+    }
+    return 0;
+}

@@ -1,0 +1,143 @@
+// Library plumbing (error reporting, ABI version), the GEMM dispatcher, and the small elementwise / reduction
+// kernels around the contractions: bias gradients, activation backward, MADE weight masking, affine flow
+// transforms, fused Adam(amsgrad).
+#include <stdarg.h>
+#include "common.cuh"
+
+char g_mmvae_err[512] = "";
+
+int mmvae_set_error(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_mmvae_err, sizeof(g_mmvae_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+extern "C" const char* mmvae_last_error(void) { return g_mmvae_err; }
+extern "C" int mmvae_abi_version(void) { return MMVAE_ABI_VERSION; }
+
+int mmvae_gemm_simt(const float* A, const float* B, const float* bias, float* C, int M, int N, int K, int a_kmajor,
+                    int b_kmajor, int act, float* workspace, long workspace_bytes, cudaStream_t st);
+int mmvae_gemm_tc(const float* A, const float* B, const float* bias, float* C, int M, int N, int K, int a_kmajor,
+                  int b_kmajor, int act, float* workspace, long workspace_bytes, cudaStream_t st);
+int mmvae_gemm_tc_supported(int M, int N, int K, int a_kmajor, int b_kmajor);
+
+extern "C" int mmvae_gemm(const float* A, const float* B, const float* bias, float* C, int M, int N, int K,
+                          int a_kmajor, int b_kmajor, int act, float* workspace, long workspace_bytes, int allow_tc,
+                          void* stream) {
+    MMVAE_REQUIRE(A && B && C, "gemm: null pointer");
+    MMVAE_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: bad sizes M=%d N=%d K=%d", M, N, K);
+    MMVAE_REQUIRE(act >= 0 && act <= 2, "gemm: bad activation %d", act);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (allow_tc && mmvae_gemm_tc_supported(M, N, K, a_kmajor, b_kmajor))
+        return mmvae_gemm_tc(A, B, bias, C, M, N, K, a_kmajor, b_kmajor, act, workspace, workspace_bytes, st);
+    return mmvae_gemm_simt(A, B, bias, C, M, N, K, a_kmajor, b_kmajor, act, workspace, workspace_bytes, st);
+}
+
+// ---- column sums (bias gradients): out[n] = sum_m A[m,n].  Two deterministic stages. ---------------------------
+#define CS_ROWS_PER_BLOCK 256
+__global__ void __launch_bounds__(256)
+colsum_stage1(const float* __restrict__ A, float* __restrict__ part, int M, int N) {
+    // block (bx, by): columns bx*32..+32, rows by*CS_ROWS..; 256 threads = 8 row-lanes x 32 columns
+    __shared__ float sm[8][33];
+    const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+    const int n = blockIdx.x * 32 + cx;
+    const int m_begin = blockIdx.y * CS_ROWS_PER_BLOCK;
+    const int m_end = min(M, m_begin + CS_ROWS_PER_BLOCK);
+    float s = 0.f;
+    if (n < N)
+        for (int m = m_begin + ry; m < m_end; m += 8) s += A[(long)m * N + n];
+    sm[ry][cx] = s;
+    __syncthreads();
+    if (ry == 0 && n < N) {
+        float t = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) t += sm[j][cx];
+        part[(long)blockIdx.y * N + n] = t;
+    }
+}
+__global__ void colsum_stage2(const float* __restrict__ part, float* __restrict__ out, int P, int N) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    float s = 0.f;
+    for (int p = 0; p < P; ++p) s += part[(long)p * N + n];
+    out[n] = s;
+}
+
+extern "C" long mmvae_colsum_workspace_bytes(int M, int N) {
+    return (long)((M + CS_ROWS_PER_BLOCK - 1) / CS_ROWS_PER_BLOCK) * N * (long)sizeof(float);
+}
+extern "C" int mmvae_colsum(const float* A, float* out, float* workspace, int M, int N, void* stream) {
+    MMVAE_REQUIRE(A && out && workspace && M > 0 && N > 0, "colsum: bad arguments");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int P = (M + CS_ROWS_PER_BLOCK - 1) / CS_ROWS_PER_BLOCK;
+    colsum_stage1<<<dim3((N + 31) / 32, P), 256, 0, st>>>(A, workspace, M, N);
+    MMVAE_LAUNCH_CHECK("colsum_stage1");
+    colsum_stage2<<<(N + 127) / 128, 128, 0, st>>>(workspace, out, P, N);
+    MMVAE_LAUNCH_CHECK("colsum_stage2");
+    return 0;
+}
+
+// ---- activation backward, in place: g *= act'(y) ---------------------------------------------------------------
+__global__ void act_bwd_kernel(const float* g, const float* __restrict__ y, float* out, long n, int act) {
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+        const float v = y[i], gi = g[i];
+        out[i] = (act == MMVAE_ACT_RELU) ? (v > 0.f ? gi : 0.f) : gi * v * (1.f - v);
+    }
+}
+extern "C" int mmvae_act_bwd(const float* g, const float* y, float* out, long n, int act, void* stream) {
+    MMVAE_REQUIRE(g && y && out && n > 0, "act_bwd: bad arguments");
+    MMVAE_REQUIRE(act == MMVAE_ACT_RELU || act == MMVAE_ACT_SIGMOID, "act_bwd: bad activation %d", act);
+    const int grid = (int)min((long)MMVAE_NUM_SMS * 16, (n + 255) / 256);
+    act_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(g, y, out, n, act);
+    MMVAE_LAUNCH_CHECK("act_bwd");
+    return 0;
+}
+
+// ---- MADE: out = w * mask (layers.py:24-25), used for the weight and for its gradient ---------------------------
+__global__ void mask_weight_kernel(const float* __restrict__ w, const float* __restrict__ mask, float* __restrict__ out,
+                                   long n) {
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
+        out[i] = w[i] * mask[i];
+}
+extern "C" int mmvae_mask_weight(const float* w, const float* mask, float* out, long n, void* stream) {
+    MMVAE_REQUIRE(w && mask && out && n > 0, "mask_weight: bad arguments");
+    const int grid = (int)min((long)MMVAE_NUM_SMS * 4, (n + 255) / 256);
+    mask_weight_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(w, mask, out, n);
+    MMVAE_LAUNCH_CHECK("mask_weight");
+    return 0;
+}
+
+// ---- fused Adam / AMSGrad over one flat parameter buffer (torch.optim.Adam semantics; main.py:114-115) ----------
+__global__ void adam_step_kernel(float* step) { step[0] += 1.f; }
+__global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                            float* __restrict__ v, float* __restrict__ vmax, long n, float lr, float b1, float b2,
+                            float eps, const float* __restrict__ step, int amsgrad) {
+    const float t = step[0];                                   // device-resident step count: CUDA-graph replayable
+    const float bc1 = 1.f - powf(b1, t);
+    const float bc2_sqrt = sqrtf(1.f - powf(b2, t));
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+        const float gi = g[i];
+        const float mi = b1 * m[i] + (1.f - b1) * gi;
+        const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+        m[i] = mi;
+        v[i] = vi;
+        float vv = vi;
+        if (amsgrad) {
+            vv = fmaxf(vmax[i], vi);
+            vmax[i] = vv;
+        }
+        const float denom = sqrtf(vv) / bc2_sqrt + eps;
+        p[i] -= (lr / bc1) * (mi / denom);
+    }
+}
+extern "C" int mmvae_adam_amsgrad(float* p, const float* g, float* m, float* v, float* vmax, long n, float lr,
+                                  float beta1, float beta2, float eps, float* step_dev, int amsgrad, void* stream) {
+    MMVAE_REQUIRE(p && g && m && v && (vmax || !amsgrad) && n > 0 && step_dev, "adam: bad arguments");
+    const int grid = (int)min((long)MMVAE_NUM_SMS * 8, (n + 255) / 256);
+    adam_step_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(step_dev);
+    adam_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(p, g, m, v, vmax, n, lr, beta1, beta2, eps, step_dev, amsgrad);
+    MMVAE_LAUNCH_CHECK("adam");
+    return 0;
+}

@@ -1,0 +1,434 @@
+"""torch.autograd bindings of the C-ABI kernels (forward + registered backward).  Device fp32 only; every op raises
+if handed a CPU tensor — there is no eager / CPU fallback on the product path.
+
+Layouts: see include/mmvae_b200.h.  Image activations are carried as tensors of LOGICAL shape (N,C,H,W) whose memory
+is channels-last (NHWC) between layers; the lowering kernels take explicit strides so NCHW tensors at the boundary
+need no transpose pass.
+"""
+import ctypes
+import math
+
+import torch
+
+from . import _lib
+
+C = _lib.CONSTS
+DIST = {"normal": C["MMVAE_DIST_NORMAL"], "laplace": C["MMVAE_DIST_LAPLACE"]}
+LIK = {"normal": C["MMVAE_LIK_NORMAL"], "laplace": C["MMVAE_LIK_LAPLACE"], "bernoulli": C["MMVAE_LIK_BERNOULLI"]}
+ACT = {None: C["MMVAE_ACT_NONE"], "none": C["MMVAE_ACT_NONE"], "relu": C["MMVAE_ACT_RELU"],
+       "sigmoid": C["MMVAE_ACT_SIGMOID"]}
+XFORM = {"exp_half": C["MMVAE_XFORM_EXP_HALF"], "softmax": C["MMVAE_XFORM_SOFTMAX"],
+         "exp_half_eps": C["MMVAE_XFORM_EXP_HALF_EPS"]}
+OBJ = {"iwae": C["MMVAE_OBJ_IWAE"], "iwae_looser": C["MMVAE_OBJ_IWAE_LOOSER"], "dreg": C["MMVAE_OBJ_DREG"],
+       "dreg_looser": C["MMVAE_OBJ_DREG_LOOSER"]}
+
+# launch counter (bench.py reports gpu_launches from it); counts C-ABI calls, each >= 1 kernel launch
+N_CALLS = 0
+ALLOW_TC = True          # let mmvae_gemm pick the tcgen05 path where it supports the shape
+
+
+def _dev(t, name="tensor"):
+    if not (torch.is_tensor(t) and t.is_cuda and t.dtype == torch.float32):
+        raise RuntimeError(f"mmvae_b200: {name} must be a CUDA float32 tensor (no CPU fallback); got "
+                           f"{type(t).__name__} {getattr(t, 'device', None)} {getattr(t, 'dtype', None)}")
+    return t
+
+
+def _c(t, name="tensor"):
+    _dev(t, name)
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _p(t):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _call(name, *args):
+    global N_CALLS
+    N_CALLS += 1
+    _lib.check(getattr(_lib.load(), name)(*args), name)
+
+
+# ------------------------------------------------------------------------------------------------ raw wrappers
+def gemm(a, b, bias, M, N, K, a_kmajor, b_kmajor, act=None, out=None):
+    """C[M,N] = act(A·B + bias); a/b are 2-D contiguous device tensors in the stated storage order."""
+    lib = _lib.load()
+    out = torch.empty((M, N), device=a.device, dtype=torch.float32) if out is None else out
+    ws_bytes = lib.mmvae_gemm_workspace_bytes(M, N, K)
+    ws = torch.empty(ws_bytes // 4, device=a.device, dtype=torch.float32) if ws_bytes else None
+    _call("mmvae_gemm", _p(a), _p(b), _p(bias), _p(out), M, N, K, int(a_kmajor), int(b_kmajor), ACT[act], _p(ws),
+          ws_bytes, int(ALLOW_TC), _stream())
+    return out
+
+
+def colsum(a2d):
+    M, N = a2d.shape
+    lib = _lib.load()
+    ws = torch.empty(lib.mmvae_colsum_workspace_bytes(M, N) // 4, device=a2d.device, dtype=torch.float32)
+    out = torch.empty(N, device=a2d.device, dtype=torch.float32)
+    _call("mmvae_colsum", _p(a2d), _p(out), _p(ws), M, N, _stream())
+    return out
+
+
+def act_bwd(g, y, act):
+    if ACT[act] == C["MMVAE_ACT_NONE"]:
+        return g
+    out = torch.empty_like(g)
+    _call("mmvae_act_bwd", _p(g), _p(y), _p(out), g.numel(), ACT[act], _stream())
+    return out
+
+
+def permute_weight(w):
+    """torch conv weight [C0,C1,kh,kw] -> lowered 2-D [C0, kh*kw*C1] (tap-major, C1 fastest)."""
+    C0, C1, kh, kw = w.shape
+    out = torch.empty((C0, kh * kw * C1), device=w.device, dtype=torch.float32)
+    _call("mmvae_permute_weight", _p(w), _p(out), C0, C1, kh * kw, 1, _stream())
+    return out
+
+
+def unpermute_weight(wp, shape):
+    C0, C1, kh, kw = shape
+    out = torch.empty(shape, device=wp.device, dtype=torch.float32)
+    _call("mmvae_permute_weight", _p(wp), _p(out), C0, C1, kh * kw, 0, _stream())
+    return out
+
+
+def _strides_nchw(t):
+    """element strides (sn, sc, sy, sx) of a logical (N,C,H,W) tensor."""
+    return t.stride(0), t.stride(1), t.stride(2), t.stride(3)
+
+
+def _dense_image(t):
+    """logical (N,C,H,W) tensor usable by the lowering kernels: non-overlapping and dense in some order."""
+    _dev(t, "image")
+    if t.is_contiguous() or t.is_contiguous(memory_format=torch.channels_last):
+        return t
+    if t.permute(0, 2, 3, 1).is_contiguous():
+        return t
+    return t.contiguous()
+
+
+def im2col(x, k, s, p):
+    N, Cc, H, W = x.shape
+    Ho, Wo = (H + 2 * p - k) // s + 1, (W + 2 * p - k) // s + 1
+    col = torch.empty((N * Ho * Wo, k * k * Cc), device=x.device, dtype=torch.float32)
+    sn, sc, sy, sx = _strides_nchw(x)
+    _call("mmvae_im2col", _p(x), _p(col), N, Cc, H, W, k, s, p, sn, sc, sy, sx, _stream())
+    return col, Ho, Wo
+
+
+def col2im(col, bias, N, Cc, H, W, k, s, p, act=None, nchw_out=False):
+    """col [N*H*W, k*k*C] -> logical (N,C,Ho,Wo); memory NHWC unless nchw_out."""
+    Ho, Wo = (H - 1) * s - 2 * p + k, (W - 1) * s - 2 * p + k
+    if nchw_out:
+        y = torch.empty((N, Cc, Ho, Wo), device=col.device, dtype=torch.float32)
+    else:
+        y = torch.empty((N, Ho, Wo, Cc), device=col.device, dtype=torch.float32).permute(0, 3, 1, 2)
+    sn, sc, sy, sx = _strides_nchw(y)
+    _call("mmvae_col2im", _p(col), _p(bias), _p(y), N, Cc, H, W, k, s, p, sn, sc, sy, sx, ACT[act], _stream())
+    return y
+
+
+def _as_rows(t):
+    """logical (N,C,H,W) -> contiguous matrix [N*H*W, C] (free when the memory is already NHWC)."""
+    N, Cc, H, W = t.shape
+    return t.permute(0, 2, 3, 1).contiguous().view(N * H * W, Cc)
+
+
+# ------------------------------------------------------------------------------------------- autograd functions
+class LinearAct(torch.autograd.Function):
+    """y = act(x @ W^T + b)   (torch.nn.Linear + ReLU/Sigmoid; pythae MLPs, joint_encoders.py:61-82)."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, act):
+        x, w = _c(x, "x"), _c(w, "weight")
+        R, K = x.shape
+        N = w.shape[0]
+        y = gemm(x, w, b, R, N, K, True, True, act)
+        ctx.act = act
+        ctx.save_for_backward(x, w, y if ACT[act] != C["MMVAE_ACT_NONE"] else None)
+        ctx.has_bias = b is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, w, y = ctx.saved_tensors
+        g = act_bwd(_c(gy, "grad"), y, ctx.act)
+        R, K = x.shape
+        N = w.shape[0]
+        gx = gemm(g, w, None, R, K, N, True, False) if ctx.needs_input_grad[0] else None
+        gw = gemm(g, x, None, N, K, R, False, False) if ctx.needs_input_grad[1] else None
+        gb = colsum(g) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        return gx, gw, gb, None
+
+
+class LinearPreact(torch.autograd.Function):
+    """Final decoder layer whose Sigmoid backward is fused into the log-likelihood backward: forward is
+    y = sigmoid(x W^T + b); backward receives the gradient w.r.t. the PRE-activation (see LogLik through_sigmoid)."""
+
+    @staticmethod
+    def forward(ctx, x, w, b):
+        x, w = _c(x, "x"), _c(w, "weight")
+        y = gemm(x, w, b, x.shape[0], w.shape[0], x.shape[1], True, True, "sigmoid")
+        ctx.save_for_backward(x, w)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        x, w = ctx.saved_tensors
+        g = _c(g, "grad")
+        R, K = x.shape
+        N = w.shape[0]
+        gx = gemm(g, w, None, R, K, N, True, False) if ctx.needs_input_grad[0] else None
+        gw = gemm(g, x, None, N, K, R, False, False) if ctx.needs_input_grad[1] else None
+        gb = colsum(g) if ctx.needs_input_grad[2] else None
+        return gx, gw, gb
+
+
+class Conv2dAct(torch.autograd.Function):
+    """y = act(conv2d(x, W, b, stride, pad))  (encoders.py:80-105).  Output memory NHWC, logical (N,Cout,Ho,Wo)."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, stride, pad, act):
+        x = _dense_image(x)
+        w = _c(w, "weight")
+        N, Cin, H, W = x.shape
+        Cout, _, k, _ = w.shape
+        col, Ho, Wo = im2col(x, k, stride, pad)
+        wp = permute_weight(w)
+        y2d = gemm(col, wp, b, N * Ho * Wo, Cout, k * k * Cin, True, True, act)
+        ctx.save_for_backward(col, wp, y2d if ACT[act] != C["MMVAE_ACT_NONE"] else None)
+        ctx.cfg = (N, Cin, H, W, Cout, k, stride, pad, Ho, Wo, act, tuple(w.shape), b is not None,
+                   x.is_contiguous() and Cin > 1)
+        return y2d.view(N, Ho, Wo, Cout).permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, gy):
+        col, wp, y2d = ctx.saved_tensors
+        N, Cin, H, W, Cout, k, s, p, Ho, Wo, act, wshape, has_bias, x_nchw = ctx.cfg
+        g = act_bwd(_as_rows(_dev(gy, "grad")), y2d, act)
+        rows, Kc = N * Ho * Wo, k * k * Cin
+        gx = gw = gb = None
+        if ctx.needs_input_grad[0]:
+            dcol = gemm(g, wp, None, rows, Kc, Cout, True, False)
+            gx = col2im(dcol, None, N, Cin, Ho, Wo, k, s, p, None, nchw_out=x_nchw)
+        if ctx.needs_input_grad[1]:
+            gwp = gemm(g, col, None, Cout, Kc, rows, False, False)
+            gw = unpermute_weight(gwp, wshape)
+        if has_bias and ctx.needs_input_grad[2]:
+            gb = colsum(g)
+        return gx, gw, gb, None, None, None
+
+
+class ConvT2dAct(torch.autograd.Function):
+    """y = act(conv_transpose2d(x, W, b, stride, pad))  (encoders.py:116-136).  W: (Cin,Cout,k,k).
+    preact_grad=True: the incoming gradient is already w.r.t. the pre-activation (fused Sigmoid backward)."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, stride, pad, act, nchw_out, preact_grad):
+        x = _dev(x, "x")
+        w = _c(w, "weight")
+        N, Cin, H, W = x.shape
+        _, Cout, k, _ = w.shape
+        x2d = _as_rows(x)
+        wp = permute_weight(w)                                  # [Cin, k*k*Cout]
+        col = gemm(x2d, wp, None, N * H * W, k * k * Cout, Cin, True, False)
+        y = col2im(col, b, N, Cout, H, W, k, stride, pad, act, nchw_out=nchw_out)
+        keep_y = (ACT[act] != C["MMVAE_ACT_NONE"]) and not preact_grad
+        ctx.save_for_backward(x2d, wp, y if keep_y else None)
+        ctx.cfg = (N, Cin, H, W, Cout, k, stride, pad, act, tuple(w.shape), b is not None, preact_grad)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        x2d, wp, y = ctx.saved_tensors
+        N, Cin, H, W, Cout, k, s, p, act, wshape, has_bias, preact_grad = ctx.cfg
+        gy = _dense_image(gy)
+        if not preact_grad and y is not None:
+            if gy.stride() != y.stride():
+                gy = gy.contiguous(memory_format=torch.channels_last) if y.stride(1) == 1 else gy.contiguous()
+            g = act_bwd(gy, y, act)                              # same memory order as y
+        else:
+            g = gy
+        rows, Kc = N * H * W, k * k * Cout
+        gx = gw = gb = None
+        dcol, _, _ = im2col(g, k, s, p)                          # [N*H*W, k*k*Cout]
+        if ctx.needs_input_grad[0]:
+            gx2d = gemm(dcol, wp, None, rows, Cin, Kc, True, True)
+            gx = gx2d.view(N, H, W, Cin).permute(0, 3, 1, 2)
+        if ctx.needs_input_grad[1]:
+            gwp = gemm(x2d, dcol, None, Cin, Kc, rows, False, False)
+            gw = unpermute_weight(gwp, wshape)
+        if has_bias and ctx.needs_input_grad[2]:
+            gb = colsum(_as_rows(g))
+        return gx, gw, gb, None, None, None, None, None
+
+
+class RSample(torch.autograd.Function):
+    """z[m,k,b,:] = mu[m,b,:] + std[m,b,:] * t(noise[m,k,b,:]);  std from the raw head by `xform`.
+    Returns (z [M,K,B,L] (or [M,B,K,L] when bk_layout), std [M,B,L])."""
+
+    @staticmethod
+    def forward(ctx, mu, raw, noise, dist, xform, bk_layout):
+        mu, raw, noise = _c(mu, "mu"), _c(raw, "raw"), _c(noise, "noise")
+        M, B, L = mu.shape
+        K = noise.shape[2] if bk_layout else noise.shape[1]
+        assert noise.shape == ((M, B, K, L) if bk_layout else (M, K, B, L)), (noise.shape, mu.shape)
+        z = torch.empty_like(noise)
+        std = torch.empty_like(mu)
+        _call("mmvae_rsample_fwd", _p(mu), _p(raw), _p(noise), _p(z), _p(std), M, K, B, L, DIST[dist], XFORM[xform],
+              int(bk_layout), _stream())
+        ctx.save_for_backward(noise, raw, std)
+        ctx.cfg = (M, K, B, L, dist, xform, bk_layout)
+        return z, std
+
+    @staticmethod
+    def backward(ctx, gz, gstd):
+        noise, raw, std = ctx.saved_tensors
+        M, K, B, L, dist, xform, bk = ctx.cfg
+        gz = _c(gz, "grad_z") if gz is not None else torch.zeros_like(noise)
+        gstd = _c(gstd, "grad_std") if gstd is not None else None
+        gmu, graw = torch.empty_like(std), torch.empty_like(std)
+        _call("mmvae_rsample_bwd", _p(gz), _p(gstd), _p(noise), _p(raw), _p(std), _p(gmu), _p(graw), M, K, B, L,
+              DIST[dist], XFORM[xform], int(bk), _stream())
+        return gmu, graw, None, None, None, None
+
+
+class LogLik(torch.autograd.Function):
+    """lp[r] = lik_scaling * sum_j log p(x[(r // x_div) % B, j] | recon[r, j]).  recon [R,D], x [B,D]."""
+
+    @staticmethod
+    def forward(ctx, recon, x, x_div, lik, lik_scaling, through_sigmoid):
+        recon, x = _c(recon, "recon"), _c(x, "x")
+        R, D = recon.shape
+        B = x.shape[0]
+        assert x.shape[1] == D
+        lp = torch.empty(R, device=recon.device, dtype=torch.float32)
+        _call("mmvae_loglik_fwd", _p(recon), _p(x), _p(lp), R, B, D, x_div, LIK[lik], float(lik_scaling), _stream())
+        ctx.save_for_backward(recon, x)
+        ctx.cfg = (R, B, D, x_div, lik, float(lik_scaling), through_sigmoid)
+        return lp
+
+    @staticmethod
+    def backward(ctx, glp):
+        recon, x = ctx.saved_tensors
+        R, B, D, x_div, lik, c, ts = ctx.cfg
+        g = torch.empty_like(recon)
+        _call("mmvae_loglik_bwd", _p(_c(glp, "grad_lp")), _p(recon), _p(x), _p(g), R, B, D, x_div, LIK[lik], c,
+              int(ts), _stream())
+        return g, None, None, None, None, None
+
+
+class MoeLogW(torch.autograd.Function):
+    """Fused mixture-of-experts objective.  Returns (loss scalar, lw [M,K,B], wt [M,K,B], per-datapoint [B])."""
+
+    @staticmethod
+    def forward(ctx, z, mu, std, lpx, pz_loc, pz_scale, dist, mode):
+        z, mu, std, lpx = _c(z, "z"), _c(mu, "mu"), _c(std, "std"), _c(lpx, "lpx")
+        pz_loc, pz_scale = _c(pz_loc.reshape(-1), "pz_loc"), _c(pz_scale.reshape(-1), "pz_scale")
+        M, K, B, L = z.shape
+        assert lpx.shape == (M, M, K, B), lpx.shape
+        lw = torch.empty((M, K, B), device=z.device, dtype=torch.float32)
+        wt = torch.empty_like(lw)
+        loss = torch.empty((), device=z.device, dtype=torch.float32)
+        per = torch.empty(B, device=z.device, dtype=torch.float32)
+        _call("mmvae_moe_logw_fwd", _p(z), _p(mu), _p(std), _p(lpx), _p(pz_loc), _p(pz_scale), _p(lw), _p(wt),
+              _p(loss), _p(per), M, K, B, L, DIST[dist], OBJ[mode], _stream())
+        ctx.save_for_backward(z, mu, std, wt, pz_loc, pz_scale)
+        ctx.cfg = (M, K, B, L, dist, mode)
+        ctx.mark_non_differentiable(lw, wt, per)
+        return loss, lw, wt, per
+
+    @staticmethod
+    def backward(ctx, gloss, _glw, _gwt, _gper):
+        z, mu, std, wt, pz_loc, pz_scale = ctx.saved_tensors
+        M, K, B, L, dist, mode = ctx.cfg
+        g = _c(gloss.reshape(1), "grad_loss")
+        gz = torch.empty_like(z)
+        gmu, gstd = torch.empty_like(mu), torch.empty_like(std)
+        glpx = torch.empty((M, M, K, B), device=z.device, dtype=torch.float32)
+        _call("mmvae_moe_logw_bwd", _p(g), _p(z), _p(mu), _p(std), _p(wt), _p(pz_loc), _p(pz_scale), _p(gz), _p(gmu),
+              _p(gstd), _p(glpx), M, K, B, L, DIST[dist], OBJ[mode], _stream())
+        dreg = mode in ("dreg", "dreg_looser")
+        return gz, (None if dreg else gmu), (None if dreg else gstd), glpx, None, None, None, None
+
+
+class Elbo(torch.autograd.Function):
+    """m_elbo (objectives.py:87-111).  z is used detached (objectives.py:101).  Returns (loss, terms [M*M], per [B])."""
+
+    @staticmethod
+    def forward(ctx, z, mu, std, lpx_diag, pz_loc, pz_scale, dist):
+        z, mu, std, lpx_diag = _c(z, "z"), _c(mu, "mu"), _c(std, "std"), _c(lpx_diag, "lpx")
+        pz_loc, pz_scale = _c(pz_loc.reshape(-1), "pz_loc"), _c(pz_scale.reshape(-1), "pz_scale")
+        M, K, B, L = z.shape
+        assert lpx_diag.shape == (M, K, B)
+        loss = torch.empty((), device=z.device, dtype=torch.float32)
+        per = torch.empty(B, device=z.device, dtype=torch.float32)
+        terms = torch.empty(M * M, device=z.device, dtype=torch.float32)
+        _call("mmvae_elbo_fwd", _p(z), _p(mu), _p(std), _p(lpx_diag), _p(pz_loc), _p(pz_scale), _p(loss), _p(per),
+              _p(terms), M, K, B, L, DIST[dist], _stream())
+        ctx.save_for_backward(z, mu, std, lpx_diag, pz_loc, pz_scale)
+        ctx.cfg = (M, K, B, L, dist)
+        ctx.mark_non_differentiable(terms, per)
+        return loss, terms, per
+
+    @staticmethod
+    def backward(ctx, gloss, _gt, _gp):
+        z, mu, std, lpx_diag, pz_loc, pz_scale = ctx.saved_tensors
+        M, K, B, L, dist = ctx.cfg
+        g = _c(gloss.reshape(1), "grad_loss")
+        gmu, gstd, glpx = torch.empty_like(mu), torch.empty_like(std), torch.empty_like(lpx_diag)
+        _call("mmvae_elbo_bwd", _p(g), _p(z), _p(mu), _p(std), _p(lpx_diag), _p(pz_loc), _p(pz_scale), _p(gmu),
+              _p(gstd), _p(glpx), M, K, B, L, DIST[dist], _stream())
+        return None, gmu, gstd, glpx, None, None, None
+
+
+# ----------------------------------------------------------------------------------- evaluator (no autograd)
+QMODE = {"mixture_half": 0, "mixture": 1, "single": 2, "none": 3, "external": 4}
+
+
+def eval_logw(z, mu, std, lpx, pz_loc, pz_scale, dist, qmode, lq_ext=None):
+    """a[b,k] = sum_d lpx[d,b,k] + log p(z[b,k]) - q-term.  z [B,K,L]; mu,std [E,B,L]; lpx [D,B,K]."""
+    z, lpx = _c(z, "z"), _c(lpx, "lpx")
+    B, K, L = z.shape
+    D = lpx.shape[0]
+    E = 0 if mu is None else mu.shape[0]
+    a = torch.empty((B, K), device=z.device, dtype=torch.float32)
+    _call("mmvae_eval_logw", _p(z), _p(None if mu is None else _c(mu, "mu")), _p(None if std is None else _c(std, "std")),
+          _p(lpx), _p(None if lq_ext is None else _c(lq_ext, "lq_ext")), _p(_c(pz_loc.reshape(-1), "pz_loc")),
+          _p(_c(pz_scale.reshape(-1), "pz_scale")), _p(a), E, D, B, K, L, DIST[dist], QMODE[qmode], _stream())
+    return a
+
+
+def lse_partial(a, mx=None, se=None):
+    """merge the K-shard a [B,Kc] into the running per-datapoint (max, sum exp) pair."""
+    a = _c(a, "a")
+    B, Kc = a.shape
+    acc = mx is not None
+    if not acc:
+        mx = torch.empty(B, device=a.device, dtype=torch.float32)
+        se = torch.empty(B, device=a.device, dtype=torch.float32)
+    _call("mmvae_lse_partial", _p(a), _p(mx), _p(se), B, Kc, int(acc), _stream())
+    return mx, se
+
+
+def lse_finish(mx, se, K_total):
+    ll = torch.empty_like(mx)
+    _call("mmvae_lse_finish", _p(mx), _p(se), _p(ll), mx.numel(), float(math.log(K_total)), _stream())
+    return ll
+
+
+def mask_weight(w, mask):
+    out = torch.empty_like(w)
+    _call("mmvae_mask_weight", _p(_c(w, "w")), _p(_c(mask, "mask")), _p(out), w.numel(), _stream())
+    return out
+
+
+def adam_amsgrad_(p, g, m, v, vmax, step_dev, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, amsgrad=True):
+    """in-place fused Adam(amsgrad) on flat buffers (main.py:114-115)."""
+    _call("mmvae_adam_amsgrad", _p(p), _p(g), _p(m), _p(v), _p(vmax), p.numel(), float(lr), float(betas[0]),
+          float(betas[1]), float(eps), _p(step_dev), int(amsgrad), _stream())

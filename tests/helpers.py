@@ -44,3 +44,31 @@ def check_digests(grads, digests, rtol, what=""):
             continue
         assert abs(f.norm().item() - ref_norm) <= rtol * ref_norm, f"{what}: {k} norm {f.norm().item()} vs {ref_norm}"
         assert err <= rtol * max(scale, 1e-3 * ref_norm), f"{what}: {k} sampled values off by {err / scale:.3e}"
+
+
+# ------------------------------------------------------------------------------------------------ GPU helpers
+def build_mmvae(spec, sd, device="cuda"):
+    """mmvae_b200 MMVAE with the architecture of `spec` and the weights of the reference-keyed state dict `sd`."""
+    import argparse
+    import torch.nn as nn
+    import mmvae_b200
+    from mmvae_b200 import networks as N
+    from mmvae_b200.vaes import VAEConfig, laplace_VAE, my_VAE
+    params = argparse.Namespace(latent_dim=spec.latent_dim, dist=spec.dist, recon_losses=list(spec.recon_losses),
+                                llik_scaling=0.0, device=device, data_path="", epochs=1)
+    vae_cls = my_VAE if spec.vae == "my_VAE" else laplace_VAE
+    vaes = []
+    for m in range(spec.M):
+        cfg = VAEConfig(tuple(spec.shapes[m]), spec.latent_dim)
+        enc = N.Encoder_VAE_MLP(cfg) if spec.enc[m] == "mlp" else N.Encoder_VAE_SVHN(cfg)
+        dec = N.Decoder_AE_MLP(cfg) if spec.dec[m] == "mlp" else N.Decoder_VAE_SVHN(cfg)
+        vaes.append(vae_cls(cfg, enc, dec))
+    model = mmvae_b200.MMVAE(params, nn.ModuleList(vaes))
+    model.lik_scaling = tuple(spec.lik_scaling)
+    model.load_state_dict(sd, strict=True)
+    return model.to(device)
+
+
+def rel_err(a, b):
+    a, b = a.detach().double().cpu().reshape(-1), b.detach().double().cpu().reshape(-1)
+    return ((a - b).norm() / b.norm().clamp_min(1e-30)).item()

@@ -1,0 +1,287 @@
+"""GPU: each C-ABI kernel against a plain torch reference (fp64 where it is a contraction), forward and backward.
+Tolerances are written beside each check."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import bivae_oracle as O
+from tests.helpers import rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ops():
+    import mmvae_b200
+    return mmvae_b200.ops
+
+
+def _rand(*shape, seed=0, scale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).cuda()
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 16), (300, 70, 37), (7680, 512, 20), (512, 20, 7680), (97, 784, 512),
+                                   (1000, 48, 32), (5, 3, 9), (128, 2048, 20)])
+@pytest.mark.parametrize("a_k,b_k", [(1, 1), (1, 0), (0, 1), (0, 0)])
+def test_gemm_layouts(ops, M, N, K, a_k, b_k):
+    A = _rand(M, K, seed=1)
+    B = _rand(N, K, seed=2)
+    bias = _rand(N, seed=3)
+    a_store = A.contiguous() if a_k else A.t().contiguous()
+    b_store = B.contiguous() if b_k else B.t().contiguous()
+    ref = A.double() @ B.double().t()
+    out = ops.gemm(a_store, b_store, None, M, N, K, a_k, b_k)
+    assert rel_err(out, ref) < 2e-6                    # fp32 FMA accumulation vs fp64
+    out = ops.gemm(a_store, b_store, bias, M, N, K, a_k, b_k, "relu")
+    assert rel_err(out, torch.relu(ref + bias.double())) < 2e-6
+    out = ops.gemm(a_store, b_store, bias, M, N, K, a_k, b_k, "sigmoid")
+    assert rel_err(out, torch.sigmoid(ref + bias.double())) < 2e-6
+
+
+def test_colsum_and_act_bwd(ops):
+    A = _rand(1000, 77, seed=4)
+    assert rel_err(ops.colsum(A), A.double().sum(0)) < 1e-6
+    y = torch.sigmoid(_rand(333, 5, seed=5))
+    g = _rand(333, 5, seed=6)
+    assert rel_err(ops.act_bwd(g, y, "sigmoid"), g * y * (1 - y)) < 1e-6
+    y = torch.relu(_rand(333, 5, seed=7))
+    assert torch.equal(ops.act_bwd(g, y, "relu"), g * (y > 0))
+
+
+def test_linear_autograd(ops):
+    x = _rand(50, 20, seed=1).requires_grad_()
+    w = _rand(64, 20, seed=2, scale=0.2).requires_grad_()
+    b = _rand(64, seed=3).requires_grad_()
+    for act, fn in (("relu", torch.relu), ("sigmoid", torch.sigmoid), (None, lambda t: t)):
+        y = ops.LinearAct.apply(x, w, b, act)
+        gy = _rand(50, 64, seed=9)
+        gx, gw, gb = torch.autograd.grad(y, (x, w, b), gy)
+        xd, wd, bd = (t.detach().double().requires_grad_() for t in (x, w, b))
+        yr = fn(xd @ wd.t() + bd)
+        rx, rw, rb = torch.autograd.grad(yr, (xd, wd, bd), gy.double())
+        assert rel_err(y, yr) < 2e-6
+        assert rel_err(gx, rx) < 5e-6 and rel_err(gw, rw) < 5e-6 and rel_err(gb, rb) < 5e-6
+
+
+@pytest.mark.parametrize("cin,cout,H,s,p,nchw_in", [(3, 32, 32, 2, 1, True), (32, 64, 16, 2, 1, False),
+                                                    (128, 20, 4, 2, 0, False), (1, 8, 28, 2, 1, True)])
+def test_conv2d_autograd(ops, cin, cout, H, s, p, nchw_in):
+    N = 5
+    x = _rand(N, cin, H, H, seed=1)
+    if not nchw_in:
+        x = x.permute(0, 2, 3, 1).contiguous().permute(0, 3, 1, 2)        # NHWC memory, logical NCHW
+    x.requires_grad_()
+    w = _rand(cout, cin, 4, 4, seed=2, scale=0.1).requires_grad_()
+    b = _rand(cout, seed=3).requires_grad_()
+    y = ops.Conv2dAct.apply(x, w, b, s, p, "relu")
+    xd, wd, bd = (t.detach().double().requires_grad_() for t in (x, w, b))
+    yr = torch.relu(F.conv2d(xd, wd, bd, stride=s, padding=p))
+    assert y.shape == yr.shape
+    assert rel_err(y, yr) < 2e-6
+    gy = _rand(*yr.shape, seed=4)
+    gx, gw, gb = torch.autograd.grad(y, (x, w, b), gy)
+    rx, rw, rb = torch.autograd.grad(yr, (xd, wd, bd), gy.double())
+    assert rel_err(gx, rx) < 5e-6 and rel_err(gw, rw) < 5e-6 and rel_err(gb, rb) < 5e-6
+
+
+@pytest.mark.parametrize("cin,cout,H,s,p,act,nchw_out", [(20, 128, 1, 1, 0, "relu", False), (128, 64, 4, 2, 1, "relu", False),
+                                                         (32, 3, 16, 2, 1, "sigmoid", True), (64, 32, 8, 2, 1, "relu", False)])
+def test_convT2d_autograd(ops, cin, cout, H, s, p, act, nchw_out):
+    N = 6
+    x = _rand(N, cin, H, H, seed=1).permute(0, 2, 3, 1).contiguous().permute(0, 3, 1, 2).requires_grad_()
+    w = _rand(cin, cout, 4, 4, seed=2, scale=0.1).requires_grad_()
+    b = _rand(cout, seed=3).requires_grad_()
+    y = ops.ConvT2dAct.apply(x, w, b, s, p, act, nchw_out, False)
+    xd, wd, bd = (t.detach().double().requires_grad_() for t in (x, w, b))
+    fn = torch.relu if act == "relu" else torch.sigmoid
+    yr = fn(F.conv_transpose2d(xd, wd, bd, stride=s, padding=p))
+    assert y.shape == yr.shape
+    assert y.is_contiguous() == nchw_out or cout == 1
+    assert rel_err(y, yr) < 2e-6
+    gy = _rand(*yr.shape, seed=4)
+    gx, gw, gb = torch.autograd.grad(y, (x, w, b), gy)
+    rx, rw, rb = torch.autograd.grad(yr, (xd, wd, bd), gy.double())
+    assert rel_err(gx, rx) < 5e-6 and rel_err(gw, rw) < 5e-6 and rel_err(gb, rb) < 5e-6
+
+
+@pytest.mark.parametrize("dist,xform", [("laplace", "softmax"), ("normal", "exp_half"), ("normal", "exp_half_eps")])
+@pytest.mark.parametrize("bk", [False, True])
+def test_rsample(ops, dist, xform, bk):
+    from oracle import synth
+    import numpy as np
+    M, K, B, L = 2, 7, 5, 20
+    mu = _rand(M, B, L, seed=1).requires_grad_()
+    raw = _rand(M, B, L, seed=2).requires_grad_()
+    noise = synth.make_noise(dist, (M, K, B, L), np.random.RandomState(3)).cuda()
+    nz = noise.permute(0, 2, 1, 3).contiguous() if bk else noise
+    z, std = ops.RSample.apply(mu, raw, nz, dist, xform, bk)
+    mud, rawd = mu.detach().double().requires_grad_(), raw.detach().double().requires_grad_()
+    if xform == "softmax":
+        sr = F.softmax(rawd, -1) * L + 1e-6
+    else:
+        sr = torch.exp(0.5 * rawd) + (1e-6 if xform == "exp_half_eps" else 0.0)
+    zr = O.lat_rsample(dist, mud.unsqueeze(1), sr.unsqueeze(1), noise.double())
+    zc = z.permute(0, 2, 1, 3) if bk else z
+    assert rel_err(zc, zr) < 1e-6 and rel_err(std, sr) < 1e-6
+    gz, gs = _rand(M, K, B, L, seed=5), _rand(M, B, L, seed=6)
+    gzz = gz.permute(0, 2, 1, 3).contiguous() if bk else gz
+    gmu, graw = torch.autograd.grad((z, std), (mu, raw), (gzz, gs))
+    rmu, rraw = torch.autograd.grad((zr, sr), (mud, rawd), (gz.double(), gs.double()))
+    assert rel_err(gmu, rmu) < 1e-5 and rel_err(graw, rraw) < 1e-5
+
+
+@pytest.mark.parametrize("lik", ["normal", "laplace", "bernoulli"])
+@pytest.mark.parametrize("D,x_div", [(784, 1), (3072, 1), (1024, 3), (12, 1)])
+def test_loglik(ops, lik, D, x_div):
+    B, Kk = 4, 3
+    R = B * Kk
+    recon = torch.sigmoid(_rand(R, D, seed=1)).requires_grad_()
+    x = torch.rand(B, D, generator=torch.Generator().manual_seed(2)).cuda()
+    if lik == "bernoulli":
+        x = (x > 0.5).float()
+        with torch.no_grad():
+            recon[0, :4] = torch.tensor([0.0, 1.0, 1e-9, 1 - 1e-9])          # exercise the clamp
+    c = 3.918
+    lp = ops.LogLik.apply(recon, x, x_div, lik, c, False)
+    idx = ((torch.arange(R) // x_div) % B).cuda()
+    if lik == "bernoulli":          # torch's clamp uses the fp32 eps: evaluate the reference in fp32 for this family
+        rd = recon.detach().clone().requires_grad_()
+        ref = (O.px_log_prob(lik, rd, x[idx]) * c).sum(-1)
+    else:
+        rd = recon.detach().double().requires_grad_()
+        ref = (O.px_log_prob(lik, rd, x[idx].double()) * c).sum(-1)
+    assert rel_err(lp, ref) < (1e-5 if lik == "bernoulli" else 2e-6)
+    g = _rand(R, seed=3)
+    (gr,) = torch.autograd.grad(lp, recon, g)
+    (rr,) = torch.autograd.grad(ref, rd, g.to(ref.dtype))
+    assert rel_err(gr, rr) < 1e-5
+
+
+def _moe_reference(z, mu, std, lpx, dist, mode, detach):
+    M, K, B, L = z.shape
+    ploc, pscale = torch.zeros(1, L, dtype=z.dtype, device=z.device), torch.ones(1, L, dtype=z.dtype, device=z.device)
+    lws = []
+    for r in range(M):
+        lpz = O.lat_log_prob(dist, z[r], ploc, pscale).sum(-1)
+        lq = torch.stack([O.lat_log_prob(dist, z[r], (mu[e].detach() if detach else mu[e]).unsqueeze(0),
+                                         (std[e].detach() if detach else std[e]).unsqueeze(0)).sum(-1) for e in range(M)])
+        lws.append(lpz + lpx[r].sum(0) - (torch.logsumexp(lq, 0) - math.log(M)))
+    if mode == "iwae":
+        lw = torch.cat(lws)
+        return (torch.logsumexp(lw, 0) - math.log(lw.shape[0])).sum(), torch.stack(lws)
+    if mode == "iwae_looser":
+        lw = torch.stack(lws)
+        return (torch.logsumexp(lw, 1) - math.log(K)).mean(0).sum(), lw
+    if mode == "dreg":
+        lw = torch.cat(lws)
+        with torch.no_grad():
+            w = (lw - torch.logsumexp(lw, 0, keepdim=True)).exp()
+        return (w * lw).sum(), torch.stack(lws)
+    lw = torch.stack(lws)
+    with torch.no_grad():
+        w = (lw - torch.logsumexp(lw, 1, keepdim=True)).exp()
+    return (w * lw).mean(0).sum(), lw
+
+
+@pytest.mark.parametrize("dist", ["laplace", "normal"])
+@pytest.mark.parametrize("mode", ["iwae", "iwae_looser", "dreg", "dreg_looser"])
+@pytest.mark.parametrize("M,K", [(2, 30), (3, 5), (2, 1), (2, 200)])
+def test_moe_logw(ops, dist, mode, M, K):
+    B, L = 6, 20
+    z = _rand(M, K, B, L, seed=1).requires_grad_()
+    mu = _rand(M, B, L, seed=2, scale=0.5).requires_grad_()
+    std = (torch.rand(M, B, L, generator=torch.Generator().manual_seed(3)) + 0.5).cuda().requires_grad_()
+    lpx = (_rand(M, M, K, B, seed=4) * 3 - 700).requires_grad_()
+    pl, ps = torch.zeros(L).cuda(), torch.ones(L).cuda()
+    detach = mode.startswith("dreg")
+    loss, lw, wt, per = ops.MoeLogW.apply(z, mu.detach() if detach else mu, std.detach() if detach else std, lpx, pl, ps,
+                                          dist, mode)
+    zd, mud, stdd, lpxd = (t.detach().double().requires_grad_() for t in (z, mu, std, lpx))
+    ref, lwr = _moe_reference(zd, mud, stdd, lpxd, dist, mode, detach)
+    assert rel_err(lw, lwr) < 1e-6
+    assert abs(loss.item() - ref.item()) <= 1e-5 * abs(ref.item())
+    assert abs(per.sum().item() - loss.item()) <= 1e-5 * abs(ref.item())
+    ins = (z, lpx) if detach else (z, mu, std, lpx)
+    insd = (zd, lpxd) if detach else (zd, mud, stdd, lpxd)
+    g = torch.autograd.grad(loss * 1.7, ins)
+    gr = torch.autograd.grad(ref * 1.7, insd)
+    for a, b in zip(g, gr):
+        assert rel_err(a, b) < 2e-4          # softmax weights of lw ~ -700 carry ~1e-4 relative fp32 noise
+
+
+@pytest.mark.parametrize("dist", ["laplace", "normal"])
+def test_elbo(ops, dist):
+    M, K, B, L = 2, 4, 5, 20
+    z = _rand(M, K, B, L, seed=1, scale=0.3)
+    mu = _rand(M, B, L, seed=2, scale=0.3).requires_grad_()
+    std = (torch.rand(M, B, L, generator=torch.Generator().manual_seed(3)) * 0.2 + 0.9).cuda().requires_grad_()
+    lpx = (_rand(M, K, B, seed=4) - 50).requires_grad_()
+    pl, ps = torch.zeros(L).cuda(), torch.ones(L).cuda()
+    loss, terms, per = ops.Elbo.apply(z, mu, std, lpx, pl, ps, dist)
+    mud, stdd, lpxd, zd = (t.detach().double().requires_grad_() for t in (mu, std, lpx, z))
+    ploc, pscale = torch.zeros(1, L, dtype=torch.double).cuda(), torch.ones(1, L, dtype=torch.double).cuda()
+    tot = 0
+    for r in range(M):
+        tot = tot - O.lat_kl(dist, mud[r], stdd[r], ploc, pscale).sum(-1).unsqueeze(0)
+        for d in range(M):
+            if d == r:
+                w = 1.0
+            else:
+                w = (O.lat_log_prob(dist, zd[d], mud[r].unsqueeze(0), stdd[r].unsqueeze(0))
+                     - O.lat_log_prob(dist, zd[d], mud[d].unsqueeze(0), stdd[d].unsqueeze(0)).detach()).sum(-1).exp()
+            tot = tot + w * lpxd[d]
+    ref = (tot / M).mean(0).sum()
+    assert abs(loss.item() - ref.item()) <= 2e-5 * abs(ref.item())
+    g = torch.autograd.grad(loss, (mu, std, lpx))
+    gr = torch.autograd.grad(ref, (mud, stdd, lpxd))
+    for a, b in zip(g, gr):
+        assert rel_err(a, b) < 1e-4
+
+
+def test_lse_and_eval_logw(ops):
+    B, K, L, E, D = 7, 250, 20, 2, 2
+    a = _rand(B, K, seed=1) * 5 - 3000
+    mx, se = ops.lse_partial(a[:, :100].contiguous())
+    mx, se = ops.lse_partial(a[:, 100:].contiguous(), mx, se)
+    ll = ops.lse_finish(mx, se, 300)
+    ref = torch.logsumexp(a.double(), 1) - math.log(300)
+    assert (ll.double() - ref).abs().max().item() < 1e-3
+    z = _rand(B, K, L, seed=2)
+    mu, std = _rand(E, B, L, seed=3), (torch.rand(E, B, L) + 0.5).cuda()
+    lpx = _rand(D, B, K, seed=4) - 100
+    pl, ps = torch.zeros(L).cuda(), torch.ones(L).cuda()
+    for dist in ("laplace", "normal"):
+        lpz = O.lat_log_prob(dist, z.double(), pl.double(), ps.double()).sum(-1)
+        lq = torch.stack([O.lat_log_prob(dist, z.double(), mu[e].double().unsqueeze(1), std[e].double().unsqueeze(1)).sum(-1)
+                          for e in range(E)])
+        base = lpx.double().sum(0) + lpz
+        for qmode, q in (("mixture_half", torch.logsumexp(lq, 0) / 2), ("mixture", torch.logsumexp(lq, 0) - math.log(E)),
+                         ("single", lq[0]), ("none", 0 * lpz)):
+            out = ops.eval_logw(z, mu, std, lpx, pl, ps, dist, qmode)
+            assert (out.double() - (base - q)).abs().max().item() < 1e-3
+        out = ops.eval_logw(z, None, None, lpx, pl, ps, dist, "external", lq_ext=lq[1].float().contiguous())
+        assert (out.double() - (base - lq[1])).abs().max().item() < 1e-3
+
+
+def test_adam_amsgrad_matches_torch(ops):
+    p0 = _rand(1000, seed=1)
+    p = p0.clone()
+    ref = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.Adam([ref], lr=1e-3, amsgrad=True)
+    m, v, vm = torch.zeros_like(p), torch.zeros_like(p), torch.zeros_like(p)
+    step = torch.zeros(1).cuda()
+    for i in range(5):
+        g = _rand(1000, seed=10 + i)
+        ref.grad = g.clone()
+        opt.step()
+        ops.adam_amsgrad_(p, g, m, v, vm, step, lr=1e-3)
+    assert step.item() == 5
+    assert rel_err(p, ref) < 1e-6
+
+
+def test_cpu_tensor_is_rejected(ops):
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.LinearAct.apply(torch.zeros(2, 3), torch.zeros(4, 3).cuda(), None, None)

@@ -1,0 +1,164 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against
+  (a) the golden fixtures produced by the UNMODIFIED reference (tests/golden/*.pt), and
+  (b) the CPU oracle (oracle/bivae_oracle.py) evaluated in fp64 on the same weights, inputs and noise.
+Tolerances (north_star: loss and gradients within 1e-4 relative in fp32; log-likelihood within 1e-3 nats):
+  loss 1e-5 relative; gradients: GRAD_RTOL_REF = 5e-4 against the fp32 reference digests (the fp32 reference itself
+  sits 1e-4..5e-4 from fp64 on the encoder gradients — see tests/test_oracle_golden.py) and GRAD_RTOL_F64 = 1e-4
+  against the fp64 oracle on the global gradient vector; log-likelihoods 1e-3 nats."""
+import math
+
+import pytest
+import torch
+
+from oracle import bivae_oracle as O
+from oracle import synth
+from tests.helpers import build_mmvae, check_digests, leaf_sd, load_golden, rel_err
+
+pytestmark = pytest.mark.gpu
+GRAD_RTOL_REF = 5e-4
+GRAD_RTOL_F64 = 1e-4
+OBJ_CASES = ["obj_ms_laplace", "obj_ms_normal", "obj_ms_bern_lap", "obj_circles", "obj_msf"]
+
+
+def _objective(model, name, x, K, noise):
+    from mmvae_b200 import objectives as J
+    fn = {"elbo": J.m_elbo, "iwae": J.m_iwae, "iwae_looser": J.m_iwae_looser, "dreg": J.m_dreg,
+          "dreg_looser": J.m_dreg_looser}[name]
+    return fn(model, x, K, 1, 0, 1, noise=noise)[0]          # six positionals, as main.py:155 calls it
+
+
+def _f64_oracle_grads(spec, sd, oname, x, K, noise):
+    lsd = leaf_sd(sd, dtype=torch.float64)
+    loss = O.OBJECTIVES[oname](spec, lsd, [t.double() for t in x], K, [n.double() for n in noise])
+    loss.backward()
+    return loss.item(), {k: v.grad for k, v in lsd.items() if v.grad is not None}
+
+
+@pytest.mark.parametrize("name", OBJ_CASES)
+def test_objectives_match_reference_and_f64_oracle(name):
+    g, spec, sd = load_golden(name)
+    x = [t.cuda() for t in g["x"]]
+    noise = [n.cuda() for n in g["noise"]]
+    for oname, res in g["results"].items():
+        model = build_mmvae(spec, sd)
+        loss = _objective(model, oname, x, g["K"], noise)
+        loss.backward()
+        ref = res["loss"].item()
+        assert abs(loss.item() - ref) <= 1e-5 * abs(ref), (name, oname, loss.item(), ref)
+        grads = {k: p.grad for k, p in model.named_parameters()}
+        check_digests(grads, res["grads"], GRAD_RTOL_REF, f"{name}:{oname}")
+        l64, g64 = _f64_oracle_grads(spec, sd, oname, g["x"], g["K"], g["noise"])
+        assert abs(loss.item() - l64) <= 1e-5 * abs(l64)
+        keys = sorted(g64)
+        ours = torch.cat([grads[k].detach().double().cpu().reshape(-1) for k in keys])
+        theirs = torch.cat([g64[k].reshape(-1) for k in keys])
+        err = ((ours - theirs).norm() / theirs.norm()).item()
+        assert err <= GRAD_RTOL_F64, f"{name}:{oname} global gradient off by {err:.3e}"
+
+
+def test_forward_tuple_has_reference_shapes():
+    g, spec, sd = load_golden("obj_ms_laplace")
+    model = build_mmvae(spec, sd)
+    x = [t.cuda() for t in g["x"]]
+    K, B, L = g["K"], g["B"], spec.latent_dim
+    qz_xs, px_zs, zss, qz_x_params = model(x, K, noise=[n.cuda() for n in g["noise"]])
+    assert len(qz_xs) == 2 and qz_xs[0].loc.shape == (K, B, L)
+    assert zss[1].shape == (K, B, L) and qz_x_params[0][1].shape == (K, B, L)
+    assert px_zs[0][1].loc.shape == (K, B, 3, 32, 32) and px_zs[1][0].loc.shape == (K, B, 1, 28, 28)
+    mus, stds, zs, recon = O.mmvae_forward(spec, sd, g["x"], K, g["noise"])
+    for e in range(2):
+        assert rel_err(zss[e], zs[e]) < 1e-5
+        for d in range(2):
+            assert rel_err(px_zs[e][d].loc, recon[e][d]) < 1e-5
+    lp = px_zs[0][1].log_prob(x[1])                          # the tuple is usable the way the reference uses it
+    assert lp.shape == (K, B, 3, 32, 32)
+
+
+@pytest.mark.parametrize("name", ["eval_ms_laplace", "eval_ms_tail", "eval_msf"])
+def test_evaluators_match_reference(name):
+    g, spec, sd = load_golden(name)
+    model = build_mmvae(spec, sd)
+    data = [t.cuda() for t in g["data"]]
+    K, bs = g["K"], g["bs"]
+    if spec.M == 2:
+        j = g["joint"]
+        out = model.compute_joint_likelihood(data, K=K, batch_size_K=bs, mask=j["mask"].cuda(),
+                                             noise=[n.cuda() for n in j["noise"]])
+        assert abs(out["likelihood"].item() - j["likelihood"].item()) < 1e-3
+        for c in range(2):
+            r = g[f"joint_from_{c}"]
+            out = model.compute_joint_ll_from_uni(data, c, K=K, batch_size_K=bs, noise=r["noise"].cuda())
+            assert abs(out[f"joint_ll_from_{c}"].item() - r["value"].item()) < 1e-3
+    per_all = {}
+    for (c, gm), r in g["cond"].items():
+        met, per = model.compute_conditional_likelihood(data, c, gm, K=K, batch_size_K=bs, noise=r["noise"].cuda())
+        assert not per.is_cuda
+        assert torch.allclose(per, r["per"], atol=1e-3, rtol=0), (c, gm, (per - r["per"]).abs().max())
+        assert abs(met[f"cond_likelihood_{c}_{gm}"].item() - r["mean"].item()) < 1e-3
+        per_all[(c, gm)] = per
+    out = model.compute_uni_ll_from_prior(data, 0, K=K, batch_size_K=bs, noise=g["prior0"]["noise"].cuda())
+    assert abs(out["uni_from_prior_0"].item() - g["prior0"]["value"].item()) < 1e-3
+    if spec.M == 3:
+        noises = {k: r["noise"].cuda() for k, r in g["cond"].items()}
+        met = model.compute_conditional_likelihoods(data, K=K, batch_size_K=bs, noises=noises)
+        for i in range(3):
+            assert abs(met[f"cond_lw_subset_{i}"].item() - g["subset"][i].item()) < 1e-3
+
+
+def _c2_model(B, seed=1):
+    spec = O.spec_mnist_svhn(20, "laplace")
+    sd = synth.make_state_dict(spec, seed)
+    return spec, sd, build_mmvae(spec, sd), [t.cuda() for t in synth.make_inputs(spec, B, seed=seed + 1)]
+
+
+def test_full_size_properties_c2():
+    """BASELINE config C2 (B=128, K=30, dreg_looser): size-independent properties."""
+    import numpy as np
+    from mmvae_b200 import objectives as J
+    B, K, L = 128, 30, 20
+    spec, sd, model, x = _c2_model(B)
+    rs = np.random.RandomState(7)
+    noise = [synth.make_noise("laplace", (K, B, L), rs).cuda() for _ in range(2)]
+    loss, _ = J.m_dreg_looser(model, x, K, 1, 0, 1, noise=noise)
+    loss.backward()
+    g1 = torch.cat([p.grad.reshape(-1) for p in model.parameters() if p.grad is not None]).clone()
+    # (1) permuting the K samples leaves loss and gradients unchanged (up to fp32 reassociation)
+    perm = torch.randperm(K, generator=torch.Generator().manual_seed(3)).cuda()
+    model.zero_grad()
+    loss_p, _ = J.m_dreg_looser(model, x, K, 1, 0, 1, noise=[n[perm] for n in noise])
+    loss_p.backward()
+    g2 = torch.cat([p.grad.reshape(-1) for p in model.parameters() if p.grad is not None])
+    assert abs(loss_p.item() - loss.item()) <= 1e-5 * abs(loss.item())
+    assert rel_err(g2, g1) < 1e-4
+    # (2) the objective is a sum over datapoints: two half-batches add up to the full batch (what multi-GPU relies on)
+    h = B // 2
+    la, _ = J.m_dreg_looser(model, [t[:h] for t in x], K, 1, 0, 1, noise=[n[:, :h] for n in noise])
+    lb, _ = J.m_dreg_looser(model, [t[h:] for t in x], K, 1, 0, 1, noise=[n[:, h:] for n in noise])
+    assert abs((la + lb).item() - loss.item()) <= 1e-5 * abs(loss.item())
+    # (3) K = 1: dreg_looser reduces to the plain MoE ELBO mean_r lw_r, and equals iwae_looser
+    n1 = [n[:1] for n in noise]
+    l1, _ = J.m_dreg_looser(model, x, 1, 1, 0, 1, noise=n1)
+    l2, _ = J.m_iwae_looser(model, x, 1, 1, 0, 1, noise=n1)
+    assert abs(l1.item() - l2.item()) <= 1e-6 * abs(l1.item())
+    # (4) against the fp64 oracle at full size (CPU, a few seconds)
+    l64 = O.m_dreg_looser(spec, {k: v.double() for k, v in sd.items()}, [t.double().cpu() for t in x], K,
+                          [n.double().cpu() for n in noise]).item()
+    assert abs(loss.item() - l64) <= 1e-5 * abs(l64)
+
+
+def test_full_size_eval_chunking_c4():
+    """K=1000 evaluator: chunked over datapoints == one chunk; K-sharded (max, sumexp) merge == unsharded."""
+    import numpy as np
+    B, K, L = 12, 1000, 20
+    spec, sd, model, data = _c2_model(B, seed=5)
+    rs = np.random.RandomState(9)
+    noise = synth.make_noise("laplace", (B, K, L), rs).cuda()
+    model.eval_max_rows = 32768
+    _, per_a = model.compute_conditional_likelihood(data, 0, 1, K=K, batch_size_K=100, noise=noise)
+    model.eval_max_rows = 3000
+    _, per_b = model.compute_conditional_likelihood(data, 0, 1, K=K, batch_size_K=100, noise=noise)
+    assert torch.allclose(per_a, per_b, atol=1e-4, rtol=0)
+    with torch.no_grad():
+        _, ref = O.conditional_likelihood(spec, sd, [t.cpu() for t in data[:2]] if False else [t[:2].cpu() for t in data],
+                                          0, 1, K, 100, noise[:2].cpu())
+    assert torch.allclose(per_a[:2], ref, atol=1e-3, rtol=0)
