@@ -73,12 +73,15 @@ moe_logw_fwd_kernel(const float* __restrict__ z, const float* __restrict__ mu, c
         for (int q = threadIdx.x; q < Pg; q += blockDim.x) se += expf(lw[(long)(g * Pg + q) * B + b] - mx);
         se = block_sum(se, red);
         const float lse = mx + logf(se);
+        const float inv_se = 1.f / se;
         const float gscale = looser ? 1.f / (float)M : 1.f;
         float dot = 0.f;
         for (int q = threadIdx.x; q < Pg; q += blockDim.x) {
             const long o = (long)(g * Pg + q) * B + b;
             const float v = lw[o];
-            const float w = expf(v - lse);         // (lw - logsumexp(lw)).exp()   objectives.py:399,435
+            // (lw - logsumexp(lw)).exp() (objectives.py:399,435), normalised by the sum itself so that sum_k w = 1 to
+            // fp32 rounding: exp(v - fp32(lse)) would scale every weight by exp(ulp(lse)) ~ 1e-4 at lw ~ -3000
+            const float w = expf(v - mx) * inv_se;
             wt[o] = w * gscale;
             dot = fmaf(w, v, dot);
         }

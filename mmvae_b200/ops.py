@@ -47,10 +47,21 @@ def _stream():
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
-def _call(name, *args):
+PROFILE = None           # set to a list to record (name, work, start_event, end_event) per C-ABI call (bench.py)
+
+
+def _call(name, *args, work=None):
+    """work: ('flop'|'byte', amount) — the ALGORITHMIC work of this call, used for roofline accounting."""
     global N_CALLS
     N_CALLS += 1
+    if PROFILE is None:
+        _lib.check(getattr(_lib.load(), name)(*args), name)
+        return
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
     _lib.check(getattr(_lib.load(), name)(*args), name)
+    e1.record()
+    PROFILE.append((name, work, e0, e1))
 
 
 # ------------------------------------------------------------------------------------------------ raw wrappers
@@ -61,7 +72,7 @@ def gemm(a, b, bias, M, N, K, a_kmajor, b_kmajor, act=None, out=None):
     ws_bytes = lib.mmvae_gemm_workspace_bytes(M, N, K)
     ws = torch.empty(ws_bytes // 4, device=a.device, dtype=torch.float32) if ws_bytes else None
     _call("mmvae_gemm", _p(a), _p(b), _p(bias), _p(out), M, N, K, int(a_kmajor), int(b_kmajor), ACT[act], _p(ws),
-          ws_bytes, int(ALLOW_TC), _stream())
+          ws_bytes, int(ALLOW_TC), _stream(), work=("flop", 2.0 * M * N * K))
     return out
 
 
@@ -78,7 +89,7 @@ def act_bwd(g, y, act):
     if ACT[act] == C["MMVAE_ACT_NONE"]:
         return g
     out = torch.empty_like(g)
-    _call("mmvae_act_bwd", _p(g), _p(y), _p(out), g.numel(), ACT[act], _stream())
+    _call("mmvae_act_bwd", _p(g), _p(y), _p(out), g.numel(), ACT[act], _stream(), work=("byte", 12.0 * g.numel()))
     return out
 
 
@@ -117,7 +128,8 @@ def im2col(x, k, s, p):
     Ho, Wo = (H + 2 * p - k) // s + 1, (W + 2 * p - k) // s + 1
     col = torch.empty((N * Ho * Wo, k * k * Cc), device=x.device, dtype=torch.float32)
     sn, sc, sy, sx = _strides_nchw(x)
-    _call("mmvae_im2col", _p(x), _p(col), N, Cc, H, W, k, s, p, sn, sc, sy, sx, _stream())
+    _call("mmvae_im2col", _p(x), _p(col), N, Cc, H, W, k, s, p, sn, sc, sy, sx, _stream(),
+          work=("byte", 4.0 * (x.numel() + col.numel())))
     return col, Ho, Wo
 
 
@@ -129,7 +141,8 @@ def col2im(col, bias, N, Cc, H, W, k, s, p, act=None, nchw_out=False):
     else:
         y = torch.empty((N, Ho, Wo, Cc), device=col.device, dtype=torch.float32).permute(0, 3, 1, 2)
     sn, sc, sy, sx = _strides_nchw(y)
-    _call("mmvae_col2im", _p(col), _p(bias), _p(y), N, Cc, H, W, k, s, p, sn, sc, sy, sx, ACT[act], _stream())
+    _call("mmvae_col2im", _p(col), _p(bias), _p(y), N, Cc, H, W, k, s, p, sn, sc, sy, sx, ACT[act], _stream(),
+          work=("byte", 4.0 * (col.numel() + y.numel())))
     return y
 
 
@@ -308,7 +321,8 @@ class LogLik(torch.autograd.Function):
         B = x.shape[0]
         assert x.shape[1] == D
         lp = torch.empty(R, device=recon.device, dtype=torch.float32)
-        _call("mmvae_loglik_fwd", _p(recon), _p(x), _p(lp), R, B, D, x_div, LIK[lik], float(lik_scaling), _stream())
+        _call("mmvae_loglik_fwd", _p(recon), _p(x), _p(lp), R, B, D, x_div, LIK[lik], float(lik_scaling), _stream(),
+              work=("byte", 4.0 * R * D))
         ctx.save_for_backward(recon, x)
         ctx.cfg = (R, B, D, x_div, lik, float(lik_scaling), through_sigmoid)
         return lp
@@ -319,7 +333,7 @@ class LogLik(torch.autograd.Function):
         R, B, D, x_div, lik, c, ts = ctx.cfg
         g = torch.empty_like(recon)
         _call("mmvae_loglik_bwd", _p(_c(glp, "grad_lp")), _p(recon), _p(x), _p(g), R, B, D, x_div, LIK[lik], c,
-              int(ts), _stream())
+              int(ts), _stream(), work=("byte", 8.0 * R * D))
         return g, None, None, None, None, None
 
 

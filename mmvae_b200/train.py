@@ -1,0 +1,86 @@
+"""Training step of the hot path (main.py:114-115,147-171): objective -> backward -> [gradient all-reduce] ->
+Adam(amsgrad).  Parameters and gradients live in two flat fp32 buffers so the optimizer is ONE fused kernel and the
+multi-GPU exchange is ONE NCCL all-reduce (SUM — the reference objective is an un-normalised sum over the batch,
+objectives.py:403,438, so batch shards add).  The whole step can be captured in a CUDA graph.
+"""
+import torch
+import torch.distributed as dist
+
+from . import objectives, ops
+
+
+class FlatParams:
+    """Re-homes every trainable parameter of `model` (and its .grad) as views into two flat buffers."""
+
+    def __init__(self, model):
+        self.params = [p for p in model.parameters() if p.requires_grad]
+        dev = self.params[0].device
+        n = sum(p.numel() for p in self.params)
+        self.flat = torch.empty(n, device=dev, dtype=torch.float32)
+        self.grad = torch.zeros(n, device=dev, dtype=torch.float32)
+        o = 0
+        for p in self.params:
+            k = p.numel()
+            self.flat[o:o + k].copy_(p.data.reshape(-1))
+            p.data = self.flat[o:o + k].view_as(p.data)
+            p.grad = self.grad[o:o + k].view_as(p.data)
+            o += k
+        self.numel = n
+
+
+class Trainer:
+    """One data-parallel training step.  `objective` is a name from mmvae_b200.objectives ('m_dreg_looser', ...)."""
+
+    def __init__(self, model, objective="m_dreg_looser", K=30, lr=1e-3, amsgrad=True, process_group=None,
+                 distributed=None):
+        self.model = model
+        self.objective = getattr(objectives, objective)
+        self.K = K
+        self.lr, self.amsgrad = lr, amsgrad
+        self.fp = FlatParams(model)
+        n, dev = self.fp.numel, self.fp.flat.device
+        self.m = torch.zeros(n, device=dev)
+        self.v = torch.zeros(n, device=dev)
+        self.vmax = torch.zeros(n, device=dev)
+        self.step_dev = torch.zeros(1, device=dev)
+        self.pg = process_group
+        self.distributed = dist.is_initialized() and dist.get_world_size() > 1 if distributed is None else distributed
+        self._graph = None
+
+    def broadcast_parameters(self, src=0):
+        if self.distributed:
+            dist.broadcast(self.fp.flat, src, group=self.pg)
+
+    def _step_impl(self, x, noise=None):
+        self.fp.grad.zero_()
+        loss, _ = self.objective(self.model, x, self.K, 1, 0, 1, noise=noise)
+        (-loss).backward()                                   # main.py:156: the objective is maximised
+        if self.distributed:
+            dist.all_reduce(self.fp.grad, op=dist.ReduceOp.SUM, group=self.pg)
+        ops.adam_amsgrad_(self.fp.flat, self.fp.grad, self.m, self.v, self.vmax, self.step_dev, lr=self.lr,
+                          amsgrad=self.amsgrad)
+        return loss.detach()
+
+    def step(self, x, noise=None):
+        """eager step -> loss (device scalar, this rank's shard)."""
+        return self._step_impl(x, noise)
+
+    # ---- CUDA-graph replay: static input buffers, RNG inside the graph -------------------------------------------
+    def capture(self, x_example, warmup=3):
+        self._static_x = [t.clone() for t in x_example]
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(warmup):
+                self._step_impl(self._static_x)
+        torch.cuda.current_stream().wait_stream(s)
+        self._graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._graph):
+            self._static_loss = self._step_impl(self._static_x)
+        return self
+
+    def step_graph(self, x):
+        for dst, src in zip(self._static_x, x):
+            dst.copy_(src, non_blocking=True)
+        self._graph.replay()
+        return self._static_loss
