@@ -116,7 +116,10 @@ int mmvae_eval_logw(const float* z, const float* mu, const float* std, const flo
 int mmvae_gemm(const float* A, const float* B, const float* bias, float* C, int M, int N, int K,
                int a_kmajor, int b_kmajor, int act, float* workspace, long workspace_bytes, int allow_tc,
                void* stream);
-long mmvae_gemm_workspace_bytes(int M, int N, int K);
+long mmvae_gemm_workspace_bytes(int M, int N, int K, int a_kmajor, int b_kmajor);
+/* debug / speed probe of the tensor-core path: 0 = 3xTF32 split (fp32 accuracy, default), 1 = single TF32 pass.
+ * Returns the previous mode. */
+int mmvae_gemm_tc_set_mode(int mode);
 /* column sums: out[n] = sum_m A[m,n]  (bias gradients); workspace >= mmvae_colsum_workspace_bytes(M,N) */
 int  mmvae_colsum(const float* A, float* out, float* workspace, int M, int N, void* stream);
 long mmvae_colsum_workspace_bytes(int M, int N);

@@ -1,6 +1,6 @@
 """Builds mmvae_b200/csrc/libmmvae_b200.so with nvcc for sm_100a (cross-compiles without a GPU).
 
-    python -m mmvae_b200.build [--force]
+    python mmvae_b200/build.py [--force] [-v]      (run by path: importing the package needs the library to exist)
 """
 import concurrent.futures
 import os

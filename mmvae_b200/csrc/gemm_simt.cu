@@ -190,10 +190,15 @@ static int pick_splits(int M, int N, int K, int BN) {
     return s < 1 ? 1 : (int)s;
 }
 
-extern "C" long mmvae_gemm_workspace_bytes(int M, int N, int K) {
+long mmvae_gemm_simt_workspace_bytes(int M, int N, int K) {
     const int BN = (N <= 64) ? 64 : 128;
     const int S = pick_splits(M, N, K, BN);
     return S > 1 ? (long)S * M * N * (long)sizeof(float) : 0;
+}
+
+void mmvae_splitk_reduce(const float* ws, const float* bias, float* C, long MN, int N, int S, int act, cudaStream_t st) {
+    const int grid = (int)min((long)MMVAE_NUM_SMS * 4, (MN + 255) / 256);
+    splitk_reduce_kernel<<<grid, 256, 0, st>>>(ws, bias, C, MN, N, S, act);
 }
 
 template <int BN>

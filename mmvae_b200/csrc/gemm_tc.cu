@@ -1,10 +1,405 @@
-// Kernel (4), tensor-core path: tcgen05.mma (kind::tf32, 3xTF32 error-compensated split) fed by TMA, accumulators
-// in TMEM.  Placeholder until the kernel lands: reports "unsupported" so the dispatcher uses the exact-fp32 SIMT GEMM.
+// Kernel (4), tensor-core path: C[M,N] = act(A*B + bias) in fp32 accuracy on the 5th-gen tensor cores.
+//   * persistent: one CTA per SM walks a static tile list; operands stream HBM -> shared memory by TMA
+//     (cp.async.bulk.tensor.2d, 128-byte swizzle, OOB zero-fill for tails) through a ring that runs across tiles;
+//   * tcgen05.mma kind::tf32, UMMA 128 x BN x 8, fp32 accumulators in TMEM, double-buffered so the epilogue of tile i
+//     overlaps the MMAs of tile i+1;
+//   * fp32 accuracy by the error-compensated 3xTF32 split done IN the kernel: a converter warpgroup writes
+//     lo = rn_tf32(a - trunc_tf32(a)) next to each landed tile (the tensor core reads the top 19 bits of the raw fp32
+//     word as the hi part — measured: it truncates), and the issuer runs lo*hi + hi*lo into a "small" accumulator and
+//     hi*hi into a "big" one (the TMEM accumulate truncates too — measured ~2^-25 relative bias per MMA — so the big
+//     chain is kept short: <= TC_MAX_CHAIN k-blocks per split, the two are added in fp32 in the epilogue);
+//   * K-major operands use SWIZZLE_128B, MN-major operands SWIZZLE_128B_BASE32B (the only MN-major tf32 layout the
+//     hardware has) with the instruction-descriptor transpose bits, so dgrad/wgrad need no transposed copies;
+//   * deterministic split-K (partials + splitk_reduce) for the huge-K weight gradients; optional transposed store.
+// Warp roles: warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer, warps 2-5 = hi/lo converter, warps 6-9 = epilogue.
+// Reference ops replaced: the same torch.nn.Linear / Conv2d / ConvTranspose2d contractions as gemm_simt.cu.
+#include <cuda.h>
+#include <cudaTypedefs.h>
 #include "common.cuh"
+#include "sm100_ptx.cuh"
 
-int mmvae_gemm_tc_supported(int, int, int, int, int) { return 0; }
-int mmvae_gemm_tc(const float*, const float*, const float*, float*, int, int, int, int, int, int, float*, long,
-                  cudaStream_t) {
-    return mmvae_set_error(1, "gemm_tc: not built");
+#define TC_BM 128
+#define TC_BK 32                       // fp32 elements per k-block = one 128-byte swizzle row
+#define TC_THREADS 320
+#define TC_A_TILE (TC_BM * TC_BK * 4)  // 16 KB
+#define TC_MAX_CHAIN 32                // k-blocks accumulated in one TMEM chain when split-K is available
+
+static int g_tc_mode = 0;              // 0 = 3xTF32 (fp32 accuracy), 1 = single TF32 pass (debug / speed probe)
+
+template <int BN> struct TcCfg {
+    static constexpr int B_TILE = BN * TC_BK * 4;
+    static constexpr int STAGE = 2 * TC_A_TILE + 2 * B_TILE;
+    static constexpr int STAGES = (BN == 128) ? 3 : 4;
+    static constexpr int SMEM = STAGES * STAGE + 1024 + 256;
+    static constexpr int TMEM_COLS = 4 * BN;          // {big, small} x 2 accumulator buffers
+};
+
+// lo part of the 3xTF32 split: residual of the hardware's truncation of `a`, itself rounded to tf32 (round-to-nearest)
+// so that the tensor core's own truncation of lo changes nothing and the split error is unbiased.
+__device__ __forceinline__ float tf32_lo(float a) {
+    const float r = a - __uint_as_float(__float_as_uint(a) & 0xFFFFE000u);
+    uint32_t o;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(o) : "f"(r));
+    return __uint_as_float(o);
 }
-extern "C" int mmvae_has_tcgen05(void) { return 0; }
+
+__device__ __forceinline__ float apply_act_tc(float v, int act) {
+    if (act == MMVAE_ACT_RELU) return fmaxf(v, 0.f);
+    if (act == MMVAE_ACT_SIGMOID) return 1.f / (1.f + expf(-v));
+    return v;
+}
+
+struct TcTile { int m0, n0, kb_begin, nk, z; };
+
+__device__ __forceinline__ TcTile tc_tile(int t, int tiles_m, int tiles_n, int BN, int nkb, int kb_per) {
+    TcTile r;
+    const int nt = t % tiles_n;
+    const int mt = (t / tiles_n) % tiles_m;
+    r.z = t / (tiles_n * tiles_m);
+    r.m0 = mt * TC_BM;
+    r.n0 = nt * BN;
+    r.kb_begin = r.z * kb_per;
+    r.nk = min(nkb, r.kb_begin + kb_per) - r.kb_begin;
+    return r;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+               const float* __restrict__ bias, float* __restrict__ C, float* __restrict__ ws, int M, int N, int K,
+               int act, int kb_per_split, int splits, int c_transposed, int passes) {
+    using Cfg = TcCfg<BN>;
+    constexpr int STAGES = Cfg::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint64_t* bars = (uint64_t*)(smem + STAGES * Cfg::STAGE);
+    uint64_t* full = bars;                      // [STAGES] TMA landed
+    uint64_t* conv = bars + STAGES;             // [STAGES] lo tiles written
+    uint64_t* empty = bars + 2 * STAGES;        // [STAGES] MMAs that read the stage completed
+    uint64_t* tfull = bars + 3 * STAGES;        // [2] accumulator buffer complete
+    uint64_t* tempty = bars + 3 * STAGES + 2;   // [2] accumulator buffer drained by the epilogue
+    uint32_t* tmem_slot = (uint32_t*)(bars + 3 * STAGES + 4);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nkb = (K + TC_BK - 1) / TC_BK;
+    const int tiles_m = (M + TC_BM - 1) / TC_BM, tiles_n = (N + BN - 1) / BN;
+    const int total = tiles_m * tiles_n * splits;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(full + s, 1); mbar_init(conv + s, 4); mbar_init(empty + s, 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 4); }
+        mbar_fence_init();
+        tma_prefetch_desc(&tmap_a);
+        tma_prefetch_desc(&tmap_b);
+    }
+    if (warp == 1) { tmem_alloc(tmem_slot, Cfg::TMEM_COLS); tmem_relinquish(); }
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer: the stage ring runs straight through tile boundaries =====
+        if (lane == 0) {
+            int it = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                const TcTile tl = tc_tile(t, tiles_m, tiles_n, BN, nkb, kb_per_split);
+                for (int i = 0; i < tl.nk; ++i, ++it) {
+                    const int s = it % STAGES, ph = (it / STAGES) & 1;
+                    mbar_wait(empty + s, ph ^ 1);
+                    uint8_t* st = smem + s * Cfg::STAGE;
+                    uint8_t* a_hi = st;
+                    uint8_t* b_hi = st + 2 * TC_A_TILE;
+                    mbar_arrive_expect_tx(full + s, TC_A_TILE + Cfg::B_TILE);
+                    const int k0 = (tl.kb_begin + i) * TC_BK;
+                    if (A_MN) {
+#pragma unroll
+                        for (int j = 0; j < TC_BM / 32; ++j)
+                            tma_load_2d(a_hi + j * 4096, &tmap_a, full + s, tl.m0 + 32 * j, k0);
+                    } else {
+                        tma_load_2d(a_hi, &tmap_a, full + s, k0, tl.m0);
+                    }
+                    if (B_MN) {
+#pragma unroll
+                        for (int j = 0; j < BN / 32; ++j)
+                            tma_load_2d(b_hi + j * 4096, &tmap_b, full + s, tl.n0 + 32 * j, k0);
+                    } else {
+                        tma_load_2d(b_hi, &tmap_b, full + s, k0, tl.n0);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (one elected lane) =====
+        constexpr uint32_t idesc = umma_idesc_tf32(TC_BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+        if (lane == 0) {
+            int it = 0, ti = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x, ++ti) {
+                const TcTile tl = tc_tile(t, tiles_m, tiles_n, BN, nkb, kb_per_split);
+                const int acc = ti & 1;
+                mbar_wait(tempty + acc, ((ti >> 1) & 1) ^ 1);          // epilogue has drained this buffer
+                tc_fence_after_sync();
+                const uint32_t d_big = tmem_base + acc * (2 * BN), d_small = d_big + BN;
+                for (int i = 0; i < tl.nk; ++i, ++it) {
+                    const int s = it % STAGES, ph = (it / STAGES) & 1;
+                    mbar_wait(passes == 3 ? conv + s : full + s, ph);
+                    tc_fence_after_sync();
+                    const uint32_t st = smem_u32(smem + s * Cfg::STAGE);
+                    const uint32_t a_hi = st, a_lo = st + TC_A_TILE;
+                    const uint32_t b_hi = st + 2 * TC_A_TILE, b_lo = b_hi + Cfg::B_TILE;
+#pragma unroll
+                    for (int kk = 0; kk < TC_BK / 8; ++kk) {
+                        // K-major (SWIZZLE_128B): 8 tf32 = 32 bytes inside the 128-byte row, 8-row groups 1024 B apart.
+                        // MN-major (SWIZZLE_128B_BASE32B): 8 k-rows of 128 B = 1024 B per MMA, 4-row swizzle atoms
+                        // 512 B apart (SBO), 32-element MN groups one TMA box = 4096 B apart (LBO).
+                        const uint32_t ao = A_MN ? kk * 1024 : kk * 32, bo = B_MN ? kk * 1024 : kk * 32;
+                        const uint32_t a_lbo = A_MN ? 4096 : 16, b_lbo = B_MN ? 4096 : 16;
+                        const uint32_t a_sbo = A_MN ? 512 : 1024, b_sbo = B_MN ? 512 : 1024;
+                        const uint32_t a_lt = A_MN ? 1 : 2, b_lt = B_MN ? 1 : 2;
+                        const uint64_t dah = umma_smem_desc(a_hi + ao, a_lbo, a_sbo, a_lt);
+                        const uint64_t dbh = umma_smem_desc(b_hi + bo, b_lbo, b_sbo, b_lt);
+                        const uint32_t first = (i | kk) != 0;
+                        if (passes == 3) {
+                            const uint64_t dal = umma_smem_desc(a_lo + ao, a_lbo, a_sbo, a_lt);
+                            const uint64_t dbl = umma_smem_desc(b_lo + bo, b_lbo, b_sbo, b_lt);
+                            umma_tf32(d_small, dal, dbh, idesc, first);
+                            umma_tf32(d_small, dah, dbl, idesc, 1);
+                        }
+                        umma_tf32(d_big, dah, dbh, idesc, first);
+                    }
+                    umma_commit(empty + s);                  // frees the stage once these MMAs have read it
+                }
+                umma_commit(tfull + acc);
+            }
+        }
+    } else if (warp < 6) {
+        // ===== converter (warps 2..5): lo = rn_tf32(a - trunc_tf32(a)), same swizzled position in the lo tile =====
+        const int tq = threadIdx.x - 64;               // 0..127
+        if (passes == 3) {
+            int it = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                const TcTile tl = tc_tile(t, tiles_m, tiles_n, BN, nkb, kb_per_split);
+                for (int i = 0; i < tl.nk; ++i, ++it) {
+                    const int s = it % STAGES, ph = (it / STAGES) & 1;
+                    mbar_wait(full + s, ph);
+                    uint8_t* st = smem + s * Cfg::STAGE;
+                    const float4* a_hi = (const float4*)st;
+                    float4* a_lo = (float4*)(st + TC_A_TILE);
+                    const float4* b_hi = (const float4*)(st + 2 * TC_A_TILE);
+                    float4* b_lo = (float4*)(st + 2 * TC_A_TILE + Cfg::B_TILE);
+#pragma unroll
+                    for (int j = 0; j < TC_A_TILE / 16 / 128; ++j) {
+                        const float4 v = a_hi[tq + j * 128];
+                        a_lo[tq + j * 128] = make_float4(tf32_lo(v.x), tf32_lo(v.y), tf32_lo(v.z), tf32_lo(v.w));
+                    }
+#pragma unroll
+                    for (int j = 0; j < Cfg::B_TILE / 16 / 128; ++j) {
+                        const float4 v = b_hi[tq + j * 128];
+                        b_lo[tq + j * 128] = make_float4(tf32_lo(v.x), tf32_lo(v.y), tf32_lo(v.z), tf32_lo(v.w));
+                    }
+                    fence_proxy_async_smem();          // generic-proxy writes -> visible to the tensor core's reads
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(conv + s);
+                }
+            }
+        }
+    } else {
+        // ===== epilogue (warps 6..9): TMEM -> registers -> global, overlapped with the next tile's MMAs =====
+        const int lane_base = (warp & 3) * 32;         // a warp may only touch TMEM lanes 32*(warp%4) .. +31
+        int ti = 0;
+        for (int t = blockIdx.x; t < total; t += gridDim.x, ++ti) {
+            const TcTile tl = tc_tile(t, tiles_m, tiles_n, BN, nkb, kb_per_split);
+            const int acc = ti & 1;
+            mbar_wait(tfull + acc, (ti >> 1) & 1);
+            tc_fence_after_sync();
+            const int row = tl.m0 + lane_base + lane;
+            float* out = (splits > 1) ? ws + (long)tl.z * M * N : C;
+            const uint32_t tb = tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)(acc * 2 * BN);
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                float v[32];
+                tmem_ld_32x32(tb + (uint32_t)c, v);
+                if (passes == 3) {
+                    float u[32];
+                    tmem_ld_32x32(tb + (uint32_t)(BN + c), u);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] += u[j];
+                }
+                if (c + 32 >= BN) {                    // last TMEM read of this buffer: hand it back to the issuer
+                    tc_fence_before_sync();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(tempty + acc);
+                }
+                if (row < M) {
+                    if (splits == 1) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const int n = tl.n0 + c + j;
+                            if (n < N) v[j] = apply_act_tc(v[j] + (bias ? __ldg(bias + n) : 0.f), act);
+                        }
+                    }
+                    if (c_transposed) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const int n = tl.n0 + c + j;
+                            if (n < N) out[(long)n * M + row] = v[j];
+                        }
+                    } else {
+                        float* p = out + (long)row * N + tl.n0 + c;
+                        if ((N & 3) == 0 && tl.n0 + c + 32 <= N) {
+#pragma unroll
+                            for (int j = 0; j < 32; j += 4)
+                                *reinterpret_cast<float4*>(p + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (tl.n0 + c + j < N) p[j] = v[j];
+                        }
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+// ------------------------------------------------------------------------------------------------------ host side
+static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
+static int g_tc_state = -1;            // -1 unknown, 0 unavailable, 1 available
+
+static int tc_init() {
+    if (g_tc_state >= 0) return g_tc_state;
+    g_tc_state = 0;
+    int dev = 0, major = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess || major != 10) return 0;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn ||
+        q != cudaDriverEntryPointSuccess) {
+        (void)cudaGetLastError();
+        return 0;
+    }
+    g_encode = (PFN_cuTensorMapEncodeTiled_v12000)fn;
+    g_tc_state = 1;
+    return 1;
+}
+
+extern "C" int mmvae_has_tcgen05(void) { return tc_init(); }
+extern "C" int mmvae_gemm_tc_set_mode(int mode) {
+    const int old = g_tc_mode;
+    g_tc_mode = (mode == 1) ? 1 : 0;
+    return old;
+}
+
+// row-major [rows, cols] fp32 matrix, box = 32 columns (128 bytes, one swizzle row) x box_rows
+static int make_tmap(CUtensorMap* m, const float* base, long rows, long cols, int box_rows, bool mn_major) {
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)cols * sizeof(float)};
+    cuuint32_t box[2] = {32u, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1u, 1u};
+    CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : (int)r;
+}
+
+struct TcPlan { int BN, S, kb_per; bool swap; };
+
+static TcPlan tc_plan(int M, int N, int K, bool can_swap) {
+    TcPlan p;
+    p.swap = can_swap && M <= 64 && N > M && N >= 32 && N % 4 == 0;
+    const int Mm = p.swap ? N : M, Nn = p.swap ? M : N;
+    p.BN = Nn <= 32 ? 32 : (Nn <= 64 ? 64 : 128);
+    const long tiles = (long)((Mm + TC_BM - 1) / TC_BM) * ((Nn + p.BN - 1) / p.BN);
+    const int nkb = (K + TC_BK - 1) / TC_BK;
+    int S = 1;
+    if (tiles < MMVAE_NUM_SMS && nkb >= 8) {                         // fill the machine
+        long s = (2L * MMVAE_NUM_SMS + tiles - 1) / tiles;
+        if (s > nkb / 2) s = nkb / 2;
+        S = (int)(s < 1 ? 1 : s);
+    }
+    if ((nkb + S - 1) / S > TC_MAX_CHAIN && nkb > 2 * TC_MAX_CHAIN)   // keep the truncating TMEM chain short
+        S = (nkb + TC_MAX_CHAIN - 1) / TC_MAX_CHAIN;
+    p.kb_per = (nkb + S - 1) / S;
+    p.S = (nkb + p.kb_per - 1) / p.kb_per;
+    return p;
+}
+
+static bool tc_shape_ok(int M, int N, int K, int a_k, int b_k) {
+    if (K < 32) return false;
+    if ((long)M * N * K < (1L << 20)) return false;                 // launch-latency-sized: SIMT is as good
+    if (a_k ? (K % 4) : (M % 4 || M < 32)) return false;            // TMA: 16-byte row pitch, inner extent >= box
+    if (b_k ? (K % 4) : (N % 4 || N < 32)) return false;
+    return true;
+}
+
+long mmvae_gemm_tc_workspace_bytes(int M, int N, int K, int a_k, int b_k) {
+    if (!tc_shape_ok(M, N, K, a_k, b_k)) return 0;
+    const TcPlan p = tc_plan(M, N, K, true);
+    return p.S > 1 ? (long)p.S * M * N * (long)sizeof(float) : 0;
+}
+
+void mmvae_splitk_reduce(const float* ws, const float* bias, float* C, long MN, int N, int S, int act, cudaStream_t st);
+
+template <int BN, bool A_MN, bool B_MN>
+static int tc_launch(const CUtensorMap& ta, const CUtensorMap& tb, const float* bias, float* C, float* ws, int M, int N,
+                     int K, int act, const TcPlan& p, int transposed, cudaStream_t st) {
+    static bool attr_done = false;
+    auto kern = gemm_tc_kernel<BN, A_MN, B_MN>;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<BN>::SMEM);
+        if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "gemm_tc: smem attribute: %s", cudaGetErrorString(e));
+        attr_done = true;
+    }
+    const long total = (long)((N + BN - 1) / BN) * ((M + TC_BM - 1) / TC_BM) * p.S;
+    const int grid = (int)(total < MMVAE_NUM_SMS ? total : MMVAE_NUM_SMS);      // persistent: one CTA per SM
+    kern<<<grid, TC_THREADS, TcCfg<BN>::SMEM, st>>>(ta, tb, bias, C, ws, M, N, K, act, p.kb_per, p.S, transposed,
+                                                    g_tc_mode == 1 ? 1 : 3);
+    MMVAE_LAUNCH_CHECK("gemm_tc");
+    return 0;
+}
+
+// returns -1 when the shape / alignment is not for this path (the dispatcher then uses the SIMT kernel)
+int mmvae_gemm_tc(const float* A, const float* B, const float* bias, float* C, int M, int N, int K, int a_kmajor,
+                  int b_kmajor, int act, float* workspace, long workspace_bytes, cudaStream_t st) {
+    if (!tc_init() || !tc_shape_ok(M, N, K, a_kmajor, b_kmajor)) return -1;
+    if (((uintptr_t)A & 15) || ((uintptr_t)B & 15) || ((uintptr_t)C & 15)) return -1;
+    TcPlan p = tc_plan(M, N, K, bias == nullptr && act == MMVAE_ACT_NONE);
+    if (p.S > 1 && (!workspace || workspace_bytes < (long)p.S * M * N * (long)sizeof(float))) {
+        p.S = 1;
+        p.kb_per = (K + TC_BK - 1) / TC_BK;
+    }
+    // after an operand swap the kernel computes C^T = B^T A^T and stores it transposed
+    const float* Ak = p.swap ? B : A;
+    const float* Bk = p.swap ? A : B;
+    const int Mk = p.swap ? N : M, Nk = p.swap ? M : N;
+    const bool a_mn = p.swap ? !b_kmajor : !a_kmajor, b_mn = p.swap ? !a_kmajor : !b_kmajor;
+    CUtensorMap ta, tb;
+    int rc;
+    rc = a_mn ? make_tmap(&ta, Ak, K, Mk, TC_BK, true) : make_tmap(&ta, Ak, Mk, K, TC_BM, false);
+    if (rc) return mmvae_set_error(1, "gemm_tc: cuTensorMapEncodeTiled(A) failed with %d (M=%d N=%d K=%d)", rc, M, N, K);
+    rc = b_mn ? make_tmap(&tb, Bk, K, Nk, TC_BK, true) : make_tmap(&tb, Bk, Nk, K, p.BN, false);
+    if (rc) return mmvae_set_error(1, "gemm_tc: cuTensorMapEncodeTiled(B) failed with %d (M=%d N=%d K=%d)", rc, M, N, K);
+    const int tr = p.swap ? 1 : 0;
+#define TC_GO(BNv, AM, BM_)                                                                                    \
+    rc = tc_launch<BNv, AM, BM_>(ta, tb, bias, C, workspace, Mk, Nk, K, act, p, tr, st)
+#define TC_PICK(BNv)                                                         \
+    do {                                                                     \
+        if (a_mn && b_mn) TC_GO(BNv, true, true);                            \
+        else if (a_mn) TC_GO(BNv, true, false);                              \
+        else if (b_mn) TC_GO(BNv, false, true);                              \
+        else TC_GO(BNv, false, false);                                       \
+    } while (0)
+    if (p.BN == 32) TC_PICK(32);
+    else if (p.BN == 64) TC_PICK(64);
+    else TC_PICK(128);
+#undef TC_PICK
+#undef TC_GO
+    if (rc) return rc;
+    if (p.S > 1) mmvae_splitk_reduce(workspace, bias, C, (long)M * N, N, p.S, act, st);
+    return 0;
+}

@@ -21,7 +21,13 @@ int mmvae_gemm_simt(const float* A, const float* B, const float* bias, float* C,
                     int b_kmajor, int act, float* workspace, long workspace_bytes, cudaStream_t st);
 int mmvae_gemm_tc(const float* A, const float* B, const float* bias, float* C, int M, int N, int K, int a_kmajor,
                   int b_kmajor, int act, float* workspace, long workspace_bytes, cudaStream_t st);
-int mmvae_gemm_tc_supported(int M, int N, int K, int a_kmajor, int b_kmajor);
+long mmvae_gemm_simt_workspace_bytes(int M, int N, int K);
+long mmvae_gemm_tc_workspace_bytes(int M, int N, int K, int a_k, int b_k);
+
+extern "C" long mmvae_gemm_workspace_bytes(int M, int N, int K, int a_kmajor, int b_kmajor) {
+    const long a = mmvae_gemm_simt_workspace_bytes(M, N, K), b = mmvae_gemm_tc_workspace_bytes(M, N, K, a_kmajor, b_kmajor);
+    return a > b ? a : b;
+}
 
 extern "C" int mmvae_gemm(const float* A, const float* B, const float* bias, float* C, int M, int N, int K,
                           int a_kmajor, int b_kmajor, int act, float* workspace, long workspace_bytes, int allow_tc,
@@ -30,8 +36,10 @@ extern "C" int mmvae_gemm(const float* A, const float* B, const float* bias, flo
     MMVAE_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: bad sizes M=%d N=%d K=%d", M, N, K);
     MMVAE_REQUIRE(act >= 0 && act <= 2, "gemm: bad activation %d", act);
     cudaStream_t st = (cudaStream_t)stream;
-    if (allow_tc && mmvae_gemm_tc_supported(M, N, K, a_kmajor, b_kmajor))
-        return mmvae_gemm_tc(A, B, bias, C, M, N, K, a_kmajor, b_kmajor, act, workspace, workspace_bytes, st);
+    if (allow_tc) {
+        const int rc = mmvae_gemm_tc(A, B, bias, C, M, N, K, a_kmajor, b_kmajor, act, workspace, workspace_bytes, st);
+        if (rc != -1) return rc;
+    }
     return mmvae_gemm_simt(A, B, bias, C, M, N, K, a_kmajor, b_kmajor, act, workspace, workspace_bytes, st);
 }
 

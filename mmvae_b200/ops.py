@@ -69,7 +69,8 @@ def gemm(a, b, bias, M, N, K, a_kmajor, b_kmajor, act=None, out=None):
     """C[M,N] = act(A·B + bias); a/b are 2-D contiguous device tensors in the stated storage order."""
     lib = _lib.load()
     out = torch.empty((M, N), device=a.device, dtype=torch.float32) if out is None else out
-    ws_bytes = lib.mmvae_gemm_workspace_bytes(M, N, K)
+    ws_bytes = lib.mmvae_gemm_workspace_bytes(M, N, K, int(a_kmajor), int(b_kmajor)) if ALLOW_TC else \
+        lib.mmvae_gemm_workspace_bytes(M, N, K, -1, -1)
     ws = torch.empty(ws_bytes // 4, device=a.device, dtype=torch.float32) if ws_bytes else None
     _call("mmvae_gemm", _p(a), _p(b), _p(bias), _p(out), M, N, K, int(a_kmajor), int(b_kmajor), ACT[act], _p(ws),
           ws_bytes, int(ALLOW_TC), _stream(), work=("flop", 2.0 * M * N * K))

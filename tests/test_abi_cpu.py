@@ -8,8 +8,9 @@ import torch
 
 
 def test_library_exports_every_declared_symbol():
-    from mmvae_b200 import _lib, build
-    build.build()
+    import __graft_entry__
+    __graft_entry__.build()
+    from mmvae_b200 import _lib
     lib = ctypes.CDLL(_lib.LIB_PATH)
     protos, consts = _lib.parse_header()
     assert len(protos) >= 24
