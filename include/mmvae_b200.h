@@ -63,8 +63,10 @@ int mmvae_rsample_bwd(const float* grad_z, const float* grad_std_direct, const f
 /* ---- kernel (2): decoder log-likelihood reduced over pixels ------------------------------------------------
  * replaces px_z(recon, 1).log_prob(x).view(K,B,-1).mul(lik_scaling).sum(-1) (objectives.py:381-385,416-419;
  * mmvae.py:154-156).  recon: [R,D]; x: [B,D]; row r uses x row (r / x_div) % B  (training: x_div=1; evaluator
- * (B,K) layout: x_div=K).  out lp: [R].  D % 4 == 0. */
-int mmvae_loglik_fwd(const float* recon, const float* x, float* lp, int R, int B, int D, int x_div,
+ * (B,K) layout: x_div=K).  out lp: [R].  D % 4 == 0.  The row sum is carried in fp64; lp = its fp32 rounding and, if
+ * lp_lo != NULL, lp_lo[R] = the residual (sum - lp) so that (lp, lp_lo) hands the softmax over K the digits an fp32
+ * |lp| ~ 3000..9000 drops. */
+int mmvae_loglik_fwd(const float* recon, const float* x, float* lp, float* lp_lo, int R, int B, int D, int x_div,
                      int lik, float lik_scaling, void* stream);
 /* grad_lp: [R]; out grad: [R,D].  If through_sigmoid != 0, `recon` is sigmoid(h) and the output is the gradient
  * w.r.t. the pre-activation h (fuses the decoder's final Sigmoid backward, encoders.py:128, pythae Decoder_AE_MLP). */
@@ -73,10 +75,11 @@ int mmvae_loglik_bwd(const float* grad_lp, const float* recon, const float* x, f
 
 /* ---- kernel (3): cross-modal log q mixture, two-level logsumexp, objective and stop-gradient weights --------
  * replaces objectives.py:117-131 / 343-359 / 372-403 / 406-438 after model(x,K).
- * z: [M,K,B,L]; mu,std: [M,B,L]; lpx: [M(expert),M(decoder),K,B] (already lik-scaled); pz_loc,pz_scale: [L].
+ * z: [M,K,B,L]; mu,std: [M,B,L]; lpx: [M(expert),M(decoder),K,B] (already lik-scaled), lpx_lo: its residuals from
+ * mmvae_loglik_fwd or NULL; pz_loc,pz_scale: [L].  lw and the softmax over samples are formed in fp64.
  * out lw: [M,K,B]; wt: [M,K,B] = d loss / d lw (softmax weights incl. the 1/M of `looser`);
  * loss: [1] = objective (sum over datapoints); loss_per: [B] = each datapoint's term. */
-int mmvae_moe_logw_fwd(const float* z, const float* mu, const float* std, const float* lpx,
+int mmvae_moe_logw_fwd(const float* z, const float* mu, const float* std, const float* lpx, const float* lpx_lo,
                        const float* pz_loc, const float* pz_scale, float* lw, float* wt, float* loss,
                        float* loss_per, int M, int K, int B, int L, int dist, int mode, void* stream);
 /* grad_loss: [1] (device scalar).  out grad_z [M,K,B,L], grad_lpx [M,M,K,B]; grad_mu, grad_std [M,B,L] are the

@@ -31,16 +31,24 @@ __device__ __forceinline__ float ll_grad(float x, float r) {
     return (x - r) / (r * (1.f - r));
 }
 
+__device__ __forceinline__ void ll_store(float* lp, float* lp_lo, long row, double v) {
+    const float hi = (float)v;
+    lp[row] = hi;
+    if (lp_lo) lp_lo[row] = (float)(v - (double)hi);
+}
+
 // TPR threads cooperate on one row; LL_THREADS/TPR rows per block.  D4 = D/4.
 template <int LIK, int TPR>
 __global__ void __launch_bounds__(LL_THREADS)
-loglik_fwd_kernel(const float4* __restrict__ recon, const float4* __restrict__ x, float* __restrict__ lp, int R,
-                  int B, int D4, int x_div, float scale, float row_const) {
-    __shared__ float red[LL_THREADS / 32];
+loglik_fwd_kernel(const float4* __restrict__ recon, const float4* __restrict__ x, float* __restrict__ lp,
+                  float* __restrict__ lp_lo, int R, int B, int D4, int x_div, float scale, double row_const) {
+    __shared__ double red[LL_THREADS / 32];
     const int rows_per_block = LL_THREADS / TPR;
     const int sub = threadIdx.x / TPR, t = threadIdx.x % TPR;
     const long row = (long)blockIdx.x * rows_per_block + sub;
-    float acc = 0.f;
+    // per-pixel terms are fp32 (as the reference's); their SUM is carried in fp64 so that lp (|lp| ~ 3000..9000, fp32
+    // ulp 2.4e-4..1e-3) can be handed to the softmax over K as a (hi, lo) pair instead of losing those digits
+    double acc = 0.0;
     if (row < R) {
         const float4* rr = recon + row * D4;
         const float4* xr = x + (long)((row / x_div) % B) * D4;
@@ -50,27 +58,27 @@ loglik_fwd_kernel(const float4* __restrict__ recon, const float4* __restrict__ x
             const float4 a2 = ld_stream4(rr + i + 2 * TPR), a3 = ld_stream4(rr + i + 3 * TPR);
             const float4 x0 = __ldg(xr + i), x1 = __ldg(xr + i + TPR);
             const float4 x2 = __ldg(xr + i + 2 * TPR), x3 = __ldg(xr + i + 3 * TPR);
-            acc += ll_elem<LIK>(x0.x, a0.x) + ll_elem<LIK>(x0.y, a0.y) + ll_elem<LIK>(x0.z, a0.z) + ll_elem<LIK>(x0.w, a0.w);
-            acc += ll_elem<LIK>(x1.x, a1.x) + ll_elem<LIK>(x1.y, a1.y) + ll_elem<LIK>(x1.z, a1.z) + ll_elem<LIK>(x1.w, a1.w);
-            acc += ll_elem<LIK>(x2.x, a2.x) + ll_elem<LIK>(x2.y, a2.y) + ll_elem<LIK>(x2.z, a2.z) + ll_elem<LIK>(x2.w, a2.w);
-            acc += ll_elem<LIK>(x3.x, a3.x) + ll_elem<LIK>(x3.y, a3.y) + ll_elem<LIK>(x3.z, a3.z) + ll_elem<LIK>(x3.w, a3.w);
+            acc += (double)(ll_elem<LIK>(x0.x, a0.x) + ll_elem<LIK>(x0.y, a0.y) + ll_elem<LIK>(x0.z, a0.z) + ll_elem<LIK>(x0.w, a0.w));
+            acc += (double)(ll_elem<LIK>(x1.x, a1.x) + ll_elem<LIK>(x1.y, a1.y) + ll_elem<LIK>(x1.z, a1.z) + ll_elem<LIK>(x1.w, a1.w));
+            acc += (double)(ll_elem<LIK>(x2.x, a2.x) + ll_elem<LIK>(x2.y, a2.y) + ll_elem<LIK>(x2.z, a2.z) + ll_elem<LIK>(x2.w, a2.w));
+            acc += (double)(ll_elem<LIK>(x3.x, a3.x) + ll_elem<LIK>(x3.y, a3.y) + ll_elem<LIK>(x3.z, a3.z) + ll_elem<LIK>(x3.w, a3.w));
         }
         for (; i < D4; i += TPR) {
             const float4 a = ld_stream4(rr + i);
             const float4 v = __ldg(xr + i);
-            acc += ll_elem<LIK>(v.x, a.x) + ll_elem<LIK>(v.y, a.y) + ll_elem<LIK>(v.z, a.z) + ll_elem<LIK>(v.w, a.w);
+            acc += (double)(ll_elem<LIK>(v.x, a.x) + ll_elem<LIK>(v.y, a.y) + ll_elem<LIK>(v.z, a.z) + ll_elem<LIK>(v.w, a.w));
         }
     }
-    acc = warp_sum(acc);
+    acc = warp_sum_d(acc);
     if (TPR == 32) {
-        if (t == 0 && row < R) lp[row] = scale * (acc + row_const);
+        if (t == 0 && row < R) ll_store(lp, lp_lo, row, (double)scale * (acc + row_const));
     } else {                                            // TPR == LL_THREADS: one row per block
         if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
         __syncthreads();
         if (threadIdx.x < 32) {
-            float v = (threadIdx.x < LL_THREADS / 32) ? red[threadIdx.x] : 0.f;
-            v = warp_sum(v);
-            if (threadIdx.x == 0 && row < R) lp[row] = scale * (v + row_const);
+            double v = (threadIdx.x < LL_THREADS / 32) ? red[threadIdx.x] : 0.0;
+            v = warp_sum_d(v);
+            if (threadIdx.x == 0 && row < R) ll_store(lp, lp_lo, row, (double)scale * (v + row_const));
         }
     }
 }
@@ -103,31 +111,32 @@ loglik_bwd_kernel(const float* __restrict__ glp, const float4* __restrict__ reco
 }
 
 template <int LIK>
-static int launch_fwd(const float* recon, const float* x, float* lp, int R, int B, int D, int x_div, float c,
-                      cudaStream_t st) {
-    const float row_const = (LIK == MMVAE_LIK_NORMAL) ? -(float)D * MMVAE_LOG_SQRT_2PI
-                          : (LIK == MMVAE_LIK_LAPLACE) ? -(float)D * MMVAE_LOG2 : 0.f;
+static int launch_fwd(const float* recon, const float* x, float* lp, float* lp_lo, int R, int B, int D, int x_div,
+                      float c, cudaStream_t st) {
+    // the reference adds the fp32 constant to every pixel term; D * fp32(const) in fp64 is that sum without rounding
+    const double row_const = (LIK == MMVAE_LIK_NORMAL) ? -(double)D * (double)MMVAE_LOG_SQRT_2PI
+                           : (LIK == MMVAE_LIK_LAPLACE) ? -(double)D * (double)MMVAE_LOG2 : 0.0;
     const int D4 = D / 4;
     if (D4 <= 512) {
         const int rpb = LL_THREADS / 32;
         loglik_fwd_kernel<LIK, 32><<<ceil_div_i(R, rpb), LL_THREADS, 0, st>>>(
-            (const float4*)recon, (const float4*)x, lp, R, B, D4, x_div, c, row_const);
+            (const float4*)recon, (const float4*)x, lp, lp_lo, R, B, D4, x_div, c, row_const);
     } else {
         loglik_fwd_kernel<LIK, LL_THREADS><<<R, LL_THREADS, 0, st>>>(
-            (const float4*)recon, (const float4*)x, lp, R, B, D4, x_div, c, row_const);
+            (const float4*)recon, (const float4*)x, lp, lp_lo, R, B, D4, x_div, c, row_const);
     }
     return 0;
 }
 
-extern "C" int mmvae_loglik_fwd(const float* recon, const float* x, float* lp, int R, int B, int D, int x_div,
-                                int lik, float lik_scaling, void* stream) {
+extern "C" int mmvae_loglik_fwd(const float* recon, const float* x, float* lp, float* lp_lo, int R, int B, int D,
+                                int x_div, int lik, float lik_scaling, void* stream) {
     MMVAE_REQUIRE(recon && x && lp, "loglik_fwd: null pointer");
     MMVAE_REQUIRE(R > 0 && B > 0 && D > 0 && D % 4 == 0 && x_div > 0, "loglik_fwd: bad sizes R=%d B=%d D=%d", R, B, D);
     MMVAE_REQUIRE(((uintptr_t)recon & 15) == 0 && ((uintptr_t)x & 15) == 0, "loglik_fwd: pointers must be 16-byte aligned");
     cudaStream_t st = (cudaStream_t)stream;
-    if (lik == MMVAE_LIK_NORMAL) launch_fwd<MMVAE_LIK_NORMAL>(recon, x, lp, R, B, D, x_div, lik_scaling, st);
-    else if (lik == MMVAE_LIK_LAPLACE) launch_fwd<MMVAE_LIK_LAPLACE>(recon, x, lp, R, B, D, x_div, lik_scaling, st);
-    else if (lik == MMVAE_LIK_BERNOULLI) launch_fwd<MMVAE_LIK_BERNOULLI>(recon, x, lp, R, B, D, x_div, lik_scaling, st);
+    if (lik == MMVAE_LIK_NORMAL) launch_fwd<MMVAE_LIK_NORMAL>(recon, x, lp, lp_lo, R, B, D, x_div, lik_scaling, st);
+    else if (lik == MMVAE_LIK_LAPLACE) launch_fwd<MMVAE_LIK_LAPLACE>(recon, x, lp, lp_lo, R, B, D, x_div, lik_scaling, st);
+    else if (lik == MMVAE_LIK_BERNOULLI) launch_fwd<MMVAE_LIK_BERNOULLI>(recon, x, lp, lp_lo, R, B, D, x_div, lik_scaling, st);
     else return mmvae_set_error(1, "loglik_fwd: bad likelihood %d", lik);
     MMVAE_LAUNCH_CHECK("loglik_fwd");
     return 0;

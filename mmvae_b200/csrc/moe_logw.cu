@@ -11,19 +11,26 @@
 
 // one block per datapoint b; threads stride over the P = M*K (expert r, sample k) pairs.
 // loss_per[b] = per-datapoint term; loss[0] = their sum (moe_loss_reduce_kernel).
+// Precision: every elementwise term is fp32 (as in the reference); the SUMS that form lw and the softmax over the
+// samples are carried in fp64 (lpx arrives as a (hi, lo) fp32 pair from the log-likelihood kernel).  |lw| is 3000..9000
+// at the MNIST-SVHN shapes, where one fp32 ulp (2.4e-4..1e-3) is a 1e-3 relative error on a softmax weight — the
+// fp32 reference carries that noise (measured 2e-4..6e-4 on encoder gradients against its own fp64 evaluation,
+// DESIGN.md §parity); this kernel does not.
 __global__ void __launch_bounds__(MOE_THREADS)
 moe_logw_fwd_kernel(const float* __restrict__ z, const float* __restrict__ mu, const float* __restrict__ stdv,
-                    const float* __restrict__ lpx, const float* __restrict__ pz_loc,
-                    const float* __restrict__ pz_scale, float* __restrict__ lw, float* __restrict__ wt,
-                    float* __restrict__ loss_per, int M, int K, int B, int L, int dist, int mode) {
-    extern __shared__ float sm[];                 // mu[M*L], std[M*L], ploc[L], pscale[L], red[32]
-    float* s_mu = sm;
-    float* s_std = sm + M * L;
-    float* s_pl = sm + 2 * M * L;
-    float* s_ps = s_pl + L;
-    float* red = s_ps + L;
-    const int b = blockIdx.x;
+                    const float* __restrict__ lpx, const float* __restrict__ lpx_lo,
+                    const float* __restrict__ pz_loc, const float* __restrict__ pz_scale, float* __restrict__ lw,
+                    float* __restrict__ wt, float* __restrict__ loss_per, int M, int K, int B, int L, int dist,
+                    int mode) {
+    extern __shared__ double smd[];               // red[32], lw[P] (fp64), then floats: mu[M*L], std[M*L], ploc[L], pscale[L]
     const int P = M * K;
+    double* red = smd;
+    double* s_lw = smd + 32;
+    float* s_mu = (float*)(s_lw + P);
+    float* s_std = s_mu + M * L;
+    float* s_pl = s_std + M * L;
+    float* s_ps = s_pl + L;
+    const int b = blockIdx.x;
     for (int i = threadIdx.x; i < M * L; i += blockDim.x) {
         const int e = i / L, l = i - e * L;
         s_mu[i] = mu[((long)e * B + b) * L + l];
@@ -31,76 +38,77 @@ moe_logw_fwd_kernel(const float* __restrict__ z, const float* __restrict__ mu, c
     }
     for (int l = threadIdx.x; l < L; l += blockDim.x) { s_pl[l] = pz_loc[l]; s_ps[l] = pz_scale[l]; }
     __syncthreads();
-    const float log_M = logf((float)M);
+    const double log_M = log((double)M);
     for (int p = threadIdx.x; p < P; p += blockDim.x) {
         const int r = p / K, k = p - r * K;
         const float* zr = z + (((long)r * K + k) * B + b) * L;
-        float lpz = 0.f, lq[MOE_MAX_M];
+        double lpz = 0.0, lq[MOE_MAX_M];
 #pragma unroll
-        for (int e = 0; e < MOE_MAX_M; ++e) lq[e] = 0.f;
+        for (int e = 0; e < MOE_MAX_M; ++e) lq[e] = 0.0;
         for (int l = 0; l < L; ++l) {
             const float zz = zr[l];
-            lpz += lat_logprob(dist, zz, s_pl[l], s_ps[l]);
+            lpz += (double)lat_logprob(dist, zz, s_pl[l], s_ps[l]);
 #pragma unroll
             for (int e = 0; e < MOE_MAX_M; ++e)
-                if (e < M) lq[e] += lat_logprob(dist, zz, s_mu[e * L + l], s_std[e * L + l]);
+                if (e < M) lq[e] += (double)lat_logprob(dist, zz, s_mu[e * L + l], s_std[e * L + l]);
         }
-        float mx = -INFINITY;
+        double mx = -INFINITY;
 #pragma unroll
-        for (int e = 0; e < MOE_MAX_M; ++e) if (e < M) mx = fmaxf(mx, lq[e]);
-        float se = 0.f;
+        for (int e = 0; e < MOE_MAX_M; ++e) if (e < M) mx = fmax(mx, lq[e]);
+        double se = 0.0;
 #pragma unroll
-        for (int e = 0; e < MOE_MAX_M; ++e) if (e < M) se += expf(lq[e] - mx);
-        const float lqmix = mx + logf(se) - log_M;
-        float lpxs = 0.f;
-        for (int d = 0; d < M; ++d) lpxs += lpx[(((long)r * M + d) * K + k) * B + b];
-        lw[((long)r * K + k) * B + b] = (lpz + lpxs) - lqmix;
+        for (int e = 0; e < MOE_MAX_M; ++e) if (e < M) se += exp(lq[e] - mx);
+        const double lqmix = mx + log(se) - log_M;
+        double lpxs = 0.0;
+        for (int d = 0; d < M; ++d) {
+            const long o = (((long)r * M + d) * K + k) * B + b;
+            lpxs += (double)lpx[o];
+            if (lpx_lo) lpxs += (double)lpx_lo[o];
+        }
+        const double v = (lpz + lpxs) - lqmix;
+        s_lw[p] = v;
+        lw[((long)r * K + k) * B + b] = (float)v;
     }
-    __syncthreads();                               // lw of this block is re-read below (global, same block)
+    __syncthreads();
     const bool looser = (mode == MMVAE_OBJ_IWAE_LOOSER || mode == MMVAE_OBJ_DREG_LOOSER);
     const bool dreg = (mode == MMVAE_OBJ_DREG || mode == MMVAE_OBJ_DREG_LOOSER);
     const int G = looser ? M : 1;                  // softmax groups: per expert (looser) or over all M*K (tight)
     const int Pg = P / G;
-    float obj = 0.f;
+    double obj = 0.0;
     for (int g = 0; g < G; ++g) {
-        float mx = -INFINITY;
+        double mx = -INFINITY;
+        for (int q = threadIdx.x; q < Pg; q += blockDim.x) mx = fmax(mx, s_lw[g * Pg + q]);
+        mx = block_max_d(mx, red);
+        double se = 0.0;
+        for (int q = threadIdx.x; q < Pg; q += blockDim.x) se += exp(s_lw[g * Pg + q] - mx);
+        se = block_sum_d(se, red);
+        const double lse = mx + log(se);
+        const double inv_se = 1.0 / se;
+        const double gscale = looser ? 1.0 / (double)M : 1.0;
+        double dot = 0.0;
         for (int q = threadIdx.x; q < Pg; q += blockDim.x) {
             const int p = g * Pg + q;
-            mx = fmaxf(mx, lw[(long)p * B + b]);
-        }
-        mx = block_max(mx, red);
-        float se = 0.f;
-        for (int q = threadIdx.x; q < Pg; q += blockDim.x) se += expf(lw[(long)(g * Pg + q) * B + b] - mx);
-        se = block_sum(se, red);
-        const float lse = mx + logf(se);
-        const float inv_se = 1.f / se;
-        const float gscale = looser ? 1.f / (float)M : 1.f;
-        float dot = 0.f;
-        for (int q = threadIdx.x; q < Pg; q += blockDim.x) {
-            const long o = (long)(g * Pg + q) * B + b;
-            const float v = lw[o];
-            // (lw - logsumexp(lw)).exp() (objectives.py:399,435), normalised by the sum itself so that sum_k w = 1 to
-            // fp32 rounding: exp(v - fp32(lse)) would scale every weight by exp(ulp(lse)) ~ 1e-4 at lw ~ -3000
-            const float w = expf(v - mx) * inv_se;
-            wt[o] = w * gscale;
-            dot = fmaf(w, v, dot);
+            const double v = s_lw[p];
+            const double w = exp(v - mx) * inv_se;        // (lw - logsumexp(lw)).exp() (objectives.py:399,435)
+            wt[(long)p * B + b] = (float)(w * gscale);
+            dot = fma(w, v, dot);
         }
         if (dreg) {
-            dot = block_sum(dot, red);
+            dot = block_sum_d(dot, red);
             obj += dot * gscale;                   // (grad_wt * lw).sum() / .mean(0).sum()
         } else {
-            obj += (lse - logf((float)Pg)) * gscale;   // log_mean_exp
+            obj += (lse - log((double)Pg)) * gscale;   // log_mean_exp
         }
     }
-    if (threadIdx.x == 0) loss_per[b] = obj;
+    if (threadIdx.x == 0) loss_per[b] = (float)obj;
 }
 
 __global__ void moe_loss_reduce_kernel(float* __restrict__ loss, const float* __restrict__ loss_per, int B) {
-    __shared__ float red[32];
-    float s = 0.f;
-    for (int i = threadIdx.x; i < B; i += blockDim.x) s += loss_per[i];
-    s = block_sum(s, red);
-    if (threadIdx.x == 0) loss[0] = s;
+    __shared__ double red[32];
+    double s = 0.0;
+    for (int i = threadIdx.x; i < B; i += blockDim.x) s += (double)loss_per[i];
+    s = block_sum_d(s, red);
+    if (threadIdx.x == 0) loss[0] = (float)s;
 }
 
 // backward.  dynamic smem: mu[M*L], std[M*L], ploc[L], pscale[L], cpi[P*M]
@@ -180,16 +188,20 @@ moe_logw_bwd_kernel(const float* __restrict__ gloss, const float* __restrict__ z
 }
 
 extern "C" int mmvae_moe_logw_fwd(const float* z, const float* mu, const float* std, const float* lpx,
-                                  const float* pz_loc, const float* pz_scale, float* lw, float* wt, float* loss,
+                                  const float* lpx_lo, const float* pz_loc, const float* pz_scale, float* lw, float* wt, float* loss,
                                   float* loss_per, int M, int K, int B, int L, int dist, int mode, void* stream) {
     MMVAE_REQUIRE(z && mu && std && lpx && pz_loc && pz_scale && lw && wt && loss && loss_per, "moe_logw_fwd: null pointer");
     MMVAE_REQUIRE(M >= 1 && M <= MOE_MAX_M && K > 0 && B > 0 && L > 0, "moe_logw_fwd: bad sizes M=%d K=%d B=%d L=%d", M, K, B, L);
     MMVAE_REQUIRE(dist == 0 || dist == 1, "moe_logw_fwd: bad dist");
     MMVAE_REQUIRE(mode >= 0 && mode <= 3, "moe_logw_fwd: bad mode %d", mode);
-    const size_t smem = ((size_t)2 * M * L + 2 * L + 32) * sizeof(float);
-    MMVAE_REQUIRE(smem <= 48 * 1024, "moe_logw_fwd: M*L too large");
+    const size_t smem = ((size_t)32 + (size_t)M * K) * sizeof(double) + ((size_t)2 * M * L + 2 * L) * sizeof(float);
+    MMVAE_REQUIRE(smem <= 200 * 1024, "moe_logw_fwd: M*K (+ M*L) too large for shared memory");
     cudaStream_t st = (cudaStream_t)stream;
-    moe_logw_fwd_kernel<<<B, MOE_THREADS, smem, st>>>(z, mu, std, lpx, pz_loc, pz_scale, lw, wt, loss_per, M, K, B, L,
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(moe_logw_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "moe_logw_fwd: %s", cudaGetErrorString(e));
+    }
+    moe_logw_fwd_kernel<<<B, MOE_THREADS, smem, st>>>(z, mu, std, lpx, lpx_lo, pz_loc, pz_scale, lw, wt, loss_per, M, K, B, L,
                                                       dist, mode);
     MMVAE_LAUNCH_CHECK("moe_logw_fwd");
     moe_loss_reduce_kernel<<<1, 256, 0, st>>>(loss, loss_per, B);

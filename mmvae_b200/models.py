@@ -64,7 +64,7 @@ class Multi_VAES(nn.Module):
         recon = self.vaes[d].decoder(z_rows)["reconstruction"]
         R = recon.shape[0]
         c = self.lik_scaling[d] if scaled else 1.0
-        return ops.LogLik.apply(recon.reshape(R, -1), self._flat_x(x_d), x_div, self.params.recon_losses[d], c, False)
+        return ops.LogLik.apply(recon.reshape(R, -1), self._flat_x(x_d), x_div, self.params.recon_losses[d], c, False)[0]
 
     def _is_loglik(self, z, data, mods, qmode, mu=None, std=None, lq_ext=None, K_total=None, with_prior=True):
         """ln p_hat per datapoint from latents z [B,Ku,L]:  logsumexp_k( sum_{d in mods} log p(x_d|z_k)
@@ -170,16 +170,18 @@ class MMVAE(Multi_VAES):
         elif not torch.is_tensor(noise):
             noise = torch.stack(list(noise))
         z, std = ops.RSample.apply(mu, raw, noise.reshape(M, K, B, L), self.params.dist, self._xform(), False)
-        recons, lps = [], []
+        recons, lps, los = [], [], []
         for d, vae in enumerate(self.vaes):
             zin = z.reshape(M * K * B, L) if cross else z[d].reshape(K * B, L)
             recon = vae.decoder(zin)["reconstruction"]
             R = recon.shape[0]
             c = self.lik_scaling[d] if scaled else 1.0
-            lp = ops.LogLik.apply(recon.reshape(R, -1), self._flat_x(x[d]), 1, self.params.recon_losses[d], c, False)
+            lp, lo = ops.LogLik.apply(recon.reshape(R, -1), self._flat_x(x[d]), 1, self.params.recon_losses[d], c, False)
             recons.append(recon.reshape(((M, K, B) if cross else (K, B)) + tuple(recon.shape[1:])))
             lps.append(lp.reshape((M, K, B) if cross else (K, B)))
+            los.append(lo.reshape((M, K, B) if cross else (K, B)))
         lpx = torch.stack(lps, dim=1) if cross else torch.stack(lps, dim=0)
+        self._lpx_lo = torch.stack(los, dim=1) if cross else torch.stack(los, dim=0)     # fp64 residuals of lpx
         return mu, std, z, recons, lpx
 
     def _likelihood(self, d, loc):
@@ -210,7 +212,7 @@ class MMVAE(Multi_VAES):
             mu_q, std_q = mu.detach(), std.detach()
         else:
             mu_q, std_q = mu, std
-        loss, lw, wt, per = ops.MoeLogW.apply(z, mu_q, std_q, lpx, self.pz_params[0], self.pz_params[1],
+        loss, lw, wt, per = ops.MoeLogW.apply(z, mu_q, std_q, lpx, self._lpx_lo, self.pz_params[0], self.pz_params[1],
                                               self.params.dist, mode)
         return loss, {"lw": lw, "grad_wt": wt, "per_datapoint": per}
 

@@ -313,7 +313,8 @@ class RSample(torch.autograd.Function):
 
 
 class LogLik(torch.autograd.Function):
-    """lp[r] = lik_scaling * sum_j log p(x[(r // x_div) % B, j] | recon[r, j]).  recon [R,D], x [B,D]."""
+    """lp[r] = lik_scaling * sum_j log p(x[(r // x_div) % B, j] | recon[r, j]).  recon [R,D], x [B,D].
+    Returns (lp, lp_lo): the fp32 value and the residual of the fp64 row sum (non-differentiable; see mmvae_b200.h)."""
 
     @staticmethod
     def forward(ctx, recon, x, x_div, lik, lik_scaling, through_sigmoid):
@@ -322,14 +323,16 @@ class LogLik(torch.autograd.Function):
         B = x.shape[0]
         assert x.shape[1] == D
         lp = torch.empty(R, device=recon.device, dtype=torch.float32)
-        _call("mmvae_loglik_fwd", _p(recon), _p(x), _p(lp), R, B, D, x_div, LIK[lik], float(lik_scaling), _stream(),
+        lo = torch.empty(R, device=recon.device, dtype=torch.float32)
+        _call("mmvae_loglik_fwd", _p(recon), _p(x), _p(lp), _p(lo), R, B, D, x_div, LIK[lik], float(lik_scaling), _stream(),
               work=("byte", 4.0 * R * D))
         ctx.save_for_backward(recon, x)
         ctx.cfg = (R, B, D, x_div, lik, float(lik_scaling), through_sigmoid)
-        return lp
+        ctx.mark_non_differentiable(lo)
+        return lp, lo
 
     @staticmethod
-    def backward(ctx, glp):
+    def backward(ctx, glp, _glo):
         recon, x = ctx.saved_tensors
         R, B, D, x_div, lik, c, ts = ctx.cfg
         g = torch.empty_like(recon)
@@ -342,8 +345,10 @@ class MoeLogW(torch.autograd.Function):
     """Fused mixture-of-experts objective.  Returns (loss scalar, lw [M,K,B], wt [M,K,B], per-datapoint [B])."""
 
     @staticmethod
-    def forward(ctx, z, mu, std, lpx, pz_loc, pz_scale, dist, mode):
+    def forward(ctx, z, mu, std, lpx, lpx_lo, pz_loc, pz_scale, dist, mode):
         z, mu, std, lpx = _c(z, "z"), _c(mu, "mu"), _c(std, "std"), _c(lpx, "lpx")
+        lpx_lo = None if lpx_lo is None else _c(lpx_lo, "lpx_lo")
+        assert lpx_lo is None or lpx_lo.shape == lpx.shape
         pz_loc, pz_scale = _c(pz_loc.reshape(-1), "pz_loc"), _c(pz_scale.reshape(-1), "pz_scale")
         M, K, B, L = z.shape
         assert lpx.shape == (M, M, K, B), lpx.shape
@@ -351,7 +356,7 @@ class MoeLogW(torch.autograd.Function):
         wt = torch.empty_like(lw)
         loss = torch.empty((), device=z.device, dtype=torch.float32)
         per = torch.empty(B, device=z.device, dtype=torch.float32)
-        _call("mmvae_moe_logw_fwd", _p(z), _p(mu), _p(std), _p(lpx), _p(pz_loc), _p(pz_scale), _p(lw), _p(wt),
+        _call("mmvae_moe_logw_fwd", _p(z), _p(mu), _p(std), _p(lpx), _p(lpx_lo), _p(pz_loc), _p(pz_scale), _p(lw), _p(wt),
               _p(loss), _p(per), M, K, B, L, DIST[dist], OBJ[mode], _stream())
         ctx.save_for_backward(z, mu, std, wt, pz_loc, pz_scale)
         ctx.cfg = (M, K, B, L, dist, mode)
@@ -369,7 +374,7 @@ class MoeLogW(torch.autograd.Function):
         _call("mmvae_moe_logw_bwd", _p(g), _p(z), _p(mu), _p(std), _p(wt), _p(pz_loc), _p(pz_scale), _p(gz), _p(gmu),
               _p(gstd), _p(glpx), M, K, B, L, DIST[dist], OBJ[mode], _stream())
         dreg = mode in ("dreg", "dreg_looser")
-        return gz, (None if dreg else gmu), (None if dreg else gstd), glpx, None, None, None, None
+        return gz, (None if dreg else gmu), (None if dreg else gstd), glpx, None, None, None, None, None
 
 
 class Elbo(torch.autograd.Function):

@@ -145,7 +145,7 @@ def test_loglik(ops, lik, D, x_div):
         with torch.no_grad():
             recon[0, :4] = torch.tensor([0.0, 1.0, 1e-9, 1 - 1e-9])          # exercise the clamp
     c = 3.918
-    lp = ops.LogLik.apply(recon, x, x_div, lik, c, False)
+    lp, lo = ops.LogLik.apply(recon, x, x_div, lik, c, False)
     idx = ((torch.arange(R) // x_div) % B).cuda()
     if lik == "bernoulli":          # torch's clamp uses the fp32 eps: evaluate the reference in fp32 for this family
         rd = recon.detach().clone().requires_grad_()
@@ -154,6 +154,9 @@ def test_loglik(ops, lik, D, x_div):
         rd = recon.detach().double().requires_grad_()
         ref = (O.px_log_prob(lik, rd, x[idx].double()) * c).sum(-1)
     assert rel_err(lp, ref) < (1e-5 if lik == "bernoulli" else 2e-6)
+    if lik != "bernoulli":          # (lp, lo) carries the fp64 row sum of the fp32 per-pixel terms
+        assert rel_err(lp.detach().double() + lo.double(), ref) < 5e-8
+        assert (lo.abs() <= lp.detach().abs() * 2.0 ** -23).all()
     g = _rand(R, seed=3)
     (gr,) = torch.autograd.grad(lp, recon, g)
     (rr,) = torch.autograd.grad(ref, rd, g.to(ref.dtype))
@@ -189,17 +192,23 @@ def _moe_reference(z, mu, std, lpx, dist, mode, detach):
 @pytest.mark.parametrize("dist", ["laplace", "normal"])
 @pytest.mark.parametrize("mode", ["iwae", "iwae_looser", "dreg", "dreg_looser"])
 @pytest.mark.parametrize("M,K", [(2, 30), (3, 5), (2, 1), (2, 200)])
-def test_moe_logw(ops, dist, mode, M, K):
+@pytest.mark.parametrize("with_lo", [False, True])
+def test_moe_logw(ops, dist, mode, M, K, with_lo):
     B, L = 6, 20
     z = _rand(M, K, B, L, seed=1).requires_grad_()
     mu = _rand(M, B, L, seed=2, scale=0.5).requires_grad_()
     std = (torch.rand(M, B, L, generator=torch.Generator().manual_seed(3)) + 0.5).cuda().requires_grad_()
-    lpx = (_rand(M, M, K, B, seed=4) * 3 - 700).requires_grad_()
+    lpx64 = _rand(M, M, K, B, seed=4).double() * 3 - (7000 if with_lo else 700)
+    if with_lo:                     # (hi, lo) pair of an fp64 log-likelihood, as mmvae_loglik_fwd hands it over
+        lpx64 = lpx64 + torch.rand(lpx64.shape, dtype=torch.float64, generator=torch.Generator().manual_seed(5)).cuda() * 1e-3
+    lpx = lpx64.float().requires_grad_()
+    lo = (lpx64 - lpx.detach().double()).float() if with_lo else None
     pl, ps = torch.zeros(L).cuda(), torch.ones(L).cuda()
     detach = mode.startswith("dreg")
-    loss, lw, wt, per = ops.MoeLogW.apply(z, mu.detach() if detach else mu, std.detach() if detach else std, lpx, pl, ps,
-                                          dist, mode)
-    zd, mud, stdd, lpxd = (t.detach().double().requires_grad_() for t in (z, mu, std, lpx))
+    loss, lw, wt, per = ops.MoeLogW.apply(z, mu.detach() if detach else mu, std.detach() if detach else std, lpx, lo,
+                                          pl, ps, dist, mode)
+    zd, mud, stdd = (t.detach().double().requires_grad_() for t in (z, mu, std))
+    lpxd = lpx64.clone().requires_grad_() if with_lo else lpx.detach().double().requires_grad_()
     ref, lwr = _moe_reference(zd, mud, stdd, lpxd, dist, mode, detach)
     assert rel_err(lw, lwr) < 1e-6
     assert abs(loss.item() - ref.item()) <= 1e-5 * abs(ref.item())          # vs fp64
@@ -209,7 +218,7 @@ def test_moe_logw(ops, dist, mode, M, K):
     g = torch.autograd.grad(loss * 1.7, ins)
     gr = torch.autograd.grad(ref * 1.7, insd)
     for a, b in zip(g, gr):
-        assert rel_err(a, b) < 2e-4          # softmax weights of lw ~ -700 carry ~1e-4 relative fp32 noise
+        assert rel_err(a, b) < 1e-5          # lw and the softmax are formed in fp64: no |lw|*eps noise on the weights
 
 
 @pytest.mark.parametrize("dist", ["laplace", "normal"])

@@ -1,16 +1,17 @@
 """GPU parity tests proper: the CUDA path (through the C ABI) against
-  (a) the golden fixtures produced by the UNMODIFIED reference (tests/golden/*.pt), and
-  (b) the CPU oracle (oracle/bivae_oracle.py) evaluated in fp64 on the same weights, inputs and noise.
+  (a) the CPU oracle (oracle/bivae_oracle.py) evaluated in fp64 on the same weights, inputs and noise, and
+  (b) the golden fixtures produced by the UNMODIFIED fp32 reference (tests/golden/*.pt).
 Tolerances (north_star: loss and gradients within 1e-4 relative in fp32; log-likelihood within 1e-3 nats):
-  loss: 1e-5 relative against the fp64 oracle, and 1e-4 relative against the fp32 reference PLUS the reference's own
-  rounding noise in the DReG modes: it forms its weights as exp(lw - fp32(logsumexp(lw))) (objectives.py:399,435), so
-  each datapoint's sum_k w*lw is scaled by exp(+-ulp(lse)/2), i.e. carries |lw|*ulp(|lw|)/2 of noise (lw ~ -6000 ->
-  1.5 nats per datapoint); the kernel normalises by the sum itself and sits on the fp64 value instead.
-  gradients: GRAD_RTOL_REF = 1e-3 per tensor against the fp32 reference digests (the fp32 reference itself sits
-  1e-4..5e-4 from fp64 on the encoder gradients — see tests/test_oracle_golden.py — and this path up to 2e-4; measured
-  worst case 6.3e-4 on obj_msf:dreg, M=3 K=2, lw ~ -9000) and GRAD_RTOL_F64 = 2e-4 against the
-  fp64 oracle on the global gradient vector (lw ~ -9000 stored in fp32 has ulp 1e-3, which the softmax over K turns
-  into ~1e-4 relative noise on the weights for ANY fp32 implementation); log-likelihoods 1e-3 nats."""
+  vs the fp64 oracle (the exact value of the reference's formulas):  loss 1e-6 relative; every gradient tensor
+  GRAD_RTOL_F64 = 2e-5 on the digest samples and on its norm, 5e-6 on the global gradient vector (measured worst
+  case 4.5e-6 / 1e-6, profiles/r1_parity_report.txt) — i.e. 5x..100x inside the 1e-4 bar.
+  vs the fp32 reference digests:  1e-4 relative PLUS the reference's own rounding noise, which this test MEASURES per
+  tensor as |reference_fp32 - oracle_fp64| (1e-4..6e-4 on encoder gradients in the importance-weighted objectives:
+  the reference stores lw ~ -3000..-9000 in fp32, one ulp of which is a 2.4e-4..1e-3 relative error on a softmax
+  weight; objectives.py:399,435).  The CUDA path forms lw and the softmax in fp64 from fp32 terms, so it sits on the
+  fp64 value; the two fp32-reference terms below are therefore bounds on the REFERENCE, not slack for this path.
+  DReG losses: the reference's exp(lw - fp32(logsumexp)) scales each datapoint's sum_k w*lw by exp(+-ulp(lse)/2),
+  i.e. |lw|*ulp(|lw|)/2 per datapoint of noise, added to its loss tolerance the same way."""
 import math
 
 import pytest
@@ -18,11 +19,11 @@ import torch
 
 from oracle import bivae_oracle as O
 from oracle import synth
-from tests.helpers import build_mmvae, check_digests, leaf_sd, load_golden, rel_err
+from tests.helpers import build_mmvae, leaf_sd, load_golden, rel_err
 
 pytestmark = pytest.mark.gpu
-GRAD_RTOL_REF = 1e-3
-GRAD_RTOL_F64 = 2e-4
+GRAD_RTOL_REF = 1e-4          # + the reference's measured fp32 noise (see above)
+GRAD_RTOL_F64 = 2e-5
 OBJ_CASES = ["obj_ms_laplace", "obj_ms_normal", "obj_ms_bern_lap", "obj_circles", "obj_msf"]
 
 
@@ -56,14 +57,29 @@ def test_objectives_match_reference_and_f64_oracle(name):
             noise_ref = float((0.5 * per * torch.finfo(torch.float32).eps * per).sum())
         assert abs(loss.item() - ref) <= 1e-4 * abs(ref) + noise_ref, (name, oname, loss.item(), ref)
         grads = {k: p.grad for k, p in model.named_parameters()}
-        check_digests(grads, res["grads"], GRAD_RTOL_REF, f"{name}:{oname}")
         l64, g64 = _f64_oracle_grads(spec, sd, oname, g["x"], g["K"], g["noise"])
-        assert abs(loss.item() - l64) <= 1e-5 * abs(l64)
+        assert abs(loss.item() - l64) <= 1e-6 * abs(l64)
+        for k, d in res["grads"].items():
+            ours = grads[k].detach().reshape(-1).double().cpu()
+            if d["norm"] == 0.0:
+                assert ours.norm().item() == 0.0, f"{name}:{oname}: {k} should have zero grad"
+                continue
+            exact = g64[k].reshape(-1)
+            idx, ref32 = d["idx"], d["vals"].double()
+            scale = max(exact[idx].norm().item(), 1e-3 * exact.norm().item())
+            e_exact = (ours[idx] - exact[idx]).norm().item()
+            assert e_exact <= GRAD_RTOL_F64 * scale, f"{name}:{oname}: {k} off the fp64 oracle by {e_exact / scale:.2e}"
+            assert abs(ours.norm().item() - exact.norm().item()) <= GRAD_RTOL_F64 * exact.norm().item(), (name, oname, k)
+            ref_noise = (ref32 - exact[idx]).norm().item()             # the fp32 reference's own distance to fp64
+            e_ref = (ours[idx] - ref32).norm().item()
+            assert e_ref <= GRAD_RTOL_REF * scale + 1.05 * ref_noise, \
+                f"{name}:{oname}: {k} off the reference by {e_ref / scale:.2e} (reference noise {ref_noise / scale:.2e})"
+            assert abs(ours.norm().item() - d["norm"]) <= GRAD_RTOL_REF * d["norm"] + 1.05 * abs(d["norm"] - exact.norm().item())
         keys = sorted(g64)
         ours = torch.cat([grads[k].detach().double().cpu().reshape(-1) for k in keys])
         theirs = torch.cat([g64[k].reshape(-1) for k in keys])
         err = ((ours - theirs).norm() / theirs.norm()).item()
-        assert err <= GRAD_RTOL_F64, f"{name}:{oname} global gradient off by {err:.3e}"
+        assert err <= 5e-6, f"{name}:{oname} global gradient off the fp64 oracle by {err:.3e}"
 
 
 def test_forward_tuple_has_reference_shapes():
