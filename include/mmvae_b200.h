@@ -29,6 +29,11 @@ extern "C" {
 #define MMVAE_LIK_NORMAL    0
 #define MMVAE_LIK_LAPLACE   1
 #define MMVAE_LIK_BERNOULLI 2
+/* "negative reconstruction loss" rows of m_jmvae_nf (recon_loss_dict, objectives.py:177,196-204): the same reduction
+ * kernel with -F.mse_loss (no 1/2, no constant), -F.l1_loss, -F.binary_cross_entropy (logs clamped at -100) */
+#define MMVAE_LIK_NEG_MSE   3
+#define MMVAE_LIK_NEG_L1    4
+#define MMVAE_LIK_NEG_BCE   5
 /* how the second encoder head becomes a scale */
 #define MMVAE_XFORM_EXP_HALF      0  /* std = exp(0.5*raw)            vae_model_adapted.py:84 */
 #define MMVAE_XFORM_SOFTMAX       1  /* std = softmax(raw)*L + 1e-6   laplace_vae.py:69 */
@@ -140,8 +145,30 @@ int mmvae_im2col(const float* x, float* col, int N, int C, int H, int W, int k, 
 int mmvae_col2im(const float* col, const float* bias, float* y, int N, int C, int H, int W, int k, int s, int p,
                  long sn, long sc, long sy, long sx, int act, void* stream);
 
-/* MADE / MAF / IAF elementwise pieces (maf_model.py:62-74,91-104; iaf_model.py:60-78,94-100) */
+/* MADE / MAF / IAF elementwise pieces (maf_model.py:62-74,91-104; iaf_model.py:60-78,94-100).  The masked-linear
+ * contractions go through mmvae_gemm with the pre-masked weight (layers.py:24-25: F.linear(x, mask*W, b)). */
 int mmvae_mask_weight(const float* w, const float* mask, float* out, long n, void* stream);
+/* affine coupling fused with the log|det J| update.  x: [R,L] block input; h: [R,2L] = MADE output (mu | log_var).
+ * mode 0 "normalise" (MAF.forward, IAF.forward): u = (x-mu)*exp(-lv), ladj_out = ladj_in - sum lv;
+ * mode 1 "generate"  (MAF.inverse, IAF.inverse): u = x*exp(lv)+mu,     ladj_out = ladj_in + sum lv.
+ * col < 0: every column, out[r, flip_out ? L-1-l : l] = u_l (the flip of maf_model.py:74 folded in).
+ * col >= 0: one step of the sequential direction: out = carry with column col replaced by u_col; ladj +-= lv[col]. */
+int mmvae_flow_affine_fwd(const float* x, const float* h, const float* carry, const float* ladj_in, float* out,
+                          float* ladj_out, int R, int L, int mode, int col, int flip_out, void* stream);
+/* g_out [R,L], g_ladj [R] or NULL -> g_x [R,L], g_h [R,2L], g_carry [R,L] (col >= 0 only). */
+int mmvae_flow_affine_bwd(const float* g_out, const float* g_ladj, const float* x, const float* h, float* g_x,
+                          float* g_h, float* g_carry, int R, int L, int mode, int col, int flip_out, void* stream);
+/* out[r, L-1-l] = x[r, l]  (x.flip(dims=(1,)), maf_model.py:74,91) */
+int mmvae_flip_cols(const float* x, float* out, int R, int L, void* stream);
+/* Gaussian row reductions of the JMVAE-NF regulariser.  z: [R,L]; mu,s: [R/div, L] (each shared by `div` rows).
+ * kind 0: out[r] = sum_l log N(z; mu, std=s)                      (qz_xy.log_prob(z), jmvae_nf.py:69,260-261)
+ * kind 1: out[r] = sum_l -0.5*(s + log 2pi + (z-mu)^2/exp(s)), s = log_var   (jmvae_nf.py:67,131-133)
+ * kind 2: out[r] = -0.5*sum_l(1 + lv - mu^2 - exp(lv)), lv = 2 log s; z unused (objectives.py:208-211) */
+int mmvae_gauss_rows_fwd(const float* z, const float* mu, const float* s, float* out, int R, int L, int kind,
+                         int div, void* stream);
+/* g: [R] -> g_z, g_mu, g_s: [R,L] (div == 1). */
+int mmvae_gauss_rows_bwd(const float* g, const float* z, const float* mu, const float* s, float* g_z, float* g_mu,
+                         float* g_s, int R, int L, int kind, void* stream);
 
 /* fused multi-tensor Adam(amsgrad) over one flat buffer (main.py:114-115).  step_dev: device fp32 scalar holding
  * the number of steps taken so far; this call increments it first (so the update is CUDA-graph replayable). */

@@ -8,5 +8,8 @@ from . import objectives, ops  # noqa: E402
 from .models import (MMVAE, MNIST_SVHN, CIRCLES_SQUARES, MNIST_SVHN_FASHION, Multi_VAES, VAE_circles_squares,  # noqa: E402
                      VAE_mmvae_msf, VAE_mnist_svhn)
 
-__all__ = ["objectives", "ops", "MMVAE", "Multi_VAES", "MNIST_SVHN", "CIRCLES_SQUARES", "MNIST_SVHN_FASHION",
+from . import flows  # noqa: E402
+from .jmvae_nf import JMVAE_NF, JMVAE_NF_DCCA_MNIST_SVHN, VAE_jnf_mnist_svhn_dcca  # noqa: E402
+
+__all__ = ["flows", "JMVAE_NF", "JMVAE_NF_DCCA_MNIST_SVHN", "VAE_jnf_mnist_svhn_dcca","objectives", "ops", "MMVAE", "Multi_VAES", "MNIST_SVHN", "CIRCLES_SQUARES", "MNIST_SVHN_FASHION",
            "VAE_mnist_svhn", "VAE_circles_squares", "VAE_mmvae_msf"]

@@ -14,9 +14,16 @@ __device__ __forceinline__ float ll_elem(float x, float r) {
         return -0.5f * d * d;
     } else if (LIK == MMVAE_LIK_LAPLACE) {    // -log 2 - |x-r|
         return -fabsf(x - r);
-    } else {                                  // Bernoulli(probs=clamp(r, eps, 1-eps))
+    } else if (LIK == MMVAE_LIK_BERNOULLI) {  // Bernoulli(probs=clamp(r, eps, 1-eps))
         const float p = fminf(fmaxf(r, MMVAE_F32_EPS), 1.f - MMVAE_F32_EPS);
         return x * logf(p) + (1.f - x) * log1pf(-p);
+    } else if (LIK == MMVAE_LIK_NEG_MSE) {    // -F.mse_loss(reduction='none'): no 1/2, no constant (objectives.py:177)
+        const float d = r - x;
+        return -(d * d);
+    } else if (LIK == MMVAE_LIK_NEG_L1) {     // -F.l1_loss
+        return -fabsf(r - x);
+    } else {                                  // -F.binary_cross_entropy: logs clamped at -100 (torch semantics)
+        return x * fmaxf(logf(r), -100.f) + (1.f - x) * fmaxf(log1pf(-r), -100.f);
     }
 }
 
@@ -27,8 +34,16 @@ __device__ __forceinline__ float ll_grad(float x, float r) {
         const float d = x - r;
         return (float)((d > 0.f) - (d < 0.f));
     }
-    if (r < MMVAE_F32_EPS || r > 1.f - MMVAE_F32_EPS) return 0.f;      // clamp passes no gradient outside
-    return (x - r) / (r * (1.f - r));
+    if (LIK == MMVAE_LIK_BERNOULLI) {
+        if (r < MMVAE_F32_EPS || r > 1.f - MMVAE_F32_EPS) return 0.f;  // clamp passes no gradient outside
+        return (x - r) / (r * (1.f - r));
+    }
+    if (LIK == MMVAE_LIK_NEG_MSE) return 2.f * (x - r);
+    if (LIK == MMVAE_LIK_NEG_L1) {
+        const float d = x - r;
+        return (float)((d > 0.f) - (d < 0.f));
+    }
+    return (x - r) / fmaxf(r * (1.f - r), 1e-12f);                     // torch binary_cross_entropy_backward
 }
 
 __device__ __forceinline__ void ll_store(float* lp, float* lp_lo, long row, double v) {
@@ -137,6 +152,9 @@ extern "C" int mmvae_loglik_fwd(const float* recon, const float* x, float* lp, f
     if (lik == MMVAE_LIK_NORMAL) launch_fwd<MMVAE_LIK_NORMAL>(recon, x, lp, lp_lo, R, B, D, x_div, lik_scaling, st);
     else if (lik == MMVAE_LIK_LAPLACE) launch_fwd<MMVAE_LIK_LAPLACE>(recon, x, lp, lp_lo, R, B, D, x_div, lik_scaling, st);
     else if (lik == MMVAE_LIK_BERNOULLI) launch_fwd<MMVAE_LIK_BERNOULLI>(recon, x, lp, lp_lo, R, B, D, x_div, lik_scaling, st);
+    else if (lik == MMVAE_LIK_NEG_MSE) launch_fwd<MMVAE_LIK_NEG_MSE>(recon, x, lp, lp_lo, R, B, D, x_div, lik_scaling, st);
+    else if (lik == MMVAE_LIK_NEG_L1) launch_fwd<MMVAE_LIK_NEG_L1>(recon, x, lp, lp_lo, R, B, D, x_div, lik_scaling, st);
+    else if (lik == MMVAE_LIK_NEG_BCE) launch_fwd<MMVAE_LIK_NEG_BCE>(recon, x, lp, lp_lo, R, B, D, x_div, lik_scaling, st);
     else return mmvae_set_error(1, "loglik_fwd: bad likelihood %d", lik);
     MMVAE_LAUNCH_CHECK("loglik_fwd");
     return 0;
@@ -152,15 +170,16 @@ extern "C" int mmvae_loglik_bwd(const float* grad_lp, const float* recon, const 
     const long total4 = (long)R * (D / 4);
     const int grid = (int)min((long)MMVAE_NUM_SMS * 8, (total4 + LL_THREADS - 1) / LL_THREADS);
     const int D4 = D / 4;
-    if (lik == MMVAE_LIK_NORMAL)
-        loglik_bwd_kernel<MMVAE_LIK_NORMAL><<<grid, LL_THREADS, 0, st>>>(grad_lp, (const float4*)recon, (const float4*)x,
-                                                                        (float4*)grad, total4, B, D4, x_div, lik_scaling, through_sigmoid);
-    else if (lik == MMVAE_LIK_LAPLACE)
-        loglik_bwd_kernel<MMVAE_LIK_LAPLACE><<<grid, LL_THREADS, 0, st>>>(grad_lp, (const float4*)recon, (const float4*)x,
-                                                                         (float4*)grad, total4, B, D4, x_div, lik_scaling, through_sigmoid);
-    else if (lik == MMVAE_LIK_BERNOULLI)
-        loglik_bwd_kernel<MMVAE_LIK_BERNOULLI><<<grid, LL_THREADS, 0, st>>>(grad_lp, (const float4*)recon, (const float4*)x,
-                                                                           (float4*)grad, total4, B, D4, x_div, lik_scaling, through_sigmoid);
+#define LL_BWD(LIKV)                                                                                              \
+    loglik_bwd_kernel<LIKV><<<grid, LL_THREADS, 0, st>>>(grad_lp, (const float4*)recon, (const float4*)x, (float4*)grad, \
+                                                         total4, B, D4, x_div, lik_scaling, through_sigmoid)
+    if (lik == MMVAE_LIK_NORMAL) LL_BWD(MMVAE_LIK_NORMAL);
+    else if (lik == MMVAE_LIK_LAPLACE) LL_BWD(MMVAE_LIK_LAPLACE);
+    else if (lik == MMVAE_LIK_BERNOULLI) LL_BWD(MMVAE_LIK_BERNOULLI);
+    else if (lik == MMVAE_LIK_NEG_MSE) LL_BWD(MMVAE_LIK_NEG_MSE);
+    else if (lik == MMVAE_LIK_NEG_L1) LL_BWD(MMVAE_LIK_NEG_L1);
+    else if (lik == MMVAE_LIK_NEG_BCE) LL_BWD(MMVAE_LIK_NEG_BCE);
+#undef LL_BWD
     else return mmvae_set_error(1, "loglik_bwd: bad likelihood %d", lik);
     MMVAE_LAUNCH_CHECK("loglik_bwd");
     return 0;

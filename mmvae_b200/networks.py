@@ -175,8 +175,8 @@ class LinearCCAEncoder(nn.Module):
         # (h - m) @ w == h @ w - m @ w: one GEMM with bias = -(m @ w); w is stored [K, N] (b_kmajor = 0)
         R, Kd = h.shape
         bias = ops.gemm(self.m.reshape(1, Kd).contiguous(), self.w, None, 1, Kd, Kd, True, False).reshape(-1).neg()
-        out = ops.gemm(ops._c(h), self.w, bias, R, Kd, Kd, True, False)
-        return ModelOutput(embedding=out[:, :self.latent_dim].contiguous())
+        out = ops.LinearAct.apply(h, self.w.t().contiguous(), bias, None)       # differentiable w.r.t. h (DCCA-space
+        return ModelOutput(embedding=out[:, :self.latent_dim].contiguous())    # reconstruction loss, jmvae_nf.py:147-156)
 
 
 class DoubleHeadJoint(BaseEncoder):
@@ -205,8 +205,11 @@ class DoubleHeadJoint(BaseEncoder):
         return _linear(self.fc21, e), _linear(self.fc22, e)
 
     def forward(self, x):
+        """joint_encoders.py:76-82: -> (mu, std) with std = exp(0.5*fc22(e)) + eta."""
         mu, raw = self.forward_raw(x)
-        return ModelOutput(embedding=mu, log_covariance=raw)
+        zero = torch.zeros((1, 1) + tuple(mu.shape), device=mu.device)
+        _, std = ops.RSample.apply(mu.unsqueeze(0), raw.unsqueeze(0), zero, "normal", "exp_half_eps", False)
+        return mu, std.reshape(mu.shape)
 
 
 class MultipleHeadJoint(DoubleHeadJoint):

@@ -83,3 +83,13 @@ def m_dreg_looser(model, x, K=1, epoch=1, warmup=0, beta_prior=1, noise=None):
     _require_mmvae(model)
     loss, _ = _split_sum(model, x, K, "dreg_looser", noise)
     return loss, {}
+
+
+def m_jmvae_nf(model, x, K=1, epoch=1, warmup=0, beta_prior=1, noise=None):
+    """objectives.py:179-220: -sum_m s_m * recon_loss_m - beta_reg * (beta_prior * KL(q(z|x,y)||p) + reg), with the
+    freezing toggles of :180-183 and the linear warm-up of :185-188 (the wandb.log of :189 is dropped — SURVEY A15).
+    noise: None or dict(eps1, eps2, eps_uni) to replay recorded draws."""
+    from .jmvae_nf import JMVAE_NF
+    if not isinstance(model, JMVAE_NF):
+        raise TypeError(f"m_jmvae_nf needs an mmvae_b200 JMVAE_NF model, got {type(model).__name__}")
+    return model.objective(x, epoch=epoch, warmup=warmup, beta_prior=beta_prior, noise=noise)

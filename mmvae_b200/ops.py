@@ -14,7 +14,8 @@ from . import _lib
 
 C = _lib.CONSTS
 DIST = {"normal": C["MMVAE_DIST_NORMAL"], "laplace": C["MMVAE_DIST_LAPLACE"]}
-LIK = {"normal": C["MMVAE_LIK_NORMAL"], "laplace": C["MMVAE_LIK_LAPLACE"], "bernoulli": C["MMVAE_LIK_BERNOULLI"]}
+LIK = {"normal": C["MMVAE_LIK_NORMAL"], "laplace": C["MMVAE_LIK_LAPLACE"], "bernoulli": C["MMVAE_LIK_BERNOULLI"],
+       "neg_mse": C["MMVAE_LIK_NEG_MSE"], "neg_l1": C["MMVAE_LIK_NEG_L1"], "neg_bce": C["MMVAE_LIK_NEG_BCE"]}
 ACT = {None: C["MMVAE_ACT_NONE"], "none": C["MMVAE_ACT_NONE"], "relu": C["MMVAE_ACT_RELU"],
        "sigmoid": C["MMVAE_ACT_SIGMOID"]}
 XFORM = {"exp_half": C["MMVAE_XFORM_EXP_HALF"], "softmax": C["MMVAE_XFORM_SOFTMAX"],
@@ -405,6 +406,99 @@ class Elbo(torch.autograd.Function):
         _call("mmvae_elbo_bwd", _p(g), _p(z), _p(mu), _p(std), _p(lpx_diag), _p(pz_loc), _p(pz_scale), _p(gmu),
               _p(gstd), _p(glpx), M, K, B, L, DIST[dist], _stream())
         return None, gmu, gstd, glpx, None, None, None
+
+
+# ------------------------------------------------------------------------------------------- flows / JMVAE-NF
+class MaskWeight(torch.autograd.Function):
+    """mask * W of MaskedLinear (layers.py:24-25); the gradient is masked the same way."""
+
+    @staticmethod
+    def forward(ctx, w, mask):
+        ctx.save_for_backward(mask)
+        return mask_weight(w, mask)
+
+    @staticmethod
+    def backward(ctx, g):
+        (mask,) = ctx.saved_tensors
+        return mask_weight(_c(g, "grad"), mask), None
+
+
+class FlowAffine(torch.autograd.Function):
+    """Affine coupling + log|det J| update (mmvae_flow_affine_fwd).  -> (out [R,L], ladj_out [R])."""
+
+    @staticmethod
+    def forward(ctx, x, h, carry, ladj_in, mode, col, flip_out):
+        x, h, ladj_in = _c(x, "x"), _c(h, "h"), _c(ladj_in, "ladj")
+        carry = None if carry is None else _c(carry, "carry")
+        R, L = x.shape
+        assert h.shape == (R, 2 * L) and ladj_in.shape == (R,)
+        out, ladj = torch.empty_like(x), torch.empty_like(ladj_in)
+        _call("mmvae_flow_affine_fwd", _p(x), _p(h), _p(carry), _p(ladj_in), _p(out), _p(ladj), R, L, int(mode), int(col),
+              int(flip_out), _stream())
+        ctx.save_for_backward(x, h)
+        ctx.cfg = (R, L, int(mode), int(col), int(flip_out), carry is not None)
+        return out, ladj
+
+    @staticmethod
+    def backward(ctx, g_out, g_ladj):
+        x, h = ctx.saved_tensors
+        R, L, mode, col, flip_out, has_carry = ctx.cfg
+        g_out = _c(g_out, "grad_out") if g_out is not None else torch.zeros_like(x)
+        g_ladj = None if g_ladj is None else _c(g_ladj, "grad_ladj")
+        g_x, g_h = torch.empty_like(x), torch.empty_like(h)
+        g_carry = torch.empty_like(x) if col >= 0 else None
+        _call("mmvae_flow_affine_bwd", _p(g_out), _p(g_ladj), _p(x), _p(h), _p(g_x), _p(g_h), _p(g_carry), R, L, mode, col,
+              flip_out, _stream())
+        return g_x, g_h, (g_carry if has_carry else None), g_ladj, None, None, None
+
+
+class FlipCols(torch.autograd.Function):
+    """x.flip(dims=(1,)) for a 2-D tensor."""
+
+    @staticmethod
+    def forward(ctx, x):
+        x = _c(x, "x")
+        out = torch.empty_like(x)
+        _call("mmvae_flip_cols", _p(x), _p(out), x.shape[0], x.shape[1], _stream())
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        return FlipCols.apply(g)
+
+
+GAUSS_KIND = {"std": 0, "log_var": 1, "kl_prior": 2}
+
+
+class GaussRows(torch.autograd.Function):
+    """Row sums of Gaussian log densities / the closed-form prior KL (mmvae_gauss_rows_fwd).  z [R,L] (None for
+    'kl_prior'); mu, s [R/div, L].  -> [R].  Differentiable for div == 1."""
+
+    @staticmethod
+    def forward(ctx, z, mu, s, kind, div):
+        mu, s = _c(mu, "mu"), _c(s, "s")
+        z = None if z is None else _c(z, "z")
+        L = mu.shape[-1]
+        R = mu.shape[0] * div if z is None else z.shape[0]
+        assert mu.shape[0] * div == R and s.shape == mu.shape
+        out = torch.empty(R, device=mu.device, dtype=torch.float32)
+        _call("mmvae_gauss_rows_fwd", _p(z), _p(mu), _p(s), _p(out), R, L, GAUSS_KIND[kind], int(div), _stream())
+        ctx.save_for_backward(z, mu, s)
+        ctx.cfg = (R, L, kind, div)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        z, mu, s = ctx.saved_tensors
+        R, L, kind, div = ctx.cfg
+        if div != 1:
+            raise RuntimeError("GaussRows is differentiable only for div == 1 (the evaluators run under no_grad)")
+        g = _c(g, "grad")
+        g_z = None if z is None else torch.empty_like(z)
+        g_mu, g_s = torch.empty_like(mu), torch.empty_like(s)
+        _call("mmvae_gauss_rows_bwd", _p(g), _p(z), _p(mu), _p(s), _p(g_z), _p(g_mu), _p(g_s), R, L, GAUSS_KIND[kind],
+              _stream())
+        return g_z, g_mu, g_s, None, None
 
 
 # ----------------------------------------------------------------------------------- evaluator (no autograd)

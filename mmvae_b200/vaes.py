@@ -105,6 +105,36 @@ class my_VAE(_BaseVAE):
     dist, xform = "normal", "exp_half"
 
 
+class _FlowVAE(my_VAE):
+    """Gaussian q(z0|x) pushed through a flow: z = flow.inverse(z0) (sampling direction), z0 = flow(z)."""
+    flow_cls = None
+
+    def __init__(self, model_config, encoder=None, decoder=None):
+        super().__init__(model_config, encoder, decoder)
+        from . import flows
+        cls = getattr(flows, self.flow_cls)
+        self.flow = cls(model_config.latent_dim, getattr(model_config, "n_made_blocks", 2),
+                        getattr(model_config, "n_hidden_in_made", 3), getattr(model_config, "hidden_size", 128))
+
+    def flow_inverse(self, z0):
+        o = self.flow.inverse(z0)
+        return o.out, o.log_abs_det_jac
+
+    def flow_forward(self, z):
+        o = self.flow(z)
+        return o.out, o.log_abs_det_jac
+
+
+class my_VAE_MAF(_FlowVAE):
+    """vae_maf/vae_maf_model_adapted.py:39-104 (the unused neg_elbo of :90 is not computed — SURVEY A5)."""
+    flow_cls = "MAF"
+
+
+class my_VAE_IAF(_FlowVAE):
+    """vae_iaf/vae_iaf_model_adapted.py:39-103."""
+    flow_cls = "IAF"
+
+
 class laplace_VAE(_BaseVAE):
     """Laplace posterior, std = softmax(log_var)*L + 1e-6 (laplace_vae.py:69-71)."""
     dist, xform = "laplace", "softmax"
