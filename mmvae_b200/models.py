@@ -66,11 +66,14 @@ class Multi_VAES(nn.Module):
         c = self.lik_scaling[d] if scaled else 1.0
         return ops.LogLik.apply(recon.reshape(R, -1), self._flat_x(x_d), x_div, self.params.recon_losses[d], c, False)[0]
 
-    def _is_loglik(self, z, data, mods, qmode, mu=None, std=None, lq_ext=None, K_total=None, with_prior=True):
+    def _is_loglik(self, z, data, mods, qmode, mu=None, std=None, lq_ext=None, K_total=None, with_prior=True,
+                   partial=False):
         """ln p_hat per datapoint from latents z [B,Ku,L]:  logsumexp_k( sum_{d in mods} log p(x_d|z_k)
-        [+ log p(z_k) - q-term] ) - ln K_total, chunked over datapoints."""
+        [+ log p(z_k) - q-term] ) - ln K_total, chunked over datapoints.  partial=True returns the per-datapoint
+        (max, sum exp) pair of this K-shard instead (merged across ranks by parallel.combine_lse)."""
         B, Ku, L = z.shape
         out = torch.empty(B, device=z.device, dtype=torch.float32)
+        out_se = torch.empty(B, device=z.device, dtype=torch.float32) if partial else None
         step = max(1, self.eval_max_rows // Ku)
         for b0 in range(0, B, step):
             b1 = min(B, b0 + step)
@@ -85,8 +88,11 @@ class Multi_VAES(nn.Module):
             else:
                 a = lpx.sum(0) if len(mods) > 1 else lpx[0]
             mx, se = ops.lse_partial(a)
-            out[b0:b1] = ops.lse_finish(mx, se, K_total)
-        return out
+            if partial:
+                out[b0:b1], out_se[b0:b1] = mx, se
+            else:
+                out[b0:b1] = ops.lse_finish(mx, se, K_total)
+        return (out, out_se) if partial else out
 
     def _cond_latents(self, cond_mod, x_c, Ku, noise):
         """z ~ q(z|x_cond), Ku draws per datapoint -> [B,Ku,L] (flow-transformed for NF models)."""
@@ -228,6 +234,13 @@ class MMVAE(Multi_VAES):
     def compute_joint_likelihood(self, data, K=1000, batch_size_K=100, mask=None, noise=None, correct_mixture=False):
         """mmvae.py:121-177.  mask (K,B) in {0,1} and noise [M] x (K,B,L) may be given for parity; the reference's
         `logsumexp(.)/2` mixture term (mmvae.py:166) is reproduced unless correct_mixture."""
+        z, mu, std = self._joint_latents(data, K, batch_size_K, mask, noise)
+        ll = self._is_loglik(z, data, range(self.mod), "mixture" if correct_mixture else "mixture_half", mu, std, K_total=K)
+        self.last_per_datapoint = ll
+        return {"likelihood": ll.mean()}
+
+    def _joint_latents(self, data, K, batch_size_K, mask=None, noise=None):
+        """mmvae.py:123-133: z_k from the 1/2-1/2 mixture of the two posteriors -> z [B,Kused,L], mu, std [M,B,L]."""
         assert self.mod == 2, "the reference's mixture sampling (mmvae.py:128-133) is written for two modalities"
         mu, raw = self._encode_all(data)
         M, B, L = mu.shape
@@ -241,9 +254,7 @@ class MMVAE(Multi_VAES):
         zs, std = ops.RSample.apply(mu, raw, noise.reshape(M, K, B, L), self.params.dist, self._xform(), False)
         bern = mask.to(device=dev, dtype=torch.float32).reshape(K, B, 1)
         z = (bern * zs[0] + (1 - bern) * zs[1]).permute(1, 0, 2)[:, :self._used(K, batch_size_K)].contiguous()
-        ll = self._is_loglik(z, data, range(M), "mixture" if correct_mixture else "mixture_half", mu, std, K_total=K)
-        self.last_per_datapoint = ll
-        return {"likelihood": ll.mean()}
+        return z, mu, std
 
     @torch.no_grad()
     def compute_joint_ll_from_uni(self, data, cond_mod, K=1000, batch_size_K=100, noise=None):

@@ -188,3 +188,31 @@ def test_full_size_eval_chunking_c4():
         _, ref = O.conditional_likelihood(spec, sd, [t.cpu() for t in data[:2]] if False else [t[:2].cpu() for t in data],
                                           0, 1, K, 100, noise[:2].cpu())
     assert torch.allclose(per_a[:2], ref, atol=1e-3, rtol=0)
+
+
+def test_sharded_evaluator_api_single_process():
+    """parallel.joint_likelihood / conditional_likelihood on one rank == the model's own evaluators, both axes; and a
+    two-shard (max, sum-exp) merge emulated in-process == unsharded."""
+    import numpy as np
+    from mmvae_b200 import parallel as P
+    B, K, L = 5, 40, 20
+    spec, sd, model, data = _c2_model(B, seed=11)
+    rs = np.random.RandomState(3)
+    noise = torch.stack([synth.make_noise("laplace", (K, B, L), rs) for _ in range(2)]).cuda()
+    mask = torch.from_numpy(rs.binomial(1, 0.5, (K, B))).float().cuda()
+    ref = model.compute_joint_likelihood(data, K=K, batch_size_K=10, mask=mask, noise=noise)["likelihood"].item()
+    per_ref = model.last_per_datapoint.clone()
+    for axis in ("batch", "samples"):
+        out, per = P.joint_likelihood(model, data, K, 10, axis=axis, mask=mask, noise=noise)
+        assert abs(out["likelihood"].item() - ref) < 1e-4 and torch.allclose(per, per_ref, atol=1e-4, rtol=0)
+    z, mu, std = model._joint_latents(data, K, 10, mask, noise)
+    parts = [model._is_loglik(z[:, a:b].contiguous(), data, range(2), "mixture_half", mu, std, K_total=K, partial=True)
+             for a, b in (P.shard_bounds(K, 0, 2), P.shard_bounds(K, 1, 2))]
+    g = torch.maximum(parts[0][0], parts[1][0])
+    merged = P.finish_lse(g, sum(se * torch.exp(mx - g) for mx, se in parts), K)
+    assert torch.allclose(merged, per_ref, atol=1e-4, rtol=0)
+    cn = synth.make_noise("laplace", (B, K, L), rs).cuda()
+    _, cref = model.compute_conditional_likelihood(data, 1, 0, K=K, batch_size_K=10, noise=cn)
+    for axis in ("batch", "samples"):
+        _, cper = P.conditional_likelihood(model, data, 1, 0, K, 10, axis=axis, noise=cn)
+        assert torch.allclose(cper.cpu(), cref, atol=1e-4, rtol=0)
