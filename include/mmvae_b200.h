@@ -145,6 +145,21 @@ int mmvae_im2col(const float* x, float* col, int N, int C, int H, int W, int k, 
 int mmvae_col2im(const float* col, const float* bias, float* y, int N, int C, int H, int W, int k, int s, int p,
                  long sn, long sc, long sy, long sx, int act, void* stream);
 
+/* ConvTranspose2d(Cin -> Cout <= 4, k=4, s=2, p=1) as direct kernels (the image-producing layer of Decoder_VAE_SVHN,
+ * encoders.py:125-126).  x: (N,H,W,Cin) NHWC; w: torch layout (Cin,Cout,4,4); y, g: (N,Cout,2H,2W) NCHW.
+ * supported(): 0 = no, 1 = fwd + dgrad, 2 = fwd + dgrad + wgrad (Cin == 32). */
+int  mmvae_convt_small_supported(int H, int W, int Cin, int Cout);
+int  mmvae_convt_small_fwd(const float* x, const float* w, const float* bias, float* y, int N, int H, int W, int Cin,
+                           int Cout, int act, void* stream);
+/* g: gradient w.r.t. y; if y_act != NULL it is multiplied by act'(y_act) on the fly (g is then post-activation).
+ * x_mask: NULL or the layer's input x (N,H,W,Cin): gx is zeroed where x <= 0 (fused ReLU backward of the layer below). */
+int  mmvae_convt_small_dgrad(const float* g, const float* y_act, const float* w, const float* x_mask, float* gx,
+                             int N, int H, int W, int Cin, int Cout, int act, void* stream);
+/* gw: (Cin,Cout,4,4); gb: [Cout] or NULL; workspace >= mmvae_convt_small_wgrad_workspace_bytes(N,Cin,Cout). */
+int  mmvae_convt_small_wgrad(const float* x, const float* g, const float* y_act, float* gw, float* gb, float* workspace,
+                             int N, int H, int W, int Cin, int Cout, int act, void* stream);
+long mmvae_convt_small_wgrad_workspace_bytes(int N, int Cin, int Cout);
+
 /* MADE / MAF / IAF elementwise pieces (maf_model.py:62-74,91-104; iaf_model.py:60-78,94-100).  The masked-linear
  * contractions go through mmvae_gemm with the pre-masked weight (layers.py:24-25: F.linear(x, mask*W, b)). */
 int mmvae_mask_weight(const float* w, const float* mask, float* out, long n, void* stream);

@@ -1,0 +1,360 @@
+// ConvTranspose2d(Cin -> Cout <= 4, kernel 4, stride 2, pad 1): the image-producing last layer of Decoder_VAE_SVHN
+// (encoders.py:125-126: ConvT(32 -> 3) + Sigmoid, 16x16 -> 32x32) as DIRECT kernels, forward / dgrad / wgrad.
+// With Cout = 3 this layer is 8.5 % of the decoder's FLOPs but, lowered to a GEMM, the widest memory hog of the step
+// (a 377 MB col buffer written and re-read in each direction, N = 3 padded to a tensor-core tile): it is HBM-bound
+// integer-stride gather work, so it runs on the FP32 pipes with the image staged in shared memory and touches HBM once:
+//   fwd  : reads x (N,H,W,Cin) NHWC once, writes y (N,Cout,2H,2W) NCHW once, bias + activation fused;
+//   dgrad: reads g once (+ y when the activation derivative is fused here), writes gx once, ReLU mask of the layer
+//          below fused (gx is then the gradient w.r.t. that layer's PRE-activation);
+//   wgrad: reads x and g once, per-CTA register accumulators across images, deterministic two-stage reduction, the
+//          bias gradient folded in.
+// Output pixel (2i+py, 2j+px) receives taps ky in {1,3} (py=0) / {0,2} (py=1) from input rows i, i-1 / i+1, i.
+#include "common.cuh"
+
+#define CS_THREADS 256
+#define CS_PAD 4                      // floats of padding per input pixel row in smem: 128-bit loads stay conflict-free
+
+__device__ __forceinline__ float cs_act(float v, int act) {
+    if (act == MMVAE_ACT_RELU) return fmaxf(v, 0.f);
+    if (act == MMVAE_ACT_SIGMOID) return 1.f / (1.f + expf(-v));
+    return v;
+}
+// derivative of the activation expressed with its OUTPUT y
+__device__ __forceinline__ float cs_dact(float y, int act) {
+    if (act == MMVAE_ACT_RELU) return y > 0.f ? 1.f : 0.f;
+    if (act == MMVAE_ACT_SIGMOID) return y * (1.f - y);
+    return 1.f;
+}
+
+// ------------------------------------------------------------------------------------------------------ forward
+// one CTA per image.  smem: xs[H*W][Cin+PAD], ws[16][COUT][Cin], bs[COUT]
+template <int COUT>
+__global__ void __launch_bounds__(CS_THREADS)
+convt_small_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                       float* __restrict__ y, int H, int W, int Cin, int act) {
+    extern __shared__ float4 smem4[];
+    float* xs = (float*)smem4;
+    const int xstride = Cin + CS_PAD;
+    float* ws = xs + H * W * xstride;
+    float* bs = ws + 16 * COUT * Cin;
+    const int n = blockIdx.x, HW = H * W;
+    const float4* xg = (const float4*)(x + (long)n * HW * Cin);
+    const int c4 = Cin / 4;
+    for (int i = threadIdx.x; i < HW * c4; i += CS_THREADS) {
+        const int p = i / c4, c = i - p * c4;
+        *(float4*)(xs + p * xstride + 4 * c) = ld_stream4(xg + i);
+    }
+    for (int i = threadIdx.x; i < 16 * COUT * Cin; i += CS_THREADS) {     // torch layout w[ci][co][tap] -> ws[tap][co][ci]
+        const int ci = i % Cin, co = (i / Cin) % COUT, tap = i / (Cin * COUT);
+        ws[i] = w[((long)ci * COUT + co) * 16 + tap];
+    }
+    if (threadIdx.x < COUT) bs[threadIdx.x] = bias ? bias[threadIdx.x] : 0.f;
+    __syncthreads();
+    const int H2 = 2 * H, W2 = 2 * W;
+    for (int p = threadIdx.x; p < HW; p += CS_THREADS) {
+        const int i = p / W, j = p - i * W;
+        float acc[2][2][COUT];
+#pragma unroll
+        for (int a = 0; a < 2; ++a)
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+#pragma unroll
+                for (int c = 0; c < COUT; ++c) acc[a][b][c] = bs[c];
+#pragma unroll
+        for (int dy = -1; dy <= 1; ++dy) {
+            const int ii = i + dy;
+            if (ii < 0 || ii >= H) continue;
+#pragma unroll
+            for (int dx = -1; dx <= 1; ++dx) {
+                const int jj = j + dx;
+                if (jj < 0 || jj >= W) continue;
+                const float* xr = xs + (ii * W + jj) * xstride;
+                for (int c = 0; c < Cin; c += 4) {
+                    const float4 xv = *(const float4*)(xr + c);
+#pragma unroll
+                    for (int ky = 0; ky < 4; ++ky) {
+                        const int py = (ky + 1) & 1;
+                        if ((py + 1 - ky) / 2 != dy) continue;          // resolved at compile time after unrolling
+#pragma unroll
+                        for (int kx = 0; kx < 4; ++kx) {
+                            const int px = (kx + 1) & 1;
+                            if ((px + 1 - kx) / 2 != dx) continue;
+                            const float* wr = ws + (ky * 4 + kx) * COUT * Cin + c;
+#pragma unroll
+                            for (int co = 0; co < COUT; ++co) {
+                                const float4 wv = *(const float4*)(wr + co * Cin);
+                                acc[py][px][co] += xv.x * wv.x + xv.y * wv.y + xv.z * wv.z + xv.w * wv.w;
+                            }
+                        }
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int co = 0; co < COUT; ++co)
+#pragma unroll
+            for (int py = 0; py < 2; ++py) {
+                float2 o = make_float2(cs_act(acc[py][0][co], act), cs_act(acc[py][1][co], act));
+                *(float2*)(y + (((long)n * COUT + co) * H2 + 2 * i + py) * W2 + 2 * j) = o;
+            }
+    }
+}
+
+// stage g (N,Cout,2H,2W) of image n into gs[COUT][2H+2][2W+2] with a zero border, optionally times act'(y)
+template <int COUT>
+__device__ __forceinline__ void cs_stage_g(float* gs, const float* __restrict__ g, const float* __restrict__ yact,
+                                           int n, int H2, int W2, int act, float* bias_acc) {
+    const int gw = W2 + 2, plane = (H2 + 2) * gw;
+    for (int i = threadIdx.x; i < COUT * plane; i += CS_THREADS) gs[i] = 0.f;
+    __syncthreads();
+    const long base = (long)n * COUT * H2 * W2;
+    for (int i = threadIdx.x; i < COUT * H2 * W2; i += CS_THREADS) {
+        const int xx = i % W2, yy = (i / W2) % H2, co = i / (W2 * H2);
+        float v = g[base + i];
+        if (yact) v *= cs_dact(yact[base + i], act);
+        gs[co * plane + (yy + 1) * gw + xx + 1] = v;
+        if (bias_acc) {
+#pragma unroll
+            for (int c = 0; c < COUT; ++c) bias_acc[c] += (c == co) ? v : 0.f;
+        }
+    }
+}
+
+// -------------------------------------------------------------------------------------------------------- dgrad
+// gx[n,i,j,ci] = sum_{ky,kx,co} g[n,co,2i-1+ky,2j-1+kx] * w[ci,co,ky,kx]   (* relu'(x_mask))
+// smem: gs[COUT][2H+2][2W+2], ws[Cin][COUT*16]
+template <int COUT>
+__global__ void __launch_bounds__(CS_THREADS)
+convt_small_dgrad_kernel(const float* __restrict__ g, const float* __restrict__ yact, const float* __restrict__ w,
+                         const float* __restrict__ x_mask, float* __restrict__ gx, int H, int W, int Cin, int act) {
+    extern __shared__ float4 smem4[];
+    float* gs = (float*)smem4;
+    const int H2 = 2 * H, W2 = 2 * W, gw = W2 + 2, plane = (H2 + 2) * gw;
+    float* ws = gs + ((COUT * plane + 3) & ~3);
+    const int n = blockIdx.x;
+    cs_stage_g<COUT>(gs, g, yact, n, H2, W2, act, nullptr);
+    for (int i = threadIdx.x; i < Cin * COUT * 16; i += CS_THREADS) ws[i] = w[i];      // torch layout is already [ci][co][tap]
+    __syncthreads();
+    for (int p = threadIdx.x; p < H * W; p += CS_THREADS) {
+        const int i = p / W, j = p - i * W;
+        float pt[COUT][16];
+#pragma unroll
+        for (int co = 0; co < COUT; ++co)
+#pragma unroll
+            for (int ky = 0; ky < 4; ++ky) {
+                const float* r = gs + co * plane + (2 * i + ky) * gw + 2 * j;       // (2i-1+ky)+1, (2j-1)+1
+                const float2 a = *(const float2*)r, b = *(const float2*)(r + 2);
+                pt[co][ky * 4 + 0] = a.x; pt[co][ky * 4 + 1] = a.y; pt[co][ky * 4 + 2] = b.x; pt[co][ky * 4 + 3] = b.y;
+            }
+        const long orow = ((long)n * H * W + p) * Cin;
+        for (int c = 0; c < Cin; c += 4) {
+            float o[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float4* wr = (const float4*)(ws + (c + q) * COUT * 16);
+                float s = 0.f;
+#pragma unroll
+                for (int co = 0; co < COUT; ++co)
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) {
+                        const float4 wv = wr[co * 4 + t];
+                        s += pt[co][4 * t] * wv.x + pt[co][4 * t + 1] * wv.y + pt[co][4 * t + 2] * wv.z + pt[co][4 * t + 3] * wv.w;
+                    }
+                o[q] = s;
+            }
+            if (x_mask) {
+                const float4 m = *(const float4*)(x_mask + orow + c);
+                o[0] = m.x > 0.f ? o[0] : 0.f; o[1] = m.y > 0.f ? o[1] : 0.f;
+                o[2] = m.z > 0.f ? o[2] : 0.f; o[3] = m.w > 0.f ? o[3] : 0.f;
+            }
+            *(float4*)(gx + orow + c) = make_float4(o[0], o[1], o[2], o[3]);
+        }
+    }
+}
+
+// -------------------------------------------------------------------------------------------------------- wgrad
+// gw[ci,co,ky,kx] = sum_{n,i,j} x[n,i,j,ci] * g[n,co,2i-1+ky,2j-1+kx];  gb[co] = sum g.   Cin == 32.
+// persistent CTAs over images; warp = one replica of the 32 x (COUT*16) accumulator tile: lane -> (ci group of 4, ky);
+// thread tile 4 ci x COUT x 4 kx.  part[cta][Cin*COUT*16 + COUT]
+template <int COUT>
+__global__ void __launch_bounds__(CS_THREADS)
+convt_small_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ g, const float* __restrict__ yact,
+                         float* __restrict__ part, int N, int H, int W, int act) {
+    constexpr int CIN = 32;
+    extern __shared__ float4 smem4[];
+    float* gs = (float*)smem4;
+    const int H2 = 2 * H, W2 = 2 * W, gw = W2 + 2, plane = (H2 + 2) * gw, HW = H * W;
+    const int xstride = CIN + CS_PAD;
+    float* xs = gs + ((COUT * plane + 3) & ~3);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int cg = lane & 7, ky = lane >> 3;
+    float acc[4][COUT][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < COUT; ++b)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) acc[a][b][c] = 0.f;
+    float bacc[COUT];
+#pragma unroll
+    for (int c = 0; c < COUT; ++c) bacc[c] = 0.f;
+    for (int n = blockIdx.x; n < N; n += gridDim.x) {
+        __syncthreads();                                             // previous image fully consumed
+        const float4* xg = (const float4*)(x + (long)n * HW * CIN);
+        for (int i = threadIdx.x; i < HW * (CIN / 4); i += CS_THREADS) {
+            const int p = i >> 3, c = i & 7;
+            *(float4*)(xs + p * xstride + 4 * c) = ld_stream4(xg + i);
+        }
+        cs_stage_g<COUT>(gs, g, yact, n, H2, W2, act, bacc);         // contains a __syncthreads after zeroing
+        __syncthreads();
+        for (int p = warp; p < HW; p += CS_THREADS / 32) {
+            const int i = p / W, j = p - i * W;
+            const float4 xv = *(const float4*)(xs + p * xstride + 4 * cg);
+#pragma unroll
+            for (int co = 0; co < COUT; ++co) {
+                const float* r = gs + co * plane + (2 * i + ky) * gw + 2 * j;
+                const float2 a = *(const float2*)r, b = *(const float2*)(r + 2);
+                acc[0][co][0] += xv.x * a.x; acc[0][co][1] += xv.x * a.y; acc[0][co][2] += xv.x * b.x; acc[0][co][3] += xv.x * b.y;
+                acc[1][co][0] += xv.y * a.x; acc[1][co][1] += xv.y * a.y; acc[1][co][2] += xv.y * b.x; acc[1][co][3] += xv.y * b.y;
+                acc[2][co][0] += xv.z * a.x; acc[2][co][1] += xv.z * a.y; acc[2][co][2] += xv.z * b.x; acc[2][co][3] += xv.z * b.y;
+                acc[3][co][0] += xv.w * a.x; acc[3][co][1] += xv.w * a.y; acc[3][co][2] += xv.w * b.x; acc[3][co][3] += xv.w * b.y;
+            }
+        }
+    }
+    // cross-warp reduction through shared memory (reuses the staging area), fixed order -> deterministic
+    __syncthreads();
+    float* red = (float*)smem4;                                      // [8 warps][CIN*COUT*16]
+    constexpr int TOT = CIN * COUT * 16;
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int co = 0; co < COUT; ++co)
+#pragma unroll
+            for (int kx = 0; kx < 4; ++kx)
+                red[warp * TOT + ((4 * cg + a) * COUT + co) * 16 + ky * 4 + kx] = acc[a][co][kx];
+    __syncthreads();
+    float* out = part + (long)blockIdx.x * (TOT + COUT);
+    for (int i = threadIdx.x; i < TOT; i += CS_THREADS) {
+        float s = 0.f;
+#pragma unroll
+        for (int wv = 0; wv < CS_THREADS / 32; ++wv) s += red[wv * TOT + i];
+        out[i] = s;
+    }
+    __syncthreads();
+    float* bred = red;                                               // [COUT][256]
+#pragma unroll
+    for (int c = 0; c < COUT; ++c) bred[c * CS_THREADS + threadIdx.x] = bacc[c];
+    __syncthreads();
+    if (threadIdx.x < COUT) {
+        float s = 0.f;
+        for (int t = 0; t < CS_THREADS; ++t) s += bred[threadIdx.x * CS_THREADS + t];
+        out[TOT + threadIdx.x] = s;
+    }
+}
+
+__global__ void convt_small_wgrad_reduce(const float* __restrict__ part, float* __restrict__ gw, float* __restrict__ gb,
+                                         int P, int tot, int cout) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= tot + cout) return;
+    float s = 0.f;
+    for (int p = 0; p < P; ++p) s += part[(long)p * (tot + cout) + i];
+    if (i < tot) gw[i] = s;
+    else if (gb) gb[i - tot] = s;
+}
+
+// ---------------------------------------------------------------------------------------------------- host side
+static int cs_wgrad_ctas(int N) { return N < 2 * MMVAE_NUM_SMS ? N : 2 * MMVAE_NUM_SMS; }
+
+extern "C" int mmvae_convt_small_supported(int H, int W, int Cin, int Cout) {
+    if (Cout < 1 || Cout > 4 || Cin % 4 || Cin < 4 || H < 1 || W < 1) return 0;
+    const size_t fwd = ((size_t)H * W * (Cin + CS_PAD) + 16 * (size_t)Cout * Cin + 4) * 4;
+    const size_t gsz = (((size_t)Cout * (2 * H + 2) * (2 * W + 2) + 3) & ~(size_t)3) * 4;
+    const size_t dg = gsz + (size_t)Cin * Cout * 16 * 4;
+    const size_t red = (size_t)(CS_THREADS / 32) * Cin * Cout * 16 * 4;
+    size_t wg = gsz + (size_t)H * W * (Cin + CS_PAD) * 4;
+    if (red > wg) wg = red;
+    const size_t lim = 200 * 1024;
+    if (fwd > lim || dg > lim) return 0;
+    return (Cin == 32 && wg <= lim) ? 2 : 1;       // 2: forward, dgrad and wgrad; 1: forward and dgrad only
+}
+extern "C" long mmvae_convt_small_wgrad_workspace_bytes(int N, int Cin, int Cout) {
+    return (long)cs_wgrad_ctas(N) * ((long)Cin * Cout * 16 + Cout) * (long)sizeof(float);
+}
+
+#define CS_SWITCH(COUTV, FN, ...)                         \
+    ((COUTV) == 1 ? FN<1>(__VA_ARGS__) : (COUTV) == 2 ? FN<2>(__VA_ARGS__) : (COUTV) == 3 ? FN<3>(__VA_ARGS__) : FN<4>(__VA_ARGS__))
+
+template <typename K>
+static int cs_smem_attr(K kern, size_t smem, const char* name) {
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "%s: %s", name, cudaGetErrorString(e));
+    }
+    return 0;
+}
+
+template <int CO>
+static int cs_fwd(const float* x, const float* w, const float* bias, float* y, int N, int H, int W, int Cin, int act,
+                  size_t smem, cudaStream_t st) {
+    const int rc = cs_smem_attr(convt_small_fwd_kernel<CO>, smem, "convt_small_fwd");
+    if (rc) return rc;
+    convt_small_fwd_kernel<CO><<<N, CS_THREADS, smem, st>>>(x, w, bias, y, H, W, Cin, act);
+    return 0;
+}
+template <int CO>
+static int cs_dgrad(const float* g, const float* y_act, const float* w, const float* x_mask, float* gx, int N, int H,
+                    int W, int Cin, int act, size_t smem, cudaStream_t st) {
+    const int rc = cs_smem_attr(convt_small_dgrad_kernel<CO>, smem, "convt_small_dgrad");
+    if (rc) return rc;
+    convt_small_dgrad_kernel<CO><<<N, CS_THREADS, smem, st>>>(g, y_act, w, x_mask, gx, H, W, Cin, act);
+    return 0;
+}
+template <int CO>
+static int cs_wgrad(const float* x, const float* g, const float* y_act, float* ws, int P, int N, int H, int W, int act,
+                    size_t smem, cudaStream_t st) {
+    const int rc = cs_smem_attr(convt_small_wgrad_kernel<CO>, smem, "convt_small_wgrad");
+    if (rc) return rc;
+    convt_small_wgrad_kernel<CO><<<P, CS_THREADS, smem, st>>>(x, g, y_act, ws, N, H, W, act);
+    return 0;
+}
+
+extern "C" int mmvae_convt_small_fwd(const float* x, const float* w, const float* bias, float* y, int N, int H, int W,
+                                     int Cin, int Cout, int act, void* stream) {
+    MMVAE_REQUIRE(x && w && y && N > 0, "convt_small_fwd: bad arguments");
+    MMVAE_REQUIRE(mmvae_convt_small_supported(H, W, Cin, Cout), "convt_small_fwd: unsupported shape H=%d W=%d Cin=%d Cout=%d", H, W, Cin, Cout);
+    const size_t smem = ((size_t)H * W * (Cin + CS_PAD) + 16 * (size_t)Cout * Cin + 4) * 4;
+    const int rc = CS_SWITCH(Cout, cs_fwd, x, w, bias, y, N, H, W, Cin, act, smem, (cudaStream_t)stream);
+    if (rc) return rc;
+    MMVAE_LAUNCH_CHECK("convt_small_fwd");
+    return 0;
+}
+
+extern "C" int mmvae_convt_small_dgrad(const float* g, const float* y_act, const float* w, const float* x_mask,
+                                       float* gx, int N, int H, int W, int Cin, int Cout, int act, void* stream) {
+    MMVAE_REQUIRE(g && w && gx && N > 0, "convt_small_dgrad: bad arguments");
+    MMVAE_REQUIRE(mmvae_convt_small_supported(H, W, Cin, Cout), "convt_small_dgrad: unsupported shape");
+    const size_t gsz = (((size_t)Cout * (2 * H + 2) * (2 * W + 2) + 3) & ~(size_t)3) * 4;
+    const size_t smem = gsz + (size_t)Cin * Cout * 16 * 4;
+    const int rc = CS_SWITCH(Cout, cs_dgrad, g, y_act, w, x_mask, gx, N, H, W, Cin, act, smem, (cudaStream_t)stream);
+    if (rc) return rc;
+    MMVAE_LAUNCH_CHECK("convt_small_dgrad");
+    return 0;
+}
+
+extern "C" int mmvae_convt_small_wgrad(const float* x, const float* g, const float* y_act, float* gw, float* gb,
+                                       float* workspace, int N, int H, int W, int Cin, int Cout, int act, void* stream) {
+    MMVAE_REQUIRE(x && g && gw && workspace && N > 0, "convt_small_wgrad: bad arguments");
+    MMVAE_REQUIRE(mmvae_convt_small_supported(H, W, Cin, Cout) == 2, "convt_small_wgrad: unsupported shape (needs Cin == 32)");
+    const size_t gsz = (((size_t)Cout * (2 * H + 2) * (2 * W + 2) + 3) & ~(size_t)3) * 4;
+    size_t smem = gsz + (size_t)H * W * (Cin + CS_PAD) * 4;
+    const size_t red = (size_t)(CS_THREADS / 32) * Cin * Cout * 16 * 4;
+    if (red > smem) smem = red;
+    const int P = cs_wgrad_ctas(N);
+    const int rc = CS_SWITCH(Cout, cs_wgrad, x, g, y_act, workspace, P, N, H, W, act, smem, (cudaStream_t)stream);
+    if (rc) return rc;
+    MMVAE_LAUNCH_CHECK("convt_small_wgrad");
+    const int tot = Cin * Cout * 16;
+    convt_small_wgrad_reduce<<<ceil_div_i(tot + Cout, 128), 128, 0, (cudaStream_t)stream>>>(workspace, gw, gb, P, tot, Cout);
+    MMVAE_LAUNCH_CHECK("convt_small_wgrad_reduce");
+    return 0;
+}

@@ -44,19 +44,27 @@ extern "C" int mmvae_gemm(const float* A, const float* B, const float* bias, flo
 }
 
 // ---- column sums (bias gradients): out[n] = sum_m A[m,n].  Two deterministic stages. ---------------------------
-#define CS_ROWS_PER_BLOCK 256
+// stage 1: grid (column groups of 32, P row-slabs); 256 threads = 8 row-lanes x 32 columns, each block strides over its
+// slab.  P is capped so the second stage stays short and the first fills the machine; partials are [P][N].
 __global__ void __launch_bounds__(256)
-colsum_stage1(const float* __restrict__ A, float* __restrict__ part, int M, int N) {
-    // block (bx, by): columns bx*32..+32, rows by*CS_ROWS..; 256 threads = 8 row-lanes x 32 columns
+colsum_stage1(const float* __restrict__ A, float* __restrict__ part, int M, int N, int rows_per_slab) {
     __shared__ float sm[8][33];
     const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
     const int n = blockIdx.x * 32 + cx;
-    const int m_begin = blockIdx.y * CS_ROWS_PER_BLOCK;
-    const int m_end = min(M, m_begin + CS_ROWS_PER_BLOCK);
-    float s = 0.f;
-    if (n < N)
-        for (int m = m_begin + ry; m < m_end; m += 8) s += A[(long)m * N + n];
-    sm[ry][cx] = s;
+    const int m_begin = blockIdx.y * rows_per_slab;
+    const int m_end = min(M, m_begin + rows_per_slab);
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    if (n < N) {
+        int m = m_begin + ry;
+        for (; m + 24 < m_end; m += 32) {                     // 4 independent loads in flight
+            s0 += A[(long)m * N + n];
+            s1 += A[(long)(m + 8) * N + n];
+            s2 += A[(long)(m + 16) * N + n];
+            s3 += A[(long)(m + 24) * N + n];
+        }
+        for (; m < m_end; m += 8) s0 += A[(long)m * N + n];
+    }
+    sm[ry][cx] = (s0 + s1) + (s2 + s3);
     __syncthreads();
     if (ry == 0 && n < N) {
         float t = 0.f;
@@ -65,24 +73,43 @@ colsum_stage1(const float* __restrict__ A, float* __restrict__ part, int M, int 
         part[(long)blockIdx.y * N + n] = t;
     }
 }
-__global__ void colsum_stage2(const float* __restrict__ part, float* __restrict__ out, int P, int N) {
-    const int n = blockIdx.x * blockDim.x + threadIdx.x;
-    if (n >= N) return;
+// stage 2: one block per 32 columns, 8 row-lanes over the P partials
+__global__ void __launch_bounds__(256)
+colsum_stage2(const float* __restrict__ part, float* __restrict__ out, int P, int N) {
+    __shared__ float sm[8][33];
+    const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+    const int n = blockIdx.x * 32 + cx;
     float s = 0.f;
-    for (int p = 0; p < P; ++p) s += part[(long)p * N + n];
-    out[n] = s;
+    if (n < N)
+        for (int p = ry; p < P; p += 8) s += part[(long)p * N + n];
+    sm[ry][cx] = s;
+    __syncthreads();
+    if (ry == 0 && n < N) {
+        float t = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) t += sm[j][cx];
+        out[n] = t;
+    }
 }
 
+static int colsum_slabs(int M, int N) {
+    const int groups = (N + 31) / 32;
+    int P = (4 * MMVAE_NUM_SMS + groups - 1) / groups;         // ~4 blocks per SM in total
+    const int maxP = (M + 255) / 256;                          // at least 256 rows per slab
+    if (P > maxP) P = maxP;
+    return P < 1 ? 1 : P;
+}
 extern "C" long mmvae_colsum_workspace_bytes(int M, int N) {
-    return (long)((M + CS_ROWS_PER_BLOCK - 1) / CS_ROWS_PER_BLOCK) * N * (long)sizeof(float);
+    return (long)colsum_slabs(M, N) * N * (long)sizeof(float);
 }
 extern "C" int mmvae_colsum(const float* A, float* out, float* workspace, int M, int N, void* stream) {
     MMVAE_REQUIRE(A && out && workspace && M > 0 && N > 0, "colsum: bad arguments");
     cudaStream_t st = (cudaStream_t)stream;
-    const int P = (M + CS_ROWS_PER_BLOCK - 1) / CS_ROWS_PER_BLOCK;
-    colsum_stage1<<<dim3((N + 31) / 32, P), 256, 0, st>>>(A, workspace, M, N);
+    const int P = colsum_slabs(M, N);
+    const int rows_per_slab = (((M + P - 1) / P) + 7) & ~7;
+    colsum_stage1<<<dim3((N + 31) / 32, P), 256, 0, st>>>(A, workspace, M, N, rows_per_slab);
     MMVAE_LAUNCH_CHECK("colsum_stage1");
-    colsum_stage2<<<(N + 127) / 128, 128, 0, st>>>(workspace, out, P, N);
+    colsum_stage2<<<(N + 31) / 32, 256, 0, st>>>(workspace, out, P, N);
     MMVAE_LAUNCH_CHECK("colsum_stage2");
     return 0;
 }

@@ -127,10 +127,12 @@ class Decoder_VAE_SVHN(BaseDecoder):
         lead = z.shape[:-1]
         h = z.reshape(-1, z.shape[-1], 1, 1)
         d = self.dec
-        h = ops.ConvT2dAct.apply(h, d[0].weight, d[0].bias, 1, 0, "relu", False, False)
-        h = ops.ConvT2dAct.apply(h, d[2].weight, d[2].bias, 2, 1, "relu", False, False)
-        h = ops.ConvT2dAct.apply(h, d[4].weight, d[4].bias, 2, 1, "relu", False, False)
-        out = ops.ConvT2dAct.apply(h, d[6].weight, d[6].bias, 2, 1, "sigmoid", True, False)     # NCHW at the boundary
+        # every layer returns the gradient w.r.t. the PRE-activation of the layer below (its ReLU backward fused into the
+        # dgrad), so layers 0, 2, 4 receive pre-activation gradients; h is never an autograd leaf here (z -> reshape).
+        h = ops.ConvT2dAct.apply(h, d[0].weight, d[0].bias, 1, 0, "relu", False, True, False)
+        h = ops.ConvT2dAct.apply(h, d[2].weight, d[2].bias, 2, 1, "relu", False, True, True)
+        h = ops.ConvT2dAct.apply(h, d[4].weight, d[4].bias, 2, 1, "relu", False, True, True)
+        out = ops.ConvT2dAct.apply(h, d[6].weight, d[6].bias, 2, 1, "sigmoid", True, False, True)  # NCHW at the boundary
         return ModelOutput(reconstruction=out.reshape(*lead, *out.shape[1:]))
 
 

@@ -241,27 +241,61 @@ class Conv2dAct(torch.autograd.Function):
 
 class ConvT2dAct(torch.autograd.Function):
     """y = act(conv_transpose2d(x, W, b, stride, pad))  (encoders.py:116-136).  W: (Cin,Cout,k,k).
-    preact_grad=True: the incoming gradient is already w.r.t. the pre-activation (fused Sigmoid backward)."""
+    preact_grad=True: the incoming gradient is already w.r.t. the pre-activation (the consumer fused act').
+    mask_input_grad=True: x is the ReLU output of the layer below and the returned gradient is w.r.t. THAT layer's
+    pre-activation (its ReLU backward fused here; the layer below must then be built with preact_grad=True).
+    Paths: Cout <= 4, k4 s2 p1, NCHW output -> direct kernels (convt_small.cu); otherwise GEMM + col2im lowering."""
 
     @staticmethod
-    def forward(ctx, x, w, b, stride, pad, act, nchw_out, preact_grad):
+    def forward(ctx, x, w, b, stride, pad, act, nchw_out, preact_grad, mask_input_grad=False):
         x = _dev(x, "x")
         w = _c(w, "weight")
         N, Cin, H, W = x.shape
         _, Cout, k, _ = w.shape
+        lib = _lib.load()
+        small = (k == 4 and stride == 2 and pad == 1 and nchw_out and w.shape[3] == 4
+                 and lib.mmvae_convt_small_supported(H, W, Cin, Cout) == 2)
         x2d = _as_rows(x)
+        if small:
+            y = torch.empty((N, Cout, 2 * H, 2 * W), device=x.device, dtype=torch.float32)
+            _call("mmvae_convt_small_fwd", _p(x2d), _p(w), _p(b), _p(y), N, H, W, Cin, Cout, ACT[act], _stream(),
+                  work=("byte", 4.0 * (x2d.numel() + y.numel())))
+            keep_y = (ACT[act] != C["MMVAE_ACT_NONE"]) and not preact_grad
+            ctx.save_for_backward(x2d, w, y if keep_y else None)
+            ctx.cfg = (N, Cin, H, W, Cout, k, stride, pad, act, tuple(w.shape), b is not None, preact_grad,
+                       mask_input_grad, True)
+            return y
         wp = permute_weight(w)                                  # [Cin, k*k*Cout]
         col = gemm(x2d, wp, None, N * H * W, k * k * Cout, Cin, True, False)
         y = col2im(col, b, N, Cout, H, W, k, stride, pad, act, nchw_out=nchw_out)
         keep_y = (ACT[act] != C["MMVAE_ACT_NONE"]) and not preact_grad
         ctx.save_for_backward(x2d, wp, y if keep_y else None)
-        ctx.cfg = (N, Cin, H, W, Cout, k, stride, pad, act, tuple(w.shape), b is not None, preact_grad)
+        ctx.cfg = (N, Cin, H, W, Cout, k, stride, pad, act, tuple(w.shape), b is not None, preact_grad,
+                   mask_input_grad, False)
         return y
 
     @staticmethod
     def backward(ctx, gy):
         x2d, wp, y = ctx.saved_tensors
-        N, Cin, H, W, Cout, k, s, p, act, wshape, has_bias, preact_grad = ctx.cfg
+        N, Cin, H, W, Cout, k, s, p, act, wshape, has_bias, preact_grad, mask_in, small = ctx.cfg
+        if small:
+            g = _c(gy, "grad")                                   # (N,Cout,2H,2W) NCHW
+            w = wp
+            gx = gw = gb = None
+            if ctx.needs_input_grad[0]:
+                gx2d = torch.empty_like(x2d)
+                _call("mmvae_convt_small_dgrad", _p(g), _p(y), _p(w), _p(x2d if mask_in else None), _p(gx2d), N, H, W,
+                      Cin, Cout, ACT[act], _stream(), work=("byte", 4.0 * (g.numel() + 2 * x2d.numel())))
+                gx = gx2d.view(N, H, W, Cin).permute(0, 3, 1, 2)
+            if ctx.needs_input_grad[1] or (has_bias and ctx.needs_input_grad[2]):
+                lib = _lib.load()
+                ws = torch.empty(lib.mmvae_convt_small_wgrad_workspace_bytes(N, Cin, Cout) // 4, device=g.device,
+                                 dtype=torch.float32)
+                gw = torch.empty(wshape, device=g.device, dtype=torch.float32)
+                gb = torch.empty(Cout, device=g.device, dtype=torch.float32) if has_bias else None
+                _call("mmvae_convt_small_wgrad", _p(x2d), _p(g), _p(y), _p(gw), _p(gb), _p(ws), N, H, W, Cin, Cout,
+                      ACT[act], _stream(), work=("byte", 4.0 * (g.numel() + x2d.numel())))
+            return gx, gw, gb, None, None, None, None, None, None
         gy = _dense_image(gy)
         if not preact_grad and y is not None:
             if gy.stride() != y.stride():
@@ -274,13 +308,15 @@ class ConvT2dAct(torch.autograd.Function):
         dcol, _, _ = im2col(g, k, s, p)                          # [N*H*W, k*k*Cout]
         if ctx.needs_input_grad[0]:
             gx2d = gemm(dcol, wp, None, rows, Cin, Kc, True, True)
+            if mask_in:
+                gx2d = act_bwd(gx2d, x2d, "relu")
             gx = gx2d.view(N, H, W, Cin).permute(0, 3, 1, 2)
         if ctx.needs_input_grad[1]:
             gwp = gemm(x2d, dcol, None, Cin, Kc, rows, False, False)
             gw = unpermute_weight(gwp, wshape)
         if has_bias and ctx.needs_input_grad[2]:
             gb = colsum(_as_rows(g))
-        return gx, gw, gb, None, None, None, None, None
+        return gx, gw, gb, None, None, None, None, None, None
 
 
 class RSample(torch.autograd.Function):

@@ -88,15 +88,17 @@ def test_conv2d_autograd(ops, cin, cout, H, s, p, nchw_in):
 
 
 @pytest.mark.parametrize("cin,cout,H,s,p,act,nchw_out", [(20, 128, 1, 1, 0, "relu", False), (128, 64, 4, 2, 1, "relu", False),
-                                                         (32, 3, 16, 2, 1, "sigmoid", True), (64, 32, 8, 2, 1, "relu", False)])
+                                                         (32, 3, 16, 2, 1, "sigmoid", True), (64, 32, 8, 2, 1, "relu", False),
+                                                         (32, 1, 14, 2, 1, "sigmoid", True), (32, 4, 5, 2, 1, "relu", True),
+                                                         (32, 3, 16, 2, 1, None, True), (16, 3, 8, 2, 1, "sigmoid", True)])
 def test_convT2d_autograd(ops, cin, cout, H, s, p, act, nchw_out):
-    N = 6
+    N = 6 if cout > 4 or H != 16 else 301          # the direct path's persistent wgrad loops over images per CTA
     x = _rand(N, cin, H, H, seed=1).permute(0, 2, 3, 1).contiguous().permute(0, 3, 1, 2).requires_grad_()
     w = _rand(cin, cout, 4, 4, seed=2, scale=0.1).requires_grad_()
     b = _rand(cout, seed=3).requires_grad_()
     y = ops.ConvT2dAct.apply(x, w, b, s, p, act, nchw_out, False)
     xd, wd, bd = (t.detach().double().requires_grad_() for t in (x, w, b))
-    fn = torch.relu if act == "relu" else torch.sigmoid
+    fn = {"relu": torch.relu, "sigmoid": torch.sigmoid, None: (lambda t: t)}[act]
     yr = fn(F.conv_transpose2d(xd, wd, bd, stride=s, padding=p))
     assert y.shape == yr.shape
     assert y.is_contiguous() == nchw_out or cout == 1
@@ -105,6 +107,32 @@ def test_convT2d_autograd(ops, cin, cout, H, s, p, act, nchw_out):
     gx, gw, gb = torch.autograd.grad(y, (x, w, b), gy)
     rx, rw, rb = torch.autograd.grad(yr, (xd, wd, bd), gy.double())
     assert rel_err(gx, rx) < 5e-6 and rel_err(gw, rw) < 5e-6 and rel_err(gb, rb) < 5e-6
+
+
+def test_convT2d_chain_fused_relu_backward(ops):
+    """Decoder_VAE_SVHN's chaining: each layer hands the layer below the gradient w.r.t. its PRE-activation."""
+    N = 9
+    z = _rand(N, 20, 1, 1, seed=1).requires_grad_()
+    shapes = [(20, 128), (128, 64), (64, 32), (32, 3)]
+    ws = [_rand(a, b, 4, 4, seed=10 + i, scale=0.1).requires_grad_() for i, (a, b) in enumerate(shapes)]
+    bs = [_rand(b, seed=20 + i).requires_grad_() for i, (a, b) in enumerate(shapes)]
+    h = ops.ConvT2dAct.apply(z, ws[0], bs[0], 1, 0, "relu", False, True, False)
+    h = ops.ConvT2dAct.apply(h, ws[1], bs[1], 2, 1, "relu", False, True, True)
+    h = ops.ConvT2dAct.apply(h, ws[2], bs[2], 2, 1, "relu", False, True, True)
+    y = ops.ConvT2dAct.apply(h, ws[3], bs[3], 2, 1, "sigmoid", True, False, True)
+    zd = z.detach().double().requires_grad_()
+    wd = [w.detach().double().requires_grad_() for w in ws]
+    bd = [b.detach().double().requires_grad_() for b in bs]
+    r = torch.relu(F.conv_transpose2d(zd, wd[0], bd[0], stride=1, padding=0))
+    r = torch.relu(F.conv_transpose2d(r, wd[1], bd[1], stride=2, padding=1))
+    r = torch.relu(F.conv_transpose2d(r, wd[2], bd[2], stride=2, padding=1))
+    yr = torch.sigmoid(F.conv_transpose2d(r, wd[3], bd[3], stride=2, padding=1))
+    assert rel_err(y, yr) < 2e-6
+    gy = _rand(*yr.shape, seed=4)
+    got = torch.autograd.grad(y, [z] + ws + bs, gy)
+    ref = torch.autograd.grad(yr, [zd] + wd + bd, gy.double())
+    for a, b in zip(got, ref):
+        assert rel_err(a, b) < 1e-5
 
 
 @pytest.mark.parametrize("dist,xform", [("laplace", "softmax"), ("normal", "exp_half"), ("normal", "exp_half_eps")])
