@@ -160,6 +160,21 @@ int  mmvae_convt_small_wgrad(const float* x, const float* g, const float* y_act,
                              int N, int H, int W, int Cin, int Cout, int act, void* stream);
 long mmvae_convt_small_wgrad_workspace_bytes(int N, int Cin, int Cout);
 
+/* ConvTranspose2d(k=4, s=2, p=1) with 32 | Cin, Cout <= 128 as an IMPLICIT GEMM on the tcgen05 path: the A operand is
+ * fetched by 4-D TMA boxes over the NHWC tensors (shifted windows forward, stride-2 gathers backward; the padding ring
+ * and ragged tiles are the TMA unit's out-of-bound zero fill), so no im2col / col2im buffer exists (encoders.py:119-124).
+ * All tensors NHWC.  wf: class-major forward weights [4*Cout, 4*Cin] from mmvae_convt_weight_classes(w torch-layout);
+ * wp / gwp: tap-major [Cin, 16*Cout] (mmvae_permute_weight layout).  g is the gradient w.r.t. the PRE-activation. */
+int  mmvae_convt_tc_supported(int H, int W, int Cin, int Cout);
+int  mmvae_convt_weight_classes(const float* w, float* wf, int Cin, int Cout, void* stream);
+int  mmvae_convt_tc_fwd(const float* x, const float* wf, const float* bias, float* y, int Nimg, int H, int W, int Cin,
+                        int Cout, int act, void* stream);
+int  mmvae_convt_tc_dgrad(const float* g, const float* wp, const float* x_mask, float* gx, int Nimg, int H, int W,
+                          int Cin, int Cout, void* stream);
+int  mmvae_convt_tc_wgrad(const float* x, const float* g, float* gwp, float* workspace, long workspace_bytes, int Nimg,
+                          int H, int W, int Cin, int Cout, void* stream);
+long mmvae_convt_tc_wgrad_workspace_bytes(int Nimg, int H, int W, int Cin, int Cout);
+
 /* MADE / MAF / IAF elementwise pieces (maf_model.py:62-74,91-104; iaf_model.py:60-78,94-100).  The masked-linear
  * contractions go through mmvae_gemm with the pre-masked weight (layers.py:24-25: F.linear(x, mask*W, b)). */
 int mmvae_mask_weight(const float* w, const float* mask, float* out, long n, void* stream);

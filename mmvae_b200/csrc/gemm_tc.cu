@@ -49,13 +49,31 @@ __device__ __forceinline__ float apply_act_tc(float v, int act) {
     return v;
 }
 
-struct TcTile { int m0, n0, kb_begin, nk, z; };
+// Implicit-GEMM transposed convolution (k4 s2 p1): the same pipeline with the A operand fetched by 4-D TMA boxes over the
+// NHWC activation / gradient tensor instead of from an im2col buffer (out-of-bound rows and the padding ring arrive as
+// zeros from the TMA unit; stride-2 gathers use the tensor map's elementStrides):
+//   mode 1 forward : per output-parity class (py,px) a GEMM rows x Cout x 4*Cin; the class is the N-tile index, the A tile
+//                    of k-block (tap,chunk) is the input window shifted by (dy,dx) in {-1,0,1}^2; the epilogue scatters
+//                    rows to y[n, 2i+py, 2j+px, :] with bias + activation;
+//   mode 2 dgrad   : rows x Cin x 16*Cout; the A tile of k-block (tap,chunk) is g[n, 2i-1+ky, 2j-1+kx, chunk] (stride-2 box);
+//                    the epilogue applies the ReLU mask of the layer below;
+//   mode 3 wgrad   : (16*Cout) x Cin x rows, both operands MN-major, A = stride-2 boxes of g, B = x; split-K over rows,
+//                    transposed store into gWp[Cin, (tap,co)].
+struct TcConv {
+    int mode;          // 0 = plain GEMM
+    int H, W;          // input (coarse) grid
+    int chunks;        // 32-channel chunks per tap (mode 1: Cin/32; modes 2: Cout/32)
+    int Cout;          // mode 3: channels per tap of the M index
+};
+
+struct TcTile { int m0, n0, kb_begin, nk, z, nt; };
 
 __device__ __forceinline__ TcTile tc_tile(int t, int tiles_m, int tiles_n, int BN, int nkb, int kb_per) {
     TcTile r;
     const int nt = t % tiles_n;
     const int mt = (t / tiles_n) % tiles_m;
     r.z = t / (tiles_n * tiles_m);
+    r.nt = nt;
     r.m0 = mt * TC_BM;
     r.n0 = nt * BN;
     r.kb_begin = r.z * kb_per;
@@ -67,7 +85,8 @@ template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const float* __restrict__ bias, float* __restrict__ C, float* __restrict__ ws, int M, int N, int K,
-               int act, int kb_per_split, int splits, int c_transposed, int passes) {
+               int act, int kb_per_split, int splits, int c_transposed, int passes, const TcConv cv,
+               const float* __restrict__ mask) {
     using Cfg = TcCfg<BN>;
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
@@ -111,13 +130,36 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     uint8_t* a_hi = st;
                     uint8_t* b_hi = st + 2 * TC_A_TILE;
                     mbar_arrive_expect_tx(full + s, TC_A_TILE + Cfg::B_TILE);
-                    const int k0 = (tl.kb_begin + i) * TC_BK;
-                    if (A_MN) {
+                    const int kbi = tl.kb_begin + i;
+                    const int k0 = kbi * TC_BK;
+                    if (cv.mode == 0) {
+                        if (A_MN) {
 #pragma unroll
-                        for (int j = 0; j < TC_BM / 32; ++j)
-                            tma_load_2d(a_hi + j * 4096, &tmap_a, full + s, tl.m0 + 32 * j, k0);
+                            for (int j = 0; j < TC_BM / 32; ++j)
+                                tma_load_2d(a_hi + j * 4096, &tmap_a, full + s, tl.m0 + 32 * j, k0);
+                        } else {
+                            tma_load_2d(a_hi, &tmap_a, full + s, k0, tl.m0);
+                        }
+                    } else if (cv.mode == 3) {
+                        // k-block = 32 consecutive pixels (n, y, x) of the coarse grid; M group j = 32 channels of one tap
+                        const int HW = cv.H * cv.W, p0 = kbi * 32;
+                        const int n0 = p0 / HW, y0 = (p0 - n0 * HW) / cv.W;
+#pragma unroll
+                        for (int j = 0; j < TC_BM / 32; ++j) {
+                            const int m = tl.m0 + 32 * j, tap = m / cv.Cout, c0 = m - tap * cv.Cout;
+                            tma_load_4d(a_hi + j * 4096, &tmap_a, full + s, c0, (tap & 3) - 1, 2 * y0 + (tap >> 2) - 1, n0);
+                        }
                     } else {
-                        tma_load_2d(a_hi, &tmap_a, full + s, k0, tl.m0);
+                        const int HW = cv.H * cv.W;
+                        const int n0 = tl.m0 / HW, y0 = (tl.m0 - n0 * HW) / cv.W;
+                        const int tap = kbi / cv.chunks, c0 = (kbi - tap * cv.chunks) * 32;
+                        if (cv.mode == 1) {                      // class (py,px) = N tile; tap (ty,tx) -> window shift
+                            const int py = tl.nt >> 1, px = tl.nt & 1;
+                            const int dy = (tap >> 1) ? 2 * py - 1 : 0, dx = (tap & 1) ? 2 * px - 1 : 0;
+                            tma_load_4d(a_hi, &tmap_a, full + s, c0, dx, y0 + dy, n0);
+                        } else {                                 // mode 2: tap (ky,kx) of the stride-2 gather
+                            tma_load_4d(a_hi, &tmap_a, full + s, c0, (tap & 3) - 1, 2 * y0 + (tap >> 2) - 1, n0);
+                        }
                     }
                     if (B_MN) {
 #pragma unroll
@@ -230,12 +272,30 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     __syncwarp();
                     if (lane == 0) mbar_arrive(tempty + acc);
                 }
-                if (row < M) {
+                if (row < M && cv.mode == 1) {
+                    // scatter: row (n,i,j) of class (py,px) -> y[n, 2i+py, 2j+px, :] (NHWC, Cout == BN columns)
+                    const int HW = cv.H * cv.W, n_img = row / HW, rem = row - n_img * HW;
+                    const int ii = rem / cv.W, jj = rem - ii * cv.W;
+                    const long orow = ((long)(n_img * 2 * cv.H + 2 * ii + (tl.nt >> 1)) * (2 * cv.W) + 2 * jj + (tl.nt & 1));
+                    float* p = C + orow * BN + c;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = apply_act_tc(v[j] + (bias ? __ldg(bias + c + j) : 0.f), act);
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4)
+                        *reinterpret_cast<float4*>(p + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                } else if (row < M) {
                     if (splits == 1) {
 #pragma unroll
                         for (int j = 0; j < 32; ++j) {
                             const int n = tl.n0 + c + j;
                             if (n < N) v[j] = apply_act_tc(v[j] + (bias ? __ldg(bias + n) : 0.f), act);
+                        }
+                        if (mask) {                            // fused ReLU backward of the layer below (mode 2)
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) {
+                                const int n = tl.n0 + c + j;
+                                if (n < N && __ldg(mask + (long)row * N + n) <= 0.f) v[j] = 0.f;
+                            }
                         }
                     }
                     if (c_transposed) {
@@ -347,9 +407,11 @@ void mmvae_splitk_reduce(const float* ws, const float* bias, float* C, long MN, 
 
 template <int BN, bool A_MN, bool B_MN>
 static int tc_launch(const CUtensorMap& ta, const CUtensorMap& tb, const float* bias, float* C, float* ws, int M, int N,
-                     int K, int act, const TcPlan& p, int transposed, cudaStream_t st) {
+                     int K, int act, const TcPlan& p, int transposed, cudaStream_t st, const TcConv& cv = TcConv{0, 0, 0, 0, 0},
+                     const float* mask = nullptr) {
     static bool attr_done = false;
     auto kern = gemm_tc_kernel<BN, A_MN, B_MN>;
+    if (tc_init() == 0) return mmvae_set_error(1, "gemm_tc: tcgen05/TMA path unavailable on this device");
     if (!attr_done) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<BN>::SMEM);
         if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "gemm_tc: smem attribute: %s", cudaGetErrorString(e));
@@ -358,7 +420,7 @@ static int tc_launch(const CUtensorMap& ta, const CUtensorMap& tb, const float* 
     const long total = (long)((N + BN - 1) / BN) * ((M + TC_BM - 1) / TC_BM) * p.S;
     const int grid = (int)(total < MMVAE_NUM_SMS ? total : MMVAE_NUM_SMS);      // persistent: one CTA per SM
     kern<<<grid, TC_THREADS, TcCfg<BN>::SMEM, st>>>(ta, tb, bias, C, ws, M, N, K, act, p.kb_per, p.S, transposed,
-                                                    g_tc_mode == 1 ? 1 : 3);
+                                                    g_tc_mode == 1 ? 1 : 3, cv, mask);
     MMVAE_LAUNCH_CHECK("gemm_tc");
     return 0;
 }
@@ -401,5 +463,155 @@ int mmvae_gemm_tc(const float* A, const float* B, const float* bias, float* C, i
 #undef TC_GO
     if (rc) return rc;
     if (p.S > 1) mmvae_splitk_reduce(workspace, bias, C, (long)M * N, N, p.S, act, st);
+    return 0;
+}
+
+// ------------------------------------------------------------------------------ implicit-GEMM transposed convolution
+// NHWC tensor [Nimg, Hh, Ww, C] as a 4-D map (C, Ww, Hh, Nimg); box = 32 channels x (bw x bh x bn pixels), every
+// `stride`-th pixel in x and y.  K-major operand tiles use SWIZZLE_128B, MN-major ones the 32-byte-atom variant.
+static int make_tmap4(CUtensorMap* m, const float* base, long Nimg, int Hh, int Ww, int C, int bw, int bh, int bn,
+                      int stride, bool mn_major) {
+    cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)Ww, (cuuint64_t)Hh, (cuuint64_t)Nimg};
+    cuuint64_t strides[3] = {(cuuint64_t)C * 4, (cuuint64_t)Ww * C * 4, (cuuint64_t)Hh * Ww * C * 4};
+    cuuint32_t box[4] = {32u, (cuuint32_t)(bw * stride), (cuuint32_t)(bh * stride), (cuuint32_t)bn};
+    cuuint32_t estr[4] = {1u, (cuuint32_t)stride, (cuuint32_t)stride, 1u};
+    CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)base, dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : (int)r;
+}
+
+// pixel box covering `rows` consecutive (n,y,x) positions of an H x W grid: whole images when the grid is small,
+// else full-width bands of one image
+static bool conv_box(int H, int W, int rows, int* bw, int* bh, int* bn) {
+    const int HW = H * W;
+    if (HW <= rows) {
+        if (rows % HW) return false;
+        *bw = W; *bh = H; *bn = rows / HW;
+    } else {
+        if (rows % W || HW % rows) return false;
+        *bw = W; *bh = rows / W; *bn = 1;
+    }
+    return *bw * 2 <= 256 && *bh * 2 <= 256 && *bn <= 256;
+}
+
+extern "C" int mmvae_convt_tc_supported(int H, int W, int Cin, int Cout) {
+    int bw, bh, bn;
+    if (!tc_init()) return 0;
+    if (Cin % 32 || Cout % 32 || Cin > 128 || Cout > 128 || (Cin & (Cin - 1)) || (Cout & (Cout - 1))) return 0;
+    if (!conv_box(H, W, TC_BM, &bw, &bh, &bn) || !conv_box(H, W, 32, &bw, &bh, &bn)) return 0;
+    return 1;
+}
+
+static TcPlan plan_fixed(int BN, int nkb) {
+    TcPlan p;
+    p.BN = BN; p.S = 1; p.kb_per = nkb; p.swap = false;
+    return p;
+}
+
+// forward.  x: [Nimg,H,W,Cin] NHWC; wf: class-major weights [4*Cout, 4*Cin] (mmvae_convt_weight_classes);
+// y: [Nimg,2H,2W,Cout] NHWC = act(convT(x) + bias)
+extern "C" int mmvae_convt_tc_fwd(const float* x, const float* wf, const float* bias, float* y, int Nimg, int H, int W,
+                                  int Cin, int Cout, int act, void* stream) {
+    MMVAE_REQUIRE(x && wf && y && Nimg > 0, "convt_tc_fwd: bad arguments");
+    MMVAE_REQUIRE(mmvae_convt_tc_supported(H, W, Cin, Cout), "convt_tc_fwd: unsupported shape H=%d W=%d Cin=%d Cout=%d", H, W, Cin, Cout);
+    int bw, bh, bn;
+    conv_box(H, W, TC_BM, &bw, &bh, &bn);
+    CUtensorMap ta, tb;
+    int rc = make_tmap4(&ta, x, Nimg, H, W, Cin, bw, bh, bn, 1, false);
+    if (rc) return mmvae_set_error(1, "convt_tc_fwd: tensor map (x) failed with %d", rc);
+    rc = make_tmap(&tb, wf, 4L * Cout, 4L * Cin, Cout, false);
+    if (rc) return mmvae_set_error(1, "convt_tc_fwd: tensor map (w) failed with %d", rc);
+    const int M = Nimg * H * W, N = 4 * Cout, K = 4 * Cin;
+    const TcPlan p = plan_fixed(Cout, K / TC_BK);
+    const TcConv cv{1, H, W, Cin / 32, Cout};
+    cudaStream_t st = (cudaStream_t)stream;
+    if (Cout == 32) rc = tc_launch<32, false, false>(ta, tb, bias, y, nullptr, M, N, K, act, p, 0, st, cv);
+    else if (Cout == 64) rc = tc_launch<64, false, false>(ta, tb, bias, y, nullptr, M, N, K, act, p, 0, st, cv);
+    else rc = tc_launch<128, false, false>(ta, tb, bias, y, nullptr, M, N, K, act, p, 0, st, cv);
+    return rc;
+}
+
+// dgrad.  g: [Nimg,2H,2W,Cout] NHWC gradient w.r.t. the layer's pre-activation; wp: [Cin, 16*Cout] (tap-major);
+// gx: [Nimg,H,W,Cin]; x_mask: NULL or the layer input (gx zeroed where x <= 0)
+extern "C" int mmvae_convt_tc_dgrad(const float* g, const float* wp, const float* x_mask, float* gx, int Nimg, int H,
+                                    int W, int Cin, int Cout, void* stream) {
+    MMVAE_REQUIRE(g && wp && gx && Nimg > 0, "convt_tc_dgrad: bad arguments");
+    MMVAE_REQUIRE(mmvae_convt_tc_supported(H, W, Cin, Cout), "convt_tc_dgrad: unsupported shape");
+    int bw, bh, bn;
+    conv_box(H, W, TC_BM, &bw, &bh, &bn);
+    CUtensorMap ta, tb;
+    int rc = make_tmap4(&ta, g, Nimg, 2 * H, 2 * W, Cout, bw, bh, bn, 2, false);
+    if (rc) return mmvae_set_error(1, "convt_tc_dgrad: tensor map (g) failed with %d", rc);
+    rc = make_tmap(&tb, wp, Cin, 16L * Cout, Cin, false);
+    if (rc) return mmvae_set_error(1, "convt_tc_dgrad: tensor map (w) failed with %d", rc);
+    const int M = Nimg * H * W, N = Cin, K = 16 * Cout;
+    const TcPlan p = plan_fixed(Cin, K / TC_BK);
+    const TcConv cv{2, H, W, Cout / 32, Cout};
+    cudaStream_t st = (cudaStream_t)stream;
+    if (Cin == 32) rc = tc_launch<32, false, false>(ta, tb, nullptr, gx, nullptr, M, N, K, 0, p, 0, st, cv, x_mask);
+    else if (Cin == 64) rc = tc_launch<64, false, false>(ta, tb, nullptr, gx, nullptr, M, N, K, 0, p, 0, st, cv, x_mask);
+    else rc = tc_launch<128, false, false>(ta, tb, nullptr, gx, nullptr, M, N, K, 0, p, 0, st, cv, x_mask);
+    return rc;
+}
+
+static TcPlan plan_wgrad(int Cin, long rows) {
+    TcPlan p;
+    p.BN = Cin; p.swap = false;
+    const int nkb = (int)((rows + 31) / 32);
+    int S = (nkb + TC_MAX_CHAIN - 1) / TC_MAX_CHAIN;
+    p.kb_per = (nkb + S - 1) / S;
+    p.S = (nkb + p.kb_per - 1) / p.kb_per;
+    return p;
+}
+extern "C" long mmvae_convt_tc_wgrad_workspace_bytes(int Nimg, int H, int W, int Cin, int Cout) {
+    const TcPlan p = plan_wgrad(Cin, (long)Nimg * H * W);
+    return p.S > 1 ? (long)p.S * 16 * Cout * Cin * (long)sizeof(float) : 0;
+}
+// wgrad.  x: [Nimg,H,W,Cin]; g: [Nimg,2H,2W,Cout]; gwp: [Cin, 16*Cout] (tap-major, as mmvae_permute_weight's layout)
+extern "C" int mmvae_convt_tc_wgrad(const float* x, const float* g, float* gwp, float* workspace, long workspace_bytes,
+                                    int Nimg, int H, int W, int Cin, int Cout, void* stream) {
+    MMVAE_REQUIRE(x && g && gwp && Nimg > 0, "convt_tc_wgrad: bad arguments");
+    MMVAE_REQUIRE(mmvae_convt_tc_supported(H, W, Cin, Cout), "convt_tc_wgrad: unsupported shape");
+    int bw, bh, bn;
+    conv_box(H, W, 32, &bw, &bh, &bn);
+    const long rows = (long)Nimg * H * W;
+    TcPlan p = plan_wgrad(Cin, rows);
+    MMVAE_REQUIRE(p.S == 1 || (workspace && workspace_bytes >= mmvae_convt_tc_wgrad_workspace_bytes(Nimg, H, W, Cin, Cout)),
+                  "convt_tc_wgrad: workspace too small");
+    CUtensorMap ta, tb;
+    int rc = make_tmap4(&ta, g, Nimg, 2 * H, 2 * W, Cout, bw, bh, bn, 2, true);
+    if (rc) return mmvae_set_error(1, "convt_tc_wgrad: tensor map (g) failed with %d", rc);
+    rc = make_tmap(&tb, x, rows, Cin, TC_BK, true);
+    if (rc) return mmvae_set_error(1, "convt_tc_wgrad: tensor map (x) failed with %d", rc);
+    const int M = 16 * Cout, N = Cin;
+    const int K = (int)(((rows + 31) / 32) * 32);
+    const TcConv cv{3, H, W, Cout / 32, Cout};
+    cudaStream_t st = (cudaStream_t)stream;
+    if (Cin == 32) rc = tc_launch<32, true, true>(ta, tb, nullptr, gwp, workspace, M, N, K, 0, p, 1, st, cv);
+    else if (Cin == 64) rc = tc_launch<64, true, true>(ta, tb, nullptr, gwp, workspace, M, N, K, 0, p, 1, st, cv);
+    else rc = tc_launch<128, true, true>(ta, tb, nullptr, gwp, workspace, M, N, K, 0, p, 1, st, cv);
+    if (rc) return rc;
+    if (p.S > 1) mmvae_splitk_reduce(workspace, nullptr, gwp, (long)M * N, N, p.S, 0, st);
+    return 0;
+}
+
+// class-major forward weights: wf[(py*2+px)*Cout + co][(ty*2+tx)*Cin + ci] = w[ci][co][ky][kx] with
+// ky = ty ? 3 - 3*py : 1 + py  (the tap that reaches output row 2i+py from input row i + (ty ? 2*py-1 : 0)); same in x
+__global__ void convt_weight_classes_kernel(const float* __restrict__ w, float* __restrict__ wf, int Cin, int Cout) {
+    const long n = 16L * Cin * Cout;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+        const int ci = (int)(i % Cin), t = (int)((i / Cin) % 4), co = (int)((i / (4L * Cin)) % Cout), cls = (int)(i / (4L * Cin * Cout));
+        const int py = cls >> 1, px = cls & 1, ty = t >> 1, tx = t & 1;
+        const int ky = ty ? 3 - 3 * py : 1 + py, kx = tx ? 3 - 3 * px : 1 + px;
+        wf[i] = w[(((long)ci * Cout + co) * 4 + ky) * 4 + kx];
+    }
+}
+extern "C" int mmvae_convt_weight_classes(const float* w, float* wf, int Cin, int Cout, void* stream) {
+    MMVAE_REQUIRE(w && wf && Cin > 0 && Cout > 0, "convt_weight_classes: bad arguments");
+    const long n = 16L * Cin * Cout;
+    convt_weight_classes_kernel<<<(int)min((long)MMVAE_NUM_SMS * 4, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(w, wf, Cin, Cout);
+    MMVAE_LAUNCH_CHECK("convt_weight_classes");
     return 0;
 }

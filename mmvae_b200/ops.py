@@ -256,6 +256,19 @@ class ConvT2dAct(torch.autograd.Function):
         small = (k == 4 and stride == 2 and pad == 1 and nchw_out and w.shape[3] == 4
                  and lib.mmvae_convt_small_supported(H, W, Cin, Cout) == 2)
         x2d = _as_rows(x)
+        tc = (ALLOW_TC and not small and k == 4 and stride == 2 and pad == 1 and not nchw_out and w.shape[3] == 4
+              and lib.mmvae_convt_tc_supported(H, W, Cin, Cout) == 1)
+        if tc:
+            wf = torch.empty((4 * Cout, 4 * Cin), device=x.device, dtype=torch.float32)
+            _call("mmvae_convt_weight_classes", _p(w), _p(wf), Cin, Cout, _stream())
+            y = torch.empty((N, 2 * H, 2 * W, Cout), device=x.device, dtype=torch.float32)
+            _call("mmvae_convt_tc_fwd", _p(x2d), _p(wf), _p(b), _p(y), N, H, W, Cin, Cout, ACT[act], _stream(),
+                  work=("flop", 2.0 * N * H * W * 16 * Cin * Cout))
+            keep_y = (ACT[act] != C["MMVAE_ACT_NONE"]) and not preact_grad
+            ctx.save_for_backward(x2d, w, y if keep_y else None)
+            ctx.cfg = (N, Cin, H, W, Cout, k, stride, pad, act, tuple(w.shape), b is not None, preact_grad,
+                       mask_input_grad, "tc")
+            return y.permute(0, 3, 1, 2)
         if small:
             y = torch.empty((N, Cout, 2 * H, 2 * W), device=x.device, dtype=torch.float32)
             _call("mmvae_convt_small_fwd", _p(x2d), _p(w), _p(b), _p(y), N, H, W, Cin, Cout, ACT[act], _stream(),
@@ -263,7 +276,7 @@ class ConvT2dAct(torch.autograd.Function):
             keep_y = (ACT[act] != C["MMVAE_ACT_NONE"]) and not preact_grad
             ctx.save_for_backward(x2d, w, y if keep_y else None)
             ctx.cfg = (N, Cin, H, W, Cout, k, stride, pad, act, tuple(w.shape), b is not None, preact_grad,
-                       mask_input_grad, True)
+                       mask_input_grad, "small")
             return y
         wp = permute_weight(w)                                  # [Cin, k*k*Cout]
         col = gemm(x2d, wp, None, N * H * W, k * k * Cout, Cin, True, False)
@@ -271,13 +284,37 @@ class ConvT2dAct(torch.autograd.Function):
         keep_y = (ACT[act] != C["MMVAE_ACT_NONE"]) and not preact_grad
         ctx.save_for_backward(x2d, wp, y if keep_y else None)
         ctx.cfg = (N, Cin, H, W, Cout, k, stride, pad, act, tuple(w.shape), b is not None, preact_grad,
-                   mask_input_grad, False)
+                   mask_input_grad, "lowered")
         return y
 
     @staticmethod
     def backward(ctx, gy):
         x2d, wp, y = ctx.saved_tensors
-        N, Cin, H, W, Cout, k, s, p, act, wshape, has_bias, preact_grad, mask_in, small = ctx.cfg
+        N, Cin, H, W, Cout, k, s, p, act, wshape, has_bias, preact_grad, mask_in, path = ctx.cfg
+        small = path == "small"
+        if path == "tc":
+            w = wp
+            g = _as_rows(_dev(gy, "grad"))                       # [N*2H*2W, Cout], NHWC
+            if y is not None:
+                g = act_bwd(g, y.view(-1, Cout), act)
+            gx = gw = gb = None
+            if ctx.needs_input_grad[0]:
+                wpm = permute_weight(w)                          # [Cin, 16*Cout]
+                gx2d = torch.empty_like(x2d)
+                _call("mmvae_convt_tc_dgrad", _p(g), _p(wpm), _p(x2d if mask_in else None), _p(gx2d), N, H, W, Cin, Cout,
+                      _stream(), work=("flop", 2.0 * N * H * W * 16 * Cin * Cout))
+                gx = gx2d.view(N, H, W, Cin).permute(0, 3, 1, 2)
+            if ctx.needs_input_grad[1]:
+                lib = _lib.load()
+                nb = lib.mmvae_convt_tc_wgrad_workspace_bytes(N, H, W, Cin, Cout)
+                ws = torch.empty(nb // 4, device=g.device, dtype=torch.float32) if nb else None
+                gwp = torch.empty((Cin, 16 * Cout), device=g.device, dtype=torch.float32)
+                _call("mmvae_convt_tc_wgrad", _p(x2d), _p(g), _p(gwp), _p(ws), nb, N, H, W, Cin, Cout, _stream(),
+                      work=("flop", 2.0 * N * H * W * 16 * Cin * Cout))
+                gw = unpermute_weight(gwp, wshape)
+            if has_bias and ctx.needs_input_grad[2]:
+                gb = colsum(g)
+            return gx, gw, gb, None, None, None, None, None, None
         if small:
             g = _c(gy, "grad")                                   # (N,Cout,2H,2W) NCHW
             w = wp

@@ -87,12 +87,16 @@ def test_conv2d_autograd(ops, cin, cout, H, s, p, nchw_in):
     assert rel_err(gx, rx) < 5e-6 and rel_err(gw, rw) < 5e-6 and rel_err(gb, rb) < 5e-6
 
 
-@pytest.mark.parametrize("cin,cout,H,s,p,act,nchw_out", [(20, 128, 1, 1, 0, "relu", False), (128, 64, 4, 2, 1, "relu", False),
-                                                         (32, 3, 16, 2, 1, "sigmoid", True), (64, 32, 8, 2, 1, "relu", False),
-                                                         (32, 1, 14, 2, 1, "sigmoid", True), (32, 4, 5, 2, 1, "relu", True),
-                                                         (32, 3, 16, 2, 1, None, True), (16, 3, 8, 2, 1, "sigmoid", True)])
-def test_convT2d_autograd(ops, cin, cout, H, s, p, act, nchw_out):
-    N = 6 if cout > 4 or H != 16 else 301          # the direct path's persistent wgrad loops over images per CTA
+@pytest.mark.parametrize("cin,cout,H,s,p,act,nchw_out,N", [(20, 128, 1, 1, 0, "relu", False, None), (128, 64, 4, 2, 1, "relu", False, None),
+                                                         (32, 3, 16, 2, 1, "sigmoid", True, None), (64, 32, 8, 2, 1, "relu", False, None),
+                                                         (32, 1, 14, 2, 1, "sigmoid", True, None), (32, 4, 5, 2, 1, "relu", True, None),
+                                                         (32, 3, 16, 2, 1, None, True, None), (16, 3, 8, 2, 1, "sigmoid", True, None),
+                                                         (128, 64, 4, 2, 1, "relu", False, 77), (64, 32, 8, 2, 1, "relu", False, 77),
+                                                         (32, 32, 16, 2, 1, None, False, 5), (32, 64, 2, 2, 1, "relu", False, 131),
+                                                         (128, 128, 8, 2, 1, "sigmoid", False, 3)])
+def test_convT2d_autograd(ops, cin, cout, H, s, p, act, nchw_out, N):
+    if N is None:
+        N = 6 if cout > 4 or H != 16 else 301      # the direct path's persistent wgrad loops over images per CTA
     x = _rand(N, cin, H, H, seed=1).permute(0, 2, 3, 1).contiguous().permute(0, 3, 1, 2).requires_grad_()
     w = _rand(cin, cout, 4, 4, seed=2, scale=0.1).requires_grad_()
     b = _rand(cout, seed=3).requires_grad_()
