@@ -51,21 +51,34 @@ class Trainer:
         if self.distributed:
             dist.broadcast(self.fp.flat, src, group=self.pg)
 
-    def _step_impl(self, x, noise=None):
+    def _fwd_bwd(self, x, noise=None):
         self.fp.grad.zero_()
         loss, _ = self.objective(self.model, x, self.K, 1, 0, 1, noise=noise)
         (-loss).backward()                                   # main.py:156: the objective is maximised
-        if self.distributed:
+        return loss.detach()
+
+    def _reduce(self):
+        if self.distributed:                                 # ONE collective per step: the flat gradient bucket
             dist.all_reduce(self.fp.grad, op=dist.ReduceOp.SUM, group=self.pg)
+
+    def _update(self):
         ops.adam_amsgrad_(self.fp.flat, self.fp.grad, self.m, self.v, self.vmax, self.step_dev, lr=self.lr,
                           amsgrad=self.amsgrad)
-        return loss.detach()
+
+    def _step_impl(self, x, noise=None):
+        loss = self._fwd_bwd(x, noise)
+        self._reduce()
+        self._update()
+        return loss
 
     def step(self, x, noise=None):
         """eager step -> loss (device scalar, this rank's shard)."""
         return self._step_impl(x, noise)
 
     # ---- CUDA-graph replay: static input buffers, RNG inside the graph -------------------------------------------
+    # Two graphs (forward+backward, optimizer) with the NCCL all-reduce issued between them on the same stream: the
+    # collective stays an ordinary stream-ordered launch (no capture of communicator state), the ~100 kernel launches
+    # around it are replayed.
     def capture(self, x_example, warmup=3):
         self._static_x = [t.clone() for t in x_example]
         s = torch.cuda.Stream()
@@ -76,11 +89,21 @@ class Trainer:
         torch.cuda.current_stream().wait_stream(s)
         self._graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self._graph):
-            self._static_loss = self._step_impl(self._static_x)
+            self._static_loss = self._fwd_bwd(self._static_x)
+            if not self.distributed:
+                self._update()
+        self._graph_upd = None
+        if self.distributed:
+            self._graph_upd = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._graph_upd):
+                self._update()
         return self
 
     def step_graph(self, x):
         for dst, src in zip(self._static_x, x):
             dst.copy_(src, non_blocking=True)
         self._graph.replay()
+        if self._graph_upd is not None:
+            self._reduce()
+            self._graph_upd.replay()
         return self._static_loss
