@@ -27,31 +27,34 @@ __device__ __forceinline__ float cs_dact(float y, int act) {
 }
 
 // ------------------------------------------------------------------------------------------------------ forward
-// one CTA per image.  smem: xs[H*W][Cin+PAD], ws[16][COUT][Cin], bs[COUT]
-template <int COUT>
-__global__ void __launch_bounds__(CS_THREADS)
+// one CTA per image.  smem: xs[H*W][CIN+PAD], ws[16][COUT][CIN], bs[COUT].  CIN is a template constant so the channel
+// loop unrolls completely: every weight address is an immediate offset and the body is FFMA + LDS.128 only
+// (the first version spent 70 % of its issue slots on address arithmetic and split FMUL/FADD pairs — ncu source page).
+#define CSF_THREADS 256
+template <int COUT, int CIN>
+__global__ void __launch_bounds__(CSF_THREADS)
 convt_small_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
-                       float* __restrict__ y, int H, int W, int Cin, int act) {
+                       float* __restrict__ y, int H, int W, int act) {
     extern __shared__ float4 smem4[];
     float* xs = (float*)smem4;
-    const int xstride = Cin + CS_PAD;
+    constexpr int xstride = CIN + CS_PAD;
     float* ws = xs + H * W * xstride;
-    float* bs = ws + 16 * COUT * Cin;
+    float* bs = ws + 16 * COUT * CIN;
     const int n = blockIdx.x, HW = H * W;
-    const float4* xg = (const float4*)(x + (long)n * HW * Cin);
-    const int c4 = Cin / 4;
-    for (int i = threadIdx.x; i < HW * c4; i += CS_THREADS) {
+    const float4* xg = (const float4*)(x + (long)n * HW * CIN);
+    constexpr int c4 = CIN / 4;
+    for (int i = threadIdx.x; i < HW * c4; i += CSF_THREADS) {
         const int p = i / c4, c = i - p * c4;
         *(float4*)(xs + p * xstride + 4 * c) = ld_stream4(xg + i);
     }
-    for (int i = threadIdx.x; i < 16 * COUT * Cin; i += CS_THREADS) {     // torch layout w[ci][co][tap] -> ws[tap][co][ci]
-        const int ci = i % Cin, co = (i / Cin) % COUT, tap = i / (Cin * COUT);
+    for (int i = threadIdx.x; i < 16 * COUT * CIN; i += CSF_THREADS) {     // torch layout w[ci][co][tap] -> ws[tap][co][ci]
+        const int ci = i % CIN, co = (i / CIN) % COUT, tap = i / (CIN * COUT);
         ws[i] = w[((long)ci * COUT + co) * 16 + tap];
     }
     if (threadIdx.x < COUT) bs[threadIdx.x] = bias ? bias[threadIdx.x] : 0.f;
     __syncthreads();
     const int H2 = 2 * H, W2 = 2 * W;
-    for (int p = threadIdx.x; p < HW; p += CS_THREADS) {
+    for (int p = threadIdx.x; p < HW; p += CSF_THREADS) {
         const int i = p / W, j = p - i * W;
         float acc[2][2][COUT];
 #pragma unroll
@@ -69,7 +72,8 @@ convt_small_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                 const int jj = j + dx;
                 if (jj < 0 || jj >= W) continue;
                 const float* xr = xs + (ii * W + jj) * xstride;
-                for (int c = 0; c < Cin; c += 4) {
+#pragma unroll
+                for (int c = 0; c < CIN; c += 4) {
                     const float4 xv = *(const float4*)(xr + c);
 #pragma unroll
                     for (int ky = 0; ky < 4; ++ky) {
@@ -79,11 +83,15 @@ convt_small_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                         for (int kx = 0; kx < 4; ++kx) {
                             const int px = (kx + 1) & 1;
                             if ((px + 1 - kx) / 2 != dx) continue;
-                            const float* wr = ws + (ky * 4 + kx) * COUT * Cin + c;
 #pragma unroll
                             for (int co = 0; co < COUT; ++co) {
-                                const float4 wv = *(const float4*)(wr + co * Cin);
-                                acc[py][px][co] += xv.x * wv.x + xv.y * wv.y + xv.z * wv.z + xv.w * wv.w;
+                                const float4 wv = *(const float4*)(ws + ((ky * 4 + kx) * COUT + co) * CIN + c);
+                                float t = acc[py][px][co];
+                                t = fmaf(xv.x, wv.x, t);
+                                t = fmaf(xv.y, wv.y, t);
+                                t = fmaf(xv.z, wv.z, t);
+                                t = fmaf(xv.w, wv.w, t);
+                                acc[py][px][co] = t;
                             }
                         }
                     }
@@ -101,14 +109,14 @@ convt_small_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
 }
 
 // stage g (N,Cout,2H,2W) of image n into gs[COUT][2H+2][2W+2] with a zero border, optionally times act'(y)
-template <int COUT>
+template <int COUT, int NT = CS_THREADS>
 __device__ __forceinline__ void cs_stage_g(float* gs, const float* __restrict__ g, const float* __restrict__ yact,
                                            int n, int H2, int W2, int act, float* bias_acc) {
     const int gw = W2 + 2, plane = (H2 + 2) * gw;
-    for (int i = threadIdx.x; i < COUT * plane; i += CS_THREADS) gs[i] = 0.f;
+    for (int i = threadIdx.x; i < COUT * plane; i += NT) gs[i] = 0.f;
     __syncthreads();
     const long base = (long)n * COUT * H2 * W2;
-    for (int i = threadIdx.x; i < COUT * H2 * W2; i += CS_THREADS) {
+    for (int i = threadIdx.x; i < COUT * H2 * W2; i += NT) {
         const int xx = i % W2, yy = (i / W2) % H2, co = i / (W2 * H2);
         float v = g[base + i];
         if (yact) v *= cs_dact(yact[base + i], act);
@@ -122,18 +130,18 @@ __device__ __forceinline__ void cs_stage_g(float* gs, const float* __restrict__ 
 
 // -------------------------------------------------------------------------------------------------------- dgrad
 // gx[n,i,j,ci] = sum_{ky,kx,co} g[n,co,2i-1+ky,2j-1+kx] * w[ci,co,ky,kx]   (* relu'(x_mask))
-// smem: gs[COUT][2H+2][2W+2], ws[Cin][COUT*16]
-template <int COUT>
+// smem: gs[COUT][2H+2][2W+2], ws[CIN][COUT*16]
+template <int COUT, int CIN>
 __global__ void __launch_bounds__(CS_THREADS)
 convt_small_dgrad_kernel(const float* __restrict__ g, const float* __restrict__ yact, const float* __restrict__ w,
-                         const float* __restrict__ x_mask, float* __restrict__ gx, int H, int W, int Cin, int act) {
+                         const float* __restrict__ x_mask, float* __restrict__ gx, int H, int W, int act) {
     extern __shared__ float4 smem4[];
     float* gs = (float*)smem4;
     const int H2 = 2 * H, W2 = 2 * W, gw = W2 + 2, plane = (H2 + 2) * gw;
     float* ws = gs + ((COUT * plane + 3) & ~3);
     const int n = blockIdx.x;
     cs_stage_g<COUT>(gs, g, yact, n, H2, W2, act, nullptr);
-    for (int i = threadIdx.x; i < Cin * COUT * 16; i += CS_THREADS) ws[i] = w[i];      // torch layout is already [ci][co][tap]
+    for (int i = threadIdx.x; i < CIN * COUT * 16; i += CS_THREADS) ws[i] = w[i];      // torch layout is already [ci][co][tap]
     __syncthreads();
     for (int p = threadIdx.x; p < H * W; p += CS_THREADS) {
         const int i = p / W, j = p - i * W;
@@ -146,21 +154,25 @@ convt_small_dgrad_kernel(const float* __restrict__ g, const float* __restrict__ 
                 const float2 a = *(const float2*)r, b = *(const float2*)(r + 2);
                 pt[co][ky * 4 + 0] = a.x; pt[co][ky * 4 + 1] = a.y; pt[co][ky * 4 + 2] = b.x; pt[co][ky * 4 + 3] = b.y;
             }
-        const long orow = ((long)n * H * W + p) * Cin;
-        for (int c = 0; c < Cin; c += 4) {
+        const long orow = ((long)n * H * W + p) * CIN;
+#pragma unroll 1
+        for (int c = 0; c < CIN; c += 4) {
             float o[4];
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 const float4* wr = (const float4*)(ws + (c + q) * COUT * 16);
-                float s = 0.f;
+                float s0 = 0.f, s1 = 0.f;                     // two chains: ILP without reassociating beyond fp32 noise
 #pragma unroll
                 for (int co = 0; co < COUT; ++co)
 #pragma unroll
                     for (int t = 0; t < 4; ++t) {
                         const float4 wv = wr[co * 4 + t];
-                        s += pt[co][4 * t] * wv.x + pt[co][4 * t + 1] * wv.y + pt[co][4 * t + 2] * wv.z + pt[co][4 * t + 3] * wv.w;
+                        s0 = fmaf(pt[co][4 * t], wv.x, s0);
+                        s1 = fmaf(pt[co][4 * t + 1], wv.y, s1);
+                        s0 = fmaf(pt[co][4 * t + 2], wv.z, s0);
+                        s1 = fmaf(pt[co][4 * t + 3], wv.w, s1);
                     }
-                o[q] = s;
+                o[q] = s0 + s1;
             }
             if (x_mask) {
                 const float4 m = *(const float4*)(x_mask + orow + c);
@@ -176,8 +188,9 @@ convt_small_dgrad_kernel(const float* __restrict__ g, const float* __restrict__ 
 // gw[ci,co,ky,kx] = sum_{n,i,j} x[n,i,j,ci] * g[n,co,2i-1+ky,2j-1+kx];  gb[co] = sum g.   Cin == 32.
 // persistent CTAs over images; warp = one replica of the 32 x (COUT*16) accumulator tile: lane -> (ci group of 4, ky);
 // thread tile 4 ci x COUT x 4 kx.  part[cta][Cin*COUT*16 + COUT]
+#define CSW_THREADS 128               // 4 warps per CTA: more, smaller CTAs per SM overlap each other's staging phases
 template <int COUT>
-__global__ void __launch_bounds__(CS_THREADS)
+__global__ void __launch_bounds__(CSW_THREADS)
 convt_small_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ g, const float* __restrict__ yact,
                          float* __restrict__ part, int N, int H, int W, int act) {
     constexpr int CIN = 32;
@@ -201,13 +214,13 @@ convt_small_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ 
     for (int n = blockIdx.x; n < N; n += gridDim.x) {
         __syncthreads();                                             // previous image fully consumed
         const float4* xg = (const float4*)(x + (long)n * HW * CIN);
-        for (int i = threadIdx.x; i < HW * (CIN / 4); i += CS_THREADS) {
+        for (int i = threadIdx.x; i < HW * (CIN / 4); i += CSW_THREADS) {
             const int p = i >> 3, c = i & 7;
             *(float4*)(xs + p * xstride + 4 * c) = ld_stream4(xg + i);
         }
-        cs_stage_g<COUT>(gs, g, yact, n, H2, W2, act, bacc);         // contains a __syncthreads after zeroing
+        cs_stage_g<COUT, CSW_THREADS>(gs, g, yact, n, H2, W2, act, bacc);         // contains a __syncthreads after zeroing
         __syncthreads();
-        for (int p = warp; p < HW; p += CS_THREADS / 32) {
+        for (int p = warp; p < HW; p += CSW_THREADS / 32) {
             const int i = p / W, j = p - i * W;
             const float4 xv = *(const float4*)(xs + p * xstride + 4 * cg);
 #pragma unroll
@@ -234,20 +247,20 @@ convt_small_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ 
                 red[warp * TOT + ((4 * cg + a) * COUT + co) * 16 + ky * 4 + kx] = acc[a][co][kx];
     __syncthreads();
     float* out = part + (long)blockIdx.x * (TOT + COUT);
-    for (int i = threadIdx.x; i < TOT; i += CS_THREADS) {
+    for (int i = threadIdx.x; i < TOT; i += CSW_THREADS) {
         float s = 0.f;
 #pragma unroll
-        for (int wv = 0; wv < CS_THREADS / 32; ++wv) s += red[wv * TOT + i];
+        for (int wv = 0; wv < CSW_THREADS / 32; ++wv) s += red[wv * TOT + i];
         out[i] = s;
     }
     __syncthreads();
     float* bred = red;                                               // [COUT][256]
 #pragma unroll
-    for (int c = 0; c < COUT; ++c) bred[c * CS_THREADS + threadIdx.x] = bacc[c];
+    for (int c = 0; c < COUT; ++c) bred[c * CSW_THREADS + threadIdx.x] = bacc[c];
     __syncthreads();
     if (threadIdx.x < COUT) {
         float s = 0.f;
-        for (int t = 0; t < CS_THREADS; ++t) s += bred[threadIdx.x * CS_THREADS + t];
+        for (int t = 0; t < CSW_THREADS; ++t) s += bred[threadIdx.x * CSW_THREADS + t];
         out[TOT + threadIdx.x] = s;
     }
 }
@@ -263,14 +276,14 @@ __global__ void convt_small_wgrad_reduce(const float* __restrict__ part, float* 
 }
 
 // ---------------------------------------------------------------------------------------------------- host side
-static int cs_wgrad_ctas(int N) { return N < 2 * MMVAE_NUM_SMS ? N : 2 * MMVAE_NUM_SMS; }
+static int cs_wgrad_ctas(int N) { return N < 4 * MMVAE_NUM_SMS ? N : 4 * MMVAE_NUM_SMS; }
 
 extern "C" int mmvae_convt_small_supported(int H, int W, int Cin, int Cout) {
-    if (Cout < 1 || Cout > 4 || Cin % 4 || Cin < 4 || H < 1 || W < 1) return 0;
+    if (Cout < 1 || Cout > 4 || Cin != 32 || H < 1 || W < 1) return 0;      // Cin is a template constant (fBase = 32)
     const size_t fwd = ((size_t)H * W * (Cin + CS_PAD) + 16 * (size_t)Cout * Cin + 4) * 4;
     const size_t gsz = (((size_t)Cout * (2 * H + 2) * (2 * W + 2) + 3) & ~(size_t)3) * 4;
     const size_t dg = gsz + (size_t)Cin * Cout * 16 * 4;
-    const size_t red = (size_t)(CS_THREADS / 32) * Cin * Cout * 16 * 4;
+    const size_t red = (size_t)(CSW_THREADS / 32) * Cin * Cout * 16 * 4 + 16;
     size_t wg = gsz + (size_t)H * W * (Cin + CS_PAD) * 4;
     if (red > wg) wg = red;
     const size_t lim = 200 * 1024;
@@ -296,17 +309,17 @@ static int cs_smem_attr(K kern, size_t smem, const char* name) {
 template <int CO>
 static int cs_fwd(const float* x, const float* w, const float* bias, float* y, int N, int H, int W, int Cin, int act,
                   size_t smem, cudaStream_t st) {
-    const int rc = cs_smem_attr(convt_small_fwd_kernel<CO>, smem, "convt_small_fwd");
+    const int rc = cs_smem_attr(convt_small_fwd_kernel<CO, 32>, smem, "convt_small_fwd");
     if (rc) return rc;
-    convt_small_fwd_kernel<CO><<<N, CS_THREADS, smem, st>>>(x, w, bias, y, H, W, Cin, act);
+    convt_small_fwd_kernel<CO, 32><<<N, CSF_THREADS, smem, st>>>(x, w, bias, y, H, W, act);
     return 0;
 }
 template <int CO>
 static int cs_dgrad(const float* g, const float* y_act, const float* w, const float* x_mask, float* gx, int N, int H,
                     int W, int Cin, int act, size_t smem, cudaStream_t st) {
-    const int rc = cs_smem_attr(convt_small_dgrad_kernel<CO>, smem, "convt_small_dgrad");
+    const int rc = cs_smem_attr(convt_small_dgrad_kernel<CO, 32>, smem, "convt_small_dgrad");
     if (rc) return rc;
-    convt_small_dgrad_kernel<CO><<<N, CS_THREADS, smem, st>>>(g, y_act, w, x_mask, gx, H, W, Cin, act);
+    convt_small_dgrad_kernel<CO, 32><<<N, CS_THREADS, smem, st>>>(g, y_act, w, x_mask, gx, H, W, act);
     return 0;
 }
 template <int CO>
@@ -314,7 +327,7 @@ static int cs_wgrad(const float* x, const float* g, const float* y_act, float* w
                     size_t smem, cudaStream_t st) {
     const int rc = cs_smem_attr(convt_small_wgrad_kernel<CO>, smem, "convt_small_wgrad");
     if (rc) return rc;
-    convt_small_wgrad_kernel<CO><<<P, CS_THREADS, smem, st>>>(x, g, y_act, ws, N, H, W, act);
+    convt_small_wgrad_kernel<CO><<<P, CSW_THREADS, smem, st>>>(x, g, y_act, ws, N, H, W, act);
     return 0;
 }
 
@@ -347,7 +360,7 @@ extern "C" int mmvae_convt_small_wgrad(const float* x, const float* g, const flo
     MMVAE_REQUIRE(mmvae_convt_small_supported(H, W, Cin, Cout) == 2, "convt_small_wgrad: unsupported shape (needs Cin == 32)");
     const size_t gsz = (((size_t)Cout * (2 * H + 2) * (2 * W + 2) + 3) & ~(size_t)3) * 4;
     size_t smem = gsz + (size_t)H * W * (Cin + CS_PAD) * 4;
-    const size_t red = (size_t)(CS_THREADS / 32) * Cin * Cout * 16 * 4;
+    const size_t red = (size_t)(CSW_THREADS / 32) * Cin * Cout * 16 * 4 + 16;
     if (red > smem) smem = red;
     const int P = cs_wgrad_ctas(N);
     const int rc = CS_SWITCH(Cout, cs_wgrad, x, g, y_act, workspace, P, N, H, W, act, smem, (cudaStream_t)stream);
