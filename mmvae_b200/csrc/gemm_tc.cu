@@ -510,8 +510,215 @@ static TcPlan plan_fixed(int BN, int nkb) {
     return p;
 }
 
-// forward.  x: [Nimg,H,W,Cin] NHWC; wf: class-major weights [4*Cout, 4*Cin] (mmvae_convt_weight_classes);
-// y: [Nimg,2H,2W,Cout] NHWC = act(convT(x) + bias)
+// ---------------------------------------------------------------------------------------- forward, 9-shift form
+// All four output-parity classes of a 128-row tile in ONE pass.  The 16 (class, tap) products of a transposed 4x4/s2
+// convolution touch only 9 distinct input windows (shifts (dy,dx) in {-1,0,1}^2): the centre window feeds all four
+// classes, an edge window two, a corner one.  Per 32-channel chunk the producer therefore loads 9 A tiles (not 16), the
+// converter splits 9, and the issuer runs the centre as ONE UMMA of N = 4*Cout, edges as N = 2*Cout (classes are laid
+// out in TMEM in Gray order (0,0),(0,1),(1,1),(1,0) so three of the four edge pairs are adjacent) and corners as N = Cout.
+// Weights arrive shift-major: w9[(rowoff[s] + q)*Cout + co][ci], q = rank of the class among those the shift feeds.
+__device__ __constant__ int8_t F9_DY[9] = {0, -1, 1, 0, 0, -1, -1, 1, 1};
+__device__ __constant__ int8_t F9_DX[9] = {0, 0, 0, 1, -1, -1, 1, 1, -1};
+__device__ __constant__ int8_t F9_NCLS[9] = {4, 2, 2, 2, 2, 1, 1, 1, 1};
+__device__ __constant__ int8_t F9_ROW[9] = {0, 4, 6, 8, 10, 12, 13, 14, 15};
+// MMA groups per shift: (first TMEM class slot, B row offset in classes, classes per MMA); shift 4 (dx=-1) has two
+__device__ __constant__ int8_t F9_G0[9][3] = {{0, 0, 4}, {0, 0, 2}, {2, 0, 2}, {1, 0, 2}, {0, 0, 1}, {0, 0, 1}, {1, 0, 1}, {2, 0, 1}, {3, 0, 1}};
+// Gray slot -> (py, px)
+__device__ __constant__ int8_t F9_PY[4] = {0, 0, 1, 1};
+__device__ __constant__ int8_t F9_PX[4] = {0, 1, 1, 0};
+
+template <int COUT> struct F9Cfg {
+    static constexpr int B_TILE = 4 * COUT * TC_BK * 4;            // up to four classes of weights per k-block
+    static constexpr int STAGE = 2 * TC_A_TILE + 2 * B_TILE;
+    static constexpr int STAGES = (COUT == 32) ? 3 : 2;
+    static constexpr int SMEM = STAGES * STAGE + 1024 + 256;
+    static constexpr int NACC = (COUT == 32) ? 2 : 1;              // 8*COUT TMEM columns per accumulator set
+    static constexpr int TMEM_COLS = 512;
+};
+
+template <int COUT>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+convt_fwd9_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                  const float* __restrict__ bias, float* __restrict__ Y, int M, int H, int W, int chunks, int act,
+                  int passes) {
+    using Cfg = F9Cfg<COUT>;
+    constexpr int STAGES = Cfg::STAGES, NACC = Cfg::NACC;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint64_t* bars = (uint64_t*)(smem + STAGES * Cfg::STAGE);
+    uint64_t* full = bars;
+    uint64_t* conv = bars + STAGES;
+    uint64_t* empty = bars + 2 * STAGES;
+    uint64_t* tfull = bars + 3 * STAGES;
+    uint64_t* tempty = bars + 3 * STAGES + 2;
+    uint32_t* tmem_slot = (uint32_t*)(bars + 3 * STAGES + 4);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tiles = (M + TC_BM - 1) / TC_BM, nk = 9 * chunks, HW = H * W;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(full + s, 1); mbar_init(conv + s, 4); mbar_init(empty + s, 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 4); }
+        mbar_fence_init();
+        tma_prefetch_desc(&tmap_a);
+        tma_prefetch_desc(&tmap_b);
+    }
+    if (warp == 1) { tmem_alloc(tmem_slot, Cfg::TMEM_COLS); tmem_relinquish(); }
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int it = 0;
+            for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+                const int m0 = t * TC_BM, n0 = m0 / HW, y0 = (m0 - n0 * HW) / W;
+                for (int kb = 0; kb < nk; ++kb, ++it) {
+                    const int s = it % STAGES, ph = (it / STAGES) & 1;
+                    const int sh = kb / chunks, c0 = (kb - sh * chunks) * 32, ncls = F9_NCLS[sh];
+                    mbar_wait(empty + s, ph ^ 1);
+                    uint8_t* st = smem + s * Cfg::STAGE;
+                    uint8_t* b_hi = st + 2 * TC_A_TILE;
+                    mbar_arrive_expect_tx(full + s, TC_A_TILE + ncls * COUT * TC_BK * 4);
+                    tma_load_4d(st, &tmap_a, full + s, c0, F9_DX[sh], y0 + F9_DY[sh], n0);
+                    for (int q = 0; q < ncls; ++q)
+                        tma_load_2d(b_hi + q * COUT * TC_BK * 4, &tmap_b, full + s, c0, (F9_ROW[sh] + q) * COUT);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc1 = umma_idesc_tf32(TC_BM, COUT, 0, 0), idesc2 = umma_idesc_tf32(TC_BM, 2 * COUT, 0, 0),
+                           idesc4 = umma_idesc_tf32(TC_BM, 4 * COUT, 0, 0);
+            int it = 0, ti = 0;
+            for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++ti) {
+                const int acc = ti % NACC, use = ti / NACC;
+                mbar_wait(tempty + acc, (use & 1) ^ 1);
+                tc_fence_after_sync();
+                const uint32_t d_big = tmem_base + acc * (8 * COUT), d_small = d_big + 4 * COUT;
+                for (int kb = 0; kb < nk; ++kb, ++it) {
+                    const int s = it % STAGES, ph = (it / STAGES) & 1;
+                    const int sh = kb / chunks;
+                    mbar_wait(passes == 3 ? conv + s : full + s, ph);
+                    tc_fence_after_sync();
+                    const uint32_t st = smem_u32(smem + s * Cfg::STAGE);
+                    const uint32_t a_hi = st, a_lo = st + TC_A_TILE;
+                    const uint32_t b_hi = st + 2 * TC_A_TILE, b_lo = b_hi + Cfg::B_TILE;
+                    const int ngroups = (sh == 4) ? 2 : 1;
+#pragma unroll
+                    for (int kk = 0; kk < TC_BK / 8; ++kk) {
+                        const uint64_t dah = umma_smem_desc(a_hi + kk * 32, 16, 1024, 2);
+                        const uint64_t dal = umma_smem_desc(a_lo + kk * 32, 16, 1024, 2);
+                        for (int gi = 0; gi < ngroups; ++gi) {
+                            const int slot = gi ? 3 : F9_G0[sh][0], brow = gi ? 1 : 0, nc = F9_G0[sh][2];
+                            const uint32_t idesc = nc == 4 ? idesc4 : (nc == 2 ? idesc2 : idesc1);
+                            const uint32_t boff = brow * COUT * TC_BK * 4 + kk * 32, col = slot * COUT;
+                            const uint64_t dbh = umma_smem_desc(b_hi + boff, 16, 1024, 2);
+                            const uint32_t first = (kb | kk) != 0;       // the centre window (kb 0) spans all four classes
+                            if (passes == 3) {
+                                const uint64_t dbl = umma_smem_desc(b_lo + boff, 16, 1024, 2);
+                                umma_tf32(d_small + col, dal, dbh, idesc, first);
+                                umma_tf32(d_small + col, dah, dbl, idesc, 1);
+                            }
+                            umma_tf32(d_big + col, dah, dbh, idesc, first);
+                        }
+                    }
+                    umma_commit(empty + s);
+                }
+                umma_commit(tfull + acc);
+            }
+        }
+    } else if (warp < 6) {
+        const int tq = threadIdx.x - 64;
+        if (passes == 3) {
+            int it = 0;
+            for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+                for (int kb = 0; kb < nk; ++kb, ++it) {
+                    const int s = it % STAGES, ph = (it / STAGES) & 1;
+                    const int nb4 = F9_NCLS[kb / chunks] * COUT * TC_BK / 4 / 128;     // float4 per thread in the B tile
+                    mbar_wait(full + s, ph);
+                    uint8_t* st = smem + s * Cfg::STAGE;
+                    const float4* a_hi = (const float4*)st;
+                    float4* a_lo = (float4*)(st + TC_A_TILE);
+                    const float4* b_hi = (const float4*)(st + 2 * TC_A_TILE);
+                    float4* b_lo = (float4*)(st + 2 * TC_A_TILE + Cfg::B_TILE);
+#pragma unroll
+                    for (int j = 0; j < TC_A_TILE / 16 / 128; ++j) {
+                        const float4 v = a_hi[tq + j * 128];
+                        a_lo[tq + j * 128] = make_float4(tf32_lo(v.x), tf32_lo(v.y), tf32_lo(v.z), tf32_lo(v.w));
+                    }
+                    for (int j = 0; j < nb4; ++j) {
+                        const float4 v = b_hi[tq + j * 128];
+                        b_lo[tq + j * 128] = make_float4(tf32_lo(v.x), tf32_lo(v.y), tf32_lo(v.z), tf32_lo(v.w));
+                    }
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(conv + s);
+                }
+            }
+        }
+    } else {
+        const int lane_base = (warp & 3) * 32;
+        int ti = 0;
+        for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++ti) {
+            const int acc = ti % NACC, use = ti / NACC;
+            mbar_wait(tfull + acc, use & 1);
+            tc_fence_after_sync();
+            const int row = t * TC_BM + lane_base + lane;
+            const int n_img = row / HW, rem = row - n_img * HW, ii = rem / W, jj = rem - ii * W;
+            const uint32_t tb = tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)(acc * 8 * COUT);
+#pragma unroll 1
+            for (int c = 0; c < 4 * COUT; c += 32) {
+                float v[32];
+                tmem_ld_32x32(tb + (uint32_t)c, v);
+                if (passes == 3) {
+                    float u[32];
+                    tmem_ld_32x32(tb + (uint32_t)(4 * COUT + c), u);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] += u[j];
+                }
+                if (c + 32 >= 4 * COUT) {
+                    tc_fence_before_sync();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(tempty + acc);
+                }
+                if (row < M) {
+                    const int slot = c / COUT, cc = c - slot * COUT;
+                    const long orow = ((long)(n_img * 2 * H + 2 * ii + F9_PY[slot]) * (2 * W) + 2 * jj + F9_PX[slot]);
+                    float* p = Y + orow * COUT + cc;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = apply_act_tc(v[j] + (bias ? __ldg(bias + cc + j) : 0.f), act);
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4)
+                        *reinterpret_cast<float4*>(p + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                }
+            }
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
+template <int COUT>
+static int fwd9_launch(const CUtensorMap& ta, const CUtensorMap& tb, const float* bias, float* y, int M, int H, int W,
+                       int chunks, int act, cudaStream_t st) {
+    static bool attr_done = false;
+    auto kern = convt_fwd9_kernel<COUT>;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, F9Cfg<COUT>::SMEM);
+        if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "convt_fwd9: smem attribute: %s", cudaGetErrorString(e));
+        attr_done = true;
+    }
+    const int tiles = (M + TC_BM - 1) / TC_BM;
+    const int grid = tiles < MMVAE_NUM_SMS ? tiles : MMVAE_NUM_SMS;
+    kern<<<grid, TC_THREADS, F9Cfg<COUT>::SMEM, st>>>(ta, tb, bias, y, M, H, W, chunks, act, g_tc_mode == 1 ? 1 : 3);
+    MMVAE_LAUNCH_CHECK("convt_fwd9");
+    return 0;
+}
+
+// forward.  x: [Nimg,H,W,Cin] NHWC; wf: forward weights from mmvae_convt_weight_classes (16*Cin*Cout floats; shift-major
+// for Cout in {32,64}, class-major for Cout = 128); y: [Nimg,2H,2W,Cout] NHWC = act(convT(x) + bias)
 extern "C" int mmvae_convt_tc_fwd(const float* x, const float* wf, const float* bias, float* y, int Nimg, int H, int W,
                                   int Cin, int Cout, int act, void* stream) {
     MMVAE_REQUIRE(x && wf && y && Nimg > 0, "convt_tc_fwd: bad arguments");
@@ -521,16 +728,20 @@ extern "C" int mmvae_convt_tc_fwd(const float* x, const float* wf, const float* 
     CUtensorMap ta, tb;
     int rc = make_tmap4(&ta, x, Nimg, H, W, Cin, bw, bh, bn, 1, false);
     if (rc) return mmvae_set_error(1, "convt_tc_fwd: tensor map (x) failed with %d", rc);
+    const int M = Nimg * H * W;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (Cout <= 64) {
+        rc = make_tmap(&tb, wf, 16L * Cout, Cin, Cout, false);
+        if (rc) return mmvae_set_error(1, "convt_tc_fwd: tensor map (w9) failed with %d", rc);
+        return Cout == 32 ? fwd9_launch<32>(ta, tb, bias, y, M, H, W, Cin / 32, act, st)
+                          : fwd9_launch<64>(ta, tb, bias, y, M, H, W, Cin / 32, act, st);
+    }
     rc = make_tmap(&tb, wf, 4L * Cout, 4L * Cin, Cout, false);
     if (rc) return mmvae_set_error(1, "convt_tc_fwd: tensor map (w) failed with %d", rc);
-    const int M = Nimg * H * W, N = 4 * Cout, K = 4 * Cin;
+    const int N = 4 * Cout, K = 4 * Cin;
     const TcPlan p = plan_fixed(Cout, K / TC_BK);
     const TcConv cv{1, H, W, Cin / 32, Cout};
-    cudaStream_t st = (cudaStream_t)stream;
-    if (Cout == 32) rc = tc_launch<32, false, false>(ta, tb, bias, y, nullptr, M, N, K, act, p, 0, st, cv);
-    else if (Cout == 64) rc = tc_launch<64, false, false>(ta, tb, bias, y, nullptr, M, N, K, act, p, 0, st, cv);
-    else rc = tc_launch<128, false, false>(ta, tb, bias, y, nullptr, M, N, K, act, p, 0, st, cv);
-    return rc;
+    return tc_launch<128, false, false>(ta, tb, bias, y, nullptr, M, N, K, act, p, 0, st, cv);
 }
 
 // dgrad.  g: [Nimg,2H,2W,Cout] NHWC gradient w.r.t. the layer's pre-activation; wp: [Cin, 16*Cout] (tap-major);
@@ -597,8 +808,9 @@ extern "C" int mmvae_convt_tc_wgrad(const float* x, const float* g, float* gwp, 
     return 0;
 }
 
-// class-major forward weights: wf[(py*2+px)*Cout + co][(ty*2+tx)*Cin + ci] = w[ci][co][ky][kx] with
-// ky = ty ? 3 - 3*py : 1 + py  (the tap that reaches output row 2i+py from input row i + (ty ? 2*py-1 : 0)); same in x
+// forward weights.  Cout = 128: class-major wf[(py*2+px)*Cout + co][(ty*2+tx)*Cin + ci] = w[ci][co][ky][kx] with
+// ky = ty ? 3 - 3*py : 1 + py  (the tap that reaches output row 2i+py from input row i + (ty ? 2*py-1 : 0)); same in x.
+// Cout <= 64: shift-major w9[(F9_ROW[s] + q)*Cout + co][ci] (see convt_fwd9_kernel), class slot in Gray order.
 __global__ void convt_weight_classes_kernel(const float* __restrict__ w, float* __restrict__ wf, int Cin, int Cout) {
     const long n = 16L * Cin * Cout;
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
@@ -608,10 +820,31 @@ __global__ void convt_weight_classes_kernel(const float* __restrict__ w, float* 
         wf[i] = w[(((long)ci * Cout + co) * 4 + ky) * 4 + kx];
     }
 }
+__global__ void convt_weight_shifts_kernel(const float* __restrict__ w, float* __restrict__ w9, int Cin, int Cout) {
+    const long n = 16L * Cin * Cout;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+        const int ci = (int)(i % Cin), co = (int)((i / Cin) % Cout), r = (int)(i / ((long)Cin * Cout));   // r: class row 0..15
+        int sh = 8;
+        while (F9_ROW[sh] > r) --sh;
+        const int q = r - F9_ROW[sh], dy = F9_DY[sh], dx = F9_DX[sh];
+        // q-th Gray slot (ascending) among the classes this shift feeds
+        int slot = -1, seen = 0;
+        for (int g = 0; g < 4; ++g) {
+            const bool oky = dy == 0 || (dy < 0 ? F9_PY[g] == 0 : F9_PY[g] == 1);
+            const bool okx = dx == 0 || (dx < 0 ? F9_PX[g] == 0 : F9_PX[g] == 1);
+            if (oky && okx) { if (seen == q) { slot = g; break; } ++seen; }
+        }
+        const int py = F9_PY[slot], px = F9_PX[slot];
+        const int ky = dy == 0 ? 1 + py : (py == 0 ? 3 : 0), kx = dx == 0 ? 1 + px : (px == 0 ? 3 : 0);
+        w9[i] = w[(((long)ci * Cout + co) * 4 + ky) * 4 + kx];
+    }
+}
 extern "C" int mmvae_convt_weight_classes(const float* w, float* wf, int Cin, int Cout, void* stream) {
     MMVAE_REQUIRE(w && wf && Cin > 0 && Cout > 0, "convt_weight_classes: bad arguments");
     const long n = 16L * Cin * Cout;
-    convt_weight_classes_kernel<<<(int)min((long)MMVAE_NUM_SMS * 4, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(w, wf, Cin, Cout);
+    const int grid = (int)min((long)MMVAE_NUM_SMS * 4, (n + 255) / 256);
+    if (Cout <= 64) convt_weight_shifts_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(w, wf, Cin, Cout);
+    else convt_weight_classes_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(w, wf, Cin, Cout);
     MMVAE_LAUNCH_CHECK("convt_weight_classes");
     return 0;
 }
