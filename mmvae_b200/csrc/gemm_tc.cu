@@ -22,6 +22,8 @@
 #define TC_BK 32                       // fp32 elements per k-block = one 128-byte swizzle row
 #define TC_THREADS 320
 #define TC_A_TILE (TC_BM * TC_BK * 4)  // 16 KB
+#define TC_EPI_PITCH 36               // floats per staged row: 16-byte aligned, conflict-free for 128-bit accesses
+#define TC_EPI_BYTES (4 * 32 * TC_EPI_PITCH * 4)     // one 32 x 32 transposition pad per epilogue warp
 #define TC_MAX_CHAIN 32                // k-blocks accumulated in one TMEM chain when split-K is available
 
 static int g_tc_mode = 0;              // 0 = 3xTF32 (fp32 accuracy), 1 = single TF32 pass (debug / speed probe)
@@ -30,7 +32,7 @@ template <int BN> struct TcCfg {
     static constexpr int B_TILE = BN * TC_BK * 4;
     static constexpr int STAGE = 2 * TC_A_TILE + 2 * B_TILE;
     static constexpr int STAGES = (BN == 128) ? 3 : 4;
-    static constexpr int SMEM = STAGES * STAGE + 1024 + 256;
+    static constexpr int SMEM = STAGES * STAGE + 1024 + 256 + TC_EPI_BYTES;
     static constexpr int TMEM_COLS = 4 * BN;          // {big, small} x 2 accumulator buffers
 };
 
@@ -98,6 +100,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     uint64_t* tfull = bars + 3 * STAGES;        // [2] accumulator buffer complete
     uint64_t* tempty = bars + 3 * STAGES + 2;   // [2] accumulator buffer drained by the epilogue
     uint32_t* tmem_slot = (uint32_t*)(bars + 3 * STAGES + 4);
+    float* epi = (float*)(smem + STAGES * Cfg::STAGE + 256);          // epilogue transposition pads (16-byte aligned)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nkb = (K + TC_BK - 1) / TC_BK;
@@ -272,51 +275,65 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     __syncwarp();
                     if (lane == 0) mbar_arrive(tempty + acc);
                 }
-                if (row < M && cv.mode == 1) {
-                    // scatter: row (n,i,j) of class (py,px) -> y[n, 2i+py, 2j+px, :] (NHWC, Cout == BN columns)
-                    const int HW = cv.H * cv.W, n_img = row / HW, rem = row - n_img * HW;
-                    const int ii = rem / cv.W, jj = rem - ii * cv.W;
-                    const long orow = ((long)(n_img * 2 * cv.H + 2 * ii + (tl.nt >> 1)) * (2 * cv.W) + 2 * jj + (tl.nt & 1));
-                    float* p = C + orow * BN + c;
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = apply_act_tc(v[j] + (bias ? __ldg(bias + c + j) : 0.f), act);
-#pragma unroll
-                    for (int j = 0; j < 32; j += 4)
-                        *reinterpret_cast<float4*>(p + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-                } else if (row < M) {
-                    if (splits == 1) {
+                if (c_transposed) {
+                    if (row < M) {
 #pragma unroll
                         for (int j = 0; j < 32; ++j) {
                             const int n = tl.n0 + c + j;
-                            if (n < N) v[j] = apply_act_tc(v[j] + (bias ? __ldg(bias + n) : 0.f), act);
-                        }
-                        if (mask) {                            // fused ReLU backward of the layer below (mode 2)
-#pragma unroll
-                            for (int j = 0; j < 32; ++j) {
-                                const int n = tl.n0 + c + j;
-                                if (n < N && __ldg(mask + (long)row * N + n) <= 0.f) v[j] = 0.f;
-                            }
+                            if (n < N) out[(long)n * M + row] = v[j];       // lanes = consecutive rows: coalesced
                         }
                     }
-                    if (c_transposed) {
+                    continue;
+                }
+                // bias + activation by column (the thread holds one row), then transpose the warp's 32 x 32 block through
+                // shared memory so that global traffic is row-coalesced: each 128-bit access instruction then covers
+                // 4 rows x 128 contiguous bytes (whole 32-byte sectors) instead of 32 rows x 16 bytes
+                if (splits == 1) {
+                    const int nb = (cv.mode == 1) ? c : tl.n0 + c;
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            const int n = tl.n0 + c + j;
-                            if (n < N) out[(long)n * M + row] = v[j];
+                    for (int j = 0; j < 32; ++j)
+                        v[j] = apply_act_tc(v[j] + ((bias && nb + j < N) ? __ldg(bias + nb + j) : 0.f), act);
+                }
+                float* pad = epi + (warp & 3) * 32 * TC_EPI_PITCH;
+#pragma unroll
+                for (int j = 0; j < 32; j += 4)
+                    *reinterpret_cast<float4*>(pad + lane * TC_EPI_PITCH + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                __syncwarp();
+                const int col = (lane & 7) * 4;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const int r = 4 * k + (lane >> 3), grow = tl.m0 + lane_base + r;
+                    if (grow >= M) continue;
+                    float4 o = *reinterpret_cast<const float4*>(pad + r * TC_EPI_PITCH + col);
+                    if (cv.mode == 1) {
+                        // scatter: row (n,i,j) of class (py,px) -> y[n, 2i+py, 2j+px, :] (NHWC, Cout == BN columns)
+                        const int HW = cv.H * cv.W, n_img = grow / HW, rem = grow - n_img * HW;
+                        const int ii = rem / cv.W, jj = rem - ii * cv.W;
+                        const long orow = ((long)(n_img * 2 * cv.H + 2 * ii + (tl.nt >> 1)) * (2 * cv.W) + 2 * jj + (tl.nt & 1));
+                        *reinterpret_cast<float4*>(C + orow * BN + c + col) = o;
+                        continue;
+                    }
+                    const int n = tl.n0 + c + col;
+                    float* p = out + (long)grow * N + n;
+                    if ((N & 3) == 0 && n + 4 <= N) {
+                        if (mask && splits == 1) {             // fused ReLU backward of the layer below (mode 2)
+                            const float4 m = __ldg(reinterpret_cast<const float4*>(mask + (long)grow * N + n));
+                            o.x = m.x > 0.f ? o.x : 0.f; o.y = m.y > 0.f ? o.y : 0.f;
+                            o.z = m.z > 0.f ? o.z : 0.f; o.w = m.w > 0.f ? o.w : 0.f;
                         }
+                        *reinterpret_cast<float4*>(p) = o;
                     } else {
-                        float* p = out + (long)row * N + tl.n0 + c;
-                        if ((N & 3) == 0 && tl.n0 + c + 32 <= N) {
+                        const float ov[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll
-                            for (int j = 0; j < 32; j += 4)
-                                *reinterpret_cast<float4*>(p + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j)
-                                if (tl.n0 + c + j < N) p[j] = v[j];
-                        }
+                        for (int q = 0; q < 4; ++q)
+                            if (n + q < N) {
+                                float val = ov[q];
+                                if (mask && splits == 1 && __ldg(mask + (long)grow * N + n + q) <= 0.f) val = 0.f;
+                                p[q] = val;
+                            }
                     }
                 }
+                __syncwarp();                                  // the pad is reused by the next 32-column chunk
             }
         }
     }
@@ -683,6 +700,7 @@ convt_fwd9_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     if (lane == 0) mbar_arrive(tempty + acc);
                 }
                 if (row < M) {
+                    // each thread owns one output row of 32 contiguous floats (one full 128-byte line): direct stores
                     const int slot = c / COUT, cc = c - slot * COUT;
                     const long orow = ((long)(n_img * 2 * H + 2 * ii + F9_PY[slot]) * (2 * W) + 2 * jj + F9_PX[slot]);
                     float* p = Y + orow * COUT + cc;
