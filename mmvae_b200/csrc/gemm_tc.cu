@@ -26,6 +26,7 @@
 #define TC_EPI_BYTES (4 * 32 * TC_EPI_PITCH * 4)     // one 32 x 32 transposition pad per epilogue warp
 #define TC_MAX_CHAIN 32                // k-blocks accumulated in one TMEM chain when split-K is available
 
+static int g_tc_dbg = 0;
 static int g_tc_mode = 0;              // 0 = 3xTF32 (fp32 accuracy), 1 = single TF32 pass (debug / speed probe)
 
 template <int BN> struct TcCfg {
@@ -366,7 +367,8 @@ static int tc_init() {
 extern "C" int mmvae_has_tcgen05(void) { return tc_init(); }
 extern "C" int mmvae_gemm_tc_set_mode(int mode) {
     const int old = g_tc_mode;
-    g_tc_mode = (mode == 1) ? 1 : 0;
+    g_tc_mode = (mode & 0xff) == 1 ? 1 : 0;
+    g_tc_dbg = mode >> 8;                 // ablation bits for tools/f9_ablate.py (0 in production)
     return old;
 }
 
@@ -557,8 +559,9 @@ template <int COUT>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 convt_fwd9_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const float* __restrict__ bias, float* __restrict__ Y, int M, int H, int W, int chunks, int act,
-                  int passes) {
+                  int passes_dbg) {
     using Cfg = F9Cfg<COUT>;
+    const int passes = passes_dbg & 0xff, dbg = passes_dbg >> 8;
     constexpr int STAGES = Cfg::STAGES, NACC = Cfg::NACC;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -596,9 +599,11 @@ convt_fwd9_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     mbar_wait(empty + s, ph ^ 1);
                     uint8_t* st = smem + s * Cfg::STAGE;
                     uint8_t* b_hi = st + 2 * TC_A_TILE;
-                    mbar_arrive_expect_tx(full + s, TC_A_TILE + ncls * COUT * TC_BK * 4);
-                    tma_load_4d(st, &tmap_a, full + s, c0, F9_DX[sh], y0 + F9_DY[sh], n0);
-                    for (int q = 0; q < ncls; ++q)
+                    const bool la = !(dbg & 2) || it < STAGES, lb = !(dbg & 4) || it < STAGES;
+                    if (!la && !lb) { mbar_arrive(full + s); continue; }
+                    mbar_arrive_expect_tx(full + s, (la ? TC_A_TILE : 0) + (lb ? ncls * COUT * TC_BK * 4 : 0));
+                    if (la) tma_load_4d(st, &tmap_a, full + s, c0, F9_DX[sh], y0 + F9_DY[sh], n0);
+                    for (int q = 0; q < ncls && lb; ++q)
                         tma_load_2d(b_hi + q * COUT * TC_BK * 4, &tmap_b, full + s, c0, (F9_ROW[sh] + q) * COUT);
                 }
             }
@@ -624,6 +629,7 @@ convt_fwd9_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     const int ngroups = (sh == 4) ? 2 : 1;
 #pragma unroll
                     for (int kk = 0; kk < TC_BK / 8; ++kk) {
+                        if ((dbg & 16) && (kb | kk) != 0) break;
                         const uint64_t dah = umma_smem_desc(a_hi + kk * 32, 16, 1024, 2);
                         const uint64_t dal = umma_smem_desc(a_lo + kk * 32, 16, 1024, 2);
                         for (int gi = 0; gi < ngroups; ++gi) {
@@ -659,6 +665,7 @@ convt_fwd9_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     float4* a_lo = (float4*)(st + TC_A_TILE);
                     const float4* b_hi = (const float4*)(st + 2 * TC_A_TILE);
                     float4* b_lo = (float4*)(st + 2 * TC_A_TILE + Cfg::B_TILE);
+                    if (dbg & 8) { __syncwarp(); if (lane == 0) mbar_arrive(conv + s); continue; }
 #pragma unroll
                     for (int j = 0; j < TC_A_TILE / 16 / 128; ++j) {
                         const float4 v = a_hi[tq + j * 128];
@@ -699,7 +706,7 @@ convt_fwd9_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     __syncwarp();
                     if (lane == 0) mbar_arrive(tempty + acc);
                 }
-                if (row < M) {
+                if (row < M && !(dbg & 1)) {
                     // each thread owns one output row of 32 contiguous floats (one full 128-byte line): direct stores
                     const int slot = c / COUT, cc = c - slot * COUT;
                     const long orow = ((long)(n_img * 2 * H + 2 * ii + F9_PY[slot]) * (2 * W) + 2 * jj + F9_PX[slot]);
@@ -730,7 +737,8 @@ static int fwd9_launch(const CUtensorMap& ta, const CUtensorMap& tb, const float
     }
     const int tiles = (M + TC_BM - 1) / TC_BM;
     const int grid = tiles < MMVAE_NUM_SMS ? tiles : MMVAE_NUM_SMS;
-    kern<<<grid, TC_THREADS, F9Cfg<COUT>::SMEM, st>>>(ta, tb, bias, y, M, H, W, chunks, act, g_tc_mode == 1 ? 1 : 3);
+    kern<<<grid, TC_THREADS, F9Cfg<COUT>::SMEM, st>>>(ta, tb, bias, y, M, H, W, chunks, act,
+                                                     (g_tc_mode == 1 ? 1 : 3) | (g_tc_dbg << 8));
     MMVAE_LAUNCH_CHECK("convt_fwd9");
     return 0;
 }
