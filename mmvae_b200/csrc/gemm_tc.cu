@@ -122,101 +122,96 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
-        // ===== TMA producer: the stage ring runs straight through tile boundaries =====
-        if (lane == 0) {
-            int it = 0;
-            for (int t = blockIdx.x; t < total; t += gridDim.x) {
-                const TcTile tl = tc_tile(t, tiles_m, tiles_n, BN, nkb, kb_per_split);
-                for (int i = 0; i < tl.nk; ++i, ++it) {
-                    const int s = it % STAGES, ph = (it / STAGES) & 1;
-                    mbar_wait(empty + s, ph ^ 1);
-                    uint8_t* st = smem + s * Cfg::STAGE;
-                    uint8_t* a_hi = st;
-                    uint8_t* b_hi = st + 2 * TC_A_TILE;
-                    mbar_arrive_expect_tx(full + s, TC_A_TILE + Cfg::B_TILE);
-                    const int kbi = tl.kb_begin + i;
-                    const int k0 = kbi * TC_BK;
-                    if (cv.mode == 0) {
-                        if (A_MN) {
+        // ===== TMA producer (whole warp converged, one elected lane issues; see sm100_ptx.cuh): the stage ring runs
+        // straight through tile boundaries =====
+        const uint32_t smem_base = smem_u32(smem);
+        int s = 0, ph = 0;
+        for (int t = blockIdx.x; t < total; t += gridDim.x) {
+            const TcTile tl = tc_tile(t, tiles_m, tiles_n, BN, nkb, kb_per_split);
+            for (int i = 0; i < tl.nk; ++i) {
+                mbar_wait(empty + s, ph ^ 1);
+                const uint32_t a_hi = smem_base + s * Cfg::STAGE, b_hi = a_hi + 2 * TC_A_TILE;
+                mbar_arrive_expect_tx_elect(full + s, TC_A_TILE + Cfg::B_TILE);
+                const int kbi = tl.kb_begin + i;
+                const int k0 = kbi * TC_BK;
+                if (cv.mode == 0) {
+                    if (A_MN) {
 #pragma unroll
-                            for (int j = 0; j < TC_BM / 32; ++j)
-                                tma_load_2d(a_hi + j * 4096, &tmap_a, full + s, tl.m0 + 32 * j, k0);
-                        } else {
-                            tma_load_2d(a_hi, &tmap_a, full + s, k0, tl.m0);
-                        }
-                    } else if (cv.mode == 3) {
-                        // k-block = 32 consecutive pixels (n, y, x) of the coarse grid; M group j = 32 channels of one tap
-                        const int HW = cv.H * cv.W, p0 = kbi * 32;
-                        const int n0 = p0 / HW, y0 = (p0 - n0 * HW) / cv.W;
-#pragma unroll
-                        for (int j = 0; j < TC_BM / 32; ++j) {
-                            const int m = tl.m0 + 32 * j, tap = m / cv.Cout, c0 = m - tap * cv.Cout;
-                            tma_load_4d(a_hi + j * 4096, &tmap_a, full + s, c0, (tap & 3) - 1, 2 * y0 + (tap >> 2) - 1, n0);
-                        }
+                        for (int j = 0; j < TC_BM / 32; ++j)
+                            tma_load_2d_elect(a_hi + j * 4096, &tmap_a, full + s, tl.m0 + 32 * j, k0);
                     } else {
-                        const int HW = cv.H * cv.W;
-                        const int n0 = tl.m0 / HW, y0 = (tl.m0 - n0 * HW) / cv.W;
-                        const int tap = kbi / cv.chunks, c0 = (kbi - tap * cv.chunks) * 32;
-                        if (cv.mode == 1) {                      // class (py,px) = N tile; tap (ty,tx) -> window shift
-                            const int py = tl.nt >> 1, px = tl.nt & 1;
-                            const int dy = (tap >> 1) ? 2 * py - 1 : 0, dx = (tap & 1) ? 2 * px - 1 : 0;
-                            tma_load_4d(a_hi, &tmap_a, full + s, c0, dx, y0 + dy, n0);
-                        } else {                                 // mode 2: tap (ky,kx) of the stride-2 gather
-                            tma_load_4d(a_hi, &tmap_a, full + s, c0, (tap & 3) - 1, 2 * y0 + (tap >> 2) - 1, n0);
-                        }
+                        tma_load_2d_elect(a_hi, &tmap_a, full + s, k0, tl.m0);
                     }
-                    if (B_MN) {
+                } else if (cv.mode == 3) {
+                    // k-block = 32 consecutive pixels (n, y, x) of the coarse grid; M group j = 32 channels of one tap
+                    const int HW = cv.H * cv.W, p0 = kbi * 32;
+                    const int n0 = p0 / HW, y0 = (p0 - n0 * HW) / cv.W;
 #pragma unroll
-                        for (int j = 0; j < BN / 32; ++j)
-                            tma_load_2d(b_hi + j * 4096, &tmap_b, full + s, tl.n0 + 32 * j, k0);
-                    } else {
-                        tma_load_2d(b_hi, &tmap_b, full + s, k0, tl.n0);
+                    for (int j = 0; j < TC_BM / 32; ++j) {
+                        const int m = tl.m0 + 32 * j, tap = m / cv.Cout, c0 = m - tap * cv.Cout;
+                        tma_load_4d_elect(a_hi + j * 4096, &tmap_a, full + s, c0, (tap & 3) - 1, 2 * y0 + (tap >> 2) - 1, n0);
+                    }
+                } else {
+                    const int HW = cv.H * cv.W;
+                    const int n0 = tl.m0 / HW, y0 = (tl.m0 - n0 * HW) / cv.W;
+                    const int tap = kbi / cv.chunks, c0 = (kbi - tap * cv.chunks) * 32;
+                    if (cv.mode == 1) {                      // class (py,px) = N tile; tap (ty,tx) -> window shift
+                        const int py = tl.nt >> 1, px = tl.nt & 1;
+                        const int dy = (tap >> 1) ? 2 * py - 1 : 0, dx = (tap & 1) ? 2 * px - 1 : 0;
+                        tma_load_4d_elect(a_hi, &tmap_a, full + s, c0, dx, y0 + dy, n0);
+                    } else {                                 // mode 2: tap (ky,kx) of the stride-2 gather
+                        tma_load_4d_elect(a_hi, &tmap_a, full + s, c0, (tap & 3) - 1, 2 * y0 + (tap >> 2) - 1, n0);
                     }
                 }
+                if (B_MN) {
+#pragma unroll
+                    for (int j = 0; j < BN / 32; ++j)
+                        tma_load_2d_elect(b_hi + j * 4096, &tmap_b, full + s, tl.n0 + 32 * j, k0);
+                } else {
+                    tma_load_2d_elect(b_hi, &tmap_b, full + s, k0, tl.n0);
+                }
+                if (++s == STAGES) { s = 0; ph ^= 1; }
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer (one elected lane) =====
+        // ===== MMA issuer (whole warp converged, one elected lane issues) =====
         constexpr uint32_t idesc = umma_idesc_tf32(TC_BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
-        if (lane == 0) {
-            int it = 0, ti = 0;
-            for (int t = blockIdx.x; t < total; t += gridDim.x, ++ti) {
-                const TcTile tl = tc_tile(t, tiles_m, tiles_n, BN, nkb, kb_per_split);
-                const int acc = ti & 1;
-                mbar_wait(tempty + acc, ((ti >> 1) & 1) ^ 1);          // epilogue has drained this buffer
+        // K-major (SWIZZLE_128B): 8 tf32 = 32 bytes inside the 128-byte row, 8-row groups 1024 B apart.
+        // MN-major (SWIZZLE_128B_BASE32B): 8 k-rows of 128 B = 1024 B per MMA, 4-row swizzle atoms
+        // 512 B apart (SBO), 32-element MN groups one TMA box = 4096 B apart (LBO).
+        constexpr uint32_t a_lbo = A_MN ? 4096 : 16, b_lbo = B_MN ? 4096 : 16;
+        constexpr uint32_t a_sbo = A_MN ? 512 : 1024, b_sbo = B_MN ? 512 : 1024;
+        constexpr uint32_t a_lt = A_MN ? 1 : 2, b_lt = B_MN ? 1 : 2;
+        constexpr uint32_t a_step = (A_MN ? 1024 : 32) >> 4, b_step = (B_MN ? 1024 : 32) >> 4;   // descriptor units
+        const uint32_t smem_base = smem_u32(smem);
+        // descriptors of stage 0; a stage / operand / k-slice offset is an add on the 14-bit address field
+        const uint64_t da0 = umma_smem_desc(smem_base, a_lbo, a_sbo, a_lt);
+        const uint64_t db0 = umma_smem_desc(smem_base + 2 * TC_A_TILE, b_lbo, b_sbo, b_lt);
+        int s = 0, ph = 0, ti = 0;
+        for (int t = blockIdx.x; t < total; t += gridDim.x, ++ti) {
+            const TcTile tl = tc_tile(t, tiles_m, tiles_n, BN, nkb, kb_per_split);
+            const int acc = ti & 1;
+            mbar_wait(tempty + acc, ((ti >> 1) & 1) ^ 1);          // epilogue has drained this buffer
+            tc_fence_after_sync();
+            const uint32_t d_big = tmem_base + acc * (2 * BN), d_small = d_big + BN;
+            for (int i = 0; i < tl.nk; ++i) {
+                mbar_wait(passes == 3 ? conv + s : full + s, ph);
                 tc_fence_after_sync();
-                const uint32_t d_big = tmem_base + acc * (2 * BN), d_small = d_big + BN;
-                for (int i = 0; i < tl.nk; ++i, ++it) {
-                    const int s = it % STAGES, ph = (it / STAGES) & 1;
-                    mbar_wait(passes == 3 ? conv + s : full + s, ph);
-                    tc_fence_after_sync();
-                    const uint32_t st = smem_u32(smem + s * Cfg::STAGE);
-                    const uint32_t a_hi = st, a_lo = st + TC_A_TILE;
-                    const uint32_t b_hi = st + 2 * TC_A_TILE, b_lo = b_hi + Cfg::B_TILE;
+                const uint64_t dah = da0 + (uint64_t)(s * (Cfg::STAGE >> 4)), dal = dah + (TC_A_TILE >> 4);
+                const uint64_t dbh = db0 + (uint64_t)(s * (Cfg::STAGE >> 4)), dbl = dbh + (Cfg::B_TILE >> 4);
 #pragma unroll
-                    for (int kk = 0; kk < TC_BK / 8; ++kk) {
-                        // K-major (SWIZZLE_128B): 8 tf32 = 32 bytes inside the 128-byte row, 8-row groups 1024 B apart.
-                        // MN-major (SWIZZLE_128B_BASE32B): 8 k-rows of 128 B = 1024 B per MMA, 4-row swizzle atoms
-                        // 512 B apart (SBO), 32-element MN groups one TMA box = 4096 B apart (LBO).
-                        const uint32_t ao = A_MN ? kk * 1024 : kk * 32, bo = B_MN ? kk * 1024 : kk * 32;
-                        const uint32_t a_lbo = A_MN ? 4096 : 16, b_lbo = B_MN ? 4096 : 16;
-                        const uint32_t a_sbo = A_MN ? 512 : 1024, b_sbo = B_MN ? 512 : 1024;
-                        const uint32_t a_lt = A_MN ? 1 : 2, b_lt = B_MN ? 1 : 2;
-                        const uint64_t dah = umma_smem_desc(a_hi + ao, a_lbo, a_sbo, a_lt);
-                        const uint64_t dbh = umma_smem_desc(b_hi + bo, b_lbo, b_sbo, b_lt);
-                        const uint32_t first = (i | kk) != 0;
-                        if (passes == 3) {
-                            const uint64_t dal = umma_smem_desc(a_lo + ao, a_lbo, a_sbo, a_lt);
-                            const uint64_t dbl = umma_smem_desc(b_lo + bo, b_lbo, b_sbo, b_lt);
-                            umma_tf32(d_small, dal, dbh, idesc, first);
-                            umma_tf32(d_small, dah, dbl, idesc, 1);
-                        }
-                        umma_tf32(d_big, dah, dbh, idesc, first);
+                for (int kk = 0; kk < TC_BK / 8; ++kk) {
+                    const uint32_t first = (i | kk) != 0;
+                    if (passes == 3) {
+                        umma_tf32_elect(d_small, dal + kk * a_step, dbh + kk * b_step, idesc, first);
+                        umma_tf32_elect(d_small, dah + kk * a_step, dbl + kk * b_step, idesc, 1);
                     }
-                    umma_commit(empty + s);                  // frees the stage once these MMAs have read it
+                    umma_tf32_elect(d_big, dah + kk * a_step, dbh + kk * b_step, idesc, first);
                 }
-                umma_commit(tfull + acc);
+                umma_commit_elect(empty + s);                  // frees the stage once these MMAs have read it
+                if (++s == STAGES) { s = 0; ph ^= 1; }
             }
+            umma_commit_elect(tfull + acc);
         }
     } else if (warp < 6) {
         // ===== converter (warps 2..5): lo = rn_tf32(a - trunc_tf32(a)), same swizzled position in the lo tile =====
@@ -546,11 +541,21 @@ __device__ __constant__ int8_t F9_G0[9][3] = {{0, 0, 4}, {0, 0, 2}, {2, 0, 2}, {
 __device__ __constant__ int8_t F9_PY[4] = {0, 0, 1, 1};
 __device__ __constant__ int8_t F9_PX[4] = {0, 1, 1, 0};
 
+// Shared-memory plan.  The stage-release chain (TMA landing -> hi/lo split -> MMAs -> commit -> producer) is several
+// thousand clocks long, so throughput = bytes in flight / chain latency: the ring must hold as many k-blocks as possible.
+// A windows (hi + lo, 32 KB) rotate through SA slots.  Weights rotate through EIGHT class slots (one class = COUT rows
+// x 32 channels): in the order of F9_NCLS = 4,2,2,2,2,1,1,1,1 the k-blocks of one channel chunk tile the eight slots
+// exactly twice (F9_ROW % 8), so every shift has a fixed, contiguous home and the slots a k-block overwrites were last
+// used F9_BACK[shift] k-blocks earlier.  Barriers are per k-block ticket (NT of each kind); MMAs retire in order, so
+// "ticket j released" implies everything older is released too.
+__device__ __constant__ int8_t F9_BACK[9] = {5, 4, 3, 3, 4, 4, 5, 5, 6};
 template <int COUT> struct F9Cfg {
-    static constexpr int B_TILE = 4 * COUT * TC_BK * 4;            // up to four classes of weights per k-block
-    static constexpr int STAGE = 2 * TC_A_TILE + 2 * B_TILE;
-    static constexpr int STAGES = (COUT == 32) ? 3 : 2;
-    static constexpr int SMEM = STAGES * STAGE + 1024 + 256;
+    static constexpr int CLS = COUT * TC_BK * 4;                   // one class of weights for one k-block
+    static constexpr int B_HALF = 8 * CLS;                         // hi ring; the lo ring follows
+    static constexpr int A_SLOT = 2 * TC_A_TILE;
+    static constexpr int SA = (COUT == 32) ? 5 : 3;
+    static constexpr int NT = 8;
+    static constexpr int SMEM = SA * A_SLOT + 2 * B_HALF + 1024 + 256;
     static constexpr int NACC = (COUT == 32) ? 2 : 1;              // 8*COUT TMEM columns per accumulator set
     static constexpr int TMEM_COLS = 512;
 };
@@ -561,22 +566,23 @@ convt_fwd9_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                   const float* __restrict__ bias, float* __restrict__ Y, int M, int H, int W, int chunks, int act,
                   int passes_dbg) {
     using Cfg = F9Cfg<COUT>;
+    constexpr int SA = Cfg::SA, NT = Cfg::NT, NACC = Cfg::NACC;
     const int passes = passes_dbg & 0xff, dbg = passes_dbg >> 8;
-    constexpr int STAGES = Cfg::STAGES, NACC = Cfg::NACC;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    uint64_t* bars = (uint64_t*)(smem + STAGES * Cfg::STAGE);
+    uint8_t* bring = smem + SA * Cfg::A_SLOT;
+    uint64_t* bars = (uint64_t*)(bring + 2 * Cfg::B_HALF);
     uint64_t* full = bars;
-    uint64_t* conv = bars + STAGES;
-    uint64_t* empty = bars + 2 * STAGES;
-    uint64_t* tfull = bars + 3 * STAGES;
-    uint64_t* tempty = bars + 3 * STAGES + 2;
-    uint32_t* tmem_slot = (uint32_t*)(bars + 3 * STAGES + 4);
+    uint64_t* conv = bars + NT;
+    uint64_t* empty = bars + 2 * NT;
+    uint64_t* tfull = bars + 3 * NT;
+    uint64_t* tempty = bars + 3 * NT + 2;
+    uint32_t* tmem_slot = (uint32_t*)(bars + 3 * NT + 4);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tiles = (M + TC_BM - 1) / TC_BM, nk = 9 * chunks, HW = H * W;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES; ++s) { mbar_init(full + s, 1); mbar_init(conv + s, 4); mbar_init(empty + s, 1); }
+        for (int s = 0; s < NT; ++s) { mbar_init(full + s, 1); mbar_init(conv + s, 4); mbar_init(empty + s, 1); }
         for (int a = 0; a < 2; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 4); }
         mbar_fence_init();
         tma_prefetch_desc(&tmap_a);
@@ -589,67 +595,78 @@ convt_fwd9_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
-        if (lane == 0) {
-            int it = 0;
-            for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
-                const int m0 = t * TC_BM, n0 = m0 / HW, y0 = (m0 - n0 * HW) / W;
-                for (int kb = 0; kb < nk; ++kb, ++it) {
-                    const int s = it % STAGES, ph = (it / STAGES) & 1;
-                    const int sh = kb / chunks, c0 = (kb - sh * chunks) * 32, ncls = F9_NCLS[sh];
-                    mbar_wait(empty + s, ph ^ 1);
-                    uint8_t* st = smem + s * Cfg::STAGE;
-                    uint8_t* b_hi = st + 2 * TC_A_TILE;
-                    const bool la = !(dbg & 2) || it < STAGES, lb = !(dbg & 4) || it < STAGES;
-                    if (!la && !lb) { mbar_arrive(full + s); continue; }
-                    mbar_arrive_expect_tx(full + s, (la ? TC_A_TILE : 0) + (lb ? ncls * COUT * TC_BK * 4 : 0));
-                    if (la) tma_load_4d(st, &tmap_a, full + s, c0, F9_DX[sh], y0 + F9_DY[sh], n0);
-                    for (int q = 0; q < ncls && lb; ++q)
-                        tma_load_2d(b_hi + q * COUT * TC_BK * 4, &tmap_b, full + s, c0, (F9_ROW[sh] + q) * COUT);
+        // producer: whole warp converged, one elected lane issues (sm100_ptx.cuh); the nine shifts are unrolled so that
+        // every table entry is an immediate
+        const uint32_t a_ring = smem_u32(smem), b_ring = smem_u32(bring);
+        int it = 0, tk = 0, as = 0;
+        for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+            const int m0 = t * TC_BM, n0 = m0 / HW, y0 = (m0 - n0 * HW) / W;
+            for (int ck = 0; ck < chunks; ++ck) {
+#pragma unroll
+                for (int sh = 0; sh < 9; ++sh) {
+                    constexpr int8_t kDy[9] = {0, -1, 1, 0, 0, -1, -1, 1, 1}, kDx[9] = {0, 0, 0, 1, -1, -1, 1, 1, -1};
+                    constexpr int8_t kNcls[9] = {4, 2, 2, 2, 2, 1, 1, 1, 1}, kRow[9] = {0, 4, 6, 8, 10, 12, 13, 14, 15};
+                    constexpr int8_t kBack[9] = {5, 4, 3, 3, 4, 4, 5, 5, 6};
+                    // the A slot was last used SA k-blocks ago, the weight slots kBack[sh] k-blocks ago
+                    const int back = kBack[sh] < SA ? kBack[sh] : SA, j = it - back;
+                    if (j >= 0) mbar_wait(empty + (j & (NT - 1)), (j / NT) & 1);
+                    const uint32_t a_hi = a_ring + as * Cfg::A_SLOT, b_hi = b_ring + (kRow[sh] & 7) * Cfg::CLS;
+                    const bool la = !(dbg & 2) || it < SA, lb = !(dbg & 4) || it < 9;
+                    mbar_arrive_expect_tx_elect(full + tk, (la ? TC_A_TILE : 0) + (lb ? kNcls[sh] * Cfg::CLS : 0));
+                    if (la) tma_load_4d_elect(a_hi, &tmap_a, full + tk, ck * 32, kDx[sh], y0 + kDy[sh], n0);
+#pragma unroll
+                    for (int q = 0; q < kNcls[sh]; ++q)
+                        if (lb) tma_load_2d_elect(b_hi + q * Cfg::CLS, &tmap_b, full + tk, ck * 32, (kRow[sh] + q) * COUT);
+                    ++it;
+                    tk = (tk + 1) & (NT - 1);
+                    if (++as == SA) as = 0;
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            const uint32_t idesc1 = umma_idesc_tf32(TC_BM, COUT, 0, 0), idesc2 = umma_idesc_tf32(TC_BM, 2 * COUT, 0, 0),
+        // MMA issuer: whole warp converged, one elected lane issues
+        constexpr uint32_t idesc1 = umma_idesc_tf32(TC_BM, COUT, 0, 0), idesc2 = umma_idesc_tf32(TC_BM, 2 * COUT, 0, 0),
                            idesc4 = umma_idesc_tf32(TC_BM, 4 * COUT, 0, 0);
-            int it = 0, ti = 0;
-            for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++ti) {
-                const int acc = ti % NACC, use = ti / NACC;
-                mbar_wait(tempty + acc, (use & 1) ^ 1);
-                tc_fence_after_sync();
-                const uint32_t d_big = tmem_base + acc * (8 * COUT), d_small = d_big + 4 * COUT;
-                for (int kb = 0; kb < nk; ++kb, ++it) {
-                    const int s = it % STAGES, ph = (it / STAGES) & 1;
-                    const int sh = kb / chunks;
-                    mbar_wait(passes == 3 ? conv + s : full + s, ph);
+        const uint64_t da0 = umma_smem_desc(smem_u32(smem), 16, 1024, 2);
+        const uint64_t db0 = umma_smem_desc(smem_u32(bring), 16, 1024, 2);
+        int tk = 0, ph = 0, as = 0, ti = 0;
+        for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++ti) {
+            const int acc = ti % NACC, use = ti / NACC;
+            mbar_wait(tempty + acc, (use & 1) ^ 1);
+            tc_fence_after_sync();
+            const uint32_t d_big = tmem_base + acc * (8 * COUT), d_small = d_big + 4 * COUT;
+            for (int ck = 0; ck < chunks; ++ck) {
+#pragma unroll
+                for (int sh = 0; sh < 9; ++sh) {
+                    constexpr int8_t kRow[9] = {0, 4, 6, 8, 10, 12, 13, 14, 15};
+                    // MMA groups per shift: first TMEM class slot and classes per MMA; shift 4 (dx=-1) = two single-class MMAs
+                    constexpr int8_t kSlot[9] = {0, 0, 2, 1, 0, 0, 1, 2, 3}, kNc[9] = {4, 2, 2, 2, 1, 1, 1, 1, 1};
+                    mbar_wait(passes == 3 ? conv + tk : full + tk, ph);
                     tc_fence_after_sync();
-                    const uint32_t st = smem_u32(smem + s * Cfg::STAGE);
-                    const uint32_t a_hi = st, a_lo = st + TC_A_TILE;
-                    const uint32_t b_hi = st + 2 * TC_A_TILE, b_lo = b_hi + Cfg::B_TILE;
-                    const int ngroups = (sh == 4) ? 2 : 1;
+                    const uint64_t dah = da0 + (uint64_t)(as * (Cfg::A_SLOT >> 4)), dal = dah + (TC_A_TILE >> 4);
+                    const uint64_t dbh = db0 + (uint64_t)((kRow[sh] & 7) * (Cfg::CLS >> 4)), dbl = dbh + (Cfg::B_HALF >> 4);
+                    const uint32_t idesc = kNc[sh] == 4 ? idesc4 : (kNc[sh] == 2 ? idesc2 : idesc1);
 #pragma unroll
                     for (int kk = 0; kk < TC_BK / 8; ++kk) {
-                        if ((dbg & 16) && (kb | kk) != 0) break;
-                        const uint64_t dah = umma_smem_desc(a_hi + kk * 32, 16, 1024, 2);
-                        const uint64_t dal = umma_smem_desc(a_lo + kk * 32, 16, 1024, 2);
-                        for (int gi = 0; gi < ngroups; ++gi) {
-                            const int slot = gi ? 3 : F9_G0[sh][0], brow = gi ? 1 : 0, nc = F9_G0[sh][2];
-                            const uint32_t idesc = nc == 4 ? idesc4 : (nc == 2 ? idesc2 : idesc1);
-                            const uint32_t boff = brow * COUT * TC_BK * 4 + kk * 32, col = slot * COUT;
-                            const uint64_t dbh = umma_smem_desc(b_hi + boff, 16, 1024, 2);
-                            const uint32_t first = (kb | kk) != 0;       // the centre window (kb 0) spans all four classes
+                        if ((dbg & 16) && (ck | sh | kk) != 0) break;
+                        const uint32_t first = (ck | sh | kk) != 0;      // the centre window (first) spans all four classes
+#pragma unroll
+                        for (int gi = 0; gi < (sh == 4 ? 2 : 1); ++gi) {
+                            const uint32_t col = (gi ? 3 : kSlot[sh]) * COUT, boff = (gi * Cfg::CLS >> 4) + kk * 2;
                             if (passes == 3) {
-                                const uint64_t dbl = umma_smem_desc(b_lo + boff, 16, 1024, 2);
-                                umma_tf32(d_small + col, dal, dbh, idesc, first);
-                                umma_tf32(d_small + col, dah, dbl, idesc, 1);
+                                umma_tf32_elect(d_small + col, dal + kk * 2, dbh + boff, idesc, first);
+                                umma_tf32_elect(d_small + col, dah + kk * 2, dbl + boff, idesc, 1);
                             }
-                            umma_tf32(d_big + col, dah, dbh, idesc, first);
+                            umma_tf32_elect(d_big + col, dah + kk * 2, dbh + boff, idesc, first);
                         }
                     }
-                    umma_commit(empty + s);
+                    umma_commit_elect(empty + tk);
+                    tk = (tk + 1) & (NT - 1);
+                    if (tk == 0) ph ^= 1;
+                    if (++as == SA) as = 0;
                 }
-                umma_commit(tfull + acc);
             }
+            umma_commit_elect(tfull + acc);
         }
     } else if (warp < 6) {
         const int tq = threadIdx.x - 64;
@@ -657,15 +674,14 @@ convt_fwd9_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             int it = 0;
             for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
                 for (int kb = 0; kb < nk; ++kb, ++it) {
-                    const int s = it % STAGES, ph = (it / STAGES) & 1;
-                    const int nb4 = F9_NCLS[kb / chunks] * COUT * TC_BK / 4 / 128;     // float4 per thread in the B tile
-                    mbar_wait(full + s, ph);
-                    uint8_t* st = smem + s * Cfg::STAGE;
-                    const float4* a_hi = (const float4*)st;
-                    float4* a_lo = (float4*)(st + TC_A_TILE);
-                    const float4* b_hi = (const float4*)(st + 2 * TC_A_TILE);
-                    float4* b_lo = (float4*)(st + 2 * TC_A_TILE + Cfg::B_TILE);
-                    if (dbg & 8) { __syncwarp(); if (lane == 0) mbar_arrive(conv + s); continue; }
+                    const int tk = it % NT, ph = (it / NT) & 1, sh = kb % 9;
+                    const int nb4 = F9_NCLS[sh] * Cfg::CLS / 16 / 128;                 // float4 per thread in the weights
+                    mbar_wait(full + tk, ph);
+                    if (dbg & 8) { __syncwarp(); if (lane == 0) mbar_arrive(conv + tk); continue; }
+                    const float4* a_hi = (const float4*)(smem + (it % SA) * Cfg::A_SLOT);
+                    float4* a_lo = (float4*)(smem + (it % SA) * Cfg::A_SLOT + TC_A_TILE);
+                    const float4* b_hi = (const float4*)(bring + (F9_ROW[sh] & 7) * Cfg::CLS);
+                    float4* b_lo = (float4*)(bring + Cfg::B_HALF + (F9_ROW[sh] & 7) * Cfg::CLS);
 #pragma unroll
                     for (int j = 0; j < TC_A_TILE / 16 / 128; ++j) {
                         const float4 v = a_hi[tq + j * 128];
@@ -677,7 +693,7 @@ convt_fwd9_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     }
                     fence_proxy_async_smem();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(conv + s);
+                    if (lane == 0) mbar_arrive(conv + tk);
                 }
             }
         }

@@ -22,7 +22,7 @@ for (H, Cin, Cout) in ((4, 128, 64), (8, 64, 32)):
     lib.mmvae_convt_weight_classes(p(w), p(wf), Cin, Cout, st())
     y = torch.empty(N, 2 * H, 2 * H, Cout, device="cuda")
     for mode in (0, 1):
-        for dbg in (0, 1, 2, 4, 6, 8, 16, 1 | 8, 2 | 4 | 8, 1 | 2 | 4 | 8, 1 | 2 | 4 | 8 | 16, 2 | 4 | 8 | 16, 1 | 8 | 16):
+        for dbg in ([int(a) for a in sys.argv[1:]] or (0, 1, 2, 4, 6, 8, 16, 1 | 8, 2 | 4 | 8, 1 | 2 | 4 | 8, 1 | 2 | 4 | 8 | 16, 2 | 4 | 8 | 16, 1 | 8 | 16)):
             lib.mmvae_gemm_tc_set_mode(mode | (dbg << 8))
             t = bench(lambda: _lib.check(lib.mmvae_convt_tc_fwd(p(x), p(wf), p(b), p(y), N, H, H, Cin, Cout, 1, st())))
             print(f"H={H} Cin={Cin} Cout={Cout} passes={3 if mode == 0 else 1} dbg={dbg:2d} "
