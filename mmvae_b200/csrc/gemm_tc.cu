@@ -37,13 +37,24 @@ template <int BN> struct TcCfg {
     static constexpr int TMEM_COLS = 4 * BN;          // {big, small} x 2 accumulator buffers
 };
 
-// lo part of the 3xTF32 split: residual of the hardware's truncation of `a`, itself rounded to tf32 (round-to-nearest)
-// so that the tensor core's own truncation of lo changes nothing and the split error is unbiased.
+// lo part of the 3xTF32 split: residual of the hardware's truncation of `a`, rounded to nearest at tf32 precision by
+// adding half a tf32 ulp to the bit pattern (the tensor core truncates the low 13 bits itself), so that the split error is
+// unbiased.  Three full-rate instructions per element; cvt.rna.tf32.f32 compiles to six (inf/nan guards) and the
+// converter warps share issue slots with the MMA issuer.
 __device__ __forceinline__ float tf32_lo(float a) {
     const float r = a - __uint_as_float(__float_as_uint(a) & 0xFFFFE000u);
-    uint32_t o;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(o) : "f"(r));
-    return __uint_as_float(o);
+    return __uint_as_float(__float_as_uint(r) + 0x1000u);
+}
+// lo tile <- split(hi tile), n4 float4 per thread of a 128-thread group, through shared-space (not generic) accesses
+__device__ __forceinline__ void tf32_split_tile(uint32_t hi_addr, uint32_t lo_addr, int tq, int n4) {
+#pragma unroll 4
+    for (int j = 0; j < n4; ++j) {
+        float4 v;
+        const uint32_t off = (uint32_t)(tq + j * 128) * 16u;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(hi_addr + off));
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(lo_addr + off), "f"(tf32_lo(v.x)), "f"(tf32_lo(v.y)),
+                     "f"(tf32_lo(v.z)), "f"(tf32_lo(v.w)) : "memory");
+    }
 }
 
 __device__ __forceinline__ float apply_act_tc(float v, int act) {
@@ -223,21 +234,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 for (int i = 0; i < tl.nk; ++i, ++it) {
                     const int s = it % STAGES, ph = (it / STAGES) & 1;
                     mbar_wait(full + s, ph);
-                    uint8_t* st = smem + s * Cfg::STAGE;
-                    const float4* a_hi = (const float4*)st;
-                    float4* a_lo = (float4*)(st + TC_A_TILE);
-                    const float4* b_hi = (const float4*)(st + 2 * TC_A_TILE);
-                    float4* b_lo = (float4*)(st + 2 * TC_A_TILE + Cfg::B_TILE);
-#pragma unroll
-                    for (int j = 0; j < TC_A_TILE / 16 / 128; ++j) {
-                        const float4 v = a_hi[tq + j * 128];
-                        a_lo[tq + j * 128] = make_float4(tf32_lo(v.x), tf32_lo(v.y), tf32_lo(v.z), tf32_lo(v.w));
-                    }
-#pragma unroll
-                    for (int j = 0; j < Cfg::B_TILE / 16 / 128; ++j) {
-                        const float4 v = b_hi[tq + j * 128];
-                        b_lo[tq + j * 128] = make_float4(tf32_lo(v.x), tf32_lo(v.y), tf32_lo(v.z), tf32_lo(v.w));
-                    }
+                    const uint32_t st = smem_u32(smem) + s * Cfg::STAGE;
+                    tf32_split_tile(st, st + TC_A_TILE, tq, TC_A_TILE / 16 / 128);
+                    tf32_split_tile(st + 2 * TC_A_TILE, st + 2 * TC_A_TILE + Cfg::B_TILE, tq, Cfg::B_TILE / 16 / 128);
                     fence_proxy_async_smem();          // generic-proxy writes -> visible to the tensor core's reads
                     __syncwarp();
                     if (lane == 0) mbar_arrive(conv + s);
@@ -678,19 +677,10 @@ convt_fwd9_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     const int nb4 = F9_NCLS[sh] * Cfg::CLS / 16 / 128;                 // float4 per thread in the weights
                     mbar_wait(full + tk, ph);
                     if (dbg & 8) { __syncwarp(); if (lane == 0) mbar_arrive(conv + tk); continue; }
-                    const float4* a_hi = (const float4*)(smem + (it % SA) * Cfg::A_SLOT);
-                    float4* a_lo = (float4*)(smem + (it % SA) * Cfg::A_SLOT + TC_A_TILE);
-                    const float4* b_hi = (const float4*)(bring + (F9_ROW[sh] & 7) * Cfg::CLS);
-                    float4* b_lo = (float4*)(bring + Cfg::B_HALF + (F9_ROW[sh] & 7) * Cfg::CLS);
-#pragma unroll
-                    for (int j = 0; j < TC_A_TILE / 16 / 128; ++j) {
-                        const float4 v = a_hi[tq + j * 128];
-                        a_lo[tq + j * 128] = make_float4(tf32_lo(v.x), tf32_lo(v.y), tf32_lo(v.z), tf32_lo(v.w));
-                    }
-                    for (int j = 0; j < nb4; ++j) {
-                        const float4 v = b_hi[tq + j * 128];
-                        b_lo[tq + j * 128] = make_float4(tf32_lo(v.x), tf32_lo(v.y), tf32_lo(v.z), tf32_lo(v.w));
-                    }
+                    const uint32_t a_hi = smem_u32(smem) + (it % SA) * Cfg::A_SLOT;
+                    const uint32_t b_hi = smem_u32(bring) + (F9_ROW[sh] & 7) * Cfg::CLS;
+                    tf32_split_tile(a_hi, a_hi + TC_A_TILE, tq, TC_A_TILE / 16 / 128);
+                    tf32_split_tile(b_hi, b_hi + Cfg::B_HALF, tq, nb4);
                     fence_proxy_async_smem();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(conv + tk);
@@ -699,6 +689,11 @@ convt_fwd9_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
     } else {
         const int lane_base = (warp & 3) * 32;
+        // the bias stays in registers for the whole kernel: reloading 32 values per 32-column chunk cost 30-90 us of
+        // issue slots that the MMA issuer and the converter warps share with these warps
+        float bv[COUT];
+#pragma unroll
+        for (int j = 0; j < COUT; ++j) bv[j] = bias ? __ldg(bias + j) : 0.f;
         int ti = 0;
         for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++ti) {
             const int acc = ti % NACC, use = ti / NACC;
@@ -707,7 +702,8 @@ convt_fwd9_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             const int row = t * TC_BM + lane_base + lane;
             const int n_img = row / HW, rem = row - n_img * HW, ii = rem / W, jj = rem - ii * W;
             const uint32_t tb = tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)(acc * 8 * COUT);
-#pragma unroll 1
+            float* const y00 = Y + ((long)(n_img * 2 * H + 2 * ii) * (2 * W) + 2 * jj) * COUT;     // class (0,0) position
+#pragma unroll
             for (int c = 0; c < 4 * COUT; c += 32) {
                 float v[32];
                 tmem_ld_32x32(tb + (uint32_t)c, v);
@@ -724,14 +720,14 @@ convt_fwd9_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                 }
                 if (row < M && !(dbg & 1)) {
                     // each thread owns one output row of 32 contiguous floats (one full 128-byte line): direct stores
+                    constexpr int kPy[4] = {0, 0, 1, 1}, kPx[4] = {0, 1, 1, 0};       // Gray slot -> (py, px)
                     const int slot = c / COUT, cc = c - slot * COUT;
-                    const long orow = ((long)(n_img * 2 * H + 2 * ii + F9_PY[slot]) * (2 * W) + 2 * jj + F9_PX[slot]);
-                    float* p = Y + orow * COUT + cc;
+                    float* p = y00 + ((long)kPy[slot] * (2 * W) + kPx[slot]) * COUT + cc;
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = apply_act_tc(v[j] + (bias ? __ldg(bias + cc + j) : 0.f), act);
+                    for (int j = 0; j < 32; ++j) v[j] = apply_act_tc(v[j] + bv[cc + j], act);
 #pragma unroll
                     for (int j = 0; j < 32; j += 4)
-                        *reinterpret_cast<float4*>(p + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                        __stcs(reinterpret_cast<float4*>(p + j), make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]));
                 }
             }
         }
