@@ -99,9 +99,10 @@ template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const float* __restrict__ bias, float* __restrict__ C, float* __restrict__ ws, int M, int N, int K,
-               int act, int kb_per_split, int splits, int c_transposed, int passes, const TcConv cv,
+               int act, int kb_per_split, int splits, int c_transposed, int passes_dbg, const TcConv cv,
                const float* __restrict__ mask) {
     using Cfg = TcCfg<BN>;
+    const int passes = passes_dbg & 0xff, dbg = passes_dbg >> 8;      // dbg: ablation bits of tools/f9_ablate.py, 0 in production
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -142,6 +143,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             for (int i = 0; i < tl.nk; ++i) {
                 mbar_wait(empty + s, ph ^ 1);
                 const uint32_t a_hi = smem_base + s * Cfg::STAGE, b_hi = a_hi + 2 * TC_A_TILE;
+                if (dbg & 6) {                                  // ablation: no operand traffic
+                    mbar_arrive_elect(full + s);
+                    if (++s == STAGES) { s = 0; ph ^= 1; }
+                    continue;
+                }
                 mbar_arrive_expect_tx_elect(full + s, TC_A_TILE + Cfg::B_TILE);
                 const int kbi = tl.kb_begin + i;
                 const int k0 = kbi * TC_BK;
@@ -212,6 +218,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 const uint64_t dbh = db0 + (uint64_t)(s * (Cfg::STAGE >> 4)), dbl = dbh + (Cfg::B_TILE >> 4);
 #pragma unroll
                 for (int kk = 0; kk < TC_BK / 8; ++kk) {
+                    if ((dbg & 16) && (i | kk) != 0) break;
                     const uint32_t first = (i | kk) != 0;
                     if (passes == 3) {
                         umma_tf32_elect(d_small, dal + kk * a_step, dbh + kk * b_step, idesc, first);
@@ -234,6 +241,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 for (int i = 0; i < tl.nk; ++i, ++it) {
                     const int s = it % STAGES, ph = (it / STAGES) & 1;
                     mbar_wait(full + s, ph);
+                    if (dbg & 8) { __syncwarp(); if (lane == 0) mbar_arrive(conv + s); continue; }
                     const uint32_t st = smem_u32(smem) + s * Cfg::STAGE;
                     tf32_split_tile(st, st + TC_A_TILE, tq, TC_A_TILE / 16 / 128);
                     tf32_split_tile(st + 2 * TC_A_TILE, st + 2 * TC_A_TILE + Cfg::B_TILE, tq, Cfg::B_TILE / 16 / 128);
@@ -246,7 +254,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     } else {
         // ===== epilogue (warps 6..9): TMEM -> registers -> global, overlapped with the next tile's MMAs =====
         const int lane_base = (warp & 3) * 32;         // a warp may only touch TMEM lanes 32*(warp%4) .. +31
+        constexpr int NCH = BN / 32;
+        const int col = (lane & 7) * 4, rsub = lane >> 3;       // this lane's place in the transposed (row-coalesced) block
+        // fused ReLU backward of the layer below (mode 2): the mask values (the layer's input, streamed from HBM) are
+        // fetched one 32-column chunk ahead of their use -- loaded at the point of use their latency made dgrad
+        // epilogue-bound (L3 dgrad 424 us with, 263 us without the mask)
+        const bool use_mask = mask && splits == 1 && (N & 3) == 0 && !(dbg & 32);
+        float4 mk[2][8];
+        auto load_mask = [&](const TcTile& tl, int c, float4* dst) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const int grow = tl.m0 + lane_base + 4 * k + rsub, n = tl.n0 + c + col;
+                dst[k] = (grow < M && n + 4 <= N) ? __ldg(reinterpret_cast<const float4*>(mask + (long)grow * N + n))
+                                                  : make_float4(1.f, 1.f, 1.f, 1.f);
+            }
+        };
         int ti = 0;
+        if (use_mask && blockIdx.x < total) load_mask(tc_tile(blockIdx.x, tiles_m, tiles_n, BN, nkb, kb_per_split), 0, mk[0]);
         for (int t = blockIdx.x; t < total; t += gridDim.x, ++ti) {
             const TcTile tl = tc_tile(t, tiles_m, tiles_n, BN, nkb, kb_per_split);
             const int acc = ti & 1;
@@ -255,8 +279,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             const int row = tl.m0 + lane_base + lane;
             float* out = (splits > 1) ? ws + (long)tl.z * M * N : C;
             const uint32_t tb = tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)(acc * 2 * BN);
-#pragma unroll 1
-            for (int c = 0; c < BN; c += 32) {
+#pragma unroll
+            for (int ci = 0; ci < NCH; ++ci) {
+                const int c = ci * 32;
+                // mask buffer parity: chunks alternate; with one chunk per tile (BN = 32) the buffer is reloaded in place
+                constexpr int kOne = (NCH == 1);
+                const int cur = kOne ? 0 : (ci & 1), nxt = kOne ? 0 : ((ci + 1) & 1);
+                if (use_mask && !kOne) {
+                    if (ci + 1 < NCH) load_mask(tl, c + 32, mk[nxt]);
+                    else if (t + (int)gridDim.x < total)
+                        load_mask(tc_tile(t + gridDim.x, tiles_m, tiles_n, BN, nkb, kb_per_split), 0, mk[nxt]);
+                }
                 float v[32];
                 tmem_ld_32x32(tb + (uint32_t)c, v);
                 if (passes == 3) {
@@ -265,11 +298,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] += u[j];
                 }
-                if (c + 32 >= BN) {                    // last TMEM read of this buffer: hand it back to the issuer
+                if (ci + 1 == NCH) {                    // last TMEM read of this buffer: hand it back to the issuer
                     tc_fence_before_sync();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(tempty + acc);
                 }
+                if (dbg & 1) continue;
                 if (c_transposed) {
                     if (row < M) {
 #pragma unroll
@@ -283,7 +317,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 // bias + activation by column (the thread holds one row), then transpose the warp's 32 x 32 block through
                 // shared memory so that global traffic is row-coalesced: each 128-bit access instruction then covers
                 // 4 rows x 128 contiguous bytes (whole 32-byte sectors) instead of 32 rows x 16 bytes
-                if (splits == 1) {
+                if (splits == 1 && (bias || act)) {
                     const int nb = (cv.mode == 1) ? c : tl.n0 + c;
 #pragma unroll
                     for (int j = 0; j < 32; ++j)
@@ -294,10 +328,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 for (int j = 0; j < 32; j += 4)
                     *reinterpret_cast<float4*>(pad + lane * TC_EPI_PITCH + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
                 __syncwarp();
-                const int col = (lane & 7) * 4;
+                if (use_mask && kOne) load_mask(tl, c, mk[0]);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
-                    const int r = 4 * k + (lane >> 3), grow = tl.m0 + lane_base + r;
+                    const int r = 4 * k + rsub, grow = tl.m0 + lane_base + r;
                     if (grow >= M) continue;
                     float4 o = *reinterpret_cast<const float4*>(pad + r * TC_EPI_PITCH + col);
                     if (cv.mode == 1) {
@@ -311,12 +345,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     const int n = tl.n0 + c + col;
                     float* p = out + (long)grow * N + n;
                     if ((N & 3) == 0 && n + 4 <= N) {
-                        if (mask && splits == 1) {             // fused ReLU backward of the layer below (mode 2)
-                            const float4 m = __ldg(reinterpret_cast<const float4*>(mask + (long)grow * N + n));
+                        if (use_mask) {
+                            const float4 m = mk[cur][k];
                             o.x = m.x > 0.f ? o.x : 0.f; o.y = m.y > 0.f ? o.y : 0.f;
                             o.z = m.z > 0.f ? o.z : 0.f; o.w = m.w > 0.f ? o.w : 0.f;
                         }
-                        *reinterpret_cast<float4*>(p) = o;
+                        if (!(dbg & 64)) *reinterpret_cast<float4*>(p) = o;
                     } else {
                         const float ov[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll
@@ -433,7 +467,7 @@ static int tc_launch(const CUtensorMap& ta, const CUtensorMap& tb, const float* 
     const long total = (long)((N + BN - 1) / BN) * ((M + TC_BM - 1) / TC_BM) * p.S;
     const int grid = (int)(total < MMVAE_NUM_SMS ? total : MMVAE_NUM_SMS);      // persistent: one CTA per SM
     kern<<<grid, TC_THREADS, TcCfg<BN>::SMEM, st>>>(ta, tb, bias, C, ws, M, N, K, act, p.kb_per, p.S, transposed,
-                                                    g_tc_mode == 1 ? 1 : 3, cv, mask);
+                                                    (g_tc_mode == 1 ? 1 : 3) | (g_tc_dbg << 8), cv, mask);
     MMVAE_LAUNCH_CHECK("gemm_tc");
     return 0;
 }
