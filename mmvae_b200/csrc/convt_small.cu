@@ -10,6 +10,7 @@
 //          bias gradient folded in.
 // Output pixel (2i+py, 2j+px) receives taps ky in {1,3} (py=0) / {0,2} (py=1) from input rows i, i-1 / i+1, i.
 #include "common.cuh"
+#include "sm100_ptx.cuh"
 
 #define CS_THREADS 256
 #define CS_PAD 4                      // floats of padding per input pixel row in smem: 128-bit loads stay conflict-free
@@ -130,56 +131,108 @@ __device__ __forceinline__ void cs_stage_g(float* gs, const float* __restrict__ 
 
 // -------------------------------------------------------------------------------------------------------- dgrad
 // gx[n,i,j,ci] = sum_{ky,kx,co} g[n,co,2i-1+ky,2j-1+kx] * w[ci,co,ky,kx]   (* relu'(x_mask))
-// smem: gs[COUT][2H+2][2W+2], ws[CIN][COUT*16]
-template <int COUT, int CIN>
-__global__ void __launch_bounds__(CS_THREADS)
+// Persistent, one CTA of 512 threads per SM.  Each lane owns TWO input channels and keeps their 2 x COUT x 16 weights
+// in registers; the two half-warps work on two horizontally adjacent pixels, so per pixel the COUT*16 gradient values
+// come from COUT*4 broadcast 128-bit shared loads and feed 2*COUT*16 FFMAs per lane, and the mask read / gx write of
+// one pixel is one contiguous 128-byte row segment per half-warp.  The inputs of image n+1 (g, y for the fused
+// activation derivative, the ReLU mask source x) are fetched by bulk asynchronous copies into a second set of
+// shared-memory buffers while image n is computed: with the loads issued at their point of use (first and second
+// versions) every warp sat out a DRAM round trip per pixel and the FMA pipe was 27 % busy.
+// The staged gradient image is kept twice, the second copy shifted by two floats, so that the 4-float window of both
+// even and odd columns starts on a 16-byte boundary.
+#define CSD_THREADS 512
+#define CSD_PITCH(W2) (((W2) + 2 + 2 + 3) & ~3)
+__host__ __device__ inline size_t csd_smem_bytes(int H, int W, int Cin, int Cout, bool has_y, bool has_mask) {
+    const size_t gs = 2 * (size_t)Cout * (2 * H + 2) * CSD_PITCH(2 * W) * 4;
+    const size_t raw = (size_t)Cout * 4 * H * W * 4;
+    return gs + 2 * raw * (has_y ? 2 : 1) + (has_mask ? 2 * (size_t)H * W * Cin * 4 : 0) + 64;
+}
+// HT, WT > 0: compile-time image size (every shared-memory offset an immediate, divisions become shifts); 0: run time
+template <int COUT, int CIN, int HT, int WT>
+__global__ void __launch_bounds__(CSD_THREADS, 1)
 convt_small_dgrad_kernel(const float* __restrict__ g, const float* __restrict__ yact, const float* __restrict__ w,
-                         const float* __restrict__ x_mask, float* __restrict__ gx, int H, int W, int act) {
+                         const float* __restrict__ x_mask, float* __restrict__ gx, int N, int Hrt, int Wrt, int act) {
+    static_assert(CIN == 32, "one lane per channel pair");
     extern __shared__ float4 smem4[];
+    const int H = HT ? HT : Hrt, W = WT ? WT : Wrt;
+    const int H2 = 2 * H, W2 = 2 * W, pitch = CSD_PITCH(W2), plane = (H2 + 2) * pitch, HW = H * W;
+    const int nraw = COUT * H2 * W2;                                 // floats of one image of g (and of y)
     float* gs = (float*)smem4;
-    const int H2 = 2 * H, W2 = 2 * W, gw = W2 + 2, plane = (H2 + 2) * gw;
-    float* ws = gs + ((COUT * plane + 3) & ~3);
-    const int n = blockIdx.x;
-    cs_stage_g<COUT>(gs, g, yact, n, H2, W2, act, nullptr);
-    for (int i = threadIdx.x; i < CIN * COUT * 16; i += CS_THREADS) ws[i] = w[i];      // torch layout is already [ci][co][tap]
-    __syncthreads();
-    for (int p = threadIdx.x; p < H * W; p += CS_THREADS) {
-        const int i = p / W, j = p - i * W;
-        float pt[COUT][16];
+    float* graw = gs + 2 * COUT * plane;                              // [2][nraw]
+    float* yraw = graw + 2 * nraw;                                    // [2][nraw] when yact
+    float* mraw = yraw + (yact ? 2 * nraw : 0);                       // [2][HW*CIN] when x_mask
+    uint64_t* full = (uint64_t*)(mraw + (x_mask ? 2 * HW * CIN : 0)); // [2]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, half = lane >> 4, cp = lane & 15;
+    const uint32_t tx_bytes = (uint32_t)(nraw * 4 * (yact ? 2 : 1) + (x_mask ? HW * CIN * 4 : 0));
+    auto issue = [&](int n, int buf) {                                // one thread
+        mbar_arrive_expect_tx(full + buf, tx_bytes);
+        bulk_load_1d(graw + buf * nraw, g + (long)n * nraw, nraw * 4, full + buf);
+        if (yact) bulk_load_1d(yraw + buf * nraw, yact + (long)n * nraw, nraw * 4, full + buf);
+        if (x_mask) bulk_load_1d(mraw + buf * HW * CIN, x_mask + (long)n * HW * CIN, HW * CIN * 4, full + buf);
+    };
+    if (threadIdx.x == 0) {
+        mbar_init(full, 1);
+        mbar_init(full + 1, 1);
+        mbar_fence_init();
+        if ((int)blockIdx.x < N) issue(blockIdx.x, 0);
+    }
+    // weights as (kx, kx+1) pairs: the inner product runs on packed FFMA2 (two fp32 FMAs per issue slot; scalar FFMA
+    // issues every other cycle per scheduler on sm_100, so FFMA2 is what reaches the fp32 peak)
+    float2 wr[2][COUT * 8];
 #pragma unroll
-        for (int co = 0; co < COUT; ++co)
+    for (int q = 0; q < 2; ++q)
 #pragma unroll
-            for (int ky = 0; ky < 4; ++ky) {
-                const float* r = gs + co * plane + (2 * i + ky) * gw + 2 * j;       // (2i-1+ky)+1, (2j-1)+1
-                const float2 a = *(const float2*)r, b = *(const float2*)(r + 2);
-                pt[co][ky * 4 + 0] = a.x; pt[co][ky * 4 + 1] = a.y; pt[co][ky * 4 + 2] = b.x; pt[co][ky * 4 + 3] = b.y;
+        for (int t = 0; t < COUT * 4; ++t) {
+            const float4 v = __ldg((const float4*)(w + (long)(2 * cp + q) * COUT * 16) + t);      // [ci][co][tap]
+            wr[q][2 * t] = make_float2(v.x, v.y);
+            wr[q][2 * t + 1] = make_float2(v.z, v.w);
+        }
+    for (int i = threadIdx.x; i < 2 * COUT * plane; i += CSD_THREADS) gs[i] = 0.f;      // the border stays zero for good
+    // copy `half`: column xx of the zero-bordered image (x = xx - 1) stored at xx + 2*half
+    const float* gmine = gs + half * COUT * plane + 2 * half;
+    int it = 0;
+    for (int n = blockIdx.x; n < N; n += gridDim.x, ++it) {
+        const int buf = it & 1;
+        __syncthreads();                          // image n-1 fully consumed: its buffers (the other set) and gs are free
+        if (threadIdx.x == 0 && n + (int)gridDim.x < N) issue(n + gridDim.x, buf ^ 1);
+        mbar_wait(full + buf, (it >> 1) & 1);
+        const float4* g4 = (const float4*)(graw + buf * nraw);
+        const float4* y4 = (const float4*)(yraw + buf * nraw);
+        for (int i = threadIdx.x; i < nraw / 4; i += CSD_THREADS) {
+            const int e = 4 * i, xx = e % W2, yy = (e / W2) % H2, co = e / (W2 * H2);
+            float4 v = g4[i];
+            if (yact) {
+                const float4 yv = y4[i];
+                v.x *= cs_dact(yv.x, act); v.y *= cs_dact(yv.y, act); v.z *= cs_dact(yv.z, act); v.w *= cs_dact(yv.w, act);
             }
-        const long orow = ((long)n * H * W + p) * CIN;
-#pragma unroll 1
-        for (int c = 0; c < CIN; c += 4) {
-            float o[4];
+            float* r0 = gs + co * plane + (yy + 1) * pitch + xx + 1;
+            r0[0] = v.x; r0[1] = v.y; r0[2] = v.z; r0[3] = v.w;
+            float* r1 = r0 + COUT * plane + 2;
+            r1[0] = v.x; r1[1] = v.y; r1[2] = v.z; r1[3] = v.w;
+        }
+        __syncthreads();
+        const float* mk = mraw + buf * HW * CIN;
+        for (int pp = warp; pp < HW / 2; pp += CSD_THREADS / 32) {
+            const int p = 2 * pp + half, i = p / W, j = p - i * W;   // W even: the pair shares a row and j's parity == half
+            float2 s0 = make_float2(0.f, 0.f), s1 = s0, t0 = s0, t1 = s0;      // two packed chains per channel
+            const float* gp = gmine + (2 * i) * pitch + 2 * j;        // row 2i-1+ky -> bordered row 2i+ky; column 2j-1 -> 2j
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const float4* wr = (const float4*)(ws + (c + q) * COUT * 16);
-                float s0 = 0.f, s1 = 0.f;                     // two chains: ILP without reassociating beyond fp32 noise
+            for (int co = 0; co < COUT; ++co)
 #pragma unroll
-                for (int co = 0; co < COUT; ++co)
-#pragma unroll
-                    for (int t = 0; t < 4; ++t) {
-                        const float4 wv = wr[co * 4 + t];
-                        s0 = fmaf(pt[co][4 * t], wv.x, s0);
-                        s1 = fmaf(pt[co][4 * t + 1], wv.y, s1);
-                        s0 = fmaf(pt[co][4 * t + 2], wv.z, s0);
-                        s1 = fmaf(pt[co][4 * t + 3], wv.w, s1);
-                    }
-                o[q] = s0 + s1;
-            }
+                for (int ky = 0; ky < 4; ++ky) {
+                    const float4 v = *(const float4*)(gp + co * plane + ky * pitch);
+                    const int t = co * 8 + ky * 2;
+                    const float2 va = make_float2(v.x, v.y), vb = make_float2(v.z, v.w);
+                    s0 = __ffma2_rn(va, wr[0][t], s0);     t0 = __ffma2_rn(va, wr[1][t], t0);
+                    s1 = __ffma2_rn(vb, wr[0][t + 1], s1); t1 = __ffma2_rn(vb, wr[1][t + 1], t1);
+                }
+            float2 o = make_float2((s0.x + s0.y) + (s1.x + s1.y), (t0.x + t0.y) + (t1.x + t1.y));
             if (x_mask) {
-                const float4 m = *(const float4*)(x_mask + orow + c);
-                o[0] = m.x > 0.f ? o[0] : 0.f; o[1] = m.y > 0.f ? o[1] : 0.f;
-                o[2] = m.z > 0.f ? o[2] : 0.f; o[3] = m.w > 0.f ? o[3] : 0.f;
+                const float2 m = *(const float2*)(mk + p * CIN + 2 * cp);
+                o.x = m.x > 0.f ? o.x : 0.f;
+                o.y = m.y > 0.f ? o.y : 0.f;
             }
-            *(float4*)(gx + orow + c) = make_float4(o[0], o[1], o[2], o[3]);
+            *(float2*)(gx + ((long)n * HW + p) * CIN + 2 * cp) = o;
         }
     }
 }
@@ -279,10 +332,10 @@ __global__ void convt_small_wgrad_reduce(const float* __restrict__ part, float* 
 static int cs_wgrad_ctas(int N) { return N < 4 * MMVAE_NUM_SMS ? N : 4 * MMVAE_NUM_SMS; }
 
 extern "C" int mmvae_convt_small_supported(int H, int W, int Cin, int Cout) {
-    if (Cout < 1 || Cout > 4 || Cin != 32 || H < 1 || W < 1) return 0;      // Cin is a template constant (fBase = 32)
+    if (Cout < 1 || Cout > 4 || Cin != 32 || H < 1 || W < 2 || (W & 1)) return 0;   // Cin is a template constant (fBase = 32)
     const size_t fwd = ((size_t)H * W * (Cin + CS_PAD) + 16 * (size_t)Cout * Cin + 4) * 4;
     const size_t gsz = (((size_t)Cout * (2 * H + 2) * (2 * W + 2) + 3) & ~(size_t)3) * 4;
-    const size_t dg = gsz + (size_t)Cin * Cout * 16 * 4;
+    const size_t dg = csd_smem_bytes(H, W, Cin, Cout, true, true);
     const size_t red = (size_t)(CSW_THREADS / 32) * Cin * Cout * 16 * 4 + 16;
     size_t wg = gsz + (size_t)H * W * (Cin + CS_PAD) * 4;
     if (red > wg) wg = red;
@@ -317,9 +370,16 @@ static int cs_fwd(const float* x, const float* w, const float* bias, float* y, i
 template <int CO>
 static int cs_dgrad(const float* g, const float* y_act, const float* w, const float* x_mask, float* gx, int N, int H,
                     int W, int Cin, int act, size_t smem, cudaStream_t st) {
-    const int rc = cs_smem_attr(convt_small_dgrad_kernel<CO, 32>, smem, "convt_small_dgrad");
+    const int ctas = N < MMVAE_NUM_SMS ? N : MMVAE_NUM_SMS;
+    if (H == 16 && W == 16) {
+        const int rc = cs_smem_attr(convt_small_dgrad_kernel<CO, 32, 16, 16>, smem, "convt_small_dgrad");
+        if (rc) return rc;
+        convt_small_dgrad_kernel<CO, 32, 16, 16><<<ctas, CSD_THREADS, smem, st>>>(g, y_act, w, x_mask, gx, N, H, W, act);
+        return 0;
+    }
+    const int rc = cs_smem_attr(convt_small_dgrad_kernel<CO, 32, 0, 0>, smem, "convt_small_dgrad");
     if (rc) return rc;
-    convt_small_dgrad_kernel<CO, 32><<<N, CS_THREADS, smem, st>>>(g, y_act, w, x_mask, gx, H, W, act);
+    convt_small_dgrad_kernel<CO, 32, 0, 0><<<ctas, CSD_THREADS, smem, st>>>(g, y_act, w, x_mask, gx, N, H, W, act);
     return 0;
 }
 template <int CO>
@@ -346,8 +406,8 @@ extern "C" int mmvae_convt_small_dgrad(const float* g, const float* y_act, const
                                        float* gx, int N, int H, int W, int Cin, int Cout, int act, void* stream) {
     MMVAE_REQUIRE(g && w && gx && N > 0, "convt_small_dgrad: bad arguments");
     MMVAE_REQUIRE(mmvae_convt_small_supported(H, W, Cin, Cout), "convt_small_dgrad: unsupported shape");
-    const size_t gsz = (((size_t)Cout * (2 * H + 2) * (2 * W + 2) + 3) & ~(size_t)3) * 4;
-    const size_t smem = gsz + (size_t)Cin * Cout * 16 * 4;
+    MMVAE_REQUIRE((W & 1) == 0 && ((H * W) & 1) == 0 && ((4L * H * W * Cout) % 4) == 0, "convt_small_dgrad: W must be even");
+    const size_t smem = csd_smem_bytes(H, W, Cin, Cout, y_act != nullptr, x_mask != nullptr);
     const int rc = CS_SWITCH(Cout, cs_dgrad, g, y_act, w, x_mask, gx, N, H, W, Cin, act, smem, (cudaStream_t)stream);
     if (rc) return rc;
     MMVAE_LAUNCH_CHECK("convt_small_dgrad");

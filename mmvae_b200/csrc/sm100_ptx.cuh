@@ -55,6 +55,14 @@ __device__ __forceinline__ void tma_load_4d(void* smem_dst, const void* tmap, ui
         : "memory");
 }
 
+// 1-D bulk copy global -> shared (bytes and both addresses multiples of 16), completion counted on an mbarrier
+__device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
 // ---- warp-uniform issue ------------------------------------------------------------------------------------------
 // The *_elect forms are called by ALL 32 converged lanes of a warp with warp-uniform arguments; one elected lane (always
 // the same one for a full mask) executes the instruction.  Measured (tools/umma_rate.cu): issuing tcgen05.mma from inside

@@ -279,6 +279,16 @@ class ConvT2dAct(torch.autograd.Function):
                        mask_input_grad, "small")
             return y
         wp = permute_weight(w)                                  # [Cin, k*k*Cout]
+        if H == 1 and W == 1 and stride == 1 and pad == 0 and not nchw_out:
+            # a 1x1 input makes the layer a linear map onto the k x k x Cout NHWC block (col2im is the identity):
+            # one GEMM with the bias (tiled over the k*k taps) and the activation in its epilogue
+            bt = b.repeat(k * k) if b is not None else None
+            y = gemm(x2d, wp, bt, N, k * k * Cout, Cin, True, False, act=act)
+            keep_y = (ACT[act] != C["MMVAE_ACT_NONE"]) and not preact_grad
+            ctx.save_for_backward(x2d, wp, y if keep_y else None)
+            ctx.cfg = (N, Cin, H, W, Cout, k, stride, pad, act, tuple(w.shape), b is not None, preact_grad,
+                       mask_input_grad, "linear")
+            return y.view(N, k, k, Cout).permute(0, 3, 1, 2)
         col = gemm(x2d, wp, None, N * H * W, k * k * Cout, Cin, True, False)
         y = col2im(col, b, N, Cout, H, W, k, stride, pad, act, nchw_out=nchw_out)
         keep_y = (ACT[act] != C["MMVAE_ACT_NONE"]) and not preact_grad
@@ -332,6 +342,22 @@ class ConvT2dAct(torch.autograd.Function):
                 gb = torch.empty(Cout, device=g.device, dtype=torch.float32) if has_bias else None
                 _call("mmvae_convt_small_wgrad", _p(x2d), _p(g), _p(y), _p(gw), _p(gb), _p(ws), N, H, W, Cin, Cout,
                       ACT[act], _stream(), work=("byte", 4.0 * (g.numel() + x2d.numel())))
+            return gx, gw, gb, None, None, None, None, None, None
+        if path == "linear":
+            Kc = k * k * Cout
+            g = _as_rows(_dev(gy, "grad")).view(N, Kc)            # NHWC rows of the k x k x Cout block
+            if y is not None:
+                g = act_bwd(g, y.view(N, Kc), act)
+            gx = gw = gb = None
+            if ctx.needs_input_grad[0]:
+                gx2d = gemm(g, wp, None, N, Cin, Kc, True, True)
+                if mask_in:
+                    gx2d = act_bwd(gx2d, x2d, "relu")
+                gx = gx2d.view(N, Cin, 1, 1)
+            if ctx.needs_input_grad[1]:
+                gw = unpermute_weight(gemm(x2d, g, None, Cin, Kc, N, False, False), wshape)
+            if has_bias and ctx.needs_input_grad[2]:
+                gb = colsum(g).view(k * k, Cout).sum(0)
             return gx, gw, gb, None, None, None, None, None, None
         gy = _dense_image(gy)
         if not preact_grad and y is not None:

@@ -51,3 +51,21 @@ for (H, Cin, Cout) in ((4, 128, 64), (8, 64, 32)):
               f"fwd {t_f:7.1f} us ({flop / t_f / 1e6:6.1f} TF)  dgrad {t_d:7.1f} us ({flop / t_d / 1e6:6.1f} TF)  "
               f"wgrad {t_w:7.1f} us ({flop / t_w / 1e6:6.1f} TF)", flush=True)
 lib.mmvae_gemm_tc_set_mode(0)
+
+# last decoder layer (Cin=32 -> Cout=3, 16x16 -> 32x32, Sigmoid, NCHW out): the direct SIMT kernels
+H, Cin, Cout = 16, 32, 3
+x = torch.randn(N, H, H, Cin, device="cuda").relu_()
+w = torch.randn(Cin, Cout, 4, 4, device="cuda") * 0.1
+b = torch.randn(Cout, device="cuda")
+y = torch.empty(N, Cout, 2 * H, 2 * H, device="cuda")
+g = torch.randn(N, Cout, 2 * H, 2 * H, device="cuda")
+gx = torch.empty_like(x)
+gw = torch.empty_like(w)
+gb = torch.empty_like(b)
+ws = torch.empty(lib.mmvae_convt_small_wgrad_workspace_bytes(N, Cin, Cout) // 4, device="cuda")
+t_f = bench(lambda: _lib.check(lib.mmvae_convt_small_fwd(p(x), p(w), p(b), p(y), N, H, H, Cin, Cout, 2, st())))
+t_d = bench(lambda: _lib.check(lib.mmvae_convt_small_dgrad(p(g), p(y), p(w), p(x), p(gx), N, H, H, Cin, Cout, 2, st())))
+t_w = bench(lambda: _lib.check(lib.mmvae_convt_small_wgrad(p(x), p(g), p(y), p(gw), p(gb), p(ws), N, H, H, Cin, Cout, 2, st())))
+flop = 2.0 * N * H * H * 16 * Cin * Cout
+print(f"L4 direct (H=16 Cin=32 Cout=3): fwd {t_f:7.1f} us ({flop / t_f / 1e6:5.1f} TF)  dgrad {t_d:7.1f} us ({flop / t_d / 1e6:5.1f} TF)  "
+      f"wgrad {t_w:7.1f} us ({flop / t_w / 1e6:5.1f} TF)", flush=True)
