@@ -239,65 +239,106 @@ convt_small_dgrad_kernel(const float* __restrict__ g, const float* __restrict__ 
 
 // -------------------------------------------------------------------------------------------------------- wgrad
 // gw[ci,co,ky,kx] = sum_{n,i,j} x[n,i,j,ci] * g[n,co,2i-1+ky,2j-1+kx];  gb[co] = sum g.   Cin == 32.
-// persistent CTAs over images; warp = one replica of the 32 x (COUT*16) accumulator tile: lane -> (ci group of 4, ky);
-// thread tile 4 ci x COUT x 4 kx.  part[cta][Cin*COUT*16 + COUT]
-#define CSW_THREADS 128               // 4 warps per CTA: more, smaller CTAs per SM overlap each other's staging phases
-template <int COUT>
-__global__ void __launch_bounds__(CSW_THREADS)
+// Persistent, one CTA of 512 threads per SM, inputs of the next image by bulk async copies (as dgrad above).
+// warp = one replica of the 32 x (COUT*16) accumulator tile, lane -> (ci group of 4, ky), thread tile 4 ci x COUT x 4 kx
+// held as (kx, kx+1) pairs for packed FFMA2; the warps split the pixels.  part[cta][Cin*COUT*16 + COUT]
+#define CSW_THREADS 512
+__host__ __device__ inline size_t csw_smem_bytes(int H, int W, int Cin, int Cout, bool has_y) {
+    const size_t gs = (size_t)Cout * (2 * H + 2) * CSD_PITCH(2 * W) * 4;
+    const size_t raw = (size_t)Cout * 4 * H * W * 4;
+    size_t tot = gs + 2 * raw * (has_y ? 2 : 1) + 2 * (size_t)H * W * Cin * 4 + 64;
+    const size_t red = (size_t)(CSW_THREADS / 32) * Cin * Cout * 16 * 4 + 64;
+    return tot > red ? tot : red;
+}
+template <int COUT, int HT, int WT>
+__global__ void __launch_bounds__(CSW_THREADS, 1)
 convt_small_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ g, const float* __restrict__ yact,
-                         float* __restrict__ part, int N, int H, int W, int act) {
+                         float* __restrict__ part, int N, int Hrt, int Wrt, int act) {
     constexpr int CIN = 32;
     extern __shared__ float4 smem4[];
-    float* gs = (float*)smem4;
-    const int H2 = 2 * H, W2 = 2 * W, gw = W2 + 2, plane = (H2 + 2) * gw, HW = H * W;
-    const int xstride = CIN + CS_PAD;
-    float* xs = gs + ((COUT * plane + 3) & ~3);
+    const int H = HT ? HT : Hrt, W = WT ? WT : Wrt;
+    const int H2 = 2 * H, W2 = 2 * W, pitch = CSD_PITCH(W2), plane = (H2 + 2) * pitch, HW = H * W;
+    const int nraw = COUT * H2 * W2;
+    float* gs = (float*)smem4;                                        // [COUT][H2+2][pitch], zero border
+    float* graw = gs + COUT * plane;                                  // [2][nraw]
+    float* yraw = graw + 2 * nraw;                                    // [2][nraw] when yact
+    float* xraw = yraw + (yact ? 2 * nraw : 0);                       // [2][HW*CIN]
+    uint64_t* full = (uint64_t*)(xraw + 2 * HW * CIN);                // [2]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int cg = lane & 7, ky = lane >> 3;
-    float acc[4][COUT][4];
+    const uint32_t tx_bytes = (uint32_t)(nraw * 4 * (yact ? 2 : 1) + HW * CIN * 4);
+    auto issue = [&](int n, int buf) {                                // one thread
+        mbar_arrive_expect_tx(full + buf, tx_bytes);
+        bulk_load_1d(graw + buf * nraw, g + (long)n * nraw, nraw * 4, full + buf);
+        if (yact) bulk_load_1d(yraw + buf * nraw, yact + (long)n * nraw, nraw * 4, full + buf);
+        bulk_load_1d(xraw + buf * HW * CIN, x + (long)n * HW * CIN, HW * CIN * 4, full + buf);
+    };
+    if (threadIdx.x == 0) {
+        mbar_init(full, 1);
+        mbar_init(full + 1, 1);
+        mbar_fence_init();
+        if ((int)blockIdx.x < N) issue(blockIdx.x, 0);
+    }
+    float2 acc[4][COUT][2];
 #pragma unroll
     for (int a = 0; a < 4; ++a)
 #pragma unroll
-        for (int b = 0; b < COUT; ++b)
-#pragma unroll
-            for (int c = 0; c < 4; ++c) acc[a][b][c] = 0.f;
+        for (int b = 0; b < COUT; ++b) acc[a][b][0] = acc[a][b][1] = make_float2(0.f, 0.f);
     float bacc[COUT];
 #pragma unroll
     for (int c = 0; c < COUT; ++c) bacc[c] = 0.f;
-    for (int n = blockIdx.x; n < N; n += gridDim.x) {
-        __syncthreads();                                             // previous image fully consumed
-        const float4* xg = (const float4*)(x + (long)n * HW * CIN);
-        for (int i = threadIdx.x; i < HW * (CIN / 4); i += CSW_THREADS) {
-            const int p = i >> 3, c = i & 7;
-            *(float4*)(xs + p * xstride + 4 * c) = ld_stream4(xg + i);
+    for (int i = threadIdx.x; i < COUT * plane; i += CSW_THREADS) gs[i] = 0.f;          // the border stays zero for good
+    int it = 0;
+    for (int n = blockIdx.x; n < N; n += gridDim.x, ++it) {
+        const int buf = it & 1;
+        __syncthreads();                          // image n-1 fully consumed: its buffers (the other set) and gs are free
+        if (threadIdx.x == 0 && n + (int)gridDim.x < N) issue(n + gridDim.x, buf ^ 1);
+        mbar_wait(full + buf, (it >> 1) & 1);
+        const float4* g4 = (const float4*)(graw + buf * nraw);
+        const float4* y4 = (const float4*)(yraw + buf * nraw);
+        for (int i = threadIdx.x; i < nraw / 4; i += CSW_THREADS) {
+            const int e = 4 * i, xx = e % W2, yy = (e / W2) % H2, co = e / (W2 * H2);
+            float4 v = g4[i];
+            if (yact) {
+                const float4 yv = y4[i];
+                v.x *= cs_dact(yv.x, act); v.y *= cs_dact(yv.y, act); v.z *= cs_dact(yv.z, act); v.w *= cs_dact(yv.w, act);
+            }
+            float* r0 = gs + co * plane + (yy + 1) * pitch + xx + 1;
+            r0[0] = v.x; r0[1] = v.y; r0[2] = v.z; r0[3] = v.w;
+            const float sv = (v.x + v.y) + (v.z + v.w);
+#pragma unroll
+            for (int c = 0; c < COUT; ++c) bacc[c] += (c == co) ? sv : 0.f;
         }
-        cs_stage_g<COUT, CSW_THREADS>(gs, g, yact, n, H2, W2, act, bacc);         // contains a __syncthreads after zeroing
         __syncthreads();
+        const float* xs = xraw + buf * HW * CIN;
+        const float* gk = gs + ky * pitch;                            // row 2i-1+ky -> bordered row 2i+ky
         for (int p = warp; p < HW; p += CSW_THREADS / 32) {
             const int i = p / W, j = p - i * W;
-            const float4 xv = *(const float4*)(xs + p * xstride + 4 * cg);
+            const float4 xv = *(const float4*)(xs + p * CIN + 4 * cg);
+            const float2 x0 = make_float2(xv.x, xv.x), x1 = make_float2(xv.y, xv.y), x2 = make_float2(xv.z, xv.z),
+                         x3 = make_float2(xv.w, xv.w);
 #pragma unroll
             for (int co = 0; co < COUT; ++co) {
-                const float* r = gs + co * plane + (2 * i + ky) * gw + 2 * j;
+                const float* r = gk + co * plane + (2 * i) * pitch + 2 * j;
                 const float2 a = *(const float2*)r, b = *(const float2*)(r + 2);
-                acc[0][co][0] += xv.x * a.x; acc[0][co][1] += xv.x * a.y; acc[0][co][2] += xv.x * b.x; acc[0][co][3] += xv.x * b.y;
-                acc[1][co][0] += xv.y * a.x; acc[1][co][1] += xv.y * a.y; acc[1][co][2] += xv.y * b.x; acc[1][co][3] += xv.y * b.y;
-                acc[2][co][0] += xv.z * a.x; acc[2][co][1] += xv.z * a.y; acc[2][co][2] += xv.z * b.x; acc[2][co][3] += xv.z * b.y;
-                acc[3][co][0] += xv.w * a.x; acc[3][co][1] += xv.w * a.y; acc[3][co][2] += xv.w * b.x; acc[3][co][3] += xv.w * b.y;
+                acc[0][co][0] = __ffma2_rn(x0, a, acc[0][co][0]); acc[0][co][1] = __ffma2_rn(x0, b, acc[0][co][1]);
+                acc[1][co][0] = __ffma2_rn(x1, a, acc[1][co][0]); acc[1][co][1] = __ffma2_rn(x1, b, acc[1][co][1]);
+                acc[2][co][0] = __ffma2_rn(x2, a, acc[2][co][0]); acc[2][co][1] = __ffma2_rn(x2, b, acc[2][co][1]);
+                acc[3][co][0] = __ffma2_rn(x3, a, acc[3][co][0]); acc[3][co][1] = __ffma2_rn(x3, b, acc[3][co][1]);
             }
         }
     }
     // cross-warp reduction through shared memory (reuses the staging area), fixed order -> deterministic
     __syncthreads();
-    float* red = (float*)smem4;                                      // [8 warps][CIN*COUT*16]
+    float* red = (float*)smem4;                                      // [warps][CIN*COUT*16]
     constexpr int TOT = CIN * COUT * 16;
 #pragma unroll
     for (int a = 0; a < 4; ++a)
 #pragma unroll
-        for (int co = 0; co < COUT; ++co)
-#pragma unroll
-            for (int kx = 0; kx < 4; ++kx)
-                red[warp * TOT + ((4 * cg + a) * COUT + co) * 16 + ky * 4 + kx] = acc[a][co][kx];
+        for (int co = 0; co < COUT; ++co) {
+            float* o = red + warp * TOT + ((4 * cg + a) * COUT + co) * 16 + ky * 4;
+            o[0] = acc[a][co][0].x; o[1] = acc[a][co][0].y; o[2] = acc[a][co][1].x; o[3] = acc[a][co][1].y;
+        }
     __syncthreads();
     float* out = part + (long)blockIdx.x * (TOT + COUT);
     for (int i = threadIdx.x; i < TOT; i += CSW_THREADS) {
@@ -307,7 +348,7 @@ convt_small_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ 
         out[i] = s;
     }
     __syncthreads();
-    float* bred = red;                                               // [COUT][256]
+    float* bred = red;                                               // [COUT][threads]
 #pragma unroll
     for (int c = 0; c < COUT; ++c) bred[c * CSW_THREADS + threadIdx.x] = bacc[c];
     __syncthreads();
@@ -322,23 +363,29 @@ __global__ void convt_small_wgrad_reduce(const float* __restrict__ part, float* 
                                          int P, int tot, int cout) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= tot + cout) return;
-    float s = 0.f;
-    for (int p = 0; p < P; ++p) s += part[(long)p * (tot + cout) + i];
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;                     // fixed association -> deterministic
+    int p = 0;
+    for (; p + 4 <= P; p += 4) {
+        s0 += part[(long)p * (tot + cout) + i];
+        s1 += part[(long)(p + 1) * (tot + cout) + i];
+        s2 += part[(long)(p + 2) * (tot + cout) + i];
+        s3 += part[(long)(p + 3) * (tot + cout) + i];
+    }
+    for (; p < P; ++p) s0 += part[(long)p * (tot + cout) + i];
+    const float s = (s0 + s1) + (s2 + s3);
     if (i < tot) gw[i] = s;
     else if (gb) gb[i - tot] = s;
 }
 
 // ---------------------------------------------------------------------------------------------------- host side
-static int cs_wgrad_ctas(int N) { return N < 4 * MMVAE_NUM_SMS ? N : 4 * MMVAE_NUM_SMS; }
+static int cs_wgrad_ctas(int N) { return N < MMVAE_NUM_SMS ? N : MMVAE_NUM_SMS; }
 
 extern "C" int mmvae_convt_small_supported(int H, int W, int Cin, int Cout) {
     if (Cout < 1 || Cout > 4 || Cin != 32 || H < 1 || W < 2 || (W & 1)) return 0;   // Cin is a template constant (fBase = 32)
     const size_t fwd = ((size_t)H * W * (Cin + CS_PAD) + 16 * (size_t)Cout * Cin + 4) * 4;
     const size_t gsz = (((size_t)Cout * (2 * H + 2) * (2 * W + 2) + 3) & ~(size_t)3) * 4;
     const size_t dg = csd_smem_bytes(H, W, Cin, Cout, true, true);
-    const size_t red = (size_t)(CSW_THREADS / 32) * Cin * Cout * 16 * 4 + 16;
-    size_t wg = gsz + (size_t)H * W * (Cin + CS_PAD) * 4;
-    if (red > wg) wg = red;
+    const size_t wg = csw_smem_bytes(H, W, Cin, Cout, true);
     const size_t lim = 200 * 1024;
     if (fwd > lim || dg > lim) return 0;
     return (Cin == 32 && wg <= lim) ? 2 : 1;       // 2: forward, dgrad and wgrad; 1: forward and dgrad only
@@ -385,9 +432,15 @@ static int cs_dgrad(const float* g, const float* y_act, const float* w, const fl
 template <int CO>
 static int cs_wgrad(const float* x, const float* g, const float* y_act, float* ws, int P, int N, int H, int W, int act,
                     size_t smem, cudaStream_t st) {
-    const int rc = cs_smem_attr(convt_small_wgrad_kernel<CO>, smem, "convt_small_wgrad");
+    if (H == 16 && W == 16) {
+        const int rc = cs_smem_attr(convt_small_wgrad_kernel<CO, 16, 16>, smem, "convt_small_wgrad");
+        if (rc) return rc;
+        convt_small_wgrad_kernel<CO, 16, 16><<<P, CSW_THREADS, smem, st>>>(x, g, y_act, ws, N, H, W, act);
+        return 0;
+    }
+    const int rc = cs_smem_attr(convt_small_wgrad_kernel<CO, 0, 0>, smem, "convt_small_wgrad");
     if (rc) return rc;
-    convt_small_wgrad_kernel<CO><<<P, CSW_THREADS, smem, st>>>(x, g, y_act, ws, N, H, W, act);
+    convt_small_wgrad_kernel<CO, 0, 0><<<P, CSW_THREADS, smem, st>>>(x, g, y_act, ws, N, H, W, act);
     return 0;
 }
 
@@ -418,10 +471,7 @@ extern "C" int mmvae_convt_small_wgrad(const float* x, const float* g, const flo
                                        float* workspace, int N, int H, int W, int Cin, int Cout, int act, void* stream) {
     MMVAE_REQUIRE(x && g && gw && workspace && N > 0, "convt_small_wgrad: bad arguments");
     MMVAE_REQUIRE(mmvae_convt_small_supported(H, W, Cin, Cout) == 2, "convt_small_wgrad: unsupported shape (needs Cin == 32)");
-    const size_t gsz = (((size_t)Cout * (2 * H + 2) * (2 * W + 2) + 3) & ~(size_t)3) * 4;
-    size_t smem = gsz + (size_t)H * W * (Cin + CS_PAD) * 4;
-    const size_t red = (size_t)(CSW_THREADS / 32) * Cin * Cout * 16 * 4 + 16;
-    if (red > smem) smem = red;
+    const size_t smem = csw_smem_bytes(H, W, Cin, Cout, y_act != nullptr);
     const int P = cs_wgrad_ctas(N);
     const int rc = CS_SWITCH(Cout, cs_wgrad, x, g, y_act, workspace, P, N, H, W, act, smem, (cudaStream_t)stream);
     if (rc) return rc;
