@@ -28,84 +28,115 @@ __device__ __forceinline__ float cs_dact(float y, int act) {
 }
 
 // ------------------------------------------------------------------------------------------------------ forward
-// one CTA per image.  smem: xs[H*W][CIN+PAD], ws[16][COUT][CIN], bs[COUT].  CIN is a template constant so the channel
-// loop unrolls completely: every weight address is an immediate offset and the body is FFMA + LDS.128 only
-// (the first version spent 70 % of its issue slots on address arithmetic and split FMUL/FADD pairs — ncu source page).
-#define CSF_THREADS 256
-template <int COUT, int CIN>
+// Persistent CTAs of 128 threads (two per SM) over images.  The NHWC image lands by one bulk async copy; a short
+// transform pass spreads it into a zero-bordered copy with a 36-float pixel pitch (conflict-free 128-bit reads), after
+// which the raw buffer is free and the NEXT image's copy is issued, to land while this image is computed.
+// One thread = two vertically adjacent input pixels = a 4 x 2 block of output pixels x COUT: every weight vector is
+// fetched once for both pixels and the channel loop runs on packed FFMA2 (pairs of channels).
+// smem: xs[(H+2)*(W+2)][CIN+PAD], raw[H*W][CIN], ws[16][COUT][CIN], bs[COUT], one mbarrier.
+#define CSF_THREADS 128
+__host__ __device__ inline size_t csf_smem_bytes(int H, int W, int Cin, int Cout) {
+    return ((size_t)(H + 2) * (W + 2) * (Cin + CS_PAD) + (size_t)H * W * Cin + 16 * (size_t)Cout * Cin + 4) * 4 + 16;
+}
+template <int COUT, int CIN, int HT, int WT>
 __global__ void __launch_bounds__(CSF_THREADS)
 convt_small_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
-                       float* __restrict__ y, int H, int W, int act) {
+                       float* __restrict__ y, int N, int Hrt, int Wrt, int act) {
     extern __shared__ float4 smem4[];
-    float* xs = (float*)smem4;
+    const int H = HT ? HT : Hrt, W = WT ? WT : Wrt, HW = H * W, Wp = W + 2;
     constexpr int xstride = CIN + CS_PAD;
-    float* ws = xs + H * W * xstride;
+    float* xs = (float*)smem4;                                        // [(H+2)*(W+2)][xstride], zero border
+    float* raw = xs + (H + 2) * Wp * xstride;                         // [HW][CIN]
+    float* ws = raw + HW * CIN;                                       // [16][COUT][CIN]
     float* bs = ws + 16 * COUT * CIN;
-    const int n = blockIdx.x, HW = H * W;
-    const float4* xg = (const float4*)(x + (long)n * HW * CIN);
-    constexpr int c4 = CIN / 4;
-    for (int i = threadIdx.x; i < HW * c4; i += CSF_THREADS) {
-        const int p = i / c4, c = i - p * c4;
-        *(float4*)(xs + p * xstride + 4 * c) = ld_stream4(xg + i);
+    uint64_t* full = (uint64_t*)(bs + 4);
+    if (threadIdx.x == 0) {
+        mbar_init(full, 1);
+        mbar_fence_init();
+        if ((int)blockIdx.x < N) {
+            mbar_arrive_expect_tx(full, HW * CIN * 4);
+            bulk_load_1d(raw, x + (long)blockIdx.x * HW * CIN, HW * CIN * 4, full);
+        }
     }
+    for (int i = threadIdx.x; i < (H + 2) * Wp * xstride; i += CSF_THREADS) xs[i] = 0.f;       // the border stays zero
     for (int i = threadIdx.x; i < 16 * COUT * CIN; i += CSF_THREADS) {     // torch layout w[ci][co][tap] -> ws[tap][co][ci]
         const int ci = i % CIN, co = (i / CIN) % COUT, tap = i / (CIN * COUT);
         ws[i] = w[((long)ci * COUT + co) * 16 + tap];
     }
     if (threadIdx.x < COUT) bs[threadIdx.x] = bias ? bias[threadIdx.x] : 0.f;
-    __syncthreads();
     const int H2 = 2 * H, W2 = 2 * W;
-    for (int p = threadIdx.x; p < HW; p += CSF_THREADS) {
-        const int i = p / W, j = p - i * W;
-        float acc[2][2][COUT];
+    int it = 0;
+    for (int n = blockIdx.x; n < N; n += gridDim.x, ++it) {
+        __syncthreads();                                              // xs of image n-1 fully consumed
+        mbar_wait(full, it & 1);
+        for (int i = threadIdx.x; i < HW * (CIN / 4); i += CSF_THREADS) {
+            const int p = i / (CIN / 4), c = i - p * (CIN / 4), pi = p / W, pj = p - pi * W;
+            *(float4*)(xs + ((pi + 1) * Wp + pj + 1) * xstride + 4 * c) = *(const float4*)(raw + 4 * i);
+        }
+        __syncthreads();                                              // xs ready, raw free
+        if (threadIdx.x == 0 && n + (int)gridDim.x < N) {
+            mbar_arrive_expect_tx(full, HW * CIN * 4);
+            bulk_load_1d(raw, x + (long)(n + gridDim.x) * HW * CIN, HW * CIN * 4, full);
+        }
+        for (int q = threadIdx.x; q < HW / 2; q += CSF_THREADS) {
+            const int r = q / W, j = q - r * W, i0 = 2 * r;           // input pixels (i0, j) and (i0+1, j)
+            float2 acc[2][2][2][COUT];                                // [pixel][py][px][co], channel-pair partial sums
 #pragma unroll
-        for (int a = 0; a < 2; ++a)
+            for (int u = 0; u < 2; ++u)
 #pragma unroll
-            for (int b = 0; b < 2; ++b)
+                for (int a = 0; a < 2; ++a)
 #pragma unroll
-                for (int c = 0; c < COUT; ++c) acc[a][b][c] = bs[c];
+                    for (int b = 0; b < 2; ++b)
 #pragma unroll
-        for (int dy = -1; dy <= 1; ++dy) {
-            const int ii = i + dy;
-            if (ii < 0 || ii >= H) continue;
+                        for (int c = 0; c < COUT; ++c) acc[u][a][b][c] = make_float2(0.f, 0.f);
+            const float* xw = xs + (i0 * Wp + j) * xstride;           // bordered (i0-1+1, j-1+1): top-left of the 4 x 3 window
+#pragma unroll 1
+            for (int c = 0; c < CIN; c += 4) {
+                float4 xv[4][3];
 #pragma unroll
-            for (int dx = -1; dx <= 1; ++dx) {
-                const int jj = j + dx;
-                if (jj < 0 || jj >= W) continue;
-                const float* xr = xs + (ii * W + jj) * xstride;
+                for (int a = 0; a < 4; ++a)
 #pragma unroll
-                for (int c = 0; c < CIN; c += 4) {
-                    const float4 xv = *(const float4*)(xr + c);
+                    for (int b = 0; b < 3; ++b) xv[a][b] = *(const float4*)(xw + (a * Wp + b) * xstride + c);
 #pragma unroll
-                    for (int ky = 0; ky < 4; ++ky) {
-                        const int py = (ky + 1) & 1;
-                        if ((py + 1 - ky) / 2 != dy) continue;          // resolved at compile time after unrolling
+                for (int ky = 0; ky < 4; ++ky) {
+                    const int py = (ky + 1) & 1, dy = (py + 1 - ky) / 2;          // compile-time after unrolling
+                    // the 4*COUT weight vectors of this kernel row are fetched as one batch: with two warps per scheduler
+                    // a load issued right before its use costs a full shared-memory round trip each time
+                    float4 wv[4][COUT];
 #pragma unroll
-                        for (int kx = 0; kx < 4; ++kx) {
-                            const int px = (kx + 1) & 1;
-                            if ((px + 1 - kx) / 2 != dx) continue;
+                    for (int kx = 0; kx < 4; ++kx)
 #pragma unroll
-                            for (int co = 0; co < COUT; ++co) {
-                                const float4 wv = *(const float4*)(ws + ((ky * 4 + kx) * COUT + co) * CIN + c);
-                                float t = acc[py][px][co];
-                                t = fmaf(xv.x, wv.x, t);
-                                t = fmaf(xv.y, wv.y, t);
-                                t = fmaf(xv.z, wv.z, t);
-                                t = fmaf(xv.w, wv.w, t);
-                                acc[py][px][co] = t;
+                        for (int co = 0; co < COUT; ++co)
+                            wv[kx][co] = *(const float4*)(ws + ((ky * 4 + kx) * COUT + co) * CIN + c);
+#pragma unroll
+                    for (int kx = 0; kx < 4; ++kx) {
+                        const int px = (kx + 1) & 1, dx = (px + 1 - kx) / 2;
+#pragma unroll
+                        for (int co = 0; co < COUT; ++co) {
+                            const float2 w0 = make_float2(wv[kx][co].x, wv[kx][co].y), w1 = make_float2(wv[kx][co].z, wv[kx][co].w);
+#pragma unroll
+                            for (int u = 0; u < 2; ++u) {
+                                const float4 v = xv[u + dy + 1][dx + 1];
+                                float2 t = acc[u][py][px][co];
+                                t = __ffma2_rn(make_float2(v.x, v.y), w0, t);
+                                t = __ffma2_rn(make_float2(v.z, v.w), w1, t);
+                                acc[u][py][px][co] = t;
                             }
                         }
                     }
                 }
             }
+#pragma unroll
+            for (int co = 0; co < COUT; ++co)
+#pragma unroll
+                for (int u = 0; u < 2; ++u)
+#pragma unroll
+                    for (int py = 0; py < 2; ++py) {
+                        const float2 a0 = acc[u][py][0][co], a1 = acc[u][py][1][co];
+                        const float2 o = make_float2(cs_act(a0.x + a0.y + bs[co], act), cs_act(a1.x + a1.y + bs[co], act));
+                        *(float2*)(y + (((long)n * COUT + co) * H2 + 2 * (i0 + u) + py) * W2 + 2 * j) = o;
+                    }
         }
-#pragma unroll
-        for (int co = 0; co < COUT; ++co)
-#pragma unroll
-            for (int py = 0; py < 2; ++py) {
-                float2 o = make_float2(cs_act(acc[py][0][co], act), cs_act(acc[py][1][co], act));
-                *(float2*)(y + (((long)n * COUT + co) * H2 + 2 * i + py) * W2 + 2 * j) = o;
-            }
     }
 }
 
@@ -381,8 +412,8 @@ __global__ void convt_small_wgrad_reduce(const float* __restrict__ part, float* 
 static int cs_wgrad_ctas(int N) { return N < MMVAE_NUM_SMS ? N : MMVAE_NUM_SMS; }
 
 extern "C" int mmvae_convt_small_supported(int H, int W, int Cin, int Cout) {
-    if (Cout < 1 || Cout > 4 || Cin != 32 || H < 1 || W < 2 || (W & 1)) return 0;   // Cin is a template constant (fBase = 32)
-    const size_t fwd = ((size_t)H * W * (Cin + CS_PAD) + 16 * (size_t)Cout * Cin + 4) * 4;
+    if (Cout < 1 || Cout > 4 || Cin != 32 || H < 2 || W < 2 || (W & 1) || (H & 1)) return 0;   // Cin is a template constant (fBase = 32)
+    const size_t fwd = csf_smem_bytes(H, W, Cin, Cout);
     const size_t gsz = (((size_t)Cout * (2 * H + 2) * (2 * W + 2) + 3) & ~(size_t)3) * 4;
     const size_t dg = csd_smem_bytes(H, W, Cin, Cout, true, true);
     const size_t wg = csw_smem_bytes(H, W, Cin, Cout, true);
@@ -409,9 +440,16 @@ static int cs_smem_attr(K kern, size_t smem, const char* name) {
 template <int CO>
 static int cs_fwd(const float* x, const float* w, const float* bias, float* y, int N, int H, int W, int Cin, int act,
                   size_t smem, cudaStream_t st) {
-    const int rc = cs_smem_attr(convt_small_fwd_kernel<CO, 32>, smem, "convt_small_fwd");
+    const int ctas = N < 2 * MMVAE_NUM_SMS ? N : 2 * MMVAE_NUM_SMS;
+    if (H == 16 && W == 16) {
+        const int rc = cs_smem_attr(convt_small_fwd_kernel<CO, 32, 16, 16>, smem, "convt_small_fwd");
+        if (rc) return rc;
+        convt_small_fwd_kernel<CO, 32, 16, 16><<<ctas, CSF_THREADS, smem, st>>>(x, w, bias, y, N, H, W, act);
+        return 0;
+    }
+    const int rc = cs_smem_attr(convt_small_fwd_kernel<CO, 32, 0, 0>, smem, "convt_small_fwd");
     if (rc) return rc;
-    convt_small_fwd_kernel<CO, 32><<<N, CSF_THREADS, smem, st>>>(x, w, bias, y, H, W, act);
+    convt_small_fwd_kernel<CO, 32, 0, 0><<<ctas, CSF_THREADS, smem, st>>>(x, w, bias, y, N, H, W, act);
     return 0;
 }
 template <int CO>
@@ -448,7 +486,8 @@ extern "C" int mmvae_convt_small_fwd(const float* x, const float* w, const float
                                      int Cin, int Cout, int act, void* stream) {
     MMVAE_REQUIRE(x && w && y && N > 0, "convt_small_fwd: bad arguments");
     MMVAE_REQUIRE(mmvae_convt_small_supported(H, W, Cin, Cout), "convt_small_fwd: unsupported shape H=%d W=%d Cin=%d Cout=%d", H, W, Cin, Cout);
-    const size_t smem = ((size_t)H * W * (Cin + CS_PAD) + 16 * (size_t)Cout * Cin + 4) * 4;
+    MMVAE_REQUIRE((H & 1) == 0, "convt_small_fwd: H must be even");
+    const size_t smem = csf_smem_bytes(H, W, Cin, Cout);
     const int rc = CS_SWITCH(Cout, cs_fwd, x, w, bias, y, N, H, W, Cin, act, smem, (cudaStream_t)stream);
     if (rc) return rc;
     MMVAE_LAUNCH_CHECK("convt_small_fwd");
