@@ -48,6 +48,23 @@ def _stream():
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+GRAD_SINK = None         # a set() while train.Trainer runs backward: see _sink()
+
+
+def _sink(p):
+    """Destination for the gradient of parameter `p`, or None.  While GRAD_SINK is a set, the FIRST gradient of a leaf
+    parameter in a backward pass is written by the producing kernel straight into the (zeroed) `p.grad` buffer and the
+    autograd Function returns None for it, so no AccumulateGrad `+=` kernel runs; later uses of the same parameter in
+    the same pass return their gradient normally and autograd adds them."""
+    if GRAD_SINK is None or p is None or not p.is_leaf or p.grad is None or not p.grad.is_contiguous():
+        return None
+    key = p.data_ptr()
+    if key in GRAD_SINK:
+        return None
+    GRAD_SINK.add(key)
+    return p.grad
+
+
 PROFILE = None           # set to a list to record (name, work, start_event, end_event) per C-ABI call (bench.py)
 
 
@@ -78,11 +95,11 @@ def gemm(a, b, bias, M, N, K, a_kmajor, b_kmajor, act=None, out=None):
     return out
 
 
-def colsum(a2d):
+def colsum(a2d, out=None):
     M, N = a2d.shape
     lib = _lib.load()
     ws = torch.empty(lib.mmvae_colsum_workspace_bytes(M, N) // 4, device=a2d.device, dtype=torch.float32)
-    out = torch.empty(N, device=a2d.device, dtype=torch.float32)
+    out = torch.empty(N, device=a2d.device, dtype=torch.float32) if out is None else out
     _call("mmvae_colsum", _p(a2d), _p(out), _p(ws), M, N, _stream())
     return out
 
@@ -103,9 +120,9 @@ def permute_weight(w):
     return out
 
 
-def unpermute_weight(wp, shape):
+def unpermute_weight(wp, shape, out=None):
     C0, C1, kh, kw = shape
-    out = torch.empty(shape, device=wp.device, dtype=torch.float32)
+    out = torch.empty(shape, device=wp.device, dtype=torch.float32) if out is None else out
     _call("mmvae_permute_weight", _p(wp), _p(out), C0, C1, kh * kw, 0, _stream())
     return out
 
@@ -167,6 +184,7 @@ class LinearAct(torch.autograd.Function):
         ctx.act = act
         ctx.save_for_backward(x, w, y if ACT[act] != C["MMVAE_ACT_NONE"] else None)
         ctx.has_bias = b is not None
+        ctx.leaves = (w, b)
         return y
 
     @staticmethod
@@ -176,8 +194,15 @@ class LinearAct(torch.autograd.Function):
         R, K = x.shape
         N = w.shape[0]
         gx = gemm(g, w, None, R, K, N, True, False) if ctx.needs_input_grad[0] else None
-        gw = gemm(g, x, None, N, K, R, False, False) if ctx.needs_input_grad[1] else None
-        gb = colsum(g) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        gw = gb = None
+        if ctx.needs_input_grad[1]:
+            dst = _sink(ctx.leaves[0])
+            gw = gemm(g, x, None, N, K, R, False, False, out=dst)
+            gw = None if dst is not None else gw
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            dst = _sink(ctx.leaves[1])
+            gb = colsum(g, out=dst)
+            gb = None if dst is not None else gb
         return gx, gw, gb, None
 
 
@@ -190,6 +215,7 @@ class LinearPreact(torch.autograd.Function):
         x, w = _c(x, "x"), _c(w, "weight")
         y = gemm(x, w, b, x.shape[0], w.shape[0], x.shape[1], True, True, "sigmoid")
         ctx.save_for_backward(x, w)
+        ctx.leaves = (w, b)
         return y
 
     @staticmethod
@@ -199,8 +225,15 @@ class LinearPreact(torch.autograd.Function):
         R, K = x.shape
         N = w.shape[0]
         gx = gemm(g, w, None, R, K, N, True, False) if ctx.needs_input_grad[0] else None
-        gw = gemm(g, x, None, N, K, R, False, False) if ctx.needs_input_grad[1] else None
-        gb = colsum(g) if ctx.needs_input_grad[2] else None
+        gw = gb = None
+        if ctx.needs_input_grad[1]:
+            dst = _sink(ctx.leaves[0])
+            gw = gemm(g, x, None, N, K, R, False, False, out=dst)
+            gw = None if dst is not None else gw
+        if ctx.needs_input_grad[2]:
+            dst = _sink(ctx.leaves[1])
+            gb = colsum(g, out=dst)
+            gb = None if dst is not None else gb
         return gx, gw, gb
 
 
@@ -219,6 +252,7 @@ class Conv2dAct(torch.autograd.Function):
         ctx.save_for_backward(col, wp, y2d if ACT[act] != C["MMVAE_ACT_NONE"] else None)
         ctx.cfg = (N, Cin, H, W, Cout, k, stride, pad, Ho, Wo, act, tuple(w.shape), b is not None,
                    x.is_contiguous() and Cin > 1)
+        ctx.leaves = (w, b)
         return y2d.view(N, Ho, Wo, Cout).permute(0, 3, 1, 2)
 
     @staticmethod
@@ -233,9 +267,13 @@ class Conv2dAct(torch.autograd.Function):
             gx = col2im(dcol, None, N, Cin, Ho, Wo, k, s, p, None, nchw_out=x_nchw)
         if ctx.needs_input_grad[1]:
             gwp = gemm(g, col, None, Cout, Kc, rows, False, False)
-            gw = unpermute_weight(gwp, wshape)
+            dst = _sink(ctx.leaves[0])
+            gw = unpermute_weight(gwp, wshape, out=dst)
+            gw = None if dst is not None else gw
         if has_bias and ctx.needs_input_grad[2]:
-            gb = colsum(g)
+            dst = _sink(ctx.leaves[1])
+            gb = colsum(g, out=dst)
+            gb = None if dst is not None else gb
         return gx, gw, gb, None, None, None
 
 
@@ -249,6 +287,7 @@ class ConvT2dAct(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, b, stride, pad, act, nchw_out, preact_grad, mask_input_grad=False):
         x = _dev(x, "x")
+        ctx.leaves = (w, b)
         w = _c(w, "weight")
         N, Cin, H, W = x.shape
         _, Cout, k, _ = w.shape
@@ -321,9 +360,13 @@ class ConvT2dAct(torch.autograd.Function):
                 gwp = torch.empty((Cin, 16 * Cout), device=g.device, dtype=torch.float32)
                 _call("mmvae_convt_tc_wgrad", _p(x2d), _p(g), _p(gwp), _p(ws), nb, N, H, W, Cin, Cout, _stream(),
                       work=("flop", 2.0 * N * H * W * 16 * Cin * Cout))
-                gw = unpermute_weight(gwp, wshape)
+                dst = _sink(ctx.leaves[0])
+                gw = unpermute_weight(gwp, wshape, out=dst)
+                gw = None if dst is not None else gw
             if has_bias and ctx.needs_input_grad[2]:
-                gb = colsum(g)
+                dst = _sink(ctx.leaves[1])
+                gb = colsum(g, out=dst)
+                gb = None if dst is not None else gb
             return gx, gw, gb, None, None, None, None, None, None
         if small:
             g = _c(gy, "grad")                                   # (N,Cout,2H,2W) NCHW
@@ -338,10 +381,14 @@ class ConvT2dAct(torch.autograd.Function):
                 lib = _lib.load()
                 ws = torch.empty(lib.mmvae_convt_small_wgrad_workspace_bytes(N, Cin, Cout) // 4, device=g.device,
                                  dtype=torch.float32)
-                gw = torch.empty(wshape, device=g.device, dtype=torch.float32)
-                gb = torch.empty(Cout, device=g.device, dtype=torch.float32) if has_bias else None
+                dw = _sink(ctx.leaves[0]) if ctx.needs_input_grad[1] else None
+                db = _sink(ctx.leaves[1]) if (has_bias and ctx.needs_input_grad[2]) else None
+                gw = torch.empty(wshape, device=g.device, dtype=torch.float32) if dw is None else dw
+                gb = (torch.empty(Cout, device=g.device, dtype=torch.float32) if db is None else db) if has_bias else None
                 _call("mmvae_convt_small_wgrad", _p(x2d), _p(g), _p(y), _p(gw), _p(gb), _p(ws), N, H, W, Cin, Cout,
                       ACT[act], _stream(), work=("byte", 4.0 * (g.numel() + x2d.numel())))
+                gw = None if dw is not None else gw
+                gb = None if db is not None else gb
             return gx, gw, gb, None, None, None, None, None, None
         if path == "linear":
             Kc = k * k * Cout
@@ -355,7 +402,9 @@ class ConvT2dAct(torch.autograd.Function):
                     gx2d = act_bwd(gx2d, x2d, "relu")
                 gx = gx2d.view(N, Cin, 1, 1)
             if ctx.needs_input_grad[1]:
-                gw = unpermute_weight(gemm(x2d, g, None, Cin, Kc, N, False, False), wshape)
+                dst = _sink(ctx.leaves[0])
+                gw = unpermute_weight(gemm(x2d, g, None, Cin, Kc, N, False, False), wshape, out=dst)
+                gw = None if dst is not None else gw
             if has_bias and ctx.needs_input_grad[2]:
                 gb = colsum(g).view(k * k, Cout).sum(0)
             return gx, gw, gb, None, None, None, None, None, None
@@ -376,7 +425,9 @@ class ConvT2dAct(torch.autograd.Function):
             gx = gx2d.view(N, H, W, Cin).permute(0, 3, 1, 2)
         if ctx.needs_input_grad[1]:
             gwp = gemm(x2d, dcol, None, Cin, Kc, rows, False, False)
-            gw = unpermute_weight(gwp, wshape)
+            dst = _sink(ctx.leaves[0])
+            gw = unpermute_weight(gwp, wshape, out=dst)
+            gw = None if dst is not None else gw
         if has_bias and ctx.needs_input_grad[2]:
             gb = colsum(_as_rows(g))
         return gx, gw, gb, None, None, None, None, None, None

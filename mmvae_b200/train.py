@@ -46,6 +46,7 @@ class Trainer:
         self.pg = process_group
         self.distributed = dist.is_initialized() and dist.get_world_size() > 1 if distributed is None else distributed
         self._graph = None
+        self.grad_sink = True
 
     def broadcast_parameters(self, src=0):
         if self.distributed:
@@ -54,7 +55,11 @@ class Trainer:
     def _fwd_bwd(self, x, noise=None):
         self.fp.grad.zero_()
         loss, _ = self.objective(self.model, x, self.K, 1, 0, 1, noise=noise)
-        (-loss).backward()                                   # main.py:156: the objective is maximised
+        ops.GRAD_SINK = set() if self.grad_sink else None    # weight/bias gradients land in the flat buffer directly
+        try:
+            (-loss).backward()                               # main.py:156: the objective is maximised
+        finally:
+            ops.GRAD_SINK = None
         return loss.detach()
 
     def _reduce(self):
