@@ -201,6 +201,8 @@ def profile_step(trainer, x, peak, detail=False):
     """One instrumented eager step: CUDA events around every C-ABI call -> per-kernel time shares and the roofline
     figures of the dominant kernel (algorithmic work / measured time)."""
     from mmvae_b200 import ops
+    branch = getattr(trainer.model, "branch_streams", False)
+    trainer.model.branch_streams = False           # serial launches: the per-call CUDA events must not overlap
     for _ in range(2):
         trainer.step(x)
     torch.cuda.synchronize()
@@ -209,6 +211,7 @@ def profile_step(trainer, x, peak, detail=False):
     trainer.step(x)
     torch.cuda.synchronize()
     rec, ops.PROFILE = ops.PROFILE, None
+    trainer.model.branch_streams = branch
     calls = ops.N_CALLS - n0
     agg = {}
     if detail:

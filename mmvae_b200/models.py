@@ -46,6 +46,48 @@ class Multi_VAES(nn.Module):
     def pz_params(self):
         return self._pz_params
 
+    # ---- independent per-modality chains on side streams -------------------------------------------------------
+    # The M encoders, and the M decoders (+ their log-likelihood reductions), are independent chains of mostly small,
+    # latency-bound launches.  With branch_streams=True (train.Trainer sets it) chain m < M-1 runs on its own side
+    # stream and the last chain on the current stream, so the small launches of one modality hide under the large
+    # kernels of another; autograd replays each backward node on the stream of its forward, so the backward overlaps the
+    # same way.  Inside a CUDA-graph capture the fork/join events become graph edges.
+    branch_streams = False
+
+    def _run_branches(self, fns, shared=()):
+        """fns: one closure per chain, each returning a tuple of tensors; shared: tensors the closures read that were
+        produced on the current stream.  -> list of the closures' results, all usable on the current stream."""
+        if not self.branch_streams or len(fns) < 2:
+            return [f() for f in fns]
+        cur = torch.cuda.current_stream()
+        side = self.__dict__.setdefault("_side_streams", [])
+        while len(side) < len(fns) - 1:
+            side.append(torch.cuda.Stream())
+        used = self.__dict__.setdefault("_side_used", set())
+        outs = [None] * len(fns)
+        for i, f in enumerate(fns[:-1]):
+            s = side[i]
+            s.wait_stream(cur)
+            for t in shared:
+                t.record_stream(s)
+            with torch.cuda.stream(s):
+                outs[i] = f()
+            used.add(i)
+        outs[-1] = fns[-1]()
+        for i in range(len(fns) - 1):
+            cur.wait_stream(side[i])
+            for t in outs[i]:
+                if torch.is_tensor(t):
+                    t.record_stream(cur)
+        return outs
+
+    def join_branch_streams(self):
+        """Makes the current stream wait for every side stream used since the last join (call after backward())."""
+        used = self.__dict__.get("_side_used", set())
+        for i in sorted(used):
+            torch.cuda.current_stream().wait_stream(self._side_streams[i])
+        used.clear()
+
     @property
     def latent_family(self):
         return self.params.dist
@@ -159,7 +201,9 @@ class MMVAE(Multi_VAES):
 
     # ---- the fused core ----------------------------------------------------------------------------------
     def _encode_all(self, x):
-        mus, raws = zip(*[vae.encode_raw(x[m]) for m, vae in enumerate(self.vaes)])
+        outs = self._run_branches([(lambda m=m, vae=vae: tuple(vae.encode_raw(x[m]))) for m, vae in enumerate(self.vaes)],
+                                  shared=tuple(x))
+        mus, raws = zip(*outs)
         return torch.stack(mus), torch.stack(raws)                                 # [M,B,L] each
 
     def _xform(self):
@@ -176,13 +220,16 @@ class MMVAE(Multi_VAES):
         elif not torch.is_tensor(noise):
             noise = torch.stack(list(noise))
         z, std = ops.RSample.apply(mu, raw, noise.reshape(M, K, B, L), self.params.dist, self._xform(), False)
-        recons, lps, los = [], [], []
-        for d, vae in enumerate(self.vaes):
+        def chain(d):
             zin = z.reshape(M * K * B, L) if cross else z[d].reshape(K * B, L)
-            recon = vae.decoder(zin)["reconstruction"]
+            recon = self.vaes[d].decoder(zin)["reconstruction"]
             R = recon.shape[0]
             c = self.lik_scaling[d] if scaled else 1.0
             lp, lo = ops.LogLik.apply(recon.reshape(R, -1), self._flat_x(x[d]), 1, self.params.recon_losses[d], c, False)
+            return recon, lp, lo
+
+        recons, lps, los = [], [], []
+        for recon, lp, lo in self._run_branches([(lambda d=d: chain(d)) for d in range(M)], shared=(z,) + tuple(x)):
             recons.append(recon.reshape(((M, K, B) if cross else (K, B)) + tuple(recon.shape[1:])))
             lps.append(lp.reshape((M, K, B) if cross else (K, B)))
             los.append(lo.reshape((M, K, B) if cross else (K, B)))

@@ -32,7 +32,7 @@ class Trainer:
     """One data-parallel training step.  `objective` is a name from mmvae_b200.objectives ('m_dreg_looser', ...)."""
 
     def __init__(self, model, objective="m_dreg_looser", K=30, lr=1e-3, amsgrad=True, process_group=None,
-                 distributed=None):
+                 distributed=None, branch_streams=True, grad_sink=True):
         self.model = model
         self.objective = getattr(objectives, objective)
         self.K = K
@@ -46,7 +46,9 @@ class Trainer:
         self.pg = process_group
         self.distributed = dist.is_initialized() and dist.get_world_size() > 1 if distributed is None else distributed
         self._graph = None
-        self.grad_sink = True
+        self.grad_sink = grad_sink
+        if branch_streams and hasattr(model, "_run_branches"):
+            model.branch_streams = True                      # per-modality chains on side streams (models.py)
 
     def broadcast_parameters(self, src=0):
         if self.distributed:
@@ -60,6 +62,8 @@ class Trainer:
             (-loss).backward()                               # main.py:156: the objective is maximised
         finally:
             ops.GRAD_SINK = None
+        if hasattr(self.model, "join_branch_streams"):
+            self.model.join_branch_streams()
         return loss.detach()
 
     def _reduce(self):

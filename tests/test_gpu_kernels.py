@@ -24,7 +24,7 @@ def _rand(*shape, seed=0, scale=1.0):
 
 
 @pytest.mark.parametrize("M,N,K", [(128, 128, 16), (300, 70, 37), (7680, 512, 20), (512, 20, 7680), (97, 784, 512),
-                                   (1000, 48, 32), (5, 3, 9), (128, 2048, 20)])
+                                   (1000, 48, 32), (5, 3, 9), (128, 2048, 20), (7680, 20, 2048), (20, 2048, 7680)])
 @pytest.mark.parametrize("a_k,b_k", [(1, 1), (1, 0), (0, 1), (0, 0)])
 def test_gemm_layouts(ops, M, N, K, a_k, b_k):
     A = _rand(M, K, seed=1)
