@@ -65,6 +65,47 @@ def _sink(p):
     return p.grad
 
 
+WGRAD_STREAM = None      # torch.cuda.Stream while train.Trainer runs backward: see _wgrad_side()
+WGRAD_USED = False       # set when a kernel was issued on WGRAD_STREAM (the trainer joins the stream only then)
+
+
+class _wgrad_side:
+    """Context for the weight / bias gradient kernels of one backward node.  They do not feed the rest of the backward
+    pass (only the optimizer reads them), so when their results are sunk into the flat gradient buffer (`sunk`) and a
+    WGRAD_STREAM is set they are issued on that stream: the data-gradient chain continues on the node's own stream and
+    the latency-bound launches further down (encoders) hide under the large weight-gradient kernels.  `reads` are the
+    tensors those kernels read (kept alive for the side stream); the trainer joins the stream before the optimizer."""
+
+    def __init__(self, sunk, *reads):
+        self.on = bool(sunk) and WGRAD_STREAM is not None
+        self.reads = reads
+
+    def __enter__(self):
+        if self.on:
+            global WGRAD_USED
+            WGRAD_USED = True
+            s = WGRAD_STREAM
+            s.wait_stream(torch.cuda.current_stream())
+            for t in self.reads:
+                if t is not None:
+                    t.record_stream(s)
+            self.ctx = torch.cuda.stream(s)
+            self.ctx.__enter__()
+        return self
+
+    def __exit__(self, *exc):
+        if self.on:
+            self.ctx.__exit__(*exc)
+        return False
+
+
+def _sinks(ctx_leaves, need_w, need_b):
+    """-> (dst_w, dst_b, all_sunk): sink buffers of the weight / bias gradients of a node (None = return it to autograd)."""
+    dw = _sink(ctx_leaves[0]) if need_w else None
+    db = _sink(ctx_leaves[1]) if need_b else None
+    return dw, db, (dw is not None or not need_w) and (db is not None or not need_b) and (need_w or need_b)
+
+
 PROFILE = None           # set to a list to record (name, work, start_event, end_event) per C-ABI call (bench.py)
 
 
@@ -195,14 +236,15 @@ class LinearAct(torch.autograd.Function):
         N = w.shape[0]
         gx = gemm(g, w, None, R, K, N, True, False) if ctx.needs_input_grad[0] else None
         gw = gb = None
-        if ctx.needs_input_grad[1]:
-            dst = _sink(ctx.leaves[0])
-            gw = gemm(g, x, None, N, K, R, False, False, out=dst)
-            gw = None if dst is not None else gw
-        if ctx.has_bias and ctx.needs_input_grad[2]:
-            dst = _sink(ctx.leaves[1])
-            gb = colsum(g, out=dst)
-            gb = None if dst is not None else gb
+        need_w, need_b = ctx.needs_input_grad[1], ctx.has_bias and ctx.needs_input_grad[2]
+        dw, db, sunk = _sinks(ctx.leaves, need_w, need_b)
+        with _wgrad_side(sunk, g, x):
+            if need_w:
+                gw = gemm(g, x, None, N, K, R, False, False, out=dw)
+                gw = None if dw is not None else gw
+            if need_b:
+                gb = colsum(g, out=db)
+                gb = None if db is not None else gb
         return gx, gw, gb, None
 
 
@@ -226,14 +268,15 @@ class LinearPreact(torch.autograd.Function):
         N = w.shape[0]
         gx = gemm(g, w, None, R, K, N, True, False) if ctx.needs_input_grad[0] else None
         gw = gb = None
-        if ctx.needs_input_grad[1]:
-            dst = _sink(ctx.leaves[0])
-            gw = gemm(g, x, None, N, K, R, False, False, out=dst)
-            gw = None if dst is not None else gw
-        if ctx.needs_input_grad[2]:
-            dst = _sink(ctx.leaves[1])
-            gb = colsum(g, out=dst)
-            gb = None if dst is not None else gb
+        need_w, need_b = ctx.needs_input_grad[1], ctx.needs_input_grad[2]
+        dw, db, sunk = _sinks(ctx.leaves, need_w, need_b)
+        with _wgrad_side(sunk, g, x):
+            if need_w:
+                gw = gemm(g, x, None, N, K, R, False, False, out=dw)
+                gw = None if dw is not None else gw
+            if need_b:
+                gb = colsum(g, out=db)
+                gb = None if db is not None else gb
         return gx, gw, gb
 
 
@@ -353,20 +396,21 @@ class ConvT2dAct(torch.autograd.Function):
                 _call("mmvae_convt_tc_dgrad", _p(g), _p(wpm), _p(x2d if mask_in else None), _p(gx2d), N, H, W, Cin, Cout,
                       _stream(), work=("flop", 2.0 * N * H * W * 16 * Cin * Cout))
                 gx = gx2d.view(N, H, W, Cin).permute(0, 3, 1, 2)
-            if ctx.needs_input_grad[1]:
-                lib = _lib.load()
-                nb = lib.mmvae_convt_tc_wgrad_workspace_bytes(N, H, W, Cin, Cout)
-                ws = torch.empty(nb // 4, device=g.device, dtype=torch.float32) if nb else None
-                gwp = torch.empty((Cin, 16 * Cout), device=g.device, dtype=torch.float32)
-                _call("mmvae_convt_tc_wgrad", _p(x2d), _p(g), _p(gwp), _p(ws), nb, N, H, W, Cin, Cout, _stream(),
-                      work=("flop", 2.0 * N * H * W * 16 * Cin * Cout))
-                dst = _sink(ctx.leaves[0])
-                gw = unpermute_weight(gwp, wshape, out=dst)
-                gw = None if dst is not None else gw
-            if has_bias and ctx.needs_input_grad[2]:
-                dst = _sink(ctx.leaves[1])
-                gb = colsum(g, out=dst)
-                gb = None if dst is not None else gb
+            need_w, need_b = ctx.needs_input_grad[1], has_bias and ctx.needs_input_grad[2]
+            dw, db, sunk = _sinks(ctx.leaves, need_w, need_b)
+            with _wgrad_side(sunk, g, x2d):
+                if need_w:
+                    lib = _lib.load()
+                    nb = lib.mmvae_convt_tc_wgrad_workspace_bytes(N, H, W, Cin, Cout)
+                    ws = torch.empty(nb // 4, device=g.device, dtype=torch.float32) if nb else None
+                    gwp = torch.empty((Cin, 16 * Cout), device=g.device, dtype=torch.float32)
+                    _call("mmvae_convt_tc_wgrad", _p(x2d), _p(g), _p(gwp), _p(ws), nb, N, H, W, Cin, Cout, _stream(),
+                          work=("flop", 2.0 * N * H * W * 16 * Cin * Cout))
+                    gw = unpermute_weight(gwp, wshape, out=dw)
+                    gw = None if dw is not None else gw
+                if need_b:
+                    gb = colsum(g, out=db)
+                    gb = None if db is not None else gb
             return gx, gw, gb, None, None, None, None, None, None
         if small:
             g = _c(gy, "grad")                                   # (N,Cout,2H,2W) NCHW
@@ -379,14 +423,16 @@ class ConvT2dAct(torch.autograd.Function):
                 gx = gx2d.view(N, H, W, Cin).permute(0, 3, 1, 2)
             if ctx.needs_input_grad[1] or (has_bias and ctx.needs_input_grad[2]):
                 lib = _lib.load()
-                ws = torch.empty(lib.mmvae_convt_small_wgrad_workspace_bytes(N, Cin, Cout) // 4, device=g.device,
-                                 dtype=torch.float32)
-                dw = _sink(ctx.leaves[0]) if ctx.needs_input_grad[1] else None
-                db = _sink(ctx.leaves[1]) if (has_bias and ctx.needs_input_grad[2]) else None
-                gw = torch.empty(wshape, device=g.device, dtype=torch.float32) if dw is None else dw
-                gb = (torch.empty(Cout, device=g.device, dtype=torch.float32) if db is None else db) if has_bias else None
-                _call("mmvae_convt_small_wgrad", _p(x2d), _p(g), _p(y), _p(gw), _p(gb), _p(ws), N, H, W, Cin, Cout,
-                      ACT[act], _stream(), work=("byte", 4.0 * (g.numel() + x2d.numel())))
+                need_w, need_b = ctx.needs_input_grad[1], has_bias and ctx.needs_input_grad[2]
+                dw, db, sunk = _sinks(ctx.leaves, need_w, need_b)
+                with _wgrad_side(sunk and need_w and (need_b or not has_bias), g, x2d, y):
+                    ws = torch.empty(lib.mmvae_convt_small_wgrad_workspace_bytes(N, Cin, Cout) // 4, device=g.device,
+                                     dtype=torch.float32)
+                    gw = torch.empty(wshape, device=g.device, dtype=torch.float32) if dw is None else dw
+                    gb = (torch.empty(Cout, device=g.device, dtype=torch.float32) if db is None else db) if has_bias \
+                        else None
+                    _call("mmvae_convt_small_wgrad", _p(x2d), _p(g), _p(y), _p(gw), _p(gb), _p(ws), N, H, W, Cin, Cout,
+                          ACT[act], _stream(), work=("byte", 4.0 * (g.numel() + x2d.numel())))
                 gw = None if dw is not None else gw
                 gb = None if db is not None else gb
             return gx, gw, gb, None, None, None, None, None, None

@@ -32,7 +32,7 @@ class Trainer:
     """One data-parallel training step.  `objective` is a name from mmvae_b200.objectives ('m_dreg_looser', ...)."""
 
     def __init__(self, model, objective="m_dreg_looser", K=30, lr=1e-3, amsgrad=True, process_group=None,
-                 distributed=None, branch_streams=True, grad_sink=True):
+                 distributed=None, branch_streams=True, grad_sink=True, wgrad_stream=True):
         self.model = model
         self.objective = getattr(objectives, objective)
         self.K = K
@@ -47,6 +47,7 @@ class Trainer:
         self.distributed = dist.is_initialized() and dist.get_world_size() > 1 if distributed is None else distributed
         self._graph = None
         self.grad_sink = grad_sink
+        self._wgrad_stream = torch.cuda.Stream(device=dev) if (wgrad_stream and grad_sink) else None
         if branch_streams and hasattr(model, "_run_branches"):
             model.branch_streams = True                      # per-modality chains on side streams (models.py)
 
@@ -58,12 +59,17 @@ class Trainer:
         self.fp.grad.zero_()
         loss, _ = self.objective(self.model, x, self.K, 1, 0, 1, noise=noise)
         ops.GRAD_SINK = set() if self.grad_sink else None    # weight/bias gradients land in the flat buffer directly
+        ops.WGRAD_STREAM = self._wgrad_stream if self.grad_sink else None   # ... computed off the data-gradient chain
         try:
             (-loss).backward()                               # main.py:156: the objective is maximised
         finally:
             ops.GRAD_SINK = None
+            ops.WGRAD_STREAM = None
         if hasattr(self.model, "join_branch_streams"):
             self.model.join_branch_streams()
+        if ops.WGRAD_USED:
+            torch.cuda.current_stream().wait_stream(self._wgrad_stream)
+            ops.WGRAD_USED = False
         return loss.detach()
 
     def _reduce(self):

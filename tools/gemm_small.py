@@ -41,5 +41,6 @@ if "--eval" in sys.argv:
     for dbg in (128, 0, 256):
         lib.mmvae_gemm_tc_set_mode(dbg << 8)
         ev = Bn.run_eval(model, dev, 64, Bn.peaks())
-        print(f"eval leg, {{128: 'strict', 0: 'thin M|N on tc', 256: '+ K<32 on tc'}[dbg]} gate: {ev['value']:.0f} datapoints/s ({ev['s_per_pass'] * 1e3:.2f} ms/pass)", flush=True)
+        tag = {128: 'strict', 0: 'thin M|N on tc', 256: '+ K<32 on tc'}[dbg]
+        print(f"eval leg, {tag} gate: {ev['value']:.0f} datapoints/s ({ev['s_per_pass'] * 1e3:.2f} ms/pass)", flush=True)
     lib.mmvae_gemm_tc_set_mode(0)
