@@ -79,7 +79,7 @@ def gather_datapoints(per, B, group=None):
 
 # --------------------------------------------------------------------------------------- sharded evaluators
 @torch.no_grad()
-def joint_likelihood(model, data, K=1000, batch_size_K=100, axis="batch", mask=None, noise=None, group=None):
+def joint_likelihood(model, data, K=1000, batch_size_K=100, axis="batch", mask=None, noise=None, group=None, seed=0):
     """MMVAE.compute_joint_likelihood (mmvae.py:121-177) over all ranks of `group`.
     axis='batch': each rank takes a slice of the datapoints; axis='samples': each rank takes a slice of the K
     importance samples of every datapoint.  mask (K,B) / noise [M] x (K,B,L) are the FULL draws (same on every rank;
@@ -88,7 +88,7 @@ def joint_likelihood(model, data, K=1000, batch_size_K=100, axis="batch", mask=N
     B = data[0].shape[0]
     M, L, dev = model.mod, model.params.latent_dim, data[0].device
     if noise is None or mask is None:
-        g = torch.Generator(device=dev).manual_seed(20240607)
+        g = torch.Generator(device=dev).manual_seed(20240607 + 1000003 * seed)   # rank-independent
         from .vaes import draw_noise
         if noise is None:
             noise = draw_noise(model.params.dist, (M, K, B, L), dev, generator=g)
@@ -122,7 +122,7 @@ def joint_likelihood(model, data, K=1000, batch_size_K=100, axis="batch", mask=N
 
 @torch.no_grad()
 def conditional_likelihood(model, data, cond_mod, gen_mod, K=1000, batch_size_K=100, axis="batch", noise=None,
-                           group=None):
+                           group=None, seed=0):
     """Multi_VAES.compute_conditional_likelihood (multi_vaes.py:271-318) over all ranks.  noise: full (B,Kused,L)."""
     rank, world = rank_world(group)
     B = data[0].shape[0]
@@ -131,7 +131,8 @@ def conditional_likelihood(model, data, cond_mod, gen_mod, K=1000, batch_size_K=
     if noise is None:
         from .vaes import draw_noise
         noise = draw_noise(model.vaes[cond_mod].dist, (B, Ku, L), dev,
-                           generator=torch.Generator(device=dev).manual_seed(20240608 + 7 * cond_mod + gen_mod))
+                           generator=torch.Generator(device=dev).manual_seed(20240608 + 7 * cond_mod + gen_mod
+                                                                                    + 1000003 * seed))
     if axis == "batch":
         b0, b1 = shard_bounds(B, rank, world)
         if b1 > b0:

@@ -114,6 +114,18 @@ class Trainer:
                 self._update()
         return self
 
+    def graph_ready(self, x):
+        """True when a captured graph exists for batches shaped like x."""
+        return self._graph is not None and all(a.shape == b.shape for a, b in zip(self._static_x, x))
+
+    def set_lr(self, lr):
+        """The learning rate is a launch argument of the fused optimizer kernel, i.e. baked into a captured graph: a
+        change (ReduceLROnPlateau, main.py:258) drops the graph; the caller re-captures on its next full batch."""
+        if lr != self.lr:
+            self.lr = lr
+            self._graph = None
+            self._graph_upd = None
+
     def step_graph(self, x):
         for dst, src in zip(self._static_x, x):
             dst.copy_(src, non_blocking=True)
