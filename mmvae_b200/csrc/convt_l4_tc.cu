@@ -1,0 +1,299 @@
+// Last decoder layer on the tensor cores: ConvTranspose2d(32 -> COUT <= 4, k4, s2, p1) + bias + activation on 16x16
+// inputs (encoders.py:124-136, `ConvTranspose2d(fBase, 3, 4, 2, 1) + Sigmoid`), NHWC input, NCHW output.
+//
+// The layer is too thin for an implicit GEMM with Cout as the N dimension (N = 3), and as a direct SIMT kernel it is
+// bound by the fp32 FMA pipe (convt_small.cu: 198 us for 7680 images, 48 % FMA-pipe utilisation, HBM floor 53 us).  Here
+// the GEMM is the LOWERED form kept entirely on the SM:
+//     col[pixel, (ky,kx,co)] = sum_ci x[pixel, ci] * w[ci, co, ky, kx]          M = 128 pixels, N = 16*COUT, K = 32
+// one 128-pixel tile = half an input image, K = Cin = one 128-byte swizzle row, so a tile is ONE TMA box and 4 k-steps
+// x 3 passes (3xTF32) = 12 UMMAs of 32 + N/4 clocks.  The col block never leaves the SM: each epilogue thread owns one
+// input pixel (one TMEM lane) and adds its 16*COUT values into the output image held in shared memory
+// (y[co, 2iy-1+ky, 2ix-1+kx]) in four barrier-separated tap phases (fixed summation order: deterministic); after the
+// two tiles of an image the four epilogue warps add the bias, apply the activation and stream the finished NCHW image
+// out with coalesced 128-bit stores.
+//
+// Warp roles (320 threads, one persistent CTA per SM): warp 0 TMA producer, warp 1 UMMA issuer, warps 2-5 hi/lo
+// converter (the landed fp32 tile is the tf32 "hi" operand by truncation; lo = rn_tf32(x - trunc_tf32(x)) is written
+// beside it), warps 6-9 epilogue.  The weights (hi and lo, 16*COUT rows x 32) are split once per CTA and written in the
+// 128-byte-swizzled K-major layout by ordinary stores.  TMEM: 4 accumulator pairs (big = hi*hi, small = lo*hi + hi*lo)
+// of 2 x 64 columns.
+#include <cuda.h>
+
+#include "common.cuh"
+#include "sm100_ptx.cuh"
+
+#define L4_THREADS 320
+#define L4_STAGES 4
+#define L4_NACC 4
+#define L4_TILE (128 * 32 * 4)          // one A tile: 128 pixels x 32 channels fp32 = 16 KB
+#define L4_BROWS 64                     // rows reserved per weight panel (16*COUT <= 64)
+#define L4_PITCH 36                     // floats per row of the smem output image: position = column + 1, 8-byte aligned pairs
+
+int mmvae_tc_tmap_rows(CUtensorMap* m, const float* base, long rows, long cols, int box_rows);   // gemm_tc.cu
+int mmvae_tc_dbg_bits();                                                                        // gemm_tc.cu
+
+__device__ __forceinline__ float l4_tf32_lo(float a) {       // as tf32_lo in gemm_tc.cu
+    const float r = a - __uint_as_float(__float_as_uint(a) & 0xFFFFE000u);
+    return __uint_as_float(__float_as_uint(r) + 0x1000u);
+}
+__device__ __forceinline__ void l4_bar_epi() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+// sigmoid through ex2.approx / rcp.approx (2 MUFU ops; |error| < 2e-7 absolute, inside the 2e-6 parity bound): the
+// IEEE expf + division of the SIMT kernel would cost ~40 issue slots per output pixel in the four epilogue warps
+__device__ __forceinline__ float l4_act_fast(float v, int act) {
+    if (act == MMVAE_ACT_RELU) return fmaxf(v, 0.f);
+    if (act == MMVAE_ACT_SIGMOID) return __fdividef(1.f, 1.f + __expf(-v));
+    return v;
+}
+// TMEM -> registers without the wait (several loads in flight, one tcgen05.wait::ld for all of them)
+__device__ __forceinline__ void l4_tmem_ld16_nowait(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void l4_tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+template <int COUT>
+__global__ void __launch_bounds__(L4_THREADS, 1)
+convt_l4_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float* __restrict__ w,
+                       const float* __restrict__ bias, float* __restrict__ y, int n_img, int act, int dbg) {
+    constexpr int NB = 16 * COUT;                 // UMMA N
+    constexpr int OUT_FLOATS = COUT * 32 * 32;
+    constexpr int OUT_SMEM = COUT * 32 * L4_PITCH;     // floats of the padded smem image
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* a_ring = smem;                                          // L4_STAGES x (hi 16 KB + lo 16 KB)
+    uint8_t* b_hi = a_ring + L4_STAGES * 2 * L4_TILE;                // 64 rows x 128 B
+    uint8_t* b_lo = b_hi + L4_BROWS * 128;
+    float* out = (float*)(b_lo + L4_BROWS * 128);                    // [COUT][32][L4_PITCH]
+    uint64_t* bars = (uint64_t*)(out + OUT_SMEM);
+    uint64_t* full = bars;
+    uint64_t* conv = bars + L4_STAGES;
+    uint64_t* empty = bars + 2 * L4_STAGES;
+    uint64_t* tfull = bars + 3 * L4_STAGES;
+    uint64_t* tempty = tfull + L4_NACC;
+    uint32_t* tmem_slot = (uint32_t*)(tempty + L4_NACC);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < L4_STAGES; ++s) { mbar_init(full + s, 1); mbar_init(conv + s, 4); mbar_init(empty + s, 1); }
+        for (int a = 0; a < L4_NACC; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 4); }
+        mbar_fence_init();
+        tma_prefetch_desc(&tmap_x);
+    }
+    if (warp == 1) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+    // weights: B[n = (ky*4+kx)*COUT + co][k = ci] = w[ci][co][ky][kx], K-major rows of 128 bytes, 16-byte chunk c of row
+    // r stored at chunk c ^ (r & 7) (SWIZZLE_128B); hi = the fp32 value (the tensor core truncates it), lo = residual
+    for (int i = threadIdx.x; i < L4_BROWS * 32; i += L4_THREADS) {
+        const int r = i >> 5, k = i & 31;
+        float v = 0.f;
+        if (r < NB) {
+            const int tap = r / COUT, co = r - tap * COUT;
+            v = __ldg(w + ((long)k * COUT + co) * 16 + tap);
+        }
+        const int off = r * 128 + (((k >> 2) ^ (r & 7)) << 4) + (k & 3) * 4;
+        *(float*)(b_hi + off) = v;
+        *(float*)(b_lo + off) = l4_tf32_lo(v);
+    }
+    for (int i = threadIdx.x; i < OUT_SMEM; i += L4_THREADS) out[i] = 0.f;
+    fence_proxy_async_smem();
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+    const int my_imgs = (n_img - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;   // images blockIdx.x, +grid, ...
+    const int my_tiles = 2 * my_imgs;
+
+    if (warp == 0) {
+        // ===== producer: one 128-pixel box per tile =====
+        for (int it = 0; it < my_tiles; ++it) {
+            const int s = it % L4_STAGES, img = blockIdx.x + (it >> 1) * gridDim.x;
+            mbar_wait(empty + s, ((it / L4_STAGES) & 1) ^ 1);
+            mbar_arrive_expect_tx_elect(full + s, L4_TILE);
+            tma_load_2d_elect(smem_u32(a_ring + s * 2 * L4_TILE), &tmap_x, full + s, 0, img * 256 + (it & 1) * 128);
+        }
+    } else if (warp == 1) {
+        // ===== UMMA issuer =====
+        constexpr uint32_t idesc = umma_idesc_tf32(128, NB, 0, 0);
+        const uint64_t da0 = umma_smem_desc(smem_u32(a_ring), 16, 1024, 2);
+        const uint64_t dbh = umma_smem_desc(smem_u32(b_hi), 16, 1024, 2);
+        const uint64_t dbl = umma_smem_desc(smem_u32(b_lo), 16, 1024, 2);
+        for (int it = 0; it < my_tiles; ++it) {
+            const int s = it % L4_STAGES, acc = it % L4_NACC;
+            mbar_wait(tempty + acc, ((it / L4_NACC) & 1) ^ 1);
+            mbar_wait(conv + s, (it / L4_STAGES) & 1);
+            tc_fence_after_sync();
+            const uint64_t dah = da0 + (uint64_t)(s * (2 * L4_TILE >> 4)), dal = dah + (L4_TILE >> 4);
+            const uint32_t d_big = tmem_base + acc * 128, d_small = d_big + 64;
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+                umma_tf32_elect(d_small, dal + kk * 2, dbh + kk * 2, idesc, kk != 0);
+                umma_tf32_elect(d_small, dah + kk * 2, dbl + kk * 2, idesc, 1);
+                umma_tf32_elect(d_big, dah + kk * 2, dbh + kk * 2, idesc, kk != 0);
+            }
+            umma_commit_elect(empty + s);
+            umma_commit_elect(tfull + acc);
+        }
+    } else if (warp < 6) {
+        // ===== converter: lo tile beside the landed tile =====
+        const int tq = threadIdx.x - 64;
+        for (int it = 0; it < my_tiles; ++it) {
+            const int s = it % L4_STAGES;
+            mbar_wait(full + s, (it / L4_STAGES) & 1);
+            const uint32_t hi = smem_u32(a_ring + s * 2 * L4_TILE), lo = hi + L4_TILE;
+#pragma unroll
+            for (int j = 0; j < ((dbg & 4) ? 0 : L4_TILE / 16 / 128); ++j) {
+                float4 v;
+                const uint32_t off = (uint32_t)(tq + j * 128) * 16u;
+                asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(hi + off));
+                asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(lo + off), "f"(l4_tf32_lo(v.x)),
+                             "f"(l4_tf32_lo(v.y)), "f"(l4_tf32_lo(v.z)), "f"(l4_tf32_lo(v.w)) : "memory");
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(conv + s);
+        }
+    } else {
+        // ===== epilogue: TMEM lane = input pixel; scatter-add into the smem output image, finalize every 2nd tile =====
+        const int lane_base = (warp & 3) * 32, e = (warp - 6) * 32 + lane;
+        const int p = lane_base + lane;                     // pixel of the tile
+        const int ix = p & 15, iyl = p >> 4;                // column, row within the half image
+        float bv[COUT];
+#pragma unroll
+        for (int c = 0; c < COUT; ++c) bv[c] = bias ? __ldg(bias + c) : 0.f;
+        for (int it = 0; it < my_tiles; ++it) {
+            const int acc = it % L4_NACC, half = it & 1;
+            mbar_wait(tfull + acc, (it / L4_NACC) & 1);
+            tc_fence_after_sync();
+            const uint32_t tb = tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)(acc * 128);
+            const int iy = half * 8 + iyl;
+            const int oy0 = 2 * iy - 1, ox0 = 2 * ix - 1;
+            float val[NB];
+            {
+                uint32_t rb[NB], rs[NB];
+#pragma unroll
+                for (int c0 = 0; c0 < NB; c0 += 16) {
+                    l4_tmem_ld16_nowait(tb + (uint32_t)c0, rb + c0);
+                    l4_tmem_ld16_nowait(tb + 64u + (uint32_t)c0, rs + c0);
+                }
+                l4_tmem_wait_ld();
+#pragma unroll
+                for (int j = 0; j < NB; ++j) val[j] = __uint_as_float(rb[j]) + __uint_as_float(rs[j]);
+            }
+            tc_fence_before_sync();                            // all TMEM reads of this accumulator pair are done
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty + acc);
+            // Column direction in registers: output columns (2ix-1, 2ix) receive taps kx = 0,1 of this pixel and kx = 2,3
+            // of its left neighbour (the previous lane; lanes 0-15 / 16-31 are two image rows), fetched by shuffles.
+            // Row direction through the smem image in two phases a = 0,1 (taps ky = 2a, 2a+1 -> output rows
+            // 2(iy+a)-1, 2(iy+a)): within a phase every thread owns its own 2x2 block, so plain 64-bit read-modify-writes
+            // are safe; the row block below is touched by the thread of the next image row in the other phase, which the
+            // barrier orders -> fixed summation order, bit-reproducible results.  Columns are stored shifted by one
+            // (position = ox + 1) so that the pair (2ix-1, 2ix) is 8-byte aligned; position 0 collects column -1 (unused).
+            const bool has_left = ix != 0;
+#pragma unroll
+            for (int a = 0; a < 2; ++a) {
+                if (dbg & 1) break;                            // ablation (tools/l4_time.py): no scatter
+                float2 add[2][COUT];
+                float last[2][COUT];
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const int ky = 2 * a + i;
+#pragma unroll
+                    for (int co = 0; co < COUT; ++co) {
+                        const float l2 = __shfl_up_sync(0xffffffffu, val[(ky * 4 + 2) * COUT + co], 1);
+                        const float l3 = __shfl_up_sync(0xffffffffu, val[(ky * 4 + 3) * COUT + co], 1);
+                        add[i][co].x = val[(ky * 4 + 0) * COUT + co] + (has_left ? l2 : 0.f);
+                        add[i][co].y = val[(ky * 4 + 1) * COUT + co] + (has_left ? l3 : 0.f);
+                        last[i][co] = val[(ky * 4 + 2) * COUT + co];          // column 31 (ix = 15 only)
+                    }
+                }
+                float2 old[2][COUT];
+                float oldl[2][COUT];
+                bool ok[2];
+                int idx[2];
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const int oy = oy0 + 2 * a + i;
+                    ok[i] = (unsigned)oy < 32u;
+                    idx[i] = (ok[i] ? oy : 0) * L4_PITCH + 2 * ix;
+#pragma unroll
+                    for (int co = 0; co < COUT; ++co) {
+                        old[i][co] = *reinterpret_cast<const float2*>(out + co * 32 * L4_PITCH + idx[i]);
+                        oldl[i][co] = (ix == 15) ? out[co * 32 * L4_PITCH + idx[i] + 2] : 0.f;
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    if (ok[i]) {
+#pragma unroll
+                        for (int co = 0; co < COUT; ++co) {
+                            *reinterpret_cast<float2*>(out + co * 32 * L4_PITCH + idx[i]) =
+                                make_float2(old[i][co].x + add[i][co].x, old[i][co].y + add[i][co].y);
+                            if (ix == 15) out[co * 32 * L4_PITCH + idx[i] + 2] = oldl[i][co] + last[i][co];
+                        }
+                    }
+                }
+                l4_bar_epi();
+            }
+            if (half && !(dbg & 2)) {                          // every pixel of the image has been scattered
+                const int img = blockIdx.x + (it >> 1) * gridDim.x;
+                // the smem rows are shifted by one column (position = ox + 1): thread (row, j) reads the aligned float4
+                // at positions 4j..4j+3 = columns 4j-1..4j+2 and takes column 4j+3 from its right neighbour's first
+                // element (the lane above; position 32 for the last float4 of a row) -> aligned 128-bit global stores
+                float4* dst = reinterpret_cast<float4*>(y + (long)img * OUT_FLOATS);
+#pragma unroll
+                for (int i = 0; i < OUT_FLOATS / 4 / 128; ++i) {
+                    const int q = e + i * 128;                 // float4 of the NCHW image: 256 per channel -> channel = i >> 1
+                    const int row = q >> 3, j = q & 7;
+                    float4* src = reinterpret_cast<float4*>(out + row * L4_PITCH + 4 * j);
+                    const float4 m = *src;
+                    float nx = __shfl_down_sync(0xffffffffu, m.x, 1);
+                    if (j == 7) nx = out[row * L4_PITCH + 32];
+                    const float b = bv[i >> 1];
+                    float4 o;
+                    o.x = l4_act_fast(m.y + b, act); o.y = l4_act_fast(m.z + b, act);
+                    o.z = l4_act_fast(m.w + b, act); o.w = l4_act_fast(nx + b, act);
+                    __stcs(dst + q, o);
+                    *src = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (j == 7) out[row * L4_PITCH + 32] = 0.f;
+                }
+                l4_bar_epi();                                  // the image is zero again before the next scatter
+            }
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+template <int COUT>
+static int l4_launch(const CUtensorMap& tm, const float* w, const float* bias, float* y, int N, int act, cudaStream_t st) {
+    static bool attr_done = false;
+    constexpr int SMEM = L4_STAGES * 2 * L4_TILE + 2 * L4_BROWS * 128 + COUT * 32 * L4_PITCH * 4 + 256 + 1024;
+    auto kern = convt_l4_fwd_tc_kernel<COUT>;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+        if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "convt_l4_fwd_tc: smem attribute: %s", cudaGetErrorString(e));
+        attr_done = true;
+    }
+    const int grid = N < MMVAE_NUM_SMS ? N : MMVAE_NUM_SMS;
+    kern<<<grid, L4_THREADS, SMEM, st>>>(tm, w, bias, y, N, act, (mmvae_tc_dbg_bits() >> 10) & 7);   // ablation bits, 0 in production
+    MMVAE_LAUNCH_CHECK("convt_l4_fwd_tc");
+    return 0;
+}
+
+// -> 0 launched, -1 not applicable (the caller uses the SIMT kernel), > 0 error
+int mmvae_convt_l4_fwd_tc(const float* x, const float* w, const float* bias, float* y, int N, int H, int W, int Cin,
+                          int Cout, int act, cudaStream_t st) {
+    if (H != 16 || W != 16 || Cin != 32 || (Cout != 3 && Cout != 1)) return -1;
+    if (((uintptr_t)x & 15) || ((uintptr_t)y & 15) || (mmvae_tc_dbg_bits() & 512)) return -1;
+    CUtensorMap tm;
+    const int rc = mmvae_tc_tmap_rows(&tm, x, (long)N * 256, 32, 128);
+    if (rc < 0) return -1;                                   // no tcgen05 / TMA on this device
+    if (rc) return mmvae_set_error(1, "convt_l4_fwd_tc: cuTensorMapEncodeTiled failed with %d", rc);
+    return Cout == 3 ? l4_launch<3>(tm, w, bias, y, N, act, st) : l4_launch<1>(tm, w, bias, y, N, act, st);
+}

@@ -425,6 +425,9 @@ extern "C" long mmvae_convt_small_wgrad_workspace_bytes(int N, int Cin, int Cout
     return (long)cs_wgrad_ctas(N) * ((long)Cin * Cout * 16 + Cout) * (long)sizeof(float);
 }
 
+int mmvae_convt_l4_fwd_tc(const float* x, const float* w, const float* bias, float* y, int N, int H, int W, int Cin,
+                          int Cout, int act, cudaStream_t st);                                   // convt_l4_tc.cu
+
 #define CS_SWITCH(COUTV, FN, ...)                         \
     ((COUTV) == 1 ? FN<1>(__VA_ARGS__) : (COUTV) == 2 ? FN<2>(__VA_ARGS__) : (COUTV) == 3 ? FN<3>(__VA_ARGS__) : FN<4>(__VA_ARGS__))
 
@@ -487,6 +490,10 @@ extern "C" int mmvae_convt_small_fwd(const float* x, const float* w, const float
     MMVAE_REQUIRE(x && w && y && N > 0, "convt_small_fwd: bad arguments");
     MMVAE_REQUIRE(mmvae_convt_small_supported(H, W, Cin, Cout), "convt_small_fwd: unsupported shape H=%d W=%d Cin=%d Cout=%d", H, W, Cin, Cout);
     MMVAE_REQUIRE((H & 1) == 0, "convt_small_fwd: H must be even");
+    {   // 16x16 inputs (the SVHN decoder's last layer): tcgen05 lowered-GEMM kernel with the col block kept on the SM
+        const int rc = mmvae_convt_l4_fwd_tc(x, w, bias, y, N, H, W, Cin, Cout, act, (cudaStream_t)stream);
+        if (rc >= 0) return rc;
+    }
     const size_t smem = csf_smem_bytes(H, W, Cin, Cout);
     const int rc = CS_SWITCH(Cout, cs_fwd, x, w, bias, y, N, H, W, Cin, act, smem, (cudaStream_t)stream);
     if (rc) return rc;

@@ -414,6 +414,13 @@ static int make_tmap(CUtensorMap* m, const float* base, long rows, long cols, in
     return r == CUDA_SUCCESS ? 0 : (int)r;
 }
 
+// used by convt_l4_tc.cu: K-major [rows, cols] map with a 32 x box_rows box; -1 = no tcgen05/TMA on this device
+int mmvae_tc_tmap_rows(CUtensorMap* m, const float* base, long rows, long cols, int box_rows) {
+    if (!tc_init()) return -1;
+    return make_tmap(m, base, rows, cols, box_rows, false);
+}
+int mmvae_tc_dbg_bits() { return g_tc_dbg; }
+
 struct TcPlan { int BN, S, kb_per; bool swap; };
 
 static TcPlan tc_plan(int M, int N, int K, bool can_swap) {

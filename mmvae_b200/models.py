@@ -121,7 +121,9 @@ class Multi_VAES(nn.Module):
             b1 = min(B, b0 + step)
             zc = z[b0:b1].contiguous()
             rows = zc.reshape(-1, L)
-            lpx = torch.stack([self._lpx_rows(d, rows, data[d][b0:b1], Ku, False).reshape(b1 - b0, Ku) for d in mods])
+            lpx = torch.stack([o[0] for o in self._run_branches(
+                [(lambda d=d: (self._lpx_rows(d, rows, data[d][b0:b1], Ku, False).reshape(b1 - b0, Ku),)) for d in mods],
+                shared=(rows,) + tuple(data[d] for d in mods))])
             if with_prior:
                 a = ops.eval_logw(zc, None if mu is None else mu[:, b0:b1].contiguous(),
                                   None if std is None else std[:, b0:b1].contiguous(), lpx, self.pz_params[0],

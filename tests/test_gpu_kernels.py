@@ -91,6 +91,7 @@ def test_conv2d_autograd(ops, cin, cout, H, s, p, nchw_in):
                                                          (32, 3, 16, 2, 1, "sigmoid", True, None), (64, 32, 8, 2, 1, "relu", False, None),
                                                          (32, 1, 14, 2, 1, "sigmoid", True, None), (32, 4, 5, 2, 1, "relu", True, None),
                                                          (32, 3, 16, 2, 1, None, True, None), (16, 3, 8, 2, 1, "sigmoid", True, None),
+                                                         (32, 1, 16, 2, 1, "sigmoid", True, None), (32, 3, 16, 2, 1, "relu", True, 1),
                                                          (128, 64, 4, 2, 1, "relu", False, 77), (64, 32, 8, 2, 1, "relu", False, 77),
                                                          (32, 32, 16, 2, 1, None, False, 5), (32, 64, 2, 2, 1, "relu", False, 131),
                                                          (128, 128, 8, 2, 1, "sigmoid", False, 3)])
@@ -111,6 +112,27 @@ def test_convT2d_autograd(ops, cin, cout, H, s, p, act, nchw_out, N):
     gx, gw, gb = torch.autograd.grad(y, (x, w, b), gy)
     rx, rw, rb = torch.autograd.grad(yr, (xd, wd, bd), gy.double())
     assert rel_err(gx, rx) < 5e-6 and rel_err(gw, rw) < 5e-6 and rel_err(gb, rb) < 5e-6
+
+
+def test_convT_last_layer_tensor_core_forward_is_deterministic_and_matches_simt(ops):
+    """convt_l4_tc.cu (tcgen05, col block kept on the SM) against the direct SIMT kernel it replaces and against fp64."""
+    from mmvae_b200 import _lib
+    lib = _lib.load()
+    N = 333
+    x = _rand(N, 16, 16, 32, seed=5).permute(0, 3, 1, 2)                # NHWC memory, logical NCHW
+    w = _rand(32, 3, 4, 4, seed=6, scale=0.1)
+    b = _rand(3, seed=7)
+    y1 = ops.ConvT2dAct.apply(x, w, b, 2, 1, "sigmoid", True, False)
+    y2 = ops.ConvT2dAct.apply(x, w, b, 2, 1, "sigmoid", True, False)
+    assert torch.equal(y1, y2)                                          # fixed summation order
+    old = lib.mmvae_gemm_tc_set_mode(512 << 8)                          # debug bit 512: force the SIMT kernel
+    try:
+        y_simt = ops.ConvT2dAct.apply(x, w, b, 2, 1, "sigmoid", True, False)
+    finally:
+        lib.mmvae_gemm_tc_set_mode(old)
+    ref = torch.sigmoid(F.conv_transpose2d(x.double(), w.double(), b.double(), stride=2, padding=1))
+    assert rel_err(y_simt, ref) < 2e-6 and rel_err(y1, ref) < 2e-6
+    assert (y1 - y_simt).abs().max().item() < 2e-6
 
 
 def test_convT2d_chain_fused_relu_backward(ops):

@@ -1,0 +1,33 @@
+"""Times the last decoder layer's forward (Cin=32 -> Cout=3, 16x16 -> 32x32, 7680 images): tcgen05 lowered-GEMM kernel
+(convt_l4_tc.cu) against the direct SIMT kernel (debug bit 512 forces it)."""
+import ctypes, os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import mmvae_b200  # noqa: F401
+from mmvae_b200 import _lib
+lib = _lib.load()
+p = lambda t: None if t is None else ctypes.c_void_p(t.data_ptr())
+st = lambda: ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def bench(fn, n=20):
+    fn(); fn(); torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(n): fn()
+    e1.record(); torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / n * 1e3
+
+
+for N in (7680, 32768):
+    x = torch.randn(N, 16, 16, 32, device="cuda").relu_()
+    w = torch.randn(32, 3, 4, 4, device="cuda") * 0.1
+    b = torch.randn(3, device="cuda")
+    y = torch.empty(N, 3, 32, 32, device="cuda")
+    mb = (x.numel() + y.numel()) * 4 / 1e6
+    for dbg, tag in ((512, "SIMT direct"), (0, "tcgen05 lowered"), (1024, "tc, no scatter"), (2048, "tc, no finalize"),
+                     (1024 | 2048, "tc, no scatter/finalize"), (4096, "tc, no hi/lo split"), (7168, "tc, MMA + TMA only")):
+        lib.mmvae_gemm_tc_set_mode(dbg << 8)
+        t = bench(lambda: _lib.check(lib.mmvae_convt_small_fwd(p(x), p(w), p(b), p(y), N, 16, 16, 32, 3, 2, st())))
+        print(f"N={N:6d} {tag:16s}: {t:7.1f} us   {mb / t:6.2f} TB/s algorithmic ({mb:.0f} MB)", flush=True)
+lib.mmvae_gemm_tc_set_mode(0)
