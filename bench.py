@@ -203,6 +203,7 @@ def profile_step(trainer, x, peak, detail=False):
     from mmvae_b200 import ops
     branch = getattr(trainer.model, "branch_streams", False)
     trainer.model.branch_streams = False           # serial launches: the per-call CUDA events must not overlap
+    wstream, trainer._wgrad_stream = trainer._wgrad_stream, None
     for _ in range(2):
         trainer.step(x)
     torch.cuda.synchronize()
@@ -212,6 +213,7 @@ def profile_step(trainer, x, peak, detail=False):
     torch.cuda.synchronize()
     rec, ops.PROFILE = ops.PROFILE, None
     trainer.model.branch_streams = branch
+    trainer._wgrad_stream = wstream
     calls = ops.N_CALLS - n0
     agg = {}
     if detail:
