@@ -193,6 +193,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     } else if (warp == 1) {
         // ===== MMA issuer (whole warp converged, one elected lane issues) =====
         constexpr uint32_t idesc = umma_idesc_tf32(TC_BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+        constexpr uint32_t idesc2 = umma_idesc_tf32(TC_BM, 2 * BN <= 256 ? 2 * BN : 256, A_MN ? 1 : 0, B_MN ? 1 : 0);
         // K-major (SWIZZLE_128B): 8 tf32 = 32 bytes inside the 128-byte row, 8-row groups 1024 B apart.
         // MN-major (SWIZZLE_128B_BASE32B): 8 k-rows of 128 B = 1024 B per MMA, 4-row swizzle atoms
         // 512 B apart (SBO), 32-element MN groups one TMA box = 4096 B apart (LBO).
@@ -220,6 +221,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 for (int kk = 0; kk < TC_BK / 8; ++kk) {
                     if ((dbg & 16) && (i | kk) != 0) break;
                     const uint32_t first = (i | kk) != 0;
+                    if (passes == 3 && BN <= 64 && !(dbg & 8192)) {            // bit 8192: A/B switch of tools/gemm_ablate.py
+                        // The lo tile of B follows its hi tile at the row-group (K-major) / column-group (MN-major)
+                        // pitch, and `small` follows `big` in TMEM: ONE instruction of N = 2*BN computes
+                        // hi*hi -> big and hi*lo -> small.  A UMMA costs 32 + N/4 clocks (the 32 = reading the A tile),
+                        // so two instructions instead of three save 22 % (BN = 64) / 27 % (BN = 32) of the issue stream.
+                        umma_tf32_elect(d_big, dah + kk * a_step, dbh + kk * b_step, idesc2, first);
+                        umma_tf32_elect(d_small, dal + kk * a_step, dbh + kk * b_step, idesc, 1);
+                        continue;
+                    }
                     if (passes == 3) {
                         umma_tf32_elect(d_small, dal + kk * a_step, dbh + kk * b_step, idesc, first);
                         umma_tf32_elect(d_small, dah + kk * a_step, dbl + kk * b_step, idesc, 1);

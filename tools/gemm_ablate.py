@@ -16,17 +16,17 @@ def bench(fn, n=10):
     e1.record(); torch.cuda.synchronize()
     return e0.elapsed_time(e1) / n * 1e3
 N = 7680
-names = {1: "noepi", 6: "noload", 8: "noconv", 16: "nomma"}
+names = {1: "noepi", 6: "noload", 8: "noconv", 16: "nomma", 8192: "3 UMMAs per k-step (no hi*[hi|lo] merge)"}
 for (H, Cin, Cout) in ((4, 128, 64), (8, 64, 32)):
     x = torch.randn(N, H, H, Cin, device="cuda"); w = torch.randn(Cin, Cout, 4, 4, device="cuda") * 0.1
     g = torch.randn(N, 2 * H, 2 * H, Cout, device="cuda")
     wp = ops.permute_weight(w); gx = torch.empty_like(x); gwp = torch.empty(Cin, 16 * Cout, device="cuda")
     nb = lib.mmvae_convt_tc_wgrad_workspace_bytes(N, H, H, Cin, Cout); ws = torch.empty(max(nb // 4, 1), device="cuda")
     for mode in (0, 1):
-        for dbg in ([int(a) for a in sys.argv[1:]] or (0, 1, 6, 8, 16, 1 | 8, 1 | 6 | 8, 1 | 6 | 8 | 16)):
+        for dbg in ([int(a) for a in sys.argv[1:]] or (0, 8192, 1, 6, 8, 16, 1 | 8, 1 | 6 | 8, 1 | 6 | 8 | 16)):
             lib.mmvae_gemm_tc_set_mode(mode | (dbg << 8))
             td = bench(lambda: _lib.check(lib.mmvae_convt_tc_dgrad(p(g), p(wp), p(x), p(gx), N, H, H, Cin, Cout, st())))
             tw = bench(lambda: _lib.check(lib.mmvae_convt_tc_wgrad(p(x), p(g), p(gwp), p(ws), nb, N, H, H, Cin, Cout, st())))
             tag = " ".join(v for k, v in names.items() if dbg & k)
-            print(f"H={H} Cin={Cin} Cout={Cout} passes={3 if mode == 0 else 1} dbg={dbg:2d} [{tag}]: dgrad {td:7.1f} us  wgrad {tw:7.1f} us", flush=True)
+            print(f"H={H} Cin={Cin} Cout={Cout} passes={3 if mode == 0 else 1} dbg={dbg:4d} [{tag}]: dgrad {td:7.1f} us  wgrad {tw:7.1f} us", flush=True)
 lib.mmvae_gemm_tc_set_mode(0)
