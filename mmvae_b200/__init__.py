@@ -11,5 +11,7 @@ from .models import (MMVAE, MNIST_SVHN, CIRCLES_SQUARES, MNIST_SVHN_FASHION, Mul
 from . import flows  # noqa: E402
 from .jmvae_nf import JMVAE_NF, JMVAE_NF_DCCA_MNIST_SVHN, VAE_jnf_mnist_svhn_dcca  # noqa: E402
 
-__all__ = ["flows", "JMVAE_NF", "JMVAE_NF_DCCA_MNIST_SVHN", "VAE_jnf_mnist_svhn_dcca","objectives", "ops", "MMVAE", "Multi_VAES", "MNIST_SVHN", "CIRCLES_SQUARES", "MNIST_SVHN_FASHION",
+from .mvae import MVAE, MVAE_MNIST_SVHN, MVAE_MNIST_SVHN_FASHION, VAE_mvae_mnist_svhn, VAE_mvae_msf  # noqa: E402
+
+__all__ = ["MVAE", "MVAE_MNIST_SVHN", "MVAE_MNIST_SVHN_FASHION", "VAE_mvae_mnist_svhn", "VAE_mvae_msf", "flows", "JMVAE_NF", "JMVAE_NF_DCCA_MNIST_SVHN", "VAE_jnf_mnist_svhn_dcca","objectives", "ops", "MMVAE", "Multi_VAES", "MNIST_SVHN", "CIRCLES_SQUARES", "MNIST_SVHN_FASHION",
            "VAE_mnist_svhn", "VAE_circles_squares", "VAE_mmvae_msf"]

@@ -1,0 +1,164 @@
+"""MVAE (product of experts with the prior) on the same kernels as the MMVAE path — SURVEY.md §8(f) rank 4.
+
+Reference: models/mvae/mvae.py:13-266 (`poe`, `forward`, `compute_joint_ll_from_uni`, `compute_joint_likelihood`),
+models/mvae/mnist_svhn.py:22-45, models/mvae/msf.py:28-57; objective `m_self_built` (objectives.py:481-483).
+
+What runs where: encoders / decoders through the GEMM and conv kernels (networks.py); the M unimodal PoE draws and the
+joint draw are ONE rsample launch ((M+1) x B latents; std = exp(lnV/2) is the kernel's `exp_half` transform of the PoE
+log-variance); each decoder runs ONCE on its unimodal and the joint latents (2B rows); the squared-error
+reconstruction terms are the `neg_mse` mode of the log-likelihood reduction kernel; the K-sample evaluators reuse the
+importance-weight / logsumexp kernels of the MMVAE evaluators (`qmode='single'`).  The PoE combination and the closed-form
+KL act on (M+1) x B x L elements and stay torch glue.
+"""
+import math
+
+import torch
+import torch.distributions as dist
+import torch.nn as nn
+
+from . import ops
+from .models import Multi_VAES
+from .networks import Decoder_AE_MLP, Decoder_VAE_SVHN, Encoder_VAE_MLP, Encoder_VAE_SVHN
+from .vaes import VAEConfig, draw_noise, my_VAE
+
+
+class MVAE(Multi_VAES):
+    """models/mvae/mvae.py:13-266."""
+
+    def __init__(self, params, vaes):
+        assert params.dist == "normal"                        # mvae.py:16: Gaussian prior and posteriors
+        super().__init__(params, vaes)
+        self.qz_x = dist.Normal
+        self.subsampling = False
+        self.subsets = []
+
+    # ---- product of experts ------------------------------------------------------------------------------------
+    @staticmethod
+    def _poe_lnv(mus, log_vars):
+        """mvae.py:27-45 -> (joint_mu, lnV) with joint_std = exp(lnV / 2); the prior N(0,1) is one more expert."""
+        lnT = torch.stack([-l for l in log_vars] + [torch.zeros_like(log_vars[0])])
+        lnV = -torch.logsumexp(lnT, dim=0)
+        mu = (torch.exp(lnT[:-1]) * torch.stack(list(mus))).sum(dim=0) * torch.exp(lnV)
+        return mu, lnV
+
+    def poe(self, mus_list, log_vars_list, eps=1e-8):
+        mu, lnV = self._poe_lnv(mus_list, log_vars_list)
+        return mu, torch.exp(0.5 * lnV)
+
+    def kl(self, mu, std):
+        """kl_divergence(N(mu,std), N(*pz_params)).sum()  (mvae.py:60-61; torch _kl_normal_normal)."""
+        ploc, pscale = self.pz_params[0], self.pz_params[1]
+        vr = (std / pscale).pow(2)
+        t1 = ((mu - ploc) / pscale).pow(2)
+        return (0.5 * (vr + t1 - 1 - vr.log())).sum()
+
+    def _encode(self, x):
+        outs = self._run_branches([(lambda m=m, vae=vae: tuple(vae.encode_raw(x[m]))) for m, vae in enumerate(self.vaes)],
+                                  shared=tuple(x))
+        return [o[0] for o in outs], [o[1] for o in outs]
+
+    def infer_latent_from_mod(self, cond_mod, x, noise=None):
+        """mvae.py:64-71."""
+        mu_u, lv_u = self.vaes[cond_mod].encode_raw(x)
+        mu, lnV = self._poe_lnv([mu_u], [lv_u])
+        B, L = mu.shape
+        if noise is None:
+            noise = draw_noise("normal", (B, L), mu.device)
+        z, _ = ops.RSample.apply(mu.unsqueeze(0), lnV.unsqueeze(0), noise.reshape(1, 1, B, L), "normal", "exp_half", False)
+        return z.reshape(B, L)
+
+    # ---- forward = the training objective (mvae.py:74-143, subsampling off) -----------------------------------------
+    def forward(self, x, noise=None):
+        """-> dict(elbo, z_joint, joint_mu, joint_std).  noise: M+1 tensors (B,L): the unimodal PoE draws, then the joint."""
+        M = self.mod
+        mus, lvs = self._encode(x)
+        B, L = mus[0].shape
+        uni = [self._poe_lnv([mus[m]], [lvs[m]]) for m in range(M)]
+        joint_mu, joint_lnV = self._poe_lnv(mus, lvs)
+        mu_all = torch.stack([u[0] for u in uni] + [joint_mu])                 # [M+1,B,L]
+        lnv_all = torch.stack([u[1] for u in uni] + [joint_lnV])
+        if noise is None:
+            noise = draw_noise("normal", (M + 1, 1, B, L), mu_all.device)
+        elif not torch.is_tensor(noise):
+            noise = torch.stack(list(noise))
+        z, std = ops.RSample.apply(mu_all, lnv_all, noise.reshape(M + 1, 1, B, L), "normal", "exp_half", False)
+        z = z.reshape(M + 1, B, L)
+
+        def chain(d):                                                          # decoder d on [z_d ; z_joint]: 2B rows
+            rows = torch.cat([z[d], z[M]], dim=0)
+            recon = self.vaes[d].decoder(rows)["reconstruction"]
+            lp, _ = ops.LogLik.apply(recon.reshape(2 * B, -1), self._flat_x(x[d]), 1, "neg_mse",
+                                     0.5 * self.lik_scaling[d], False)       # -1/2 sum (x - recon)^2 * lik_scaling
+            return (lp,)
+
+        rec = sum(o[0].sum() for o in self._run_branches([(lambda d=d: chain(d)) for d in range(M)],
+                                                         shared=(z,) + tuple(x)))
+        elbo = rec - self.kl(mu_all, std)
+        return dict(elbo=elbo, z_joint=z[M], joint_mu=joint_mu, joint_std=std[M])
+
+    # ---- K-sample importance-sampled likelihoods -------------------------------------------------------------------
+    @torch.no_grad()
+    def compute_joint_likelihood(self, data, K=1000, batch_size_K=100, noise=None):
+        """mvae.py:219-266: z ~ N(joint_mu, joint_std), K // batch_size_K chunks of batch_size_K draws, weights
+        p(x,y|z) p(z) / q(z|x,y), ln K subtracted.  noise: (B, Kused, L)."""
+        mus, lvs = self._encode(data)
+        mu, lnV = self._poe_lnv(mus, lvs)
+        B, L = mu.shape
+        Ku = self._used(K, batch_size_K)
+        if noise is None:
+            noise = draw_noise("normal", (B, Ku, L), mu.device)
+        z, std = ops.RSample.apply(mu.unsqueeze(0), lnV.unsqueeze(0), noise.reshape(1, B, Ku, L), "normal", "exp_half", True)
+        ll = self._is_loglik(z.reshape(B, Ku, L), data, range(self.mod), "single", mu.unsqueeze(0), std, K_total=K)
+        self.last_per_datapoint = ll
+        return {"likelihood": ll.mean()}
+
+    @torch.no_grad()
+    def compute_joint_ll_from_uni(self, data, cond_mod, K=1000, batch_size_K=100, noise=None):
+        """mvae.py:160-217: z ~ the ENCODER's Gaussian of the conditioning modality (the reference's own warning at
+        :172-173: not the PoE with the prior).  noise: (K,B,L)."""
+        vae = self.vaes[cond_mod]
+        mu, raw = vae.encode_raw(data[cond_mod])
+        B, L = mu.shape
+        if noise is None:
+            noise = draw_noise("normal", (K, B, L), mu.device)
+        z, std = ops.RSample.apply(mu.unsqueeze(0), raw.unsqueeze(0), noise.reshape(1, K, B, L), "normal", "exp_half", False)
+        z = z[0].permute(1, 0, 2)[:, :self._used(K, batch_size_K)].contiguous()
+        ll = self._is_loglik(z, data, range(self.mod), "single", mu.unsqueeze(0), std, K_total=K)
+        return {f"joint_ll_from_{cond_mod}": ll.mean()}
+
+
+class MVAE_MNIST_SVHN(MVAE):
+    """models/mvae/mnist_svhn.py:22-45."""
+    shape_mods = [(1, 28, 28), (3, 32, 32)]
+
+    def __init__(self, params):
+        c1, c2 = VAEConfig((1, 28, 28), params.latent_dim), VAEConfig((3, 32, 32), params.latent_dim)
+        vaes = nn.ModuleList([my_VAE(c1, Encoder_VAE_MLP(c1), Decoder_AE_MLP(c1)),
+                              my_VAE(c2, Encoder_VAE_SVHN(c2), Decoder_VAE_SVHN(c2))])
+        super().__init__(params, vaes)
+        self.modelName = "mvae_mnist_svhn"
+        self.vaes[0].modelName, self.vaes[1].modelName = "mnist", "svhn"
+        s = getattr(params, "llik_scaling", 0.0)
+        self.lik_scaling = ((3 * 32 * 32) / (1 * 28 * 28), 1.0) if s == 0 else (float(s), 1.0)
+
+
+class MVAE_MNIST_SVHN_FASHION(MVAE):
+    """models/mvae/msf.py:28-57 (subsampling of expert subsets off, as in the shipped config)."""
+    shape_mods = [(1, 28, 28), (3, 32, 32), (1, 28, 28)]
+
+    def __init__(self, params):
+        c1, c2, c3 = (VAEConfig(s, params.latent_dim) for s in self.shape_mods)
+        vaes = nn.ModuleList([my_VAE(c1, Encoder_VAE_MLP(c1), Decoder_AE_MLP(c1)),
+                              my_VAE(c2, Encoder_VAE_SVHN(c2), Decoder_VAE_SVHN(c2)),
+                              my_VAE(c3, Encoder_VAE_MLP(c3), Decoder_AE_MLP(c3))])
+        super().__init__(params, vaes)
+        self.modelName = "mvae_msf"
+        for v, n in zip(self.vaes, ("mnist", "svhn", "fashion")):
+            v.modelName = n
+        r = (3 * 32 * 32) / (1 * 28 * 28)
+        s = getattr(params, "llik_scaling", 0.0)
+        self.lik_scaling = (r, 1.0, r) if s == 0 else (float(s), 1.0, float(s))
+
+
+VAE_mvae_mnist_svhn = MVAE_MNIST_SVHN
+VAE_mvae_msf = MVAE_MNIST_SVHN_FASHION

@@ -93,3 +93,11 @@ def m_jmvae_nf(model, x, K=1, epoch=1, warmup=0, beta_prior=1, noise=None):
     if not isinstance(model, JMVAE_NF):
         raise TypeError(f"m_jmvae_nf needs an mmvae_b200 JMVAE_NF model, got {type(model).__name__}")
     return model.objective(x, epoch=epoch, warmup=warmup, beta_prior=beta_prior, noise=noise)
+
+
+def m_self_built(model, x, K=1, epoch=1, warmup=0, beta_prior=1, noise=None):
+    """objectives.py:481-483: the model computes its own ELBO (MVAE.forward, mvae.py:74-143)."""
+    from .mvae import MVAE
+    if not isinstance(model, MVAE):
+        raise TypeError(f"m_self_built needs an mmvae_b200 MVAE model, got {type(model).__name__}")
+    return model.forward(x, noise=noise)["elbo"], {}

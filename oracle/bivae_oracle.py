@@ -663,3 +663,67 @@ def logsumexp_combine(ms, ss):
     m = torch.stack(ms).max(0).values
     s = sum(s_i * torch.exp(m_i - m) for m_i, s_i in zip(ms, ss))
     return m + torch.log(s)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# MVAE (product of experts with the prior) — models/mvae/mvae.py; objective `m_self_built` (objectives.py:481-483)
+# ----------------------------------------------------------------------------------------------------------
+def mvae_poe(mus, log_vars):
+    """MVAE.poe, mvae.py:27-45: product of the Gaussian experts and the N(0,1) prior -> (joint_mu, joint_std)."""
+    mus = list(mus) + [torch.zeros_like(mus[0])]
+    log_vars = list(log_vars) + [torch.zeros_like(log_vars[0])]
+    lnT = torch.stack([-l for l in log_vars])
+    lnV = -torch.logsumexp(lnT, dim=0)
+    joint_mu = (torch.exp(lnT) * torch.stack(mus)).sum(dim=0) * torch.exp(lnV)
+    return joint_mu, torch.exp(0.5 * lnV)
+
+
+def mvae_forward(spec: Spec, sd, x, noise):
+    """MVAE.forward, mvae.py:74-143 without subsampling.  noise: M+1 tensors (B,L) in the order the reference draws them
+    (one per unimodal PoE, then the joint).  -> dict(elbo, z_joint, joint_mu, joint_std)."""
+    ploc, pscale = None, None
+    elbo = 0
+    mus, lvs = [], []
+    for m in range(spec.M):
+        mu_u, lv_u = encode(spec, sd, m, x[m])
+        mus.append(mu_u)
+        lvs.append(lv_u)
+        mu, std = mvae_poe([mu_u], [lv_u])
+        if ploc is None:
+            ploc, pscale = pz_params(spec, sd, mu)
+        z = mu + noise[m] * std
+        recon = decode(spec, sd, m, z)
+        elbo = elbo - 0.5 * torch.sum((x[m] - recon) ** 2) * spec.lik_scaling[m] - lat_kl("normal", mu, std, ploc, pscale).sum()
+    joint_mu, joint_std = mvae_poe(mus, lvs)
+    z_joint = joint_mu + noise[spec.M] * joint_std
+    for m in range(spec.M):
+        recon = decode(spec, sd, m, z_joint)
+        elbo = elbo - 0.5 * torch.sum((x[m] - recon) ** 2) * spec.lik_scaling[m]
+    elbo = elbo - lat_kl("normal", joint_mu, joint_std, ploc, pscale).sum()
+    return {"elbo": elbo, "z_joint": z_joint, "joint_mu": joint_mu, "joint_std": joint_std}
+
+
+def mvae_joint_likelihood(spec, sd, data, K, batch_size_K, noise):
+    """MVAE.compute_joint_likelihood, mvae.py:219-266: z ~ N(joint_mu, joint_std), K // batch_size_K chunks of
+    batch_size_K draws per datapoint, ln K subtracted.  noise: (B, Kused, L).  -> (mean, per-datapoint (B,))."""
+    enc = [encode(spec, sd, m, data[m]) for m in range(spec.M)]
+    mu, std = mvae_poe([e[0] for e in enc], [e[1] for e in enc])
+    z = mu.unsqueeze(1) + noise * std.unsqueeze(1)                              # (B,Ku,L)
+    ploc, pscale = pz_params(spec, sd, z)
+    a = (_decode_all(spec, sd, z, data) + lat_log_prob("normal", z, ploc, pscale).sum(-1)
+         - lat_log_prob("normal", z, mu.unsqueeze(1), std.unsqueeze(1)).sum(-1))
+    ll = torch.logsumexp(a, dim=1) - math.log(K)
+    return ll.mean(), ll
+
+
+def mvae_joint_ll_from_uni(spec, sd, data, cond_mod, K, batch_size_K, noise):
+    """MVAE.compute_joint_ll_from_uni, mvae.py:160-217: z ~ q(z|x_cond) = the ENCODER's Gaussian (not the PoE with the
+    prior — the reference's own warning at :172-173).  noise: (K,B,L) (`rsample([K])`)."""
+    mu, lv = encode(spec, sd, cond_mod, data[cond_mod])
+    std = torch.exp(0.5 * lv)
+    z = (mu.unsqueeze(0) + noise * std.unsqueeze(0)).permute(1, 0, 2)[:, :_used(K, batch_size_K)]
+    ploc, pscale = pz_params(spec, sd, z)
+    a = (_decode_all(spec, sd, z, data) + lat_log_prob("normal", z, ploc, pscale).sum(-1)
+         - lat_log_prob("normal", z, mu.unsqueeze(1), std.unsqueeze(1)).sum(-1))
+    ll = torch.logsumexp(a, dim=1) - math.log(K)
+    return ll.mean(), ll

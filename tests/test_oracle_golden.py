@@ -90,3 +90,25 @@ def test_microbatch_split_and_combine():
     ms = [a[:, :13].max(1).values, a[:, 13:].max(1).values]
     ss = [torch.exp(a[:, :13] - ms[0][:, None]).sum(1), torch.exp(a[:, 13:] - ms[1][:, None]).sum(1)]
     assert torch.allclose(O.logsumexp_combine(ms, ss), full, atol=1e-6)
+
+
+@pytest.mark.parametrize("name", ["mvae_ms", "mvae_msf"])
+def test_mvae_matches_reference(name):
+    """MVAE (models/mvae/mvae.py): objective `m_self_built` with gradients, forward outputs, and both evaluators."""
+    g, spec, sd = load_golden(name)
+    x, K, bs = g["x"], g["K"], g["bs"]
+    lsd = leaf_sd(sd)
+    out = O.mvae_forward(spec, lsd, x, g["train"]["noise"])
+    out["elbo"].backward()
+    ref = g["train"]["loss"].item()
+    assert abs(out["elbo"].item() - ref) <= 1e-5 * abs(ref), (out["elbo"].item(), ref)
+    check_digests({k: v.grad for k, v in lsd.items()}, g["train"]["grads"], GRAD_RTOL, name)
+    with torch.no_grad():
+        fw = O.mvae_forward(spec, sd, x, g["forward"]["noise"])
+        for k in ("joint_mu", "joint_std", "z_joint"):
+            assert torch.allclose(fw[k], g["forward"][k], rtol=1e-5, atol=1e-6), k
+        mean, _ = O.mvae_joint_likelihood(spec, sd, x, K, bs, g["joint"]["noise"])
+        assert abs(mean.item() - g["joint"]["likelihood"].item()) < 1e-3
+        for c in range(spec.M):
+            mean, _ = O.mvae_joint_ll_from_uni(spec, sd, x, c, K, bs, g[f"joint_from_{c}"]["noise"])
+            assert abs(mean.item() - float(g[f"joint_from_{c}"]["value"])) < 1e-3
