@@ -93,6 +93,38 @@ def cpu_port_step_rate(steps, warmup, B=B_PER_GPU, K=K_TRAIN):
     return B / dt, cores, dt * 1e3
 
 
+def port_eager_gpu_rate(dev, steps=5, warmup=3, B=B_PER_GPU, K=K_TRAIN):
+    """The same port (torch ops, fp32, the reference's op sequence incl. its K-fold encoder-free restatement) run
+    EAGERLY on the B200 — the reference's real deployment mode is `model.to('cuda')` (main.py:64-71), so this, not the
+    CPU figure, is the number the kernels have to beat.  Reported inside cpu_baseline as `eager_b200`."""
+    from oracle import bivae_oracle as O
+    from oracle import synth
+    spec = O.spec_mnist_svhn(LATENT, "laplace")
+    sd = {k: v.to(dev) for k, v in synth.make_state_dict(spec, 1).items()}
+    leaves = {k: v.clone().requires_grad_(k.endswith(("weight", "bias"))) for k, v in sd.items()}
+    opt = torch.optim.Adam([v for v in leaves.values() if v.requires_grad], lr=1e-3, amsgrad=True)
+    x = [t.to(dev) for t in synth.make_inputs(spec, B, seed=2)]
+    rs = np.random.RandomState(3)
+    noises = [[synth.make_noise("laplace", (K, B, LATENT), rs).to(dev) for _ in range(2)] for _ in range(2)]
+
+    def step(i):
+        opt.zero_grad(set_to_none=True)
+        loss = O.m_dreg_looser(spec, leaves, x, K, noises[i % 2])
+        (-loss).backward()
+        opt.step()
+    for i in range(warmup):
+        step(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        step(i)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    return B / (ms * 1e-3), ms
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -356,6 +388,14 @@ def run_b200(args):
             line["cpu_baseline"] = {"value": v, "unit": "samples/s", "cores": cores, "kind": "port",
                                     "sample": "2 full C2 steps (B=128,K=30) fwd+bwd+Adam after 1 warm-up",
                                     "ms_per_step": cms}
+            try:
+                gv, gms = port_eager_gpu_rate(dev)
+                line["cpu_baseline"]["eager_b200"] = {
+                    "value": gv, "unit": "samples/s", "ms_per_step": gms,
+                    "what": "the same port (torch eager ops, cuDNN/cuBLAS, TF32 off) on this B200: the reference's own "
+                            "deployment mode; 5 steps after 3 warm-up"}
+            except Exception as e:                  # informational only
+                line["cpu_baseline"]["eager_b200"] = {"error": f"{type(e).__name__}: {e}"[:200]}
         _OUT.write(json.dumps(line) + "\n")
         _OUT.flush()
     if dist_on:

@@ -162,3 +162,105 @@ class MVAE_MNIST_SVHN_FASHION(MVAE):
 
 VAE_mvae_mnist_svhn = MVAE_MNIST_SVHN
 VAE_mvae_msf = MVAE_MNIST_SVHN_FASHION
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# MoPoE — models/moepoe/moepoe.py
+# ---------------------------------------------------------------------------------------------------------------
+class MOEPOE(Multi_VAES):
+    """Mixture of products of experts (models/moepoe/moepoe.py:75-214).  The mixture components are the M unimodal
+    posteriors and the PoE of every subset of >= 2 modalities (only the full subset includes the prior); one latent per
+    datapoint is drawn from the component its batch position selects (mixture_component_selection, :20-40)."""
+
+    def __init__(self, params, vaes):
+        super().__init__(params, vaes)
+        self.lik_scaling = tuple(1.0 for _ in vaes)               # moepoe.py:80 (subclasses set the pixel ratio)
+        self.qz_x = dist.Normal
+
+    @staticmethod
+    def _components(mus, log_vars):
+        """compute_poe_for_all_subsets, moepoe.py:44-70, appended to the unimodal experts (:93-100)."""
+        from itertools import combinations
+        M = len(mus)
+        out_mu, out_lv = list(mus), list(log_vars)
+        for k in range(2, M + 1):
+            for tup in combinations(range(M), k):
+                ms, ls = [mus[i] for i in tup], [log_vars[i] for i in tup]
+                if k == M:
+                    ms, ls = ms + [torch.zeros_like(mus[0])], ls + [torch.zeros_like(log_vars[0])]
+                lnT = torch.stack([-l for l in ls])
+                lnV = -torch.logsumexp(lnT, dim=0)
+                out_mu.append((torch.exp(lnT) * torch.stack(ms)).sum(dim=0) * torch.exp(lnV))
+                out_lv.append(lnV)
+        return out_mu, out_lv
+
+    @staticmethod
+    def _select(mus, log_vars):
+        C, B = len(mus), mus[0].shape[0]
+        step = B // C
+        bounds = [(k * step, B if k == C - 1 else (k + 1) * step) for k in range(C)]
+        return (torch.cat([mus[k][a:b] for k, (a, b) in enumerate(bounds)]),
+                torch.cat([log_vars[k][a:b] for k, (a, b) in enumerate(bounds)]))
+
+    def forward(self, x, noise=None):
+        """moepoe.py:83-135 -> dict(elbo, z_joint, mus, log_vars).  noise: (B,L)."""
+        M = self.mod
+        outs = self._run_branches([(lambda m=m, vae=vae: tuple(vae.encode_raw(x[m]))) for m, vae in enumerate(self.vaes)],
+                                  shared=tuple(x))
+        mus, lvs = self._components([o[0] for o in outs], [o[1] for o in outs])
+        mu_r, lv_r = self._select(mus, lvs)
+        B, L = mu_r.shape
+        if noise is None:
+            noise = draw_noise("normal", (B, L), mu_r.device)
+        z, _ = ops.RSample.apply(mu_r.unsqueeze(0), lv_r.unsqueeze(0), noise.reshape(1, 1, B, L), "normal", "exp_half", False)
+        z = z.reshape(B, L)
+
+        def chain(d):
+            recon = self.vaes[d].decoder(z)["reconstruction"]
+            lp, _ = ops.LogLik.apply(recon.reshape(B, -1), self._flat_x(x[d]), 1, self.params.recon_losses[d],
+                                     self.lik_scaling[d], False)
+            return (lp,)
+
+        elbo = sum(o[0].sum() for o in self._run_branches([(lambda d=d: chain(d)) for d in range(M)],
+                                                          shared=(z,) + tuple(x)))
+        mu_all, lv_all = torch.stack(mus), torch.stack(lvs)
+        ploc, pscale = self.pz_params[0], self.pz_params[1]
+        vr = torch.exp(lv_all) / pscale.pow(2)
+        kld = 0.5 * (vr + ((mu_all - ploc) / pscale).pow(2) - 1 - vr.log())
+        elbo = elbo - kld.sum() * getattr(self.params, "beta_kl", 1.0) / len(mus)
+        return dict(elbo=elbo, z_joint=z, mus=mu_all, log_vars=lv_all)
+
+    @torch.no_grad()
+    def compute_joint_ll_from_uni(self, data, cond_mod, K=1000, batch_size_K=100, noise=None):
+        """moepoe.py:160-214: as MVAE.compute_joint_ll_from_uni, but ln K is not subtracted (:212)."""
+        vae = self.vaes[cond_mod]
+        mu, raw = vae.encode_raw(data[cond_mod])
+        B, L = mu.shape
+        if noise is None:
+            noise = draw_noise("normal", (K, B, L), mu.device)
+        z, std = ops.RSample.apply(mu.unsqueeze(0), raw.unsqueeze(0), noise.reshape(1, K, B, L), "normal", "exp_half", False)
+        z = z[0].permute(1, 0, 2)[:, :self._used(K, batch_size_K)].contiguous()
+        ll = self._is_loglik(z, data, range(self.mod), "single", mu.unsqueeze(0), std, K_total=1)
+        return {f"joint_ll_from_{cond_mod}": ll.mean()}
+
+    def compute_joint_likelihood(self, data, K=1000, batch_size_K=100):
+        raise NotImplementedError("the reference's MOEPOE.compute_joint_likelihood is unfinished (moepoe.py:217-245 "
+                                  "raises ZeroDivisionError); there is nothing to be in parity with")
+
+
+class MOEPOE_MNIST_SVHN(MOEPOE):
+    """models/moepoe/mnist_svhn.py."""
+    shape_mods = [(1, 28, 28), (3, 32, 32)]
+
+    def __init__(self, params):
+        c1, c2 = VAEConfig((1, 28, 28), params.latent_dim), VAEConfig((3, 32, 32), params.latent_dim)
+        vaes = nn.ModuleList([my_VAE(c1, Encoder_VAE_MLP(c1), Decoder_AE_MLP(c1)),
+                              my_VAE(c2, Encoder_VAE_SVHN(c2), Decoder_VAE_SVHN(c2))])
+        super().__init__(params, vaes)
+        self.modelName = "moepoe_mnist_svhn"
+        self.vaes[0].modelName, self.vaes[1].modelName = "mnist", "svhn"
+        s = getattr(params, "llik_scaling", 0.0)
+        self.lik_scaling = ((3 * 32 * 32) / (1 * 28 * 28), 1.0) if s == 0 else (float(s), 1.0)
+
+
+VAE_moepoe_mnist_svhn = MOEPOE_MNIST_SVHN

@@ -96,8 +96,8 @@ def m_jmvae_nf(model, x, K=1, epoch=1, warmup=0, beta_prior=1, noise=None):
 
 
 def m_self_built(model, x, K=1, epoch=1, warmup=0, beta_prior=1, noise=None):
-    """objectives.py:481-483: the model computes its own ELBO (MVAE.forward, mvae.py:74-143)."""
-    from .mvae import MVAE
-    if not isinstance(model, MVAE):
-        raise TypeError(f"m_self_built needs an mmvae_b200 MVAE model, got {type(model).__name__}")
+    """objectives.py:481-483: the model computes its own ELBO (MVAE.forward, mvae.py:74-143; MOEPOE.forward, moepoe.py:83-135)."""
+    from .mvae import MOEPOE, MVAE
+    if not isinstance(model, (MVAE, MOEPOE)):
+        raise TypeError(f"m_self_built needs an mmvae_b200 MVAE / MOEPOE model, got {type(model).__name__}")
     return model.forward(x, noise=noise)["elbo"], {}

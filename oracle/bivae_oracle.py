@@ -727,3 +727,58 @@ def mvae_joint_ll_from_uni(spec, sd, data, cond_mod, K, batch_size_K, noise):
          - lat_log_prob("normal", z, mu.unsqueeze(1), std.unsqueeze(1)).sum(-1))
     ll = torch.logsumexp(a, dim=1) - math.log(K)
     return ll.mean(), ll
+
+
+# ----------------------------------------------------------------------------------------------------------
+# MoPoE (mixture of products of experts) — models/moepoe/moepoe.py
+# ----------------------------------------------------------------------------------------------------------
+def mopoe_components(mus, log_vars):
+    """The mixture components of MOEPOE.forward (moepoe.py:93-100): the M unimodal posteriors followed by the PoE of
+    every subset of >= 2 modalities in itertools.combinations order; only the FULL subset includes the N(0,1) prior
+    (compute_poe_for_all_subsets, :44-70).  -> (list of mu, list of log-variance)."""
+    from itertools import combinations
+    M = len(mus)
+    out_mu, out_lv = list(mus), list(log_vars)
+    for k in range(2, M + 1):
+        for tup in combinations(range(M), k):
+            ms = [mus[i] for i in tup]
+            ls = [log_vars[i] for i in tup]
+            if k == M:
+                ms, ls = ms + [torch.zeros_like(mus[0])], ls + [torch.zeros_like(log_vars[0])]
+            lnT = torch.stack([-l for l in ls])
+            lnV = -torch.logsumexp(lnT, dim=0)
+            out_mu.append((torch.exp(lnT) * torch.stack(ms)).sum(dim=0) * torch.exp(lnV))
+            out_lv.append(lnV)
+    return out_mu, out_lv
+
+
+def mopoe_select(mus, log_vars):
+    """mixture_component_selection, moepoe.py:20-40: datapoints [k*(B//C), (k+1)*(B//C)) take component k, the last
+    component takes the remainder."""
+    C, B = len(mus), mus[0].shape[0]
+    step = B // C
+    bounds = [(k * step, B if k == C - 1 else (k + 1) * step) for k in range(C)]
+    return (torch.cat([mus[k][a:b] for k, (a, b) in enumerate(bounds)]),
+            torch.cat([log_vars[k][a:b] for k, (a, b) in enumerate(bounds)]))
+
+
+def mopoe_forward(spec: Spec, sd, x, noise, beta_kl=1.0):
+    """MOEPOE.forward, moepoe.py:83-135.  noise: (B,L).  -> dict(elbo, z_joint, mus, log_vars)."""
+    enc = [encode(spec, sd, m, x[m]) for m in range(spec.M)]
+    mus, lvs = mopoe_components([e[0] for e in enc], [e[1] for e in enc])
+    mu_r, lv_r = mopoe_select(mus, lvs)
+    z = mu_r + noise * torch.exp(0.5 * lv_r)
+    ploc, pscale = pz_params(spec, sd, z)
+    elbo = 0
+    for m in range(spec.M):
+        recon = decode(spec, sd, m, z)
+        elbo = elbo + px_log_prob(spec.recon_losses[m], recon, x[m]).sum() * spec.lik_scaling[m]
+    for mu, lv in zip(mus, lvs):
+        elbo = elbo - lat_kl("normal", mu, torch.exp(0.5 * lv), ploc, pscale).sum() * beta_kl / len(mus)
+    return {"elbo": elbo, "z_joint": z, "mus": torch.stack(mus), "log_vars": torch.stack(lvs)}
+
+
+def mopoe_joint_ll_from_uni(spec, sd, data, cond_mod, K, batch_size_K, noise):
+    """MOEPOE.compute_joint_ll_from_uni, moepoe.py:160-214: as the MVAE one but ln K is NOT subtracted (:212)."""
+    mean, ll = mvae_joint_ll_from_uni(spec, sd, data, cond_mod, K, batch_size_K, noise)
+    return mean + math.log(K), ll + math.log(K)

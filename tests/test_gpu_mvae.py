@@ -90,3 +90,54 @@ def test_mvae_registry_and_trainer_step():
     x = [torch.rand(64, 1, 28, 28, generator=g).cuda(), torch.rand(64, 3, 32, 32, generator=g).cuda()]
     losses = [tr.step(x).item() for _ in range(15)]
     assert losses[-1] > losses[0]                                # the ELBO is maximised
+
+
+def build_mopoe(spec, sd, beta_kl):
+    import mmvae_b200
+    from mmvae_b200 import networks as N
+    from mmvae_b200.vaes import VAEConfig, my_VAE
+    params = argparse.Namespace(latent_dim=spec.latent_dim, dist="normal", recon_losses=list(spec.recon_losses),
+                                llik_scaling=0.0, device="cuda", data_path="", epochs=1, beta_kl=beta_kl)
+    vaes = []
+    for m in range(spec.M):
+        cfg = VAEConfig(tuple(spec.shapes[m]), spec.latent_dim)
+        enc = N.Encoder_VAE_MLP(cfg) if spec.enc[m] == "mlp" else N.Encoder_VAE_SVHN(cfg)
+        dec = N.Decoder_AE_MLP(cfg) if spec.dec[m] == "mlp" else N.Decoder_VAE_SVHN(cfg)
+        vaes.append(my_VAE(cfg, enc, dec))
+    model = mmvae_b200.MOEPOE(params, nn.ModuleList(vaes))
+    model.lik_scaling = tuple(spec.lik_scaling)
+    model.load_state_dict(sd, strict=True)
+    return model.cuda()
+
+
+@pytest.mark.parametrize("name", ["mopoe_ms", "mopoe_msf"])
+def test_mopoe_matches_reference_and_f64_oracle(name):
+    """MoPoE (models/moepoe/moepoe.py:83-214): objective with gradients, mixture components, joint_ll_from_uni."""
+    from mmvae_b200 import objectives as J
+    g, spec, sd = load_golden(name)
+    x = [t.cuda() for t in g["x"]]
+    K, bs = g["K"], g["bs"]
+    model = build_mopoe(spec, sd, g["beta_kl"])
+    loss, _ = J.m_self_built(model, x, 1, 1, 0, 1, noise=g["train"]["noise"].cuda())
+    loss.backward()
+    ref = g["train"]["loss"].item()
+    assert abs(loss.item() - ref) <= 1e-4 * abs(ref), (loss.item(), ref)
+    grads = {k: p.grad for k, p in model.named_parameters()}
+    check_digests(grads, g["train"]["grads"], 1e-4, name)
+    lsd = leaf_sd(sd, dtype=torch.float64)
+    l64 = O.mopoe_forward(spec, lsd, [t.double() for t in g["x"]], g["train"]["noise"].double(), g["beta_kl"])["elbo"]
+    l64.backward()
+    assert abs(loss.item() - l64.item()) <= 1e-6 * abs(l64.item())
+    keys = sorted(k for k, v in lsd.items() if v.grad is not None)
+    ours = torch.cat([grads[k].detach().double().cpu().reshape(-1) for k in keys])
+    theirs = torch.cat([lsd[k].grad.reshape(-1) for k in keys])
+    assert rel_err(ours, theirs) <= 2e-5
+    with torch.no_grad():
+        fw = model(x, noise=g["forward"]["noise"].cuda())
+        for k in ("mus", "log_vars", "z_joint"):
+            assert torch.allclose(fw[k].cpu(), g["forward"][k], rtol=1e-4, atol=1e-5), k
+        for c in range(spec.M):
+            r = model.compute_joint_ll_from_uni(x, c, K=K, batch_size_K=bs, noise=g[f"joint_from_{c}"]["noise"].cuda())
+            assert abs(r[f"joint_ll_from_{c}"].item() - float(g[f"joint_from_{c}"]["value"])) < 1e-3
+    with pytest.raises(NotImplementedError):
+        model.compute_joint_likelihood(x)

@@ -112,3 +112,23 @@ def test_mvae_matches_reference(name):
         for c in range(spec.M):
             mean, _ = O.mvae_joint_ll_from_uni(spec, sd, x, c, K, bs, g[f"joint_from_{c}"]["noise"])
             assert abs(mean.item() - float(g[f"joint_from_{c}"]["value"])) < 1e-3
+
+
+@pytest.mark.parametrize("name", ["mopoe_ms", "mopoe_msf"])
+def test_mopoe_matches_reference(name):
+    """MoPoE (models/moepoe/moepoe.py): objective `m_self_built` with gradients, mixture components, evaluator."""
+    g, spec, sd = load_golden(name)
+    x, K, bs = g["x"], g["K"], g["bs"]
+    lsd = leaf_sd(sd)
+    out = O.mopoe_forward(spec, lsd, x, g["train"]["noise"], g["beta_kl"])
+    out["elbo"].backward()
+    ref = g["train"]["loss"].item()
+    assert abs(out["elbo"].item() - ref) <= 1e-5 * abs(ref), (out["elbo"].item(), ref)
+    check_digests({k: v.grad for k, v in lsd.items()}, g["train"]["grads"], GRAD_RTOL, name)
+    with torch.no_grad():
+        fw = O.mopoe_forward(spec, sd, x, g["forward"]["noise"], g["beta_kl"])
+        for k in ("mus", "log_vars", "z_joint"):
+            assert torch.allclose(fw[k], g["forward"][k], rtol=1e-5, atol=1e-6), k
+        for c in range(spec.M):
+            mean, _ = O.mopoe_joint_ll_from_uni(spec, sd, x, c, K, bs, g[f"joint_from_{c}"]["noise"])
+            assert abs(mean.item() - float(g[f"joint_from_{c}"]["value"])) < 1e-3
