@@ -297,3 +297,260 @@ int mmvae_convt_l4_fwd_tc(const float* x, const float* w, const float* bias, flo
     if (rc) return mmvae_set_error(1, "convt_l4_fwd_tc: cuTensorMapEncodeTiled failed with %d", rc);
     return Cout == 3 ? l4_launch<3>(tm, w, bias, y, N, act, st) : l4_launch<1>(tm, w, bias, y, N, act, st);
 }
+
+// =====================================================================================================================
+// dgrad of the same layer on tcgen05: gx[pixel, ci] = mask(x) * sum_{(ky,kx,co)} G[pixel,(ky,kx,co)] * w[ci,co,ky,kx]
+// with G = the gather (im2col) of the pre-activation gradient, G[pixel,(ky,kx,co)] = g_pre[co, 2iy-1+ky, 2ix-1+kx].
+// M = 128 pixels (half an image), N = Cin = 32, K = 16*COUT = 48.  G never exists in memory: per image the builder
+// warps turn g (and y for the activation derivative) into a zero-bordered g_pre image in shared memory and gather the
+// two 128 x 48 tiles from it straight into the swizzled K-major operand layout, hi and lo (3xTF32) in one pass.
+// UMMAs per tile: 6 k-steps x 2 (hi*[hi|lo] as one N = 64 instruction + lo*hi, N = 32).  Epilogue: one pixel per
+// thread, ReLU mask of the layer below (the pixel's 128-byte row of x, fetched before the accumulator wait) and a
+// full-line store of the pixel's 32 gradients.
+// Warp roles (448 threads): 0 bulk-copy producer (g / y images, L2 prefetch of the mask rows), 1 UMMA issuer,
+// 2-5 and 10-13 builder (one group per image half), 6-9 epilogue.
+// =====================================================================================================================
+#define L4D_PITCH 36                      // floats per row of the padded g_pre image (34 used)
+#define L4D_ASTAGE (2 * 2 * L4_TILE)      // one A stage: 2 swizzle atoms (k 0-31, 32-63) x (hi + lo) x 16 KB
+#define L4D_NACC 4
+#define L4D_EPI_PITCH 36                  // floats per staged row: 16-byte aligned, conflict-free for 128-bit accesses
+
+#define L4D_THREADS 448                   // warps 0 producer, 1 issuer, 2-5 + 10-13 builder, 6-9 epilogue
+__device__ __forceinline__ void l4_bar_build() { asm volatile("bar.sync 2, 256;" ::: "memory"); }
+
+template <int COUT>
+__global__ void __launch_bounds__(L4D_THREADS, 1)
+convt_l4_dgrad_tc_kernel(const float* __restrict__ g, const float* __restrict__ y_act, const float* __restrict__ w,
+                         const float* __restrict__ x_mask, float* __restrict__ gx, int n_img, int act, int dbg) {
+    constexpr int KT = 16 * COUT;                       // 48
+    constexpr int NKK = (KT + 7) / 8;                   // k-steps of 8: 6
+    constexpr int IMG = COUT * 1024;                    // floats per g / y image
+    constexpr int PIMG = COUT * 34 * L4D_PITCH;         // padded g_pre image
+    static_assert(KT <= 64 && KT % 4 == 0, "two swizzle atoms");
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* a_ring = smem;                                          // 2 stages x 64 KB
+    uint8_t* b_pan = a_ring + 2 * L4D_ASTAGE;                        // per atom: [hi 32 rows | lo 32 rows] x 128 B = 8 KB
+    float* raw = (float*)(b_pan + 2 * 8192);                         // 2 stages x (g image + y image)
+    float* pimg = raw + 2 * 2 * IMG;
+    float* epi_pad = pimg + ((PIMG + 3) & ~3);                       // 4 warps x 32 rows x L4D_EPI_PITCH
+    uint64_t* bars = (uint64_t*)(epi_pad + 4 * 32 * L4D_EPI_PITCH);
+    uint64_t* raw_full = bars;            // [2]
+    uint64_t* raw_empty = bars + 2;       // [2] count 4
+    uint64_t* a_full = bars + 4;          // [2] count 4
+    uint64_t* a_empty = bars + 6;         // [2] count 1 (commit)
+    uint64_t* tfull = bars + 8;           // [NACC]
+    uint64_t* tempty = bars + 8 + L4D_NACC;
+    uint32_t* tmem_slot = (uint32_t*)(tempty + L4D_NACC);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool has_y = y_act != nullptr && act != MMVAE_ACT_NONE;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < 2; ++s) { mbar_init(raw_full + s, 1); mbar_init(raw_empty + s, 8); mbar_init(a_full + s, 4); mbar_init(a_empty + s, 1); }
+        for (int a = 0; a < L4D_NACC; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 4); }
+        mbar_fence_init();
+    }
+    if (warp == 1) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
+    // weights: B[n = ci][k = (ky*4+kx)*COUT + co] = w[ci][co][ky][kx]; atom a = k / 32; rows 0-31 hi, rows 32-63 lo
+    for (int i = threadIdx.x; i < 32 * 64; i += L4D_THREADS) {
+        const int n = i >> 6, k = i & 63;
+        float v = 0.f;
+        if (k < KT) {
+            const int tap = k / COUT, co = k - tap * COUT;
+            v = __ldg(w + ((long)n * COUT + co) * 16 + tap);
+        }
+        const int atom = k >> 5, kk = k & 31;
+        const int off = atom * 8192 + n * 128 + (((kk >> 2) ^ (n & 7)) << 4) + (kk & 3) * 4;
+        *(float*)(b_pan + off) = v;
+        *(float*)(b_pan + off + 4096) = l4_tf32_lo(v);
+    }
+    for (int i = threadIdx.x; i < PIMG; i += L4D_THREADS) pimg[i] = 0.f;     // the border stays zero
+    fence_proxy_async_smem();
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+    const int my_imgs = (n_img - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+
+    if (warp == 0) {
+        // ===== producer: the g and y images of every image of this CTA, two in flight =====
+        for (int j = 0; j < my_imgs; ++j) {
+            const int s = j & 1;
+            const long img = blockIdx.x + (long)j * gridDim.x;
+            // the ReLU-mask rows the epilogue will read two images from now: pull them into L2 (32 KB per image), so
+            // that its register-staged loads see L2 latency instead of HBM latency
+            if (x_mask && lane == 0 && j + 2 < my_imgs && !(dbg & 1)) {
+                const float* pf = x_mask + (img + 2L * gridDim.x) * 256 * 32;
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(pf), "r"(256 * 32 * 4) : "memory");
+            }
+            mbar_wait(raw_empty + s, ((j >> 1) & 1) ^ 1);
+            if (lane == 0) {
+                mbar_arrive_expect_tx(raw_full + s, (has_y ? 2 : 1) * IMG * 4);
+                bulk_load_1d(raw + s * 2 * IMG, g + img * IMG, IMG * 4, raw_full + s);
+                if (has_y) bulk_load_1d(raw + s * 2 * IMG + IMG, y_act + img * IMG, IMG * 4, raw_full + s);
+            }
+            __syncwarp();
+        }
+    } else if (warp == 1) {
+        // ===== UMMA issuer =====
+        constexpr uint32_t idesc64 = umma_idesc_tf32(128, 64, 0, 0), idesc32 = umma_idesc_tf32(128, 32, 0, 0);
+        const uint64_t da0 = umma_smem_desc(smem_u32(a_ring), 16, 1024, 2);
+        const uint64_t db0 = umma_smem_desc(smem_u32(b_pan), 16, 1024, 2);
+        for (int it = 0; it < 2 * my_imgs; ++it) {
+            const int s = it & 1, acc = it % L4D_NACC;
+            mbar_wait(tempty + acc, ((it / L4D_NACC) & 1) ^ 1);
+            mbar_wait(a_full + s, (it >> 1) & 1);
+            tc_fence_after_sync();
+            const uint32_t d = tmem_base + acc * 64;                 // [big 32 | small 32]
+#pragma unroll
+            for (int kk = 0; kk < NKK; ++kk) {
+                const int atom = kk >> 2, kin = kk & 3;
+                const uint64_t dah = da0 + (uint64_t)((s * L4D_ASTAGE + atom * 2 * L4_TILE) >> 4) + kin * 2;
+                const uint64_t dal = dah + (L4_TILE >> 4);
+                const uint64_t db = db0 + (uint64_t)((atom * 8192) >> 4) + kin * 2;
+                umma_tf32_elect(d, dah, db, idesc64, kk != 0);        // hi*hi -> big, hi*lo -> small
+                umma_tf32_elect(d + 32, dal, db, idesc32, 1);         // lo*hi -> small
+            }
+            umma_commit_elect(a_empty + s);
+            umma_commit_elect(tfull + acc);
+        }
+    } else if (warp < 6 || warp >= 10) {
+        // ===== builder (two groups of four warps): all eight build the g_pre image, then group bg gathers the operand
+        // tile of image half bg (which always lives in A stage bg) =====
+        const int bg = warp >= 10 ? 1 : 0;
+        const int t = threadIdx.x - (bg ? 320 : 64);                 // 0..127 = pixel row of the group's tile
+        const int ix = t & 15, iyl = t >> 4;
+        for (int j = 0; j < my_imgs; ++j) {
+            const int rs = j & 1;
+            mbar_wait(raw_full + rs, (j >> 1) & 1);
+            const float* gi = raw + rs * 2 * IMG;
+            const float* yi = gi + IMG;
+#pragma unroll
+            for (int q = 0; q < ((dbg & 4) ? 0 : IMG / 256); ++q) {      // dbg: ablation bits of tools/l4_time.py
+                const int e = t + 128 * bg + q * 256, co = e >> 10, oy = (e >> 5) & 31, ox = e & 31;
+                float v = gi[e];
+                if (has_y) {
+                    const float yy = yi[e];
+                    v *= (act == MMVAE_ACT_SIGMOID) ? yy * (1.f - yy) : (yy > 0.f ? 1.f : 0.f);
+                }
+                pimg[(co * 34 + oy + 1) * L4D_PITCH + ox + 1] = v;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(raw_empty + rs);
+            l4_bar_build();                                          // the whole g_pre image is in place
+            {
+                const int half = bg, it = 2 * j + half, s = bg;
+                mbar_wait(a_empty + s, ((it >> 1) & 1) ^ 1);
+                const int iy = half * 8 + iyl;
+                const float* p0 = pimg + (2 * iy) * L4D_PITCH + 2 * ix;          // P[co][2iy+ky][2ix+kx]
+                uint8_t* row = a_ring + s * L4D_ASTAGE + t * 128;
+#pragma unroll
+                for (int c = 0; c < ((dbg & 2) ? 0 : KT / 4); ++c) {   // 16-byte chunk c = k 4c..4c+3
+                    float v[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int k = 4 * c + u, tap = k / COUT, co = k - tap * COUT, ky = tap >> 2, kx = tap & 3;
+                        v[u] = p0[(co * 34 + ky) * L4D_PITCH + kx];
+                    }
+                    const int atom = c >> 3, cc = c & 7;
+                    // plain stores (no asm barrier): the compiler batches the gather loads of all 12 chunks
+                    uint8_t* dst = row + atom * 2 * L4_TILE + ((cc ^ (t & 7)) << 4);
+                    *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+                    *reinterpret_cast<float4*>(dst + L4_TILE) =
+                        make_float4(l4_tf32_lo(v[0]), l4_tf32_lo(v[1]), l4_tf32_lo(v[2]), l4_tf32_lo(v[3]));
+                }
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(a_full + s);
+            }
+            l4_bar_build();                                          // everyone has gathered: the image may be overwritten
+        }
+    } else {
+        // ===== epilogue: TMEM lane = pixel; the warp's 32 rows x 128 B are one contiguous 4 KB block of gx (and of x):
+        // rows go through a padded smem tile so that the mask loads and the stores are fully coalesced 128-bit accesses
+        // (one 128-byte row per thread cost > 100 us: 32 cache lines per instruction) =====
+        const int lane_base = (warp & 3) * 32;
+        float* pad = epi_pad + (warp & 3) * 32 * L4D_EPI_PITCH;
+        // the mask rows of tile it+1 are requested before tile it is processed (a full tile of work hides the latency)
+        auto blk_of = [&](int it) {
+            const long img = blockIdx.x + (long)(it >> 1) * gridDim.x;
+            return (img * 256 + (it & 1) * 128 + lane_base) * 8;               // float4 index of the warp's 4 KB block
+        };
+        float4 mk_next[8];
+        if (x_mask && !(dbg & 1) && my_imgs > 0) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q) mk_next[q] = __ldcs(reinterpret_cast<const float4*>(x_mask) + blk_of(0) + lane + 32 * q);
+        }
+        for (int it = 0; it < 2 * my_imgs; ++it) {
+            const int acc = it % L4D_NACC;
+            const long blk = blk_of(it);
+            float4 mk[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) mk[q] = mk_next[q];
+            if (x_mask && !(dbg & 1) && it + 1 < 2 * my_imgs) {
+#pragma unroll
+                for (int q = 0; q < 8; ++q)
+                    mk_next[q] = __ldcs(reinterpret_cast<const float4*>(x_mask) + blk_of(it + 1) + lane + 32 * q);
+            }
+            mbar_wait(tfull + acc, (it / L4D_NACC) & 1);
+            tc_fence_after_sync();
+            const uint32_t tb = tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)(acc * 64);
+            uint32_t rb[32], rsm[32];
+            l4_tmem_ld16_nowait(tb, rb);
+            l4_tmem_ld16_nowait(tb + 16, rb + 16);
+            l4_tmem_ld16_nowait(tb + 32, rsm);
+            l4_tmem_ld16_nowait(tb + 48, rsm + 16);
+            l4_tmem_wait_ld();
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty + acc);
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+                *reinterpret_cast<float4*>(pad + lane * L4D_EPI_PITCH + 4 * q) =
+                    make_float4(__uint_as_float(rb[4 * q]) + __uint_as_float(rsm[4 * q]),
+                                __uint_as_float(rb[4 * q + 1]) + __uint_as_float(rsm[4 * q + 1]),
+                                __uint_as_float(rb[4 * q + 2]) + __uint_as_float(rsm[4 * q + 2]),
+                                __uint_as_float(rb[4 * q + 3]) + __uint_as_float(rsm[4 * q + 3]));
+            __syncwarp();
+            float4* dst = reinterpret_cast<float4*>(gx) + blk;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                if (dbg & 1) continue;
+                const int idx = lane + 32 * q;                       // float4 of the block: row idx >> 3, chunk idx & 7
+                float4 o = *reinterpret_cast<const float4*>(pad + (idx >> 3) * L4D_EPI_PITCH + 4 * (idx & 7));
+                if (x_mask) {
+                    o.x = mk[q].x > 0.f ? o.x : 0.f; o.y = mk[q].y > 0.f ? o.y : 0.f;
+                    o.z = mk[q].z > 0.f ? o.z : 0.f; o.w = mk[q].w > 0.f ? o.w : 0.f;
+                }
+                __stcs(dst + idx, o);
+            }
+            __syncwarp();
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, 256);
+}
+
+// -> 0 launched, -1 not applicable (the caller uses the SIMT kernel), > 0 error
+int mmvae_convt_l4_dgrad_tc(const float* g, const float* y_act, const float* w, const float* x_mask, float* gx, int N,
+                            int H, int W, int Cin, int Cout, int act, cudaStream_t st) {
+    if (H != 16 || W != 16 || Cin != 32 || Cout != 3) return -1;
+    if (((uintptr_t)g & 15) || ((uintptr_t)gx & 15) || ((uintptr_t)y_act & 15) || ((uintptr_t)x_mask & 15)) return -1;
+    if (mmvae_tc_dbg_bits() & 512) return -1;
+    CUtensorMap tm;
+    if (mmvae_tc_tmap_rows(&tm, gx, (long)N * 256, 32, 128) < 0) return -1;      // only asks: tcgen05 device?
+    constexpr int COUT = 3;
+    constexpr int SMEM = 2 * L4D_ASTAGE + 2 * 8192 + 2 * 2 * COUT * 1024 * 4 + ((COUT * 34 * L4D_PITCH + 3) & ~3) * 4 + 4 * 32 * L4D_EPI_PITCH * 4 + 256 + 1024;
+    static bool attr_done = false;
+    auto kern = convt_l4_dgrad_tc_kernel<COUT>;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+        if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "convt_l4_dgrad_tc: smem attribute: %s", cudaGetErrorString(e));
+        attr_done = true;
+    }
+    const int grid = N < MMVAE_NUM_SMS ? N : MMVAE_NUM_SMS;
+    kern<<<grid, L4D_THREADS, SMEM, st>>>(g, y_act, w, x_mask, gx, N, act, (mmvae_tc_dbg_bits() >> 10) & 7);
+    MMVAE_LAUNCH_CHECK("convt_l4_dgrad_tc");
+    return 0;
+}

@@ -428,6 +428,9 @@ extern "C" long mmvae_convt_small_wgrad_workspace_bytes(int N, int Cin, int Cout
 int mmvae_convt_l4_fwd_tc(const float* x, const float* w, const float* bias, float* y, int N, int H, int W, int Cin,
                           int Cout, int act, cudaStream_t st);                                   // convt_l4_tc.cu
 
+int mmvae_convt_l4_dgrad_tc(const float* g, const float* y_act, const float* w, const float* x_mask, float* gx, int N,
+                            int H, int W, int Cin, int Cout, int act, cudaStream_t st);          // convt_l4_tc.cu
+
 #define CS_SWITCH(COUTV, FN, ...)                         \
     ((COUTV) == 1 ? FN<1>(__VA_ARGS__) : (COUTV) == 2 ? FN<2>(__VA_ARGS__) : (COUTV) == 3 ? FN<3>(__VA_ARGS__) : FN<4>(__VA_ARGS__))
 
@@ -506,6 +509,10 @@ extern "C" int mmvae_convt_small_dgrad(const float* g, const float* y_act, const
     MMVAE_REQUIRE(g && w && gx && N > 0, "convt_small_dgrad: bad arguments");
     MMVAE_REQUIRE(mmvae_convt_small_supported(H, W, Cin, Cout), "convt_small_dgrad: unsupported shape");
     MMVAE_REQUIRE((W & 1) == 0 && ((H * W) & 1) == 0 && ((4L * H * W * Cout) % 4) == 0, "convt_small_dgrad: W must be even");
+    {   // 16x16 inputs: tcgen05 kernel with the gathered operand built in shared memory (convt_l4_tc.cu)
+        const int rc = mmvae_convt_l4_dgrad_tc(g, y_act, w, x_mask, gx, N, H, W, Cin, Cout, act, (cudaStream_t)stream);
+        if (rc >= 0) return rc;
+    }
     const size_t smem = csd_smem_bytes(H, W, Cin, Cout, y_act != nullptr, x_mask != nullptr);
     const int rc = CS_SWITCH(Cout, cs_dgrad, g, y_act, w, x_mask, gx, N, H, W, Cin, act, smem, (cudaStream_t)stream);
     if (rc) return rc;

@@ -29,5 +29,14 @@ for N in (7680, 32768):
                      (1024 | 2048, "tc, no scatter/finalize"), (4096, "tc, no hi/lo split"), (7168, "tc, MMA + TMA only")):
         lib.mmvae_gemm_tc_set_mode(dbg << 8)
         t = bench(lambda: _lib.check(lib.mmvae_convt_small_fwd(p(x), p(w), p(b), p(y), N, 16, 16, 32, 3, 2, st())))
-        print(f"N={N:6d} {tag:16s}: {t:7.1f} us   {mb / t:6.2f} TB/s algorithmic ({mb:.0f} MB)", flush=True)
+        print(f"N={N:6d} {tag:28s}: {t:7.1f} us   {mb / t:6.2f} TB/s algorithmic ({mb:.0f} MB)", flush=True)
+    g = torch.randn(N, 3, 32, 32, device="cuda")
+    gx = torch.empty_like(x)
+    mb = (2 * y.numel() + 2 * x.numel()) * 4 / 1e6
+    for dbg, tag in ((512, "dgrad SIMT direct"), (0, "dgrad tcgen05"), (1024, "dgrad tc, no epilogue ld/st"), (2048, "dgrad tc, no gather"),
+                     (4096, "dgrad tc, no g_pre image"), (2048 | 4096, "dgrad tc, no build"), (1024 | 2048, "dgrad tc, no epi, no gather"),
+                     (1024 | 4096, "dgrad tc, no epi, no g_pre"), (7168, "dgrad tc, skeleton")):
+        lib.mmvae_gemm_tc_set_mode(dbg << 8)
+        t = bench(lambda: _lib.check(lib.mmvae_convt_small_dgrad(p(g), p(y), p(w), p(x), p(gx), N, 16, 16, 32, 3, 2, st())))
+        print(f"N={N:6d} {tag:28s}: {t:7.1f} us   {mb / t:6.2f} TB/s algorithmic ({mb:.0f} MB)", flush=True)
 lib.mmvae_gemm_tc_set_mode(0)
