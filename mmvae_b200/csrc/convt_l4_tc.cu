@@ -68,19 +68,22 @@ convt_l4_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float* 
     uint8_t* a_ring = smem;                                          // L4_STAGES x (hi 16 KB + lo 16 KB)
     uint8_t* b_hi = a_ring + L4_STAGES * 2 * L4_TILE;                // 64 rows x 128 B
     uint8_t* b_lo = b_hi + L4_BROWS * 128;
-    float* out = (float*)(b_lo + L4_BROWS * 128);                    // [COUT][32][L4_PITCH]
-    uint64_t* bars = (uint64_t*)(out + OUT_SMEM);
+    float* out0 = (float*)(b_lo + L4_BROWS * 128);                   // 2 x [COUT][32][L4_PITCH]: image n in buffer n & 1
+    uint64_t* bars = (uint64_t*)(out0 + 2 * OUT_SMEM);
     uint64_t* full = bars;
     uint64_t* conv = bars + L4_STAGES;
     uint64_t* empty = bars + 2 * L4_STAGES;
     uint64_t* tfull = bars + 3 * L4_STAGES;
     uint64_t* tempty = tfull + L4_NACC;
-    uint32_t* tmem_slot = (uint32_t*)(tempty + L4_NACC);
+    uint64_t* img_full = tempty + L4_NACC;        // [2] scattered image complete (epilogue -> converter warps)
+    uint64_t* img_empty = img_full + 2;           // [2] image stored and zeroed again (converter -> epilogue warps)
+    uint32_t* tmem_slot = (uint32_t*)(img_empty + 2);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < L4_STAGES; ++s) { mbar_init(full + s, 1); mbar_init(conv + s, 4); mbar_init(empty + s, 1); }
         for (int a = 0; a < L4_NACC; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 4); }
+        for (int b = 0; b < 2; ++b) { mbar_init(img_full + b, 1); mbar_init(img_empty + b, 4); }
         mbar_fence_init();
         tma_prefetch_desc(&tmap_x);
     }
@@ -98,7 +101,7 @@ convt_l4_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float* 
         *(float*)(b_hi + off) = v;
         *(float*)(b_lo + off) = l4_tf32_lo(v);
     }
-    for (int i = threadIdx.x; i < OUT_SMEM; i += L4_THREADS) out[i] = 0.f;
+    for (int i = threadIdx.x; i < 2 * OUT_SMEM; i += L4_THREADS) out0[i] = 0.f;
     fence_proxy_async_smem();
     tc_fence_before_sync();
     __syncthreads();
@@ -138,8 +141,42 @@ convt_l4_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float* 
             umma_commit_elect(tfull + acc);
         }
     } else if (warp < 6) {
-        // ===== converter: lo tile beside the landed tile =====
+        // ===== converter: lo tile beside the landed tile; these warps also FINALIZE the images the epilogue warps have
+        // scattered (bias + activation + NCHW store + re-zero), one image behind, so that the scatter of image n+1
+        // overlaps the store of image n (two smem images; img_full / img_empty hand them over) =====
         const int tq = threadIdx.x - 64;
+        float bv[COUT];
+#pragma unroll
+        for (int c = 0; c < COUT; ++c) bv[c] = bias ? __ldg(bias + c) : 0.f;
+        auto finalize = [&](int n) {
+            float* out = out0 + (n & 1) * OUT_SMEM;
+            mbar_wait(img_full + (n & 1), (n >> 1) & 1);
+            if (!(dbg & 2)) {
+                const int img = blockIdx.x + n * gridDim.x;
+                // the smem rows are shifted by one column (position = ox + 1): thread (row, j) reads the aligned float4
+                // at positions 4j..4j+3 = columns 4j-1..4j+2 and takes column 4j+3 from its right neighbour's first
+                // element (the lane above; position 32 for the last float4 of a row) -> aligned 128-bit global stores
+                float4* dst = reinterpret_cast<float4*>(y + (long)img * OUT_FLOATS);
+#pragma unroll
+                for (int i = 0; i < OUT_FLOATS / 4 / 128; ++i) {
+                    const int q = tq + i * 128;                // float4 of the NCHW image: 256 per channel -> channel = i >> 1
+                    const int row = q >> 3, j = q & 7;
+                    float4* src = reinterpret_cast<float4*>(out + row * L4_PITCH + 4 * j);
+                    const float4 m = *src;
+                    float nx = __shfl_down_sync(0xffffffffu, m.x, 1);
+                    if (j == 7) nx = out[row * L4_PITCH + 32];
+                    const float b = bv[i >> 1];
+                    float4 o;
+                    o.x = l4_act_fast(m.y + b, act); o.y = l4_act_fast(m.z + b, act);
+                    o.z = l4_act_fast(m.w + b, act); o.w = l4_act_fast(nx + b, act);
+                    __stcs(dst + q, o);
+                    *src = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (j == 7) out[row * L4_PITCH + 32] = 0.f;
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(img_empty + (n & 1));
+        };
         for (int it = 0; it < my_tiles; ++it) {
             const int s = it % L4_STAGES;
             mbar_wait(full + s, (it / L4_STAGES) & 1);
@@ -155,17 +192,18 @@ convt_l4_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float* 
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(conv + s);
+            if ((it & 1) && it >= 3) finalize((it >> 1) - 1);   // one image behind the conversion
         }
+        if (my_imgs > 0) finalize(my_imgs - 1);
     } else {
-        // ===== epilogue: TMEM lane = input pixel; scatter-add into the smem output image, finalize every 2nd tile =====
+        // ===== epilogue: TMEM lane = input pixel; its 16*COUT values are added into the smem image of its output =====
         const int lane_base = (warp & 3) * 32, e = (warp - 6) * 32 + lane;
         const int p = lane_base + lane;                     // pixel of the tile
         const int ix = p & 15, iyl = p >> 4;                // column, row within the half image
-        float bv[COUT];
-#pragma unroll
-        for (int c = 0; c < COUT; ++c) bv[c] = bias ? __ldg(bias + c) : 0.f;
         for (int it = 0; it < my_tiles; ++it) {
-            const int acc = it % L4_NACC, half = it & 1;
+            const int acc = it % L4_NACC, half = it & 1, n = it >> 1;
+            float* out = out0 + (n & 1) * OUT_SMEM;
+            if (!half) mbar_wait(img_empty + (n & 1), ((n >> 1) & 1) ^ 1);   // image n-2 has left this buffer
             mbar_wait(tfull + acc, (it / L4_NACC) & 1);
             tc_fence_after_sync();
             const uint32_t tb = tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)(acc * 128);
@@ -239,30 +277,7 @@ convt_l4_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float* 
                 }
                 l4_bar_epi();
             }
-            if (half && !(dbg & 2)) {                          // every pixel of the image has been scattered
-                const int img = blockIdx.x + (it >> 1) * gridDim.x;
-                // the smem rows are shifted by one column (position = ox + 1): thread (row, j) reads the aligned float4
-                // at positions 4j..4j+3 = columns 4j-1..4j+2 and takes column 4j+3 from its right neighbour's first
-                // element (the lane above; position 32 for the last float4 of a row) -> aligned 128-bit global stores
-                float4* dst = reinterpret_cast<float4*>(y + (long)img * OUT_FLOATS);
-#pragma unroll
-                for (int i = 0; i < OUT_FLOATS / 4 / 128; ++i) {
-                    const int q = e + i * 128;                 // float4 of the NCHW image: 256 per channel -> channel = i >> 1
-                    const int row = q >> 3, j = q & 7;
-                    float4* src = reinterpret_cast<float4*>(out + row * L4_PITCH + 4 * j);
-                    const float4 m = *src;
-                    float nx = __shfl_down_sync(0xffffffffu, m.x, 1);
-                    if (j == 7) nx = out[row * L4_PITCH + 32];
-                    const float b = bv[i >> 1];
-                    float4 o;
-                    o.x = l4_act_fast(m.y + b, act); o.y = l4_act_fast(m.z + b, act);
-                    o.z = l4_act_fast(m.w + b, act); o.w = l4_act_fast(nx + b, act);
-                    __stcs(dst + q, o);
-                    *src = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (j == 7) out[row * L4_PITCH + 32] = 0.f;
-                }
-                l4_bar_epi();                                  // the image is zero again before the next scatter
-            }
+            if (half && e == 0) mbar_arrive(img_full + (n & 1));   // every pixel of image n has been scattered
         }
     }
     tc_fence_before_sync();
@@ -273,7 +288,7 @@ convt_l4_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float* 
 template <int COUT>
 static int l4_launch(const CUtensorMap& tm, const float* w, const float* bias, float* y, int N, int act, cudaStream_t st) {
     static bool attr_done = false;
-    constexpr int SMEM = L4_STAGES * 2 * L4_TILE + 2 * L4_BROWS * 128 + COUT * 32 * L4_PITCH * 4 + 256 + 1024;
+    constexpr int SMEM = L4_STAGES * 2 * L4_TILE + 2 * L4_BROWS * 128 + 2 * COUT * 32 * L4_PITCH * 4 + 256 + 1024;
     auto kern = convt_l4_fwd_tc_kernel<COUT>;
     if (!attr_done) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
@@ -552,5 +567,247 @@ int mmvae_convt_l4_dgrad_tc(const float* g, const float* y_act, const float* w, 
     const int grid = N < MMVAE_NUM_SMS ? N : MMVAE_NUM_SMS;
     kern<<<grid, L4D_THREADS, SMEM, st>>>(g, y_act, w, x_mask, gx, N, act, (mmvae_tc_dbg_bits() >> 10) & 7);
     MMVAE_LAUNCH_CHECK("convt_l4_dgrad_tc");
+    return 0;
+}
+
+// =====================================================================================================================
+// wgrad of the same layer on tcgen05: gw[ci,co,ky,kx] = sum_pixels x[pixel,ci] * G[pixel,(ky,kx,co)] (+ gb[co] = sum g_pre)
+// as D[m = (ky,kx,co)][n = ci] with K = pixels.  Per 32-pixel k-block ("atom"): A = G^T, K-major rows m with the 32
+// pixels contiguous, gathered from the zero-bordered g_pre image in shared memory (hi and lo) by ONE builder warp per
+// atom (8 warps = the 8 atoms of an image); B = the x rows as an MN-major TMA box (32 pixels x 32 channels), lo written
+// beside it by the same warp.  8 UMMAs per atom (hi*[hi|lo] N = 64 + lo*hi N = 32, M = 128 with rows >= 48 unused).
+// The TMEM accumulation chain is drained into registers every 4 images (128 UMMAs per accumulator: the tensor core
+// truncates its fp32 accumulate, see gemm_tc.cu), double-buffered so the UMMAs never wait for the drain.  Each CTA writes
+// one partial in the layout of convt_small_wgrad_reduce (fixed-order, deterministic).
+// Warp roles (448 threads): 0 producer (g / y bulk copies, x TMA boxes), 1 UMMA issuer, 2-5 + 10-13 builders, 6-9 drain.
+// =====================================================================================================================
+#define L4W_THREADS 448
+#define L4W_STAGES 4
+#define L4W_ASTAGE 16384                  // A_hi rows 0..47 at +0, A_lo at +8192 (UMMA reads 128 rows: the tail is unused)
+#define L4W_BSTAGE 8192                   // B_hi 4 KB | B_lo 4 KB
+#define L4W_CHAIN 4                       // images per TMEM accumulation chain
+
+int mmvae_tc_tmap_mn(CUtensorMap* m, const float* base, long krows, long ncols, int box_rows);   // gemm_tc.cu
+
+template <int COUT>
+__global__ void __launch_bounds__(L4W_THREADS, 1)
+convt_l4_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float* __restrict__ g,
+                         const float* __restrict__ y_act, float* __restrict__ part, int n_img, int act) {
+    constexpr int KT = 16 * COUT;                       // 48 rows of D
+    constexpr int IMG = COUT * 1024;
+    constexpr int PIMG = COUT * 34 * L4D_PITCH;
+    constexpr int TOT = 32 * COUT * 16;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* a_ring = smem;
+    uint8_t* b_ring = a_ring + L4W_STAGES * L4W_ASTAGE;
+    float* raw = (float*)(b_ring + L4W_STAGES * L4W_BSTAGE);
+    float* pimg = raw + 2 * 2 * IMG;
+    float* bias_part = pimg + ((PIMG + 3) & ~3);                     // [8 warps][COUT]
+    uint64_t* bars = (uint64_t*)(bias_part + 32);
+    uint64_t* raw_full = bars;                 // [2]
+    uint64_t* raw_empty = bars + 2;            // [2] count 8
+    uint64_t* b_full = bars + 4;               // [STAGES] TMA
+    uint64_t* st_full = bars + 4 + L4W_STAGES; // [STAGES] count 1 (the atom's builder warp)
+    uint64_t* st_empty = bars + 4 + 2 * L4W_STAGES;
+    uint64_t* tfull = bars + 4 + 3 * L4W_STAGES;        // [2]
+    uint64_t* tempty = tfull + 2;                       // [2] count 4
+    uint32_t* tmem_slot = (uint32_t*)(tempty + 2);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool has_y = y_act != nullptr && act != MMVAE_ACT_NONE;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < 2; ++s) { mbar_init(raw_full + s, 1); mbar_init(raw_empty + s, 8); mbar_init(tfull + s, 1); mbar_init(tempty + s, 4); }
+        for (int s = 0; s < L4W_STAGES; ++s) { mbar_init(b_full + s, 1); mbar_init(st_full + s, 1); mbar_init(st_empty + s, 1); }
+        mbar_fence_init();
+        tma_prefetch_desc(&tmap_x);
+    }
+    if (warp == 1) { tmem_alloc(tmem_slot, 128); tmem_relinquish(); }
+    for (int i = threadIdx.x; i < PIMG; i += L4W_THREADS) pimg[i] = 0.f;
+    // rows 48..127 of the A tiles are read by the M = 128 UMMAs but never used: keep them finite
+    for (int i = threadIdx.x; i < (L4W_STAGES * L4W_ASTAGE + L4W_STAGES * L4W_BSTAGE) / 4; i += L4W_THREADS) ((float*)a_ring)[i] = 0.f;
+    fence_proxy_async_smem();
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+    const int my_imgs = (n_img - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int chains = (my_imgs + L4W_CHAIN - 1) / L4W_CHAIN;
+
+    if (warp == 0) {
+        // ===== producer =====
+        auto load_raw = [&](int j) {
+            const int s = j & 1;
+            const long img = blockIdx.x + (long)j * gridDim.x;
+            mbar_wait(raw_empty + s, ((j >> 1) & 1) ^ 1);
+            if (lane == 0) {
+                mbar_arrive_expect_tx(raw_full + s, (has_y ? 2 : 1) * IMG * 4);
+                bulk_load_1d(raw + s * 2 * IMG, g + img * IMG, IMG * 4, raw_full + s);
+                if (has_y) bulk_load_1d(raw + s * 2 * IMG + IMG, y_act + img * IMG, IMG * 4, raw_full + s);
+            }
+            __syncwarp();
+        };
+        if (my_imgs > 0) load_raw(0);
+        for (int j = 0; j < my_imgs; ++j) {
+            if (j + 1 < my_imgs) load_raw(j + 1);
+            const long img = blockIdx.x + (long)j * gridDim.x;
+#pragma unroll 1
+            for (int a = 0; a < 8; ++a) {
+                const int s = a & 3, u = 2 * j + (a >> 2);
+                mbar_wait(st_empty + s, (u & 1) ^ 1);
+                mbar_arrive_expect_tx_elect(b_full + s, 4096);
+                tma_load_2d_elect(smem_u32(b_ring + s * L4W_BSTAGE), &tmap_x, b_full + s, 0, (int)(img * 256 + a * 32));
+            }
+        }
+    } else if (warp == 1) {
+        // ===== UMMA issuer =====
+        constexpr uint32_t idesc64 = umma_idesc_tf32(128, 64, 0, 1), idesc32 = umma_idesc_tf32(128, 32, 0, 1);
+        const uint64_t da0 = umma_smem_desc(smem_u32(a_ring), 16, 1024, 2);
+        const uint64_t db0 = umma_smem_desc(smem_u32(b_ring), 4096, 512, 1);      // MN-major, SWIZZLE_128B_BASE32B
+        for (int j = 0; j < my_imgs; ++j) {
+            const int c = j / L4W_CHAIN, acc = c & 1;
+            if (j % L4W_CHAIN == 0) {
+                mbar_wait(tempty + acc, ((c >> 1) & 1) ^ 1);
+                tc_fence_after_sync();
+            }
+            const uint32_t d = tmem_base + acc * 64;
+#pragma unroll 1
+            for (int a = 0; a < 8; ++a) {
+                const int s = a & 3, u = 2 * j + (a >> 2);
+                mbar_wait(st_full + s, u & 1);
+                tc_fence_after_sync();
+                const uint64_t dah = da0 + (uint64_t)((s * L4W_ASTAGE) >> 4), dal = dah + (8192 >> 4);
+                const uint64_t db = db0 + (uint64_t)((s * L4W_BSTAGE) >> 4);
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk) {
+                    const uint32_t first = !(j % L4W_CHAIN == 0 && a == 0 && kk == 0);
+                    umma_tf32_elect(d, dah + kk * 2, db + kk * (1024 >> 4), idesc64, first);       // hi*hi | hi*lo
+                    umma_tf32_elect(d + 32, dal + kk * 2, db + kk * (1024 >> 4), idesc32, 1);      // lo*hi
+                }
+                umma_commit_elect(st_empty + s);
+            }
+            if (j % L4W_CHAIN == L4W_CHAIN - 1 || j == my_imgs - 1) umma_commit_elect(tfull + acc);
+        }
+    } else if (warp < 6 || warp >= 10) {
+        // ===== builders: warp w owns atom w (pixels 32w..32w+31) of every image =====
+        const int w = warp < 6 ? warp - 2 : warp - 6;                // 0..7
+        const int tb = w * 32 + lane;                                // 0..255
+        const int c = lane & 7, ml = lane >> 3;                      // 16-byte pixel chunk of the atom, row within a group of 4
+        const int iy = 2 * w + (c >> 2), ix0 = (c & 3) * 4;
+        float bs[COUT];
+#pragma unroll
+        for (int co = 0; co < COUT; ++co) bs[co] = 0.f;
+        for (int j = 0; j < my_imgs; ++j) {
+            const int rs = j & 1;
+            mbar_wait(raw_full + rs, (j >> 1) & 1);
+            const float* gi = raw + rs * 2 * IMG;
+            const float* yi = gi + IMG;
+#pragma unroll
+            for (int q = 0; q < IMG / 256; ++q) {
+                const int e = tb + q * 256, co = e >> 10, oy = (e >> 5) & 31, ox = e & 31;
+                float v = gi[e];
+                if (has_y) {
+                    const float yy = yi[e];
+                    v *= (act == MMVAE_ACT_SIGMOID) ? yy * (1.f - yy) : (yy > 0.f ? 1.f : 0.f);
+                }
+                pimg[(co * 34 + oy + 1) * L4D_PITCH + ox + 1] = v;
+                bs[q >> 2] += v;                                     // 1024 elements per channel = 4 values of q
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(raw_empty + rs);
+            l4_bar_build();
+            const int s = w & 3, u = 2 * j + (w >> 2);
+            mbar_wait(st_empty + s, (u & 1) ^ 1);
+            uint8_t* ah = a_ring + s * L4W_ASTAGE;
+            const float* p0 = pimg + (2 * iy) * L4D_PITCH + 2 * ix0;
+#pragma unroll
+            for (int jj = 0; jj < KT / 4; ++jj) {
+                const int m = 4 * jj + ml, tap = m / COUT, co = m - tap * COUT, ky = tap >> 2, kx = tap & 3;
+                const float* pp = p0 + (co * 34 + ky) * L4D_PITCH + kx;
+                const float4 v = make_float4(pp[0], pp[2], pp[4], pp[6]);
+                uint8_t* dst = ah + m * 128 + ((c ^ (m & 7)) << 4);
+                *reinterpret_cast<float4*>(dst) = v;
+                *reinterpret_cast<float4*>(dst + 8192) = make_float4(l4_tf32_lo(v.x), l4_tf32_lo(v.y), l4_tf32_lo(v.z), l4_tf32_lo(v.w));
+            }
+            mbar_wait(b_full + s, u & 1);
+            float4* bh = reinterpret_cast<float4*>(b_ring + s * L4W_BSTAGE);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const float4 v = bh[lane + 32 * q];
+                bh[256 + lane + 32 * q] = make_float4(l4_tf32_lo(v.x), l4_tf32_lo(v.y), l4_tf32_lo(v.z), l4_tf32_lo(v.w));
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(st_full + s);
+            l4_bar_build();
+        }
+#pragma unroll
+        for (int co = 0; co < COUT; ++co) {
+            const float t = warp_sum(bs[co]);
+            if (lane == 0) bias_part[w * COUT + co] = t;
+        }
+        l4_bar_build();
+        if (w == 0 && lane < COUT) {
+            float t = 0.f;
+            for (int k = 0; k < 8; ++k) t += bias_part[k * COUT + lane];
+            part[(long)blockIdx.x * (TOT + COUT) + TOT + lane] = t;
+        }
+    } else {
+        // ===== drain: TMEM lane = row m of D; registers accumulate the chains =====
+        const int lane_base = (warp & 3) * 32, m = lane_base + lane;
+        float accv[32];
+#pragma unroll
+        for (int n = 0; n < 32; ++n) accv[n] = 0.f;
+        for (int c = 0; c < chains; ++c) {
+            const int acc = c & 1;
+            mbar_wait(tfull + acc, (c >> 1) & 1);
+            tc_fence_after_sync();
+            const uint32_t tbm = tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)(acc * 64);
+            uint32_t rb[32], rsm[32];
+            l4_tmem_ld16_nowait(tbm, rb);
+            l4_tmem_ld16_nowait(tbm + 16, rb + 16);
+            l4_tmem_ld16_nowait(tbm + 32, rsm);
+            l4_tmem_ld16_nowait(tbm + 48, rsm + 16);
+            l4_tmem_wait_ld();
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty + acc);
+#pragma unroll
+            for (int n = 0; n < 32; ++n) accv[n] += __uint_as_float(rb[n]) + __uint_as_float(rsm[n]);
+        }
+        if (m < KT) {
+            const int tap = m / COUT, co = m - tap * COUT;
+            float* dst = part + (long)blockIdx.x * (TOT + COUT);
+#pragma unroll
+            for (int n = 0; n < 32; ++n) dst[(n * COUT + co) * 16 + tap] = accv[n];
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, 128);
+}
+
+// partials for convt_small_wgrad_reduce.  -> 0 launched, -1 not applicable, > 0 error
+int mmvae_convt_l4_wgrad_tc(const float* x, const float* g, const float* y_act, float* part, int P, int N, int H, int W,
+                            int Cin, int Cout, int act, cudaStream_t st) {
+    if (H != 16 || W != 16 || Cin != 32 || Cout != 3) return -1;
+    if (((uintptr_t)x & 15) || ((uintptr_t)g & 15) || ((uintptr_t)y_act & 15) || (mmvae_tc_dbg_bits() & 512)) return -1;
+    if (P != (N < MMVAE_NUM_SMS ? N : MMVAE_NUM_SMS)) return -1;
+    CUtensorMap tm;
+    const int rc = mmvae_tc_tmap_mn(&tm, x, (long)N * 256, 32, 32);
+    if (rc < 0) return -1;
+    if (rc) return mmvae_set_error(1, "convt_l4_wgrad_tc: cuTensorMapEncodeTiled failed with %d", rc);
+    constexpr int COUT = 3;
+    constexpr int SMEM = L4W_STAGES * (L4W_ASTAGE + L4W_BSTAGE) + 2 * 2 * COUT * 1024 * 4 +
+                         ((COUT * 34 * L4D_PITCH + 3) & ~3) * 4 + 128 + 256 + 1024 + 8192;   // + slack read by the last A_lo tile
+    static bool attr_done = false;
+    auto kern = convt_l4_wgrad_tc_kernel<COUT>;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+        if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "convt_l4_wgrad_tc: smem attribute: %s", cudaGetErrorString(e));
+        attr_done = true;
+    }
+    kern<<<P, L4W_THREADS, SMEM, st>>>(tm, g, y_act, part, N, act);
+    MMVAE_LAUNCH_CHECK("convt_l4_wgrad_tc");
     return 0;
 }

@@ -431,6 +431,11 @@ int mmvae_convt_l4_fwd_tc(const float* x, const float* w, const float* bias, flo
 int mmvae_convt_l4_dgrad_tc(const float* g, const float* y_act, const float* w, const float* x_mask, float* gx, int N,
                             int H, int W, int Cin, int Cout, int act, cudaStream_t st);          // convt_l4_tc.cu
 
+int mmvae_convt_l4_wgrad_tc(const float* x, const float* g, const float* y_act, float* part, int P, int N, int H, int W,
+                            int Cin, int Cout, int act, cudaStream_t st);                        // convt_l4_tc.cu
+int mmvae_tc_dbg_bits();                                                                         // gemm_tc.cu
+static inline int mmvae_tc_dbg_bits_() { return mmvae_tc_dbg_bits(); }
+
 #define CS_SWITCH(COUTV, FN, ...)                         \
     ((COUTV) == 1 ? FN<1>(__VA_ARGS__) : (COUTV) == 2 ? FN<2>(__VA_ARGS__) : (COUTV) == 3 ? FN<3>(__VA_ARGS__) : FN<4>(__VA_ARGS__))
 
@@ -526,9 +531,13 @@ extern "C" int mmvae_convt_small_wgrad(const float* x, const float* g, const flo
     MMVAE_REQUIRE(mmvae_convt_small_supported(H, W, Cin, Cout) == 2, "convt_small_wgrad: unsupported shape (needs Cin == 32)");
     const size_t smem = csw_smem_bytes(H, W, Cin, Cout, y_act != nullptr);
     const int P = cs_wgrad_ctas(N);
-    const int rc = CS_SWITCH(Cout, cs_wgrad, x, g, y_act, workspace, P, N, H, W, act, smem, (cudaStream_t)stream);
-    if (rc) return rc;
-    MMVAE_LAUNCH_CHECK("convt_small_wgrad");
+    int rc = (mmvae_tc_dbg_bits_() & 16384) ? mmvae_convt_l4_wgrad_tc(x, g, y_act, workspace, P, N, H, W, Cin, Cout, act, (cudaStream_t)stream) : -1;
+    if (rc > 0) return rc;
+    if (rc < 0) {
+        rc = CS_SWITCH(Cout, cs_wgrad, x, g, y_act, workspace, P, N, H, W, act, smem, (cudaStream_t)stream);
+        if (rc) return rc;
+        MMVAE_LAUNCH_CHECK("convt_small_wgrad");
+    }
     const int tot = Cin * Cout * 16;
     convt_small_wgrad_reduce<<<ceil_div_i(tot + Cout, 128), 128, 0, (cudaStream_t)stream>>>(workspace, gw, gb, P, tot, Cout);
     MMVAE_LAUNCH_CHECK("convt_small_wgrad_reduce");

@@ -430,6 +430,11 @@ int mmvae_tc_tmap_rows(CUtensorMap* m, const float* base, long rows, long cols, 
     return make_tmap(m, base, rows, cols, box_rows, false);
 }
 int mmvae_tc_dbg_bits() { return g_tc_dbg; }
+// MN-major operand [krows, ncols] (ncols contiguous), box = 32 columns x box_rows k-rows, SWIZZLE_128B_ATOM_32B
+int mmvae_tc_tmap_mn(CUtensorMap* m, const float* base, long krows, long ncols, int box_rows) {
+    if (!tc_init()) return -1;
+    return make_tmap(m, base, krows, ncols, box_rows, true);
+}
 
 struct TcPlan { int BN, S, kb_per; bool swap; };
 

@@ -135,6 +135,33 @@ def test_convT_last_layer_tensor_core_forward_is_deterministic_and_matches_simt(
     assert (y1 - y_simt).abs().max().item() < 2e-6
 
 
+@pytest.mark.parametrize("N", [1, 7, 333, 1200])
+def test_convT_last_layer_tensor_core_wgrad(ops, N):
+    """convt_l4_wgrad_tc_kernel against fp64 autograd and the SIMT kernel (chains of 4 images per accumulator, several
+    chains per CTA at N = 1200)."""
+    from mmvae_b200 import _lib
+    lib = _lib.load()
+    x = _rand(N, 16, 16, 32, seed=5).relu().permute(0, 3, 1, 2).requires_grad_()
+    w = _rand(32, 3, 4, 4, seed=6, scale=0.1).requires_grad_()
+    b = _rand(3, seed=7).requires_grad_()
+    gy = _rand(N, 3, 32, 32, seed=8)
+    xd, wd, bd = (t.detach().double().requires_grad_() for t in (x, w, b))
+    yr = torch.sigmoid(F.conv_transpose2d(xd, wd, bd, stride=2, padding=1))
+    rw, rb = torch.autograd.grad(yr, (wd, bd), gy.double())
+    res = {}
+    for bit in (0, 16384):
+        old = lib.mmvae_gemm_tc_set_mode(bit << 8)
+        try:
+            y = ops.ConvT2dAct.apply(x, w, b, 2, 1, "sigmoid", True, False)
+            res[bit] = torch.autograd.grad(y, (w, b), gy)
+            again = torch.autograd.grad(ops.ConvT2dAct.apply(x, w, b, 2, 1, "sigmoid", True, False), (w, b), gy)
+            assert torch.equal(res[bit][0], again[0]) and torch.equal(res[bit][1], again[1])     # deterministic
+        finally:
+            lib.mmvae_gemm_tc_set_mode(old)
+        assert rel_err(res[bit][0], rw) < 5e-6 and rel_err(res[bit][1], rb) < 5e-6, bit
+    assert rel_err(res[16384][0], res[0][0]) < 5e-6
+
+
 def test_convT2d_chain_fused_relu_backward(ops):
     """Decoder_VAE_SVHN's chaining: each layer hands the layer below the gradient w.r.t. its PRE-activation."""
     N = 9
