@@ -582,8 +582,9 @@ int mmvae_convt_l4_dgrad_tc(const float* g, const float* y_act, const float* w, 
 // Warp roles (448 threads): 0 producer (g / y bulk copies, x TMA boxes), 1 UMMA issuer, 2-5 + 10-13 builders, 6-9 drain.
 // =====================================================================================================================
 #define L4W_THREADS 448
-#define L4W_STAGES 4
-#define L4W_ASTAGE 16384                  // A_hi rows 0..47 at +0, A_lo at +8192 (UMMA reads 128 rows: the tail is unused)
+#define L4W_STAGES 8                      // one stage per atom of an image = per builder warp
+#define L4W_ASTAGE 12288                  // A_hi rows 0..47 at +0 (6 KB), A_lo at +6144 (UMMA reads 128 rows: the tail is unused)
+#define L4W_ALO 6144
 #define L4W_BSTAGE 8192                   // B_hi 4 KB | B_lo 4 KB
 #define L4W_CHAIN 4                       // images per TMEM accumulation chain
 
@@ -591,8 +592,8 @@ int mmvae_tc_tmap_mn(CUtensorMap* m, const float* base, long krows, long ncols, 
 
 template <int COUT>
 __global__ void __launch_bounds__(L4W_THREADS, 1)
-convt_l4_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float* __restrict__ g,
-                         const float* __restrict__ y_act, float* __restrict__ part, int n_img, int act) {
+convt_l4_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float* __restrict__ x_base,
+                         const float* __restrict__ g, const float* __restrict__ y_act, float* __restrict__ part, int n_img, int act, int dbg) {
     constexpr int KT = 16 * COUT;                       // 48 rows of D
     constexpr int IMG = COUT * 1024;
     constexpr int PIMG = COUT * 34 * L4D_PITCH;
@@ -647,13 +648,24 @@ convt_l4_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float
             }
             __syncwarp();
         };
+        // x boxes can only be requested when their stage is free (one use per image), so their latency is exposed unless
+        // the rows are already in L2: pull the x block of the image after next (32 KB) into L2 now
+        auto prefetch_x = [&](int j) {
+            if (lane == 0 && j < my_imgs) {
+                const float* pf = x_base + (blockIdx.x + (long)j * gridDim.x) * 256 * 32;
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(pf), "r"(256 * 32 * 4) : "memory");
+            }
+        };
+        prefetch_x(0);
+        prefetch_x(1);
         if (my_imgs > 0) load_raw(0);
         for (int j = 0; j < my_imgs; ++j) {
+            prefetch_x(j + 2);
             if (j + 1 < my_imgs) load_raw(j + 1);
             const long img = blockIdx.x + (long)j * gridDim.x;
 #pragma unroll 1
             for (int a = 0; a < 8; ++a) {
-                const int s = a & 3, u = 2 * j + (a >> 2);
+                const int s = a, u = j;
                 mbar_wait(st_empty + s, (u & 1) ^ 1);
                 mbar_arrive_expect_tx_elect(b_full + s, 4096);
                 tma_load_2d_elect(smem_u32(b_ring + s * L4W_BSTAGE), &tmap_x, b_full + s, 0, (int)(img * 256 + a * 32));
@@ -673,13 +685,13 @@ convt_l4_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float
             const uint32_t d = tmem_base + acc * 64;
 #pragma unroll 1
             for (int a = 0; a < 8; ++a) {
-                const int s = a & 3, u = 2 * j + (a >> 2);
+                const int s = a, u = j;
                 mbar_wait(st_full + s, u & 1);
                 tc_fence_after_sync();
-                const uint64_t dah = da0 + (uint64_t)((s * L4W_ASTAGE) >> 4), dal = dah + (8192 >> 4);
+                const uint64_t dah = da0 + (uint64_t)((s * L4W_ASTAGE) >> 4), dal = dah + (L4W_ALO >> 4);
                 const uint64_t db = db0 + (uint64_t)((s * L4W_BSTAGE) >> 4);
 #pragma unroll
-                for (int kk = 0; kk < 4; ++kk) {
+                for (int kk = 0; kk < ((dbg & 4) ? 1 : 4); ++kk) {
                     const uint32_t first = !(j % L4W_CHAIN == 0 && a == 0 && kk == 0);
                     umma_tf32_elect(d, dah + kk * 2, db + kk * (1024 >> 4), idesc64, first);       // hi*hi | hi*lo
                     umma_tf32_elect(d + 32, dal + kk * 2, db + kk * (1024 >> 4), idesc32, 1);      // lo*hi
@@ -703,7 +715,7 @@ convt_l4_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float
             const float* gi = raw + rs * 2 * IMG;
             const float* yi = gi + IMG;
 #pragma unroll
-            for (int q = 0; q < IMG / 256; ++q) {
+            for (int q = 0; q < ((dbg & 2) ? 0 : IMG / 256); ++q) {          // dbg: ablation bits of tools/l4_time.py
                 const int e = tb + q * 256, co = e >> 10, oy = (e >> 5) & 31, ox = e & 31;
                 float v = gi[e];
                 if (has_y) {
@@ -716,18 +728,18 @@ convt_l4_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float
             __syncwarp();
             if (lane == 0) mbar_arrive(raw_empty + rs);
             l4_bar_build();
-            const int s = w & 3, u = 2 * j + (w >> 2);
+            const int s = w, u = j;
             mbar_wait(st_empty + s, (u & 1) ^ 1);
             uint8_t* ah = a_ring + s * L4W_ASTAGE;
             const float* p0 = pimg + (2 * iy) * L4D_PITCH + 2 * ix0;
 #pragma unroll
-            for (int jj = 0; jj < KT / 4; ++jj) {
+            for (int jj = 0; jj < ((dbg & 1) ? 0 : KT / 4); ++jj) {
                 const int m = 4 * jj + ml, tap = m / COUT, co = m - tap * COUT, ky = tap >> 2, kx = tap & 3;
                 const float* pp = p0 + (co * 34 + ky) * L4D_PITCH + kx;
                 const float4 v = make_float4(pp[0], pp[2], pp[4], pp[6]);
                 uint8_t* dst = ah + m * 128 + ((c ^ (m & 7)) << 4);
                 *reinterpret_cast<float4*>(dst) = v;
-                *reinterpret_cast<float4*>(dst + 8192) = make_float4(l4_tf32_lo(v.x), l4_tf32_lo(v.y), l4_tf32_lo(v.z), l4_tf32_lo(v.w));
+                *reinterpret_cast<float4*>(dst + L4W_ALO) = make_float4(l4_tf32_lo(v.x), l4_tf32_lo(v.y), l4_tf32_lo(v.z), l4_tf32_lo(v.w));
             }
             mbar_wait(b_full + s, u & 1);
             float4* bh = reinterpret_cast<float4*>(b_ring + s * L4W_BSTAGE);
@@ -799,7 +811,7 @@ int mmvae_convt_l4_wgrad_tc(const float* x, const float* g, const float* y_act, 
     if (rc) return mmvae_set_error(1, "convt_l4_wgrad_tc: cuTensorMapEncodeTiled failed with %d", rc);
     constexpr int COUT = 3;
     constexpr int SMEM = L4W_STAGES * (L4W_ASTAGE + L4W_BSTAGE) + 2 * 2 * COUT * 1024 * 4 +
-                         ((COUT * 34 * L4D_PITCH + 3) & ~3) * 4 + 128 + 256 + 1024 + 8192;   // + slack read by the last A_lo tile
+                         ((COUT * 34 * L4D_PITCH + 3) & ~3) * 4 + 128 + 512 + 1024;   // the A over-read of the last stage lands in the B ring
     static bool attr_done = false;
     auto kern = convt_l4_wgrad_tc_kernel<COUT>;
     if (!attr_done) {
@@ -807,7 +819,7 @@ int mmvae_convt_l4_wgrad_tc(const float* x, const float* g, const float* y_act, 
         if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "convt_l4_wgrad_tc: smem attribute: %s", cudaGetErrorString(e));
         attr_done = true;
     }
-    kern<<<P, L4W_THREADS, SMEM, st>>>(tm, g, y_act, part, N, act);
+    kern<<<P, L4W_THREADS, SMEM, st>>>(tm, x, g, y_act, part, N, act, (mmvae_tc_dbg_bits() >> 10) & 7);
     MMVAE_LAUNCH_CHECK("convt_l4_wgrad_tc");
     return 0;
 }

@@ -42,7 +42,9 @@ for N in (7680, 32768):
     gw = torch.empty_like(w); gb = torch.empty(3, device="cuda")
     ws = torch.empty(lib.mmvae_convt_small_wgrad_workspace_bytes(N, 32, 3) // 4, device="cuda")
     mb = (2 * y.numel() + x.numel()) * 4 / 1e6
-    for dbg, tag in ((0, "wgrad SIMT direct"), (16384, "wgrad tcgen05")):
+    for dbg, tag in ((0, "wgrad SIMT direct"), (16384, "wgrad tcgen05"), (16384 | 1024, "wgrad tc, no gather"),
+                     (16384 | 2048, "wgrad tc, no g_pre image"), (16384 | 4096, "wgrad tc, 1/4 of the UMMAs"),
+                     (16384 | 7168, "wgrad tc, skeleton")):
         lib.mmvae_gemm_tc_set_mode(dbg << 8)
         t = bench(lambda: _lib.check(lib.mmvae_convt_small_wgrad(p(x), p(g), p(y), p(gw), p(gb), p(ws), N, 16, 16, 32, 3, 2, st())))
         print(f"N={N:6d} {tag:28s}: {t:7.1f} us   {mb / t:6.2f} TB/s algorithmic ({mb:.0f} MB)", flush=True)
