@@ -782,3 +782,134 @@ def mopoe_joint_ll_from_uni(spec, sd, data, cond_mod, K, batch_size_K, noise):
     """MOEPOE.compute_joint_ll_from_uni, moepoe.py:160-214: as the MVAE one but ln K is NOT subtracted (:212)."""
     mean, ll = mvae_joint_ll_from_uni(spec, sd, data, cond_mod, K, batch_size_K, noise)
     return mean + math.log(K), ll + math.log(K)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# MMVAE-NF (mixture of flow-transformed unimodal posteriors) — models/mmvae_nf/mmvae_nf.py; objective `m_elbo_nf`
+# ----------------------------------------------------------------------------------------------------------
+def spec_mmvae_nf_mnist_svhn(latent_dim=20, n_made_blocks=2, llik_scaling=0.0):
+    """mmvae_nf/mnist_svhn.py:41-68: my_VAE_IAF unimodal VAEs (pythae MLP / SVHN conv nets), Gaussian prior."""
+    s = (3 * 32 * 32) / (1 * 28 * 28) if llik_scaling == 0 else llik_scaling
+    return Spec(shapes=[(1, 28, 28), (3, 32, 32)], enc=["mlp", "svhn"], dec=["mlp", "svhn"], latent_dim=latent_dim,
+                dist="normal", recon_losses=("normal", "normal"), lik_scaling=(s, 1.0), vae="my_VAE_IAF",
+                n_made_blocks=n_made_blocks)
+
+
+def mmvae_nf_forward(spec: Spec, sd, x, noise):
+    """MMVAE_NF.forward, mmvae_nf.py:30-62 -> (ln_qz_xs [M x (B,)], zs [M x (B,L)], recons[e][d]).
+    ln q(z_m|x_m) = sum_L -1/2 (lv + (z0-mu)^2 / e^lv) - log|det J| (no 2 pi term, :47-50).  noise: M tensors (B,L)."""
+    ln_q, zs = [], []
+    for m in range(spec.M):
+        mu, lv, _, z0, z, ladj = vae_sample(spec, sd, m, x[m], noise[m])
+        ln_q.append((-0.5 * (lv + torch.pow(z0 - mu, 2) / torch.exp(lv))).sum(dim=1) - ladj)
+        zs.append(z)
+    recons = [[decode(spec, sd, d, zs[e]) for d in range(spec.M)] for e in range(spec.M)]
+    return ln_q, zs, recons
+
+
+def m_elbo_nf(spec: Spec, sd, x, noise):
+    """objectives.py:463-479.  `row[e].sum()` (:471) indexes the (B,) tensor ln q(z_e|x_e) with the MODALITY index e, so
+    only datapoint e's log-density enters the KL term — the reference's arithmetic, reproduced as is."""
+    ln_q, zs, recons = mmvae_nf_forward(spec, sd, x, noise)
+    elbo = 0
+    for e in range(spec.M):
+        kld = ln_q[e][e].sum() - (-0.5 * torch.sum(zs[e] ** 2))
+        elbo = elbo - kld / spec.M
+        for d in range(spec.M):
+            elbo = elbo + (-0.5 * torch.sum((recons[e][d] - x[d]) ** 2)) / spec.M * spec.lik_scaling[d]
+    return elbo
+
+
+# ----------------------------------------------------------------------------------------------------------
+# product-of-experts SUBSET posteriors: density, Hamiltonian sampler, importance-sampled conditional likelihood
+# (jmvae_nf.py:272-437; mvae.py:268-327; modalities/trimodal.py:158-230)
+# ----------------------------------------------------------------------------------------------------------
+def jmvae_nf_poe_posterior(spec: Spec, sd, subset, z, data, divide_prior=True):
+    """JMVAE_NF.compute_poe_posterior value, jmvae_nf.py:294-329: sum_{m in subset} [log N(flow_m(z); mu_m, e^{lv_m}) +
+    log|det J_m|] - log p(z) (when divide_prior) -> (n,)."""
+    lnq = 0
+    if divide_prior:
+        lnq = lnq + (0.5 * (torch.pow(z, 2) + LOG2PI)).sum(dim=1)
+    for m in subset:
+        z0, ladj = flow_forward(spec, sd, m, z)
+        mu, lv = encode(spec, sd, m, data[m])
+        lnq = lnq + (-0.5 * (lv + LOG2PI + torch.pow(z0 - mu, 2) / torch.exp(lv))).sum(dim=1) + ladj
+    return lnq
+
+
+def jmvae_nf_poe_posterior_grad(spec: Spec, sd, subset, z, data, divide_prior=True):
+    """(value, d value.sum() / dz) as jmvae_nf.py:307,323-327."""
+    zz = z.clone().detach().requires_grad_(True)
+    with torch.enable_grad():
+        v = jmvae_nf_poe_posterior(spec, sd, subset, zz, data, divide_prior)
+        g = torch.autograd.grad(v.sum(), zz)[0]
+    return v.detach(), g
+
+
+def jmvae_nf_hmc_poe_subset(spec: Spec, sd, subset, data, K, z_init, gammas, accepts, n_lf=10, eps_lf=0.01,
+                            divide_prior=True):
+    """JMVAE_NF.sample_from_poe_subset, jmvae_nf.py:332-437.  data is repeated K times (row k*n+b); z_init (K*n,L) is
+    the mixture-of-experts start (sample_from_moe_subset), gammas [steps,(K*n,L)] the momenta, accepts [steps,(K*n,)]
+    the uniforms of the accept test.  -> (z [K,n,L], acceptance counts (K*n,))."""
+    n = len(data[0])
+    data = [torch.cat([d] * K) for d in data]
+    z0 = z_init
+    z = z0
+    acc_nbr = torch.zeros(len(z))
+    for gamma, u in zip(gammas, accepts):
+        rho = gamma
+        lnq, g = jmvae_nf_poe_posterior_grad(spec, sd, subset, z, data, divide_prior)
+        H0 = -lnq + 0.5 * torch.norm(rho, dim=1) ** 2
+        for _ in range(n_lf):
+            rho_ = rho - (eps_lf / 2) * (-g)
+            z = z + eps_lf * rho_
+            lnq, g = jmvae_nf_poe_posterior_grad(spec, sd, subset, z, data, divide_prior)
+            rho = rho_ - (eps_lf / 2) * (-g)
+        H = -lnq + 0.5 * torch.norm(rho, dim=1) ** 2
+        alpha = torch.exp(H0 - H)
+        moves = (u < alpha).to(z.dtype).reshape(-1, 1)
+        acc_nbr = acc_nbr + moves[:, 0]
+        z = z * moves + (1 - moves) * z0
+        z0 = z
+    return z.reshape(K, n, -1), acc_nbr
+
+
+def mvae_poe_posterior(spec: Spec, sd, subset, z, data):
+    """MVAE.compute_poe_posterior, mvae.py:304-327.  `poe` returns (mu, STD) and the density below reads the second value
+    as a log-variance — the reference's own arithmetic, reproduced as is."""
+    lq = 0
+    for m in subset:
+        mu_u, lv_u = encode(spec, sd, m, data[m])
+        t0, t1 = mvae_poe([mu_u], [lv_u])
+        lq = lq + (-0.5 * (t1 + LOG2PI + torch.pow(z - t0, 2) / torch.exp(t1))).sum(dim=1)
+    return lq - (-0.5 * (LOG2PI + torch.pow(z, 2))).sum(dim=1)
+
+
+def cond_ll_from_poe_subset(kind, spec: Spec, sd, data, subset, gen_mod, K, batch_size_K, i_s, noise):
+    """compute_cond_ll_from_poe_subset, modalities/trimodal.py:158-216.  kind: 'mvae' | 'jmvae_nf'.  i_s (B,) in {0,1}: the
+    member of the subset used as the importance distribution for each datapoint (np.random.randint, :184); noise
+    (B, nb*batch_size_K, L).  As in the reference, `lnpxs` is re-created inside the chunk loop (:188), so only the LAST
+    chunk enters the numerator while every chunk enters the normaliser.  -> (mean, per-datapoint (B,))."""
+    nb = K // batch_size_K
+    out = []
+    for i in range(len(data[0])):
+        a, o = subset[int(i_s[i])], subset[1 - int(i_s[i])]
+        norm, last = [], None
+        for n in range(nb):
+            eps = noise[i, n * batch_size_K:(n + 1) * batch_size_K]
+            rep = [torch.stack(batch_size_K * [data[m][i]]) for m in range(spec.M)]
+            if kind == "mvae":
+                mu_u, lv_u = encode(spec, sd, a, rep[a])
+                mu, std = mvae_poe([mu_u], [lv_u])
+                z = mu + eps * std
+                lnq = mvae_poe_posterior(spec, sd, [o], z, rep)
+            else:
+                z = vae_sample(spec, sd, a, rep[a], eps)[4]
+                lnq = jmvae_nf_poe_posterior(spec, sd, [o], z, rep, True)
+            recon = decode(spec, sd, gen_mod, z)
+            lpx = px_log_prob(spec.recon_losses[gen_mod], recon, data[gen_mod][i]).sum(dim=(1, 2, 3)) + lnq
+            norm.append(torch.logsumexp(lnq, dim=0))
+            last = torch.logsumexp(lpx, dim=0)
+        out.append(last - torch.logsumexp(torch.stack(norm), dim=0))
+    per = torch.stack(out)
+    return per.sum() / len(per), per

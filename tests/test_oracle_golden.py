@@ -132,3 +132,68 @@ def test_mopoe_matches_reference(name):
         for c in range(spec.M):
             mean, _ = O.mopoe_joint_ll_from_uni(spec, sd, x, c, K, bs, g[f"joint_from_{c}"]["noise"])
             assert abs(mean.item() - float(g[f"joint_from_{c}"]["value"])) < 1e-3
+
+
+def test_mmvae_nf_matches_reference():
+    """MMVAE-NF (models/mmvae_nf/mmvae_nf.py:30-62) forward and `m_elbo_nf` (objectives.py:463-479) with gradients."""
+    g, spec, sd = load_golden("mmvae_nf_ms")
+    x = g["x"]
+    lsd = leaf_sd(sd)
+    elbo = O.m_elbo_nf(spec, lsd, x, g["train"]["noise"])
+    elbo.backward()
+    ref = g["train"]["loss"].item()
+    assert abs(elbo.item() - ref) <= 1e-5 * abs(ref), (elbo.item(), ref)
+    check_digests({k: v.grad for k, v in lsd.items()}, g["train"]["grads"], GRAD_RTOL, "mmvae_nf_ms")
+    with torch.no_grad():
+        ln_q, zs, recons = O.mmvae_nf_forward(spec, sd, x, g["train"]["noise"])
+        for m in range(spec.M):
+            assert torch.allclose(ln_q[m], g["forward"]["ln_qz_xs"][m], rtol=1e-5, atol=1e-4), m
+            assert torch.allclose(zs[m], g["forward"]["zs"][m], rtol=1e-5, atol=1e-5), m
+            for d in range(spec.M):
+                ref_s = g["forward"]["recon_sums"][m][d]
+                assert abs(recons[m][d].double().sum().item() - ref_s) <= 1e-5 * abs(ref_s)
+
+
+def oracle_hmc_start(spec, sd, x, h):
+    """sample_from_moe_subset (jmvae_nf.py:272-291) on the K-times repeated data, with the recorded indices / noise."""
+    n = len(x[0])
+    rep = [torch.cat([d] * h["K"]) for d in x]
+    idx = h["indices"].numpy()
+    z_init = torch.zeros(n * h["K"], spec.latent_dim, dtype=x[0].dtype)
+    with torch.no_grad():
+        for j, m in enumerate(h["subset"]):
+            sel = torch.from_numpy(idx == m)
+            if sel.any():
+                z_init[sel] = O.vae_sample(spec, sd, m, rep[m][sel], h["init_noise"][j].to(x[0].dtype))[4]
+    return z_init
+
+
+@pytest.mark.parametrize("name", ["poe_mvae_msf", "poe_jnf_maf"])
+def test_poe_subset_matches_reference(name):
+    """PoE-subset density (jmvae_nf.py:294-329, mvae.py:304-327), its importance-sampled conditional likelihood
+    (modalities/trimodal.py:158-216) and the Hamiltonian sampler (jmvae_nf.py:332-437)."""
+    g, spec, sd = load_golden(name)
+    x, K, bs, kind = g["x"], g["K"], g["bs"], g["model"]
+    zq = g["posterior"]["z"]
+    for c in g["posterior"]["cases"]:
+        if kind == "mvae":
+            with torch.no_grad():
+                v = O.mvae_poe_posterior(spec, sd, c["subset"], zq, x)
+            assert torch.allclose(v, c["value"], rtol=1e-5, atol=1e-4)
+        else:
+            v, gr = O.jmvae_nf_poe_posterior_grad(spec, sd, c["subset"], zq, x, True)
+            assert torch.allclose(v, c["value"], rtol=1e-5, atol=1e-4)
+            assert torch.allclose(gr, c["grad"], rtol=1e-4, atol=1e-5)
+            with torch.no_grad():
+                v2 = O.jmvae_nf_poe_posterior(spec, sd, c["subset"], zq, x, False)
+            assert torch.allclose(v2, c["value_noprior"], rtol=1e-5, atol=1e-4)
+    with torch.no_grad():
+        for c in g["cond"]:
+            mean, _ = O.cond_ll_from_poe_subset(kind, spec, sd, x, c["subset"], c["gen_mod"], K, bs, c["i_s"], c["noise"])
+            assert abs(mean.item() - float(c["value"])) < 1e-3, (mean.item(), float(c["value"]))
+    if "hmc" in g:
+        h = g["hmc"]
+        z_init = oracle_hmc_start(spec, sd, x, h)
+        z, acc = O.jmvae_nf_hmc_poe_subset(spec, sd, h["subset"], x, h["K"], z_init, h["gammas"], h["accepts"], h["n_lf"],
+                                           h["eps_lf"], True)
+        assert torch.allclose(z, h["z"], rtol=1e-4, atol=1e-5), (z - h["z"]).abs().max()
