@@ -10,6 +10,7 @@ autograd bookkeeping, views and the final scalar sums.
 """
 import math
 
+import numpy as np
 import torch
 import torch.distributions as dist
 import torch.nn as nn
@@ -20,6 +21,7 @@ from .networks import (Decoder_AE_MLP, Decoder_VAE_SVHN, DoubleHeadJoint, Encode
                        LinearCCAEncoder, TwoStepsEncoder)
 from .vaes import VAE_IAF_Config, VAE_MAF_Config, VAEConfig, draw_noise, my_VAE, my_VAE_IAF, my_VAE_MAF
 
+LOG2PI = math.log(2 * math.pi)
 NEG_LOSS = {"normal": "neg_mse", "laplace": "neg_l1", "bernoulli": "neg_bce"}       # recon_loss_dict, objectives.py:177
 
 
@@ -166,6 +168,123 @@ class JMVAE_NF(Multi_VAES):
             lq = lq - ladj
         ll = self._is_loglik(z.contiguous(), data, range(self.mod), "external", lq_ext=lq.reshape(B, Ku), K_total=K)
         return {f"joint_ll_from_{cond_mod}": ll.mean()}
+
+
+    # ---- product-of-experts subset posteriors (jmvae_nf.py:272-437) ----------------------------------------------------
+    @torch.no_grad()
+    def sample_from_moe_subset(self, subset, data, indices=None, noise=None):
+        """jmvae_nf.py:272-291: one latent per datapoint from the mixture of the subset's unimodal posteriors.
+        indices: the modality drawn for each datapoint (np.random.choice(subset, n) when None); noise: one (n_m, L)
+        tensor per subset member."""
+        n = len(data[0])
+        if indices is None:
+            indices = np.random.choice(subset, size=n)
+        indices = torch.as_tensor(np.asarray(indices), device=data[0].device)
+        zs = torch.zeros((n, self.params.latent_dim), device=data[0].device)
+        for j, m in enumerate(subset):
+            sel = indices == m
+            if bool(sel.any()):
+                zs[sel] = self.vaes[m].sample(data[m][sel].contiguous(), noise=None if noise is None else noise[j], decode=False).z
+        return zs
+
+    @torch.no_grad()
+    def poe_experts(self, subset, data):
+        """(mu_m, log_var_m) of the subset's encoders.  They do not depend on z: the sampler evaluates them ONCE, where the
+        reference re-runs every encoder at each of the mcmc_steps * (n_lf + 1) density evaluations (jmvae_nf.py:317)."""
+        return {m: self.vaes[m].encode_raw(data[m]) for m in subset}
+
+    def compute_poe_posterior(self, subset, z_, data, divide_prior=True, grad=True, experts=None):
+        """jmvae_nf.py:294-329: ln q(z|X_s) = sum_{m in s} [ln N(flow_m(z); mu_m, e^{lv_m}) + ln|det J_m|] - ln p(z) (when
+        divide_prior) -> (values (n,), d values.sum()/dz) when grad, else values."""
+        z = z_.clone().detach().requires_grad_(grad)
+        n, L = z.shape
+        with torch.set_grad_enabled(grad or torch.is_grad_enabled()):
+            lnq = 0
+            if divide_prior:
+                lnq = lnq + (0.5 * (z * z + LOG2PI)).sum(dim=1)
+            for m in subset:
+                vae = self.vaes[m]
+                z0, ladj = vae.flow_forward(z)
+                mu, lv = experts[m] if experts is not None else vae.encode_raw(data[m])
+                lq = ops.GaussRows.apply(z0, mu, lv, "log_var", 1)
+                lnq = lnq + (lq if ladj is None else lq + ladj)
+            if grad:
+                g = torch.autograd.grad(lnq.sum(), z)[0]
+                return lnq.detach(), g
+        return lnq
+
+    def sample_from_poe_subset(self, subset, data, ax=None, mcmc_steps=100, n_lf=10, eps_lf=0.01, K=1, divide_prior=True,
+                               indices=None, noise=None, gammas=None, accepts=None, graph=None):
+        """jmvae_nf.py:332-437: Hamiltonian Monte-Carlo on ln q(z|X_s), K chains per datapoint started from the mixture of
+        experts -> z (K, n_data, L).  `ax` (trajectory plot) is ignored.  indices / noise feed sample_from_moe_subset;
+        gammas [steps x (K*n,L)] are the momenta and accepts [steps x (K*n,)] the uniforms of the accept test (drawn on
+        the device when None).  graph (default: on when every draw is internal or supplied as tensors): one leapfrog step
+        — density, its z-gradient through the flows, the two half kicks and the drift — is captured in a CUDA graph and
+        replayed mcmc_steps * n_lf times, as the ~100 launches of a step are otherwise launch-latency-bound."""
+        n_data = len(data[0])
+        data = [torch.cat([d] * K) for d in data]
+        n = len(data[0])
+        dev = data[0].device
+        L = self.params.latent_dim
+        z0 = self.sample_from_moe_subset(subset, data, indices, noise)
+        experts = self.poe_experts(subset, data)
+        acc_nbr = torch.zeros(n, 1, device=dev)
+        graph = (dev.type == "cuda") if graph is None else graph
+
+        def density(zz):
+            return self.compute_poe_posterior(subset, zz, data, divide_prior=divide_prior, grad=True, experts=experts)
+
+        zb, rb = torch.empty(n, L, device=dev), torch.empty(n, L, device=dev)       # static buffers of the leapfrog step
+        gb, lb = torch.empty(n, L, device=dev), torch.empty(n, device=dev)
+        half = eps_lf / 2
+
+        def leapfrog():
+            rho_ = rb + half * gb                      # step 1 (rho - eps/2 * (-g))
+            zb.add_(rho_, alpha=eps_lf)                # step 2
+            lnq, g = density(zb)
+            gb.copy_(g)
+            lb.copy_(lnq)
+            rb.copy_(rho_ + half * g)                  # step 3
+
+        cg = None
+        if graph and n_lf > 0:
+            zb.copy_(z0)
+            rb.zero_()
+            lb_, g_ = density(zb)
+            gb.copy_(g_)
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(2):                     # warm the allocator / autograd on the side stream
+                    leapfrog()
+            torch.cuda.current_stream().wait_stream(side)
+            cg = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(cg):
+                leapfrog()
+
+        z = z0
+        for i in range(mcmc_steps):
+            rho = torch.randn_like(z) if gammas is None else gammas[i].to(dev)
+            lnq, g = density(z)
+            H0 = -lnq + 0.5 * torch.norm(rho, dim=1) ** 2
+            zb.copy_(z)
+            rb.copy_(rho)
+            gb.copy_(g)
+            lb.copy_(lnq)
+            for _ in range(n_lf):
+                if cg is not None:
+                    cg.replay()
+                else:
+                    leapfrog()
+            H = -lb + 0.5 * torch.norm(rb, dim=1) ** 2
+            alpha = torch.exp(H0 - H)
+            u = torch.rand(n, device=dev) if accepts is None else accepts[i].to(dev)
+            moves = (u < alpha).to(torch.float32).reshape(n, 1)
+            acc_nbr += moves
+            z = zb * moves + (1 - moves) * z0
+            z0 = z
+        self.last_acceptance = acc_nbr / max(mcmc_steps, 1)
+        return z.detach().reshape(K, n_data, L)
 
 
 class JMVAE_NF_DCCA_MNIST_SVHN(JMVAE_NF):

@@ -127,6 +127,38 @@ class MVAE(Multi_VAES):
         return {f"joint_ll_from_{cond_mod}": ll.mean()}
 
 
+    # ---- product-of-experts subset posteriors (mvae.py:268-327) ---------------------------------------------------------
+    @torch.no_grad()
+    def sample_from_poe_subset(self, subset, data, K=1, divide_prior=True, noise=None):
+        """mvae.py:268-301: K draws per datapoint from the PoE of the subset's experts and the prior -> (K, n, L).
+        `poe` returns (mu, STD) and the reference samples with exp(0.5 * that) as the scale (:296-298); kept as is:
+        the rsample kernel's `exp_half` transform is applied to the PoE standard deviation.  noise: (K, n, L)."""
+        mus, lvs = [], []
+        for m in subset:
+            mu_u, lv_u = self.vaes[m].encode_raw(data[m])
+            mus.append(mu_u)
+            lvs.append(lv_u)
+        joint_mu, joint_std = self.poe(mus, lvs)
+        n, L = joint_mu.shape
+        if noise is None:
+            noise = draw_noise("normal", (K, n, L), joint_mu.device)
+        z, _ = ops.RSample.apply(joint_mu.unsqueeze(0), joint_std.unsqueeze(0), noise.reshape(1, K, n, L), "normal",
+                                 "exp_half", False)
+        return z.reshape(K, n, L)
+
+    def compute_poe_posterior(self, subset, z, data, divide_prior=True, grad=False, experts=None):
+        """mvae.py:304-327: sum_{m in s} ln N(z; PoE(q_m, p)) - ln p(z) -> (n,).  The second value `poe` returns (a standard
+        deviation) is read as a log-variance by the reference (:320-321); kept as is.  z may hold `div` rows per
+        datapoint (row r belongs to datapoint r // div)."""
+        R, L = z.shape
+        lq = 0
+        for m in subset:
+            mu_u, lv_u = experts[m] if experts is not None else self.vaes[m].encode_raw(data[m])
+            t0, t1 = self.poe([mu_u], [lv_u])
+            lq = lq + ops.GaussRows.apply(z, t0, t1, "log_var", R // t0.shape[0])
+        return lq + (0.5 * (z * z + math.log(2 * math.pi))).sum(dim=1)
+
+
 class MVAE_MNIST_SVHN(MVAE):
     """models/mvae/mnist_svhn.py:22-45."""
     shape_mods = [(1, 28, 28), (3, 32, 32)]
@@ -158,6 +190,14 @@ class MVAE_MNIST_SVHN_FASHION(MVAE):
         r = (3 * 32 * 32) / (1 * 28 * 28)
         s = getattr(params, "llik_scaling", 0.0)
         self.lik_scaling = (r, 1.0, r) if s == 0 else (float(s), 1.0, float(s))
+
+    @torch.no_grad()
+    def compute_conditional_likelihoods(self, data, K=1000, batch_size_K=100, noises=None):
+        """msf.py:101-108: the pairwise conditionals plus `cond_poe_ll_{g}` from the two-modality PoE posteriors."""
+        from .poe_subset import compute_all_cond_ll_from_poe_subsets
+        d = super().compute_conditional_likelihoods(data, K, batch_size_K, noises)
+        d.update(compute_all_cond_ll_from_poe_subsets(self, data, K, batch_size_K))
+        return d
 
 
 VAE_mvae_mnist_svhn = MVAE_MNIST_SVHN

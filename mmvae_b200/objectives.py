@@ -101,3 +101,11 @@ def m_self_built(model, x, K=1, epoch=1, warmup=0, beta_prior=1, noise=None):
     if not isinstance(model, (MVAE, MOEPOE)):
         raise TypeError(f"m_self_built needs an mmvae_b200 MVAE / MOEPOE model, got {type(model).__name__}")
     return model.forward(x, noise=noise)["elbo"], {}
+
+
+def m_elbo_nf(model, x, K=1, epoch=1, warmup=0, beta_prior=1, noise=None):
+    """objectives.py:463-479: ELBO of the MMVAE-NF with the KL developed (MMVAE_NF.objective)."""
+    from .mmvae_nf import MMVAE_NF
+    if not isinstance(model, MMVAE_NF):
+        raise TypeError(f"m_elbo_nf needs an mmvae_b200 MMVAE_NF model, got {type(model).__name__}")
+    return model.objective(x, noise=noise), {}
