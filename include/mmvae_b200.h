@@ -178,6 +178,18 @@ long mmvae_convt_tc_wgrad_workspace_bytes(int Nimg, int H, int W, int Cin, int C
 /* MADE / MAF / IAF elementwise pieces (maf_model.py:62-74,91-104; iaf_model.py:60-78,94-100).  The masked-linear
  * contractions go through mmvae_gemm with the pre-masked weight (layers.py:24-25: F.linear(x, mask*W, b)). */
 int mmvae_mask_weight(const float* w, const float* mask, float* out, long n, void* stream);
+/* The sequential direction of one MADE flow block (MAF.inverse maf_model.py:91-104; IAF.forward iaf_model.py:60-78; MADE
+ * made_model.py:21-111) as ONE kernel: replaces L MADE passes (4 masked GEMMs each) + L affine steps.  Every hidden unit
+ * is evaluated once, when the last column it depends on is produced.  y [R,L] block input (read at column L-1-i when
+ * flip_in), out [R,L] (written at L-1-i when flip_out), ladj_out = ladj_in -/+ sum_i log_var_i (mode 0 / 1 as in
+ * mmvae_flow_affine_fwd).  cnt[d] (d < L-1; host and device copies) = number of hidden units of degree <= d, at most 8
+ * units per degree; pack = the degree-sorted masked weights, mmvae_made_seq_pack_floats(cnt, L) floats (layout:
+ * csrc/made_seq.cu).  H = hidden width (three hidden layers).  Inference only (no backward). */
+long mmvae_made_seq_pack_floats(const int* cnt_host, int L);
+long mmvae_made_seq_smem_bytes(const int* cnt_host, int L, int H);
+int mmvae_made_seq_fwd(const float* y, const float* ladj_in, float* out, float* ladj_out, const float* pack,
+                       const int* cnt_dev, const int* cnt_host, int R, int L, int H, int mode, int flip_in, int flip_out,
+                       void* stream);
 /* affine coupling fused with the log|det J| update.  x: [R,L] block input; h: [R,2L] = MADE output (mu | log_var).
  * mode 0 "normalise" (MAF.forward, IAF.forward): u = (x-mu)*exp(-lv), ladj_out = ladj_in - sum lv;
  * mode 1 "generate"  (MAF.inverse, IAF.inverse): u = x*exp(lv)+mu,     ladj_out = ladj_in + sum lv.

@@ -77,6 +77,9 @@ class MADE(nn.Module):
         return ModelOutput(mu=h[:, :self.input_dim], log_var=h[:, self.input_dim:])
 
 
+FUSED_SEQUENTIAL = True      # tests switch it off to compare with the L-pass GEMM formulation
+
+
 class _Flow(nn.Module):
     def __init__(self, input_dim, n_made_blocks=2, n_hidden_in_made=3, hidden_size=128):
         super().__init__()
@@ -101,6 +104,12 @@ class _Flow(nn.Module):
         the MADE of the columns already produced."""
         ladj = self._zeros(y)
         L = self.input_dim
+        if FUSED_SEQUENTIAL and not (torch.is_grad_enabled() and (y.requires_grad or any(p.requires_grad for p in self.parameters()))) \
+                and all(ops.made_seq_plan(made).ok for made in blocks):
+            # inference: one kernel per block, every hidden unit evaluated once (csrc/made_seq.cu)
+            for made in blocks:
+                y, ladj = ops.made_seq(y, ladj, made, made.masked_weights(), mode, flip_first, not flip_first)
+            return y, ladj
         for made in blocks:
             if flip_first:
                 y = ops.FlipCols.apply(y)

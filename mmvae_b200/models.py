@@ -192,6 +192,16 @@ class Multi_VAES(nn.Module):
         ll = self._is_loglik(z, data, [mod], None, K_total=K, with_prior=False)
         return {f"uni_from_prior_{mod}": ll.mean()}
 
+    @torch.no_grad()
+    def compute_conditional_likelihood_bis(self, data, cond_mod, gen_mod, K=1000, batch_size_K=100, noise=None,
+                                           noise_prior=None):
+        """multi_vaes.py:253-268: ln p(x_gen|x_cond) ~ ln E_q(z|x_cond)[p(x,z)/q] - ln E_p(z)[p(x_cond|z)], each term by
+        importance sampling.  The key carries the reference's trailing blank."""
+        t1 = self.compute_joint_ll_from_uni(data, cond_mod, K, batch_size_K, noise=noise)[f"joint_ll_from_{cond_mod}"]
+        t2 = self.compute_uni_ll_from_prior(data, cond_mod, K=K, batch_size_K=batch_size_K,
+                                            noise=noise_prior)[f"uni_from_prior_{cond_mod}"]
+        return {f"conditional_likelihood_bis_{cond_mod}_{gen_mod} ": t1 - t2}
+
 
 class MMVAE(Multi_VAES):
     """mmvae.py:24-234."""

@@ -742,3 +742,103 @@ def adam_amsgrad_(p, g, m, v, vmax, step_dev, lr=1e-3, betas=(0.9, 0.999), eps=1
     """in-place fused Adam(amsgrad) on flat buffers (main.py:114-115)."""
     _call("mmvae_adam_amsgrad", _p(p), _p(g), _p(m), _p(v), _p(vmax), p.numel(), float(lr), float(betas[0]),
           float(betas[1]), float(eps), _p(step_dev), int(amsgrad), _stream())
+
+
+# ------------------------------------------------------------------------- fused sequential MADE direction (inference)
+class MadeSeqPlan:
+    """Degree-sorted packing of one MADE (flows.MADE with three equal hidden layers and the reference's sequential degrees,
+    made_model.py:68-95) for mmvae_made_seq_fwd: the gather index that turns (biases | masked weights) into the pack of
+    csrc/made_seq.cu, and the per-degree unit counts.  Built once per MADE; `ok` is False when the kernel does not apply
+    (other depth, more than 8 units per degree, masks that are not the sequential ones, shared memory) — the caller then
+    keeps the GEMM formulation."""
+
+    def __init__(self, made):
+        import numpy as np
+        lay = made.layers()
+        L, hs = made.input_dim, made.hidden_sizes
+        self.ok = False
+        if len(hs) != 3 or len(set(hs)) != 1 or made.output_dim != 2 * L or not (2 <= L <= 32):
+            return
+        H = hs[0]
+        from .flows import made_masks
+        std = made_masks(L, hs, 2 * L)
+        if any(tuple(l.mask.shape) != tuple(m.shape) or not torch.equal(l.mask.detach().cpu(), m) for l, m in zip(lay, std)):
+            return
+        deg = np.arange(H) % (L - 1)
+        perm = np.argsort(deg, kind="stable")
+        G = L - 1
+        cnt = np.array([(deg <= d).sum() for d in range(G)], dtype=np.int32)
+        c0 = np.concatenate([[0], cnt])                       # c0[d] = units of degree < d
+        if (np.diff(c0) > 8).any():
+            return
+        lib = _lib.load()
+        self.cnt_host = (ctypes.c_int * G)(*[int(v) for v in cnt])
+        n = lib.mmvae_made_seq_pack_floats(ctypes.cast(self.cnt_host, ctypes.c_void_p), L)
+        if n <= 0 or lib.mmvae_made_seq_smem_bytes(ctypes.cast(self.cnt_host, ctypes.c_void_p), L, H) > 227 * 1024:
+            return
+        ob = [0, H, 2 * H, 3 * H]
+        oW1 = 3 * H + 2 * L
+        oW2, oW3 = oW1 + H * L, oW1 + H * L + H * H
+        oW4 = oW3 + H * H
+        zero = oW4 + 2 * L * H
+        idx = np.full(n, zero, dtype=np.int64)
+        pos = 0
+        for layer in range(3):                                # b1g, b2g, b3g [G][8]
+            for d in range(G):
+                for u in range(c0[d + 1] - c0[d]):
+                    idx[pos + 8 * d + u] = ob[layer] + perm[c0[d] + u]
+            pos += 8 * G
+        idx[pos:pos + 2 * L] = ob[3] + np.arange(2 * L)       # b4
+        pos += (2 * L + 3) & ~3
+        for d in range(G):                                    # W1g: [d+1][8]
+            for u in range(c0[d + 1] - c0[d]):
+                j = perm[c0[d] + u]
+                idx[pos + 8 * np.arange(d + 1) + u] = oW1 + j * L + np.arange(d + 1)
+            pos += 8 * (d + 1)
+        for oW in (oW2, oW3):                                 # W2g, W3g: [cnt[d]][8]
+            for d in range(G):
+                kk = perm[:c0[d + 1]]
+                for u in range(c0[d + 1] - c0[d]):
+                    j = perm[c0[d] + u]
+                    idx[pos + 8 * np.arange(c0[d + 1]) + u] = oW + j * H + kk
+                pos += 8 * c0[d + 1]
+        for i in range(L):                                    # W4g: [cnt[i-1]][2]
+            kk = perm[:c0[i]]
+            for c in range(2):
+                idx[pos + 2 * np.arange(c0[i]) + c] = oW4 + (c * L + i) * H + kk
+            pos += 2 * c0[i]
+        assert pos <= n
+        self.L, self.H, self.n = L, H, int(n)
+        self.idx_cpu = torch.from_numpy(idx)
+        self.cnt_cpu = torch.from_numpy(cnt.copy())
+        self._dev = {}
+        self.ok = True
+
+    def on(self, device):
+        if device not in self._dev:
+            self._dev[device] = (self.idx_cpu.to(device), self.cnt_cpu.to(device))
+        return self._dev[device]
+
+
+def made_seq_plan(made):
+    plan = getattr(made, "_seq_plan", None)
+    if plan is None:
+        plan = MadeSeqPlan(made)
+        object.__setattr__(made, "_seq_plan", plan)
+    return plan
+
+
+def made_seq(y, ladj, made, mw, mode, flip_in, flip_out):
+    """One flow block in the sequential direction, fused (inference only).  y [R,L], ladj [R]; mw = made.masked_weights()."""
+    plan = made_seq_plan(made)
+    y, ladj = _c(y, "y"), _c(ladj, "ladj")
+    R, L = y.shape
+    idx, cnt_dev = plan.on(y.device)
+    lay = made.layers()
+    src = torch.cat([l.bias.detach().reshape(-1) for l in lay] + [w.detach().reshape(-1) for w in mw] +
+                    [torch.zeros(1, device=y.device)])
+    pack = src.index_select(0, idx)
+    out, ladj_out = torch.empty_like(y), torch.empty_like(ladj)
+    _call("mmvae_made_seq_fwd", _p(y), _p(ladj), _p(out), _p(ladj_out), _p(pack), ctypes.c_void_p(cnt_dev.data_ptr()),
+          ctypes.cast(plan.cnt_host, ctypes.c_void_p), R, L, plan.H, int(mode), int(flip_in), int(flip_out), _stream())
+    return out, ladj_out

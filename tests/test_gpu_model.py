@@ -124,6 +124,11 @@ def test_evaluators_match_reference(name):
         per_all[(c, gm)] = per
     out = model.compute_uni_ll_from_prior(data, 0, K=K, batch_size_K=bs, noise=g["prior0"]["noise"].cuda())
     assert abs(out["uni_from_prior_0"].item() - g["prior0"]["value"].item()) < 1e-3
+    if spec.M == 2:                                              # multi_vaes.py:253-268: the difference of the two above
+        bis = model.compute_conditional_likelihood_bis(data, 0, 1, K=K, batch_size_K=bs, noise=g["joint_from_0"]["noise"].cuda(),
+                                                       noise_prior=g["prior0"]["noise"].cuda())
+        ref_bis = g["joint_from_0"]["value"].item() - g["prior0"]["value"].item()
+        assert abs(bis["conditional_likelihood_bis_0_1 "].item() - ref_bis) < 2e-3
     if spec.M == 3:
         noises = {k: r["noise"].cuda() for k, r in g["cond"].items()}
         met = model.compute_conditional_likelihoods(data, K=K, batch_size_K=bs, noises=noises)
