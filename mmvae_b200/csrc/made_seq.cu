@@ -5,9 +5,11 @@
 // every hidden unit is evaluated exactly ONCE over the whole sweep (1/L of the reference's arithmetic) and the hidden
 // activations never leave the SM.
 //
-// Layout: one thread = one row; the packed, degree-sorted weights of the block (~100 KB for L=20, H=128) sit in shared
-// memory and are read as warp-wide broadcasts; the row's activations h1,h2,h3 [H] and outputs x [L] live in a
-// lane-private column of shared memory ([k][lane]: conflict-free), so the kernel needs no barrier after the weight load.
+// Layout: a warp owns 16 rows, lane = (k-half, row): the two half-warps split every dot product over even / odd k and
+// add their halves with one shuffle.  The packed, degree-sorted weights of the block (~100 KB for L=20, H=128) sit in
+// shared memory and are read as half-warp broadcasts; a row's activations h1,h2,h3 [H] and outputs x [L] live in a
+// warp-private column of shared memory ([k][row]: conflict-free), so after the weight load only __syncwarp is needed
+// and four warps fit beside the weights (one per scheduler).
 // Units of degree d form group d (<= 8 units, padded to 8 accumulators): group d of layer 1 reads x[0..d], of layers
 // 2 / 3 the first cnt[d] units of the layer below, and output column i the first cnt[i-1] units of h3.
 //
@@ -16,10 +18,11 @@
 //   [cnt[i-1]][2] (mu, log_var)          with G = L-1 groups and cnt[d] = number of hidden units of degree <= d.
 #include "common.cuh"
 
-#define MS_THREADS 64
+#define MS_MAX_WARPS 4
+#define MS_ROWS 16                            // rows per warp: lane = (k-half, row)
 #define MS_MAXL 32
 
-__global__ void __launch_bounds__(MS_THREADS, 1)   // launched with 64 threads, or 32 when two warps' activations do not fit
+__global__ void __launch_bounds__(MS_MAX_WARPS * 32, 1)
 made_seq_kernel(const float* __restrict__ y, const float* __restrict__ ladj_in, float* __restrict__ out,
                 float* __restrict__ ladj_out, const float* __restrict__ pack, int pack_floats, const int* __restrict__ cnt_g,
                 int R, int L, int H, int mode, int flip_in, int flip_out) {
@@ -46,35 +49,43 @@ made_seq_kernel(const float* __restrict__ y, const float* __restrict__ ladj_in, 
     const float* W2g = W1g + 8 * (G * (G + 1) / 2);
     const float* W3g = W2g + o2[G];
     const float* W4g = W3g + o2[G];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    float* h1 = sm + pack_floats + warp * (3 * H + L) * 32 + lane;
-    float* h2 = h1 + H * 32;
-    float* h3 = h2 + H * 32;
-    float* xs = h3 + H * 32;
+    // A warp owns 16 rows; its two half-warps split every dot product over k (even / odd k) and add the halves with one
+    // shuffle, so four warps fit beside the weights and each scheduler of the SM has a warp to issue from.
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, half = lane >> 4, rl = lane & 15;
+    const int rows_cta = (blockDim.x >> 5) * MS_ROWS;
+    float* h1 = sm + pack_floats + warp * (3 * H + L) * MS_ROWS + rl;
+    float* h2 = h1 + H * MS_ROWS;
+    float* h3 = h2 + H * MS_ROWS;
+    float* xs = h3 + H * MS_ROWS;
 
-    for (long tile = blockIdx.x; tile * blockDim.x < R; tile += gridDim.x) {
-        const long r = tile * blockDim.x + threadIdx.x;
+    for (long tile = blockIdx.x; tile * rows_cta < R; tile += gridDim.x) {
+        const long r = tile * rows_cta + warp * MS_ROWS + rl;
         const bool live = r < R;
         const long rr = live ? r : R - 1;
         float ladj = ladj_in[rr];
         for (int i = 0; i < L; ++i) {
             // column i: (mu, log_var) from the h3 units of degree < i
             const int n = cnt[i];
-            float mu = b4[i], lv = b4[L + i];
+            float mu = half ? 0.f : b4[i], lv = half ? 0.f : b4[L + i];
             const float2* w4 = reinterpret_cast<const float2*>(W4g + o4[i]);
 #pragma unroll 4
-            for (int k = 0; k < n; ++k) {
-                const float h = h3[k * 32];
+            for (int k = half; k < n; k += 2) {
+                const float h = h3[k * MS_ROWS];
                 const float2 w = w4[k];
                 mu = fmaf(w.x, h, mu);
                 lv = fmaf(w.y, h, lv);
             }
+            mu += __shfl_xor_sync(0xffffffffu, mu, 16);
+            lv += __shfl_xor_sync(0xffffffffu, lv, 16);
             const float yi = y[rr * L + (flip_in ? L - 1 - i : i)];
             float u;
             if (mode == 0) { u = (yi - mu) * expf(-lv); ladj -= lv; }
             else           { u = yi * expf(lv) + mu;    ladj += lv; }
-            xs[i * 32] = u;
-            if (live) out[r * L + (flip_out ? L - 1 - i : i)] = u;
+            if (!half) {
+                xs[i * MS_ROWS] = u;
+                if (live) out[r * L + (flip_out ? L - 1 - i : i)] = u;
+            }
+            __syncwarp();
             if (i >= G) continue;
             // the hidden units of degree i, layer by layer
             const int u0 = cnt[i], n1 = cnt[i + 1], nu = n1 - u0;
@@ -87,10 +98,10 @@ made_seq_kernel(const float* __restrict__ y, const float* __restrict__ ladj_in, 
                 float* dst = layer == 0 ? h1 : layer == 1 ? h2 : h3;
                 const int kn = layer == 0 ? i + 1 : n1;
 #pragma unroll
-                for (int q = 0; q < 8; ++q) acc[q] = bg[q];
+                for (int q = 0; q < 8; ++q) acc[q] = half ? 0.f : bg[q];
 #pragma unroll 4
-                for (int k = 0; k < kn; ++k) {
-                    const float v = src[k * 32];
+                for (int k = half; k < kn; k += 2) {
+                    const float v = src[k * MS_ROWS];
                     const float4 wa = *reinterpret_cast<const float4*>(W + 8 * k);
                     const float4 wb = *reinterpret_cast<const float4*>(W + 8 * k + 4);
                     acc[0] = fmaf(wa.x, v, acc[0]); acc[1] = fmaf(wa.y, v, acc[1]);
@@ -99,11 +110,17 @@ made_seq_kernel(const float* __restrict__ y, const float* __restrict__ ladj_in, 
                     acc[6] = fmaf(wb.z, v, acc[6]); acc[7] = fmaf(wb.w, v, acc[7]);
                 }
 #pragma unroll
-                for (int q = 0; q < 8; ++q)
-                    if (q < nu) dst[(u0 + q) * 32] = fmaxf(acc[q], 0.f);
+                for (int q = 0; q < 8; ++q) acc[q] += __shfl_xor_sync(0xffffffffu, acc[q], 16);
+#pragma unroll
+                for (int qq = 0; qq < 4; ++qq) {           // half h stores the units q = 2*qq + h
+                    const float v = half ? acc[2 * qq + 1] : acc[2 * qq];
+                    const int q = 2 * qq + half;
+                    if (q < nu) dst[(u0 + q) * MS_ROWS] = fmaxf(v, 0.f);
+                }
+                __syncwarp();
             }
         }
-        if (live) ladj_out[r] = ladj;
+        if (live && !half) ladj_out[r] = ladj;
     }
 }
 
@@ -122,14 +139,19 @@ extern "C" long mmvae_made_seq_pack_floats(const int* cnt_host, int L) {
 }
 
 static long made_seq_smem(const int* cnt_host, int L, int H, int warps) {
-    return (made_seq_pack_floats_host(cnt_host, L) + (long)warps * (3 * H + L) * 32) * 4;
+    return (made_seq_pack_floats_host(cnt_host, L) + (long)warps * (3 * H + L) * MS_ROWS) * 4;
 }
 
-// shared memory of the launch configuration the library picks: two warps per CTA, one when that does not fit
+static int made_seq_warps(const int* cnt_host, int L, int H) {
+    for (int w = MS_MAX_WARPS; w > 1; w >>= 1)
+        if (made_seq_smem(cnt_host, L, H, w) <= 227 * 1024) return w;
+    return 1;
+}
+
+// shared memory of the launch configuration the library picks: four warps (16 rows each) per CTA, fewer when that does not fit
 extern "C" long mmvae_made_seq_smem_bytes(const int* cnt_host, int L, int H) {
     if (!cnt_host || L < 2 || L > MS_MAXL) return -1;
-    const long two = made_seq_smem(cnt_host, L, H, 2);
-    return two <= 227 * 1024 ? two : made_seq_smem(cnt_host, L, H, 1);
+    return made_seq_smem(cnt_host, L, H, made_seq_warps(cnt_host, L, H));
 }
 
 extern "C" int mmvae_made_seq_fwd(const float* y, const float* ladj_in, float* out, float* ladj_out, const float* pack,
@@ -153,8 +175,9 @@ extern "C" int mmvae_made_seq_fwd(const float* y, const float* ladj_in, float* o
         if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "made_seq_fwd: %s", cudaGetErrorString(e));
         attr_set = smem;
     }
-    const int threads = smem == made_seq_smem(cnt_host, L, H, 2) ? 64 : 32;
-    const int tiles = ceil_div_i(R, threads);
+    const int warps = made_seq_warps(cnt_host, L, H);
+    const int threads = 32 * warps;
+    const int tiles = ceil_div_i(R, warps * MS_ROWS);
     const int grid = tiles < MMVAE_NUM_SMS ? tiles : MMVAE_NUM_SMS;
     made_seq_kernel<<<grid, threads, smem, (cudaStream_t)stream>>>(y, ladj_in, out, ladj_out, pack, (int)pf, cnt_dev, R, L, H,
                                                                       mode, flip_in, flip_out);
