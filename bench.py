@@ -380,9 +380,11 @@ def run_b200(args):
     ev = None
     if not args.no_eval:
         ev = run_eval(model, dev, args.eval_datapoints * world, peak, dist_on)       # every rank: batch-sharded
+        ev_jnf = run_eval_jmvae_nf(dev, args.eval_datapoints, dist_on)
     if rank == 0:
         if ev is not None:
             line["eval"] = ev
+            line["eval_jmvae_nf"] = ev_jnf
         if world == 1 and not args.no_cpu_baseline:
             v, cores, cms = cpu_port_step_rate(2, 1)
             line["cpu_baseline"] = {"value": v, "unit": "samples/s", "cores": cores, "kind": "port",
@@ -432,6 +434,47 @@ def run_eval(model, dev, n, peak, dist_on=False):
     return {"metric": "K=1000 NLL eval samples/s (joint + both conditionals)", "value": n / s, "unit": "samples/s",
             "datapoints": n, "K": 1000, "batch_size_K": 100, "s_per_pass": s, "joint_ll": float(ll),
             "sharding": "batch", "achieved_tflops_algorithmic": n * EVAL_FLOP_PER_DATAPOINT / s / 1e12}
+
+
+def run_eval_jmvae_nf(dev, n_per_rank, dist_on=False):
+    """The same K=1000 evaluator trio on BASELINE config C3's model (JMVAE-NF, MAF flows, DCCA two-step encoders,
+    jmvae_nf_dcca.json): joint ln p(x,y) from the joint encoder and both conditionals, whose latents go through the
+    sequential direction of the flow (csrc/made_seq.cu).  Each rank evaluates its own n_per_rank datapoints."""
+    import argparse
+    import torch.distributed as dist
+    import mmvae_b200
+    params = argparse.Namespace(latent_dim=20, dist="normal", recon_losses=["normal", "normal"], llik_scaling=0.0,
+                                num_hidden_layers=1, beta_kl=1.0, decrease_beta_kl=1.0, fix_jencoder=True, fix_decoders=True,
+                                no_recon=True, warmup=100, dcca=True, dim_dcca=9, flow="maf", no_nf=False, device="cuda",
+                                data_path="", epochs=1)
+    torch.manual_seed(1)
+    model = mmvae_b200.VAE_jnf_mnist_svhn_dcca(params).to(dev)
+    data = synth_batch(n_per_rank, seed=998, device=dev)
+
+    def once():
+        for c, g in ((0, 1), (1, 0)):
+            model.compute_conditional_likelihood(data, c, g, K=1000, batch_size_K=100)
+        return model.compute_joint_likelihood(data, K=1000, batch_size_K=100)["likelihood"]
+    once()
+    if dist_on:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    reps = 2
+    for _ in range(reps):
+        ll = once()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    world = 1
+    if dist_on:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        world = dist.get_world_size()
+    s = ms.item() * 1e-3 / reps
+    return {"metric": "K=1000 NLL eval samples/s (joint + both conditionals), JMVAE-NF MAF model (config C3)",
+            "value": n_per_rank * world / s, "unit": "samples/s", "datapoints": n_per_rank * world, "K": 1000,
+            "batch_size_K": 100, "s_per_pass": s, "joint_ll": float(ll), "sharding": "batch"}
 
 
 def _claim_stdout():
