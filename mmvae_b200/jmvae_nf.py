@@ -70,7 +70,7 @@ class JMVAE_NF(Multi_VAES):
         (the reference's second stochastic forward; its discarded decodes are skipped — SURVEY A14)."""
         mu, std, z = self._joint_sample(x, noise)
         z_xy = z[0]
-        self.qz_xy_params = (mu, std)
+        self.qz_xy_params = (mu.detach(), std.detach())       # no autograd graph kept alive between steps (CUDA-graph capture)
         lq_xy = ops.GaussRows.apply(z_xy, mu, std, "std", 1).sum()
         reg, details = 0, {}
         for m, vae in enumerate(self.vaes):
@@ -125,7 +125,7 @@ class JMVAE_NF(Multi_VAES):
         beta_reg = ((epoch - 1) / warmup if epoch - 1 <= warmup else 1) if self.linear_warmup else 1
         mu, std, z = self._joint_sample(x, noise.get("eps1"))
         z_xy = z[0]
-        self.qz_xy_params = (mu, std)
+        self.qz_xy_params = (mu.detach(), std.detach())       # no autograd graph kept alive between steps (CUDA-graph capture)
         loss, details = 0, {}
         for m, xm in enumerate(x):
             recon = self.vaes[m].decoder(z_xy)["reconstruction"]

@@ -2,6 +2,8 @@
 K-sample evaluators against the fp64 oracle and the golden fixtures of the unmodified reference.
 Tolerances: loss 1e-5 relative to the fp32 reference and 1e-6 to the fp64 oracle; gradients 5e-5 per tensor against the
 fp64 oracle and 1e-4 (+ the reference's own measured fp32 noise) against the reference digests; likelihoods 1e-3 nats."""
+import math
+
 import pytest
 import torch
 
@@ -97,6 +99,32 @@ def test_forward_tuple_and_step():
     assert model.beta_kl == 1.0                             # jmvae_nf.py:189-193: only from the warm-up epoch on
     model.step(2)
     assert model.beta_kl == 0.5
+
+
+@pytest.mark.parametrize("frozen", [True, False])
+def test_trainer_graph_replay_after_eager_steps(frozen):
+    """Config C3 (jmvae_nf_dcca.json) through train.Trainer: eager steps followed by CUDA-graph capture and replay.  With the
+    joint encoder trainable its parameters are used twice per step (objective + compute_kld); the model must not keep
+    the autograd graph of the previous step alive (stored posterior parameters are detached) or the capture fails."""
+    import argparse
+    import mmvae_b200
+    from mmvae_b200.train import Trainer
+    params = argparse.Namespace(latent_dim=20, dist="normal", recon_losses=["normal", "normal"], llik_scaling=0.0,
+                                num_hidden_layers=1, beta_kl=1.0, decrease_beta_kl=1.0, fix_jencoder=frozen, fix_decoders=frozen,
+                                no_recon=True, warmup=0, dcca=True, dim_dcca=9, flow="maf", no_nf=False, device="cuda",
+                                data_path="", epochs=1)
+    torch.manual_seed(1)
+    model = mmvae_b200.VAE_jnf_mnist_svhn_dcca(params).cuda()
+    tr = Trainer(model, "m_jmvae_nf", K=1, lr=1e-4, distributed=False)
+    g = torch.Generator().manual_seed(3)
+    x = [torch.rand(32, 1, 28, 28, generator=g).cuda(), torch.rand(32, 3, 32, 32, generator=g).cuda()]
+    first = [tr.step(x).item() for _ in range(3)]
+    tr.capture(x)
+    later = [tr.step_graph(x).item() for _ in range(20)]
+    assert all(map(math.isfinite, first + later))
+    n = sum(p.numel() for p in model.joint_encoder.parameters() if p.grad is not None and p.grad.abs().sum() > 0)
+    assert (n == 0) == frozen                                    # frozen phase: no gradient reaches the joint encoder
+    assert sum(later[-5:]) / 5 > sum(first) / 3                  # the objective is maximised (same batch)
 
 
 @pytest.mark.parametrize("flow", ["maf", "iaf"])
