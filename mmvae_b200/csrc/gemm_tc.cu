@@ -462,6 +462,11 @@ static bool tc_shape_ok(int M, int N, int K, int a_k, int b_k) {
     if ((g_tc_dbg & 128) && ((!a_k && M < 32) || (!b_k && N < 32))) return false;   // tools/gemm_small.py A/B switch
     if (K < ((g_tc_dbg & 256) ? 8 : 32)) return false;              // K = latent size: store-bound, the SIMT kernel wins (measured)
     if ((long)M * N * K < (1L << 20)) return false;                 // launch-latency-sized: SIMT is as good
+    // Below ~0.4 GMAC the persistent tcgen05 kernel is latency-bound (TMEM allocation, barrier set-up, a serial k-block
+    // chain on a handful of CTAs: 20-37 us where the SIMT kernel takes 9-21 us, tools/gemm_tiny.py), unless K is long
+    // (split-K chains of the weight gradients) or an operand is thin (measured faster here, tools/gemm_small.py).
+    // Debug bit 32768 restores the old gate.
+    if (!(g_tc_dbg & 32768) && (long)M * N * K < (3L << 27) && K < 4096 && M >= 32 && N >= 32) return false;
     // TMA: 16-byte row pitch.  An inner extent below the 32-float box is fine (zero-filled past the edge): thin
     // MN-major operands of the huge-K weight gradients (N = 20) run here 3x faster than on the SIMT kernel.
     if (a_k ? (K % 4) : (M % 4 || M < 8)) return false;

@@ -11,6 +11,8 @@ import mmvae_b200                             # noqa: E402
 from mmvae_b200 import ops                    # noqa: E402
 from mmvae_b200.train import Trainer          # noqa: E402
 
+if "--simt" in sys.argv:
+    ops.ALLOW_TC = False                       # every GEMM on the exact-fp32 SIMT kernel
 for fixed in (True, False):
     params = argparse.Namespace(latent_dim=20, dist="normal", recon_losses=["normal", "normal"], llik_scaling=0.0,
                                 num_hidden_layers=1, beta_kl=1.0, decrease_beta_kl=1.0, fix_jencoder=fixed, fix_decoders=fixed,
