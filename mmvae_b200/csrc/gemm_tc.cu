@@ -328,10 +328,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 // shared memory so that global traffic is row-coalesced: each 128-bit access instruction then covers
                 // 4 rows x 128 contiguous bytes (whole 32-byte sectors) instead of 32 rows x 16 bytes
                 if (splits == 1 && (bias || act)) {
+                    // one coalesced bias load per 32-column chunk, broadcast by shuffles: 32 predicated scalar loads
+                    // per thread serialised at L2 latency (17 us per 128-column tile, tools/gemm_fixed_cost.py)
                     const int nb = (cv.mode == 1) ? c : tl.n0 + c;
+                    const float bl = (bias && nb + lane < N) ? __ldg(bias + nb + lane) : 0.f;
+                    if (act == MMVAE_ACT_RELU) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        v[j] = apply_act_tc(v[j] + ((bias && nb + j < N) ? __ldg(bias + nb + j) : 0.f), act);
+                        for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j] + __shfl_sync(0xffffffffu, bl, j), 0.f);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = apply_act_tc(v[j] + __shfl_sync(0xffffffffu, bl, j), act);
+                    }
                 }
                 float* pad = epi + (warp & 3) * 32 * TC_EPI_PITCH;
 #pragma unroll
