@@ -15,7 +15,7 @@ for M, N, K in ((128, 512, 64), (128, 128, 64), (128, 32, 64), (2048, 2048, 64))
     out = torch.empty(M, N, device="cuda")
     row = []
     for tag, mode, b, act in (("full", 0, bias, "relu"), ("no bias/act", 0, None, None), ("no stores", 1 << 8, bias, "relu"),
-                              ("no split", 8 << 8, bias, "relu"), ("one MMA", 16 << 8, bias, "relu"), ("1xTF32", 1, bias, "relu"),
+                              ("no global store instr", 64 << 8, bias, "relu"), ("no split", 8 << 8, bias, "relu"), ("one MMA", 16 << 8, bias, "relu"), ("1xTF32", 1, bias, "relu"),
                               ("no stores+no split+one MMA", (1 | 8 | 16) << 8, bias, "relu")):
         lib.mmvae_gemm_tc_set_mode(mode | (32768 << 8))
         row.append(f"{tag}: {bench(lambda: ops.gemm(A, B, b, M, N, K, 1, 1, act=act, out=out), n=20):.1f}")
