@@ -289,12 +289,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             const int row = tl.m0 + lane_base + lane;
             float* out = (splits > 1) ? ws + (long)tl.z * M * N : C;
             const uint32_t tb = tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)(acc * 2 * BN);
+            // The chunk loop is unrolled by two only (the mask buffers alternate with the chunk parity): fully unrolled the
+            // epilogue of a 128-column tile is ~8K instructions that each run once per tile, and the epilogue warps stall
+            // on instruction fetch (ncu: no_instruction 8.3 per issue, 12 us per tile with one k-block per tile).
+            constexpr int CSTEP = (NCH >= 2) ? 2 : 1;
+#pragma unroll 1
+            for (int cp = 0; cp < NCH; cp += CSTEP)
 #pragma unroll
-            for (int ci = 0; ci < NCH; ++ci) {
+            for (int hh = 0; hh < CSTEP; ++hh) {
+                const int ci = cp + hh;
                 const int c = ci * 32;
                 // mask buffer parity: chunks alternate; with one chunk per tile (BN = 32) the buffer is reloaded in place
                 constexpr int kOne = (NCH == 1);
-                const int cur = kOne ? 0 : (ci & 1), nxt = kOne ? 0 : ((ci + 1) & 1);
+                const int cur = kOne ? 0 : hh, nxt = kOne ? 0 : (hh ^ 1);
                 if (use_mask && !kOne) {
                     if (ci + 1 < NCH) load_mask(tl, c + 32, mk[nxt]);
                     else if (t + (int)gridDim.x < total)
