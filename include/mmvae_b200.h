@@ -131,6 +131,18 @@ int mmvae_gemm_tc_set_mode(int mode);
 /* column sums: out[n] = sum_m A[m,n]  (bias gradients); workspace >= mmvae_colsum_workspace_bytes(M,N) */
 int  mmvae_colsum(const float* A, float* out, float* workspace, int M, int N, void* stream);
 long mmvae_colsum_workspace_bytes(int M, int N);
+/* mmvae_colsum without a workspace argument and without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving
+ * loops, harnesses that forbid it).  The stage-1 partials live in a file-scope `static __device__` array of
+ * mmvae_colsum_static_max_bytes() = 1 MiB that every GPU loading the library holds until exit; its device address is
+ * resolved once per device (cudaGetSymbolAddress, with the caller's current device) and the call itself performs no
+ * cudaMalloc / cudaFree / allocating library call.  Shapes whose partials (slabs(M,N) * N floats, the same count as
+ * mmvae_colsum_workspace_bytes) exceed the array are rejected with code 1 and a message naming both sizes.  All calls
+ * share the array: calls that may overlap on the GPU (different streams, no ordering) race on it; calls on one stream
+ * are safe.  Nothing needs clearing between calls (every partial read is written first).  Result is bit-identical to
+ * mmvae_colsum. */
+int  mmvae_colsum_static(const float* A, float* out, int M, int N, void* stream);
+long mmvae_colsum_static_max_bytes(void);
 /* activation backward: out = g * act'(y)  (relu: y>0; sigmoid: y(1-y)); out may alias g */
 int mmvae_act_bwd(const float* g, const float* y, float* out, long n, int act, void* stream);
 

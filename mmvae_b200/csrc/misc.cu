@@ -114,6 +114,52 @@ extern "C" int mmvae_colsum(const float* A, float* out, float* workspace, int M,
     return 0;
 }
 
+// ---- column sums without any allocation: the stage-1 partials live in a file-scope device array -----------------
+// For callers that may not allocate (CUDA-graph capture, serving loops).  Every GPU that loads the library holds the
+// array (1 MiB) until exit.  All calls share it: two calls that overlap on the GPU (different streams) race.  Nothing
+// in it has to start at zero: stage 1 writes every partial [P][N] that stage 2 reads, so stale contents of an earlier
+// call are never observed.
+#define MMVAE_COLSUM_STATIC_MAX_FLOATS (1 << 18)
+static __device__ __align__(256) float g_colsum_scratch[MMVAE_COLSUM_STATIC_MAX_FLOATS];
+#define MMVAE_MAX_DEVICES 64
+static float* g_colsum_scratch_ptr[MMVAE_MAX_DEVICES];         // device address of the array, per device (0 = not set up)
+
+// In host code `g_colsum_scratch` is only a stand-in for the symbol: the device address comes from the runtime, once per
+// device, with that device current.
+static int colsum_static_scratch(float** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "colsum_static: cudaGetDevice: %s", cudaGetErrorString(e));
+    MMVAE_REQUIRE(dev >= 0 && dev < MMVAE_MAX_DEVICES, "colsum_static: device ordinal %d out of range", dev);
+    float* p = __atomic_load_n(&g_colsum_scratch_ptr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        e = cudaGetSymbolAddress((void**)&p, g_colsum_scratch);
+        if (e != cudaSuccess || !p)
+            return mmvae_set_error(1000 + (int)e, "colsum_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        __atomic_store_n(&g_colsum_scratch_ptr[dev], p, __ATOMIC_RELEASE);   // same value from every thread
+    }
+    *out = p;
+    return 0;
+}
+extern "C" long mmvae_colsum_static_max_bytes(void) { return (long)MMVAE_COLSUM_STATIC_MAX_FLOATS * (long)sizeof(float); }
+extern "C" int mmvae_colsum_static(const float* A, float* out, int M, int N, void* stream) {
+    MMVAE_REQUIRE(A && out && M > 0 && N > 0, "colsum_static: bad arguments");
+    const int P = colsum_slabs(M, N);
+    MMVAE_REQUIRE((long)P * N <= (long)MMVAE_COLSUM_STATIC_MAX_FLOATS,
+                  "colsum_static: M=%d N=%d needs %ld scratch bytes, the static scratch holds %ld; use mmvae_colsum with a "
+                  "caller-provided workspace", M, N, (long)P * N * (long)sizeof(float), mmvae_colsum_static_max_bytes());
+    float* scratch = nullptr;
+    const int rc = colsum_static_scratch(&scratch);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int rows_per_slab = (((M + P - 1) / P) + 7) & ~7;
+    colsum_stage1<<<dim3((N + 31) / 32, P), 256, 0, st>>>(A, scratch, M, N, rows_per_slab);
+    MMVAE_LAUNCH_CHECK("colsum_static stage1");
+    colsum_stage2<<<(N + 31) / 32, 256, 0, st>>>(scratch, out, P, N);
+    MMVAE_LAUNCH_CHECK("colsum_static stage2");
+    return 0;
+}
+
 // ---- activation backward, in place: g *= act'(y) ---------------------------------------------------------------
 __global__ void act_bwd_kernel(const float* g, const float* __restrict__ y, float* out, long n, int act) {
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
