@@ -187,6 +187,21 @@ int  mmvae_convt_tc_wgrad(const float* x, const float* g, float* gwp, float* wor
                           int H, int W, int Cin, int Cout, void* stream);
 long mmvae_convt_tc_wgrad_workspace_bytes(int Nimg, int H, int W, int Cin, int Cout);
 
+/* Second generation of the same layer (32 | Cin, Cout; forward Cout in {32,64}; dgrad Cin in {32,64,128}; H*W | 128):
+ * ConvTranspose2d(k4,s2,p1) forward and data gradient of encoders.py:113-124 with the activation operand read from TENSOR
+ * MEMORY (tcgen05.mma "TS" form), operands split into bf16 (hi, mid) with hi*hi + hi*mid + mid*hi accumulated in fp32
+ * (relative error <= 3*2^-18 per product), one TMA halo tile per 128-pixel tile instead of 9 / 16 shifted re-fetches, and
+ * the weights resident in shared memory when they fit.  wf / wd: the layer's weights as bf16 operand matrices, written by
+ * mmvae_convt_ts_pack_weights from the torch layout w (Cin,Cout,4,4); each holds mmvae_convt_ts_packed_elems() 16-bit
+ * elements.  Tensors NHWC fp32 as above; g is the gradient w.r.t. the PRE-activation. */
+int  mmvae_convt_ts_supported(int H, int W, int Cin, int Cout);
+long mmvae_convt_ts_packed_elems(int Cin, int Cout);
+int  mmvae_convt_ts_pack_weights(const float* w, void* wf, void* wd, int Cin, int Cout, void* stream);
+int  mmvae_convt_ts_fwd(const float* x, const void* wf, const float* bias, float* y, int Nimg, int H, int W, int Cin,
+                        int Cout, int act, void* stream);
+int  mmvae_convt_ts_dgrad(const float* g, const void* wd, const float* x_mask, float* gx, int Nimg, int H, int W, int Cin,
+                          int Cout, void* stream);
+
 /* MADE / MAF / IAF elementwise pieces (maf_model.py:62-74,91-104; iaf_model.py:60-78,94-100).  The masked-linear
  * contractions go through mmvae_gemm with the pre-masked weight (layers.py:24-25: F.linear(x, mask*W, b)). */
 int mmvae_mask_weight(const float* w, const float* mask, float* out, long n, void* stream);

@@ -14,7 +14,7 @@ HEADER_PATH = os.path.join(os.path.dirname(HERE), "include", "mmvae_b200.h")
 _CTYPES = {
     "int": ctypes.c_int, "long": ctypes.c_long, "float": ctypes.c_float,
     "const float*": ctypes.c_void_p, "float*": ctypes.c_void_p, "void*": ctypes.c_void_p,
-    "const int*": ctypes.c_void_p,
+    "const int*": ctypes.c_void_p, "const void*": ctypes.c_void_p,
     "const char*": ctypes.c_char_p, "void": None,
 }
 _PROTO = re.compile(r"^\s*(int|long|const char\*)\s+(mmvae_\w+)\s*\(([^;{]*?)\)\s*;", re.M | re.S)

@@ -1,0 +1,521 @@
+// ConvTranspose2d(k4, s2, p1) forward and data gradient, second generation (replaces the shared-memory-operand kernels of
+// gemm_tc.cu for the decoder's middle layers, encoders.py:113-124 and their autograd backward).
+//
+// What bounded the first generation (profiles/r1_decoder_kernels_ncu_full_4d1e464.txt): a tcgen05.mma whose A operand is in
+// shared memory costs max(32 + N/4, N/2) clocks — the 32 is the read of the 128-row A tile — so with N = Cout <= 128 and three
+// tf32 passes the issue stream was operand-read-bound (tensor pipe 26-47 % active); every A window was fetched 9 / 16 times from
+// L2; the hi/lo split went through shared memory.  Here (measured in tools/ts_probe.cu, profiles/r2_umma_ts_probe.txt):
+//   * the A operand is read from TENSOR MEMORY ("TS" form): N/2 clocks per MMA, no shared-memory read of A at all;
+//   * operands are split into bf16 (hi, mid) and the product is hi*hi + hi*mid + mid*hi in kind::f16 — K = 16 per MMA at the
+//     clocks tf32 needs for K = 8; the dropped terms (mid*mid, hi*lo, lo*hi) are <= 3 * 2^-18 of |a||b| per product;
+//   * ONE halo tile per 128-pixel tile and 32-channel chunk arrives by TMA (out-of-image rows / columns = the unit's zero fill);
+//     the 9 (forward) or 4x4 (dgrad, per output-parity class) shifted windows are sub-views of it;
+//   * eight converter warps split the landed fp32 tile IN PLACE into packed bf16 pairs (row = 32 fp32 -> 16 hi words | 16 mid
+//     words, same 128 bytes, same 128-byte swizzle) and then copy, per shifted window, each pixel's row into the TMEM lane that
+//     owns the pixel (8 conflict-free 128-bit shared loads + one tcgen05.st of 32 columns): no conversion arithmetic per window;
+//   * weights are prepared once per step as bf16 (hi | mid) K-major rows (mmvae_convt_ts_pack_weights) and stay RESIDENT in
+//     shared memory when they fit (128 KB: the Cin*Cout = 2048 layer), else stream through a block ring.
+// Warp roles (480 threads): 0 = activation (A) TMA producer, 1 = weight (B) TMA producer, 2 = TMEM owner + MMA issuer,
+// 3-10 = converters (two warps per TMEM lane quarter, alternating windows), 11-14 = epilogue.
+// TMEM: columns 0..255 accumulators (double-buffered when they need <= 128 columns), 256..511 a ring of eight A slots
+// (32 columns: 16 hi-pair + 16 mid-pair columns = 32 channels).
+#include <cuda.h>
+#include <cudaTypedefs.h>
+#include "common.cuh"
+#include "sm100_ptx.cuh"
+
+#define TS_THREADS 480
+#define TS_NCONV 256                  // converter threads (warps 3..10)
+#define TS_NAS 8                      // A slots in TMEM
+#define TS_ND 16                      // per-window completion tickets
+#define TS_A_COL 256                  // first TMEM column of the A ring
+#define TS_FWD 0
+#define TS_DGRAD 1
+
+int mmvae_tc_dbg_bits();
+int mmvae_tc_encode(CUtensorMap* m, int is_bf16, int rank, const void* base, const cuuint64_t* dims, const cuuint64_t* strides,
+                    const cuuint32_t* box, const cuuint32_t* estr);
+
+// ---- window schedule ----------------------------------------------------------------------------------------------------
+// forward: one halo tile per chunk, 9 windows (dy,dx); window s feeds kNcls[s] output-parity classes whose accumulators are
+// adjacent in TMEM (Gray order of (py,px): (0,0),(0,1),(1,1),(1,0)) except dx = -1 (slots 0 and 3: two MMA groups).
+// Weight blocks (one class x 32 channels: Cout rows of 128 bytes) come in consumption order: block kRow[s] + q.
+// dgrad: per chunk one halo tile per output-parity class of g (stride-2 TMA box), 4 windows (ey,ex) each; block = cls*4+ey*2+ex.
+template <int MODE> struct TsSched;
+template <> struct TsSched<TS_FWD> {
+    static constexpr int STAGES = 1, WINDOWS = 9, BLOCKS = 16;
+};
+template <> struct TsSched<TS_DGRAD> {
+    static constexpr int STAGES = 4, WINDOWS = 4, BLOCKS = 16;
+};
+
+struct TsArgs {
+    int M;            // pixels of the coarse (input) grid = Nimg * H * W
+    int H, W;         // coarse grid
+    int chunks;       // 32-channel chunks of the contraction (fwd: Cin/32, dgrad: Cout/32)
+    int act;
+    int stage_bytes;  // one landed halo tile, rounded up to 1024
+    int stage_tx;     // bytes the TMA writes per tile
+    int nstg;         // halo tiles in flight
+    int nbs;          // weight-block slots (streaming) / 16*chunks (resident)
+    int resident;
+    int dbg;          // ablation bits (tools/ts_time.py), 0 in production: 1 no global stores, 2 no window copies, 4 no split,
+                      // 8 no MMAs, 16 no activation loads
+};
+
+// in-place split of one landed row: 32 fp32 -> 16 words of packed bf16 hi pairs | 16 words of packed bf16 mid pairs.
+// cvt.rn.bf16x2.f32 d, a, b: upper half = a, lower half = b; the lower half holds the even k.
+__device__ __forceinline__ void ts_split_row(uint32_t row_addr, int sw) {
+    float f[32];
+#pragma unroll
+    for (int c = 0; c < 8; ++c)
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(f[4 * c]), "=f"(f[4 * c + 1]), "=f"(f[4 * c + 2]), "=f"(f[4 * c + 3])
+                     : "r"(row_addr + ((uint32_t)(c ^ sw) << 4)));
+    uint32_t hp[16], mp[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hp[j]) : "f"(f[2 * j + 1]), "f"(f[2 * j]));
+        const float r0 = f[2 * j] - __uint_as_float(hp[j] << 16), r1 = f[2 * j + 1] - __uint_as_float(hp[j] & 0xffff0000u);
+        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(mp[j]) : "f"(r1), "f"(r0));
+    }
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row_addr + ((uint32_t)(c ^ sw) << 4)), "r"(hp[4 * c]), "r"(hp[4 * c + 1]),
+                     "r"(hp[4 * c + 2]), "r"(hp[4 * c + 3]) : "memory");
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row_addr + ((uint32_t)((4 + c) ^ sw) << 4)), "r"(mp[4 * c]), "r"(mp[4 * c + 1]),
+                     "r"(mp[4 * c + 2]), "r"(mp[4 * c + 3]) : "memory");
+    }
+}
+
+// NB: rows of one weight block = MMA N of one class (forward: Cout) / of the tile (dgrad: Cin)
+template <int MODE, int NB>
+__global__ void __launch_bounds__(TS_THREADS, 1)
+convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                const float* __restrict__ bias, const float* __restrict__ mask, float* __restrict__ out, const TsArgs ar) {
+    using S = TsSched<MODE>;
+    constexpr int BLOCK_BYTES = NB * 128;
+    constexpr int ACC_COLS = (MODE == TS_FWD) ? 4 * NB : NB;
+    constexpr int NACC = (2 * ACC_COLS <= TS_A_COL) ? 2 : 1;
+    constexpr int IPC = S::STAGES * S::WINDOWS;                 // windows per chunk
+    static_assert(ACC_COLS <= TS_A_COL, "accumulators overlap the A ring");
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* bring = smem + ar.nstg * ar.stage_bytes;
+    uint64_t* bars = (uint64_t*)(bring + (size_t)ar.nbs * BLOCK_BYTES);
+    uint64_t* full = bars;                 // [8]  halo tile landed
+    uint64_t* empty = bars + 8;            // [8]  halo tile read by all converter warps
+    uint64_t* a_full = bars + 16;          // [TS_NAS] window copied into its TMEM slot
+    uint64_t* done = bars + 24;            // [TS_ND] MMAs of a window completed (frees its A slot and weight blocks)
+    uint64_t* b_full = bars + 40;          // [32] weight blocks of a window landed
+    uint64_t* tfull = bars + 72;           // [2]
+    uint64_t* tempty = bars + 74;          // [2]
+    uint32_t* tmem_slot = (uint32_t*)(bars + 76);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int H = ar.H, W = ar.W, HW = H * W, IMGS = 128 / HW;
+    const int tiles = (ar.M + 127) / 128;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < 8; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, TS_NCONV / 32); mbar_init(a_full + s, 4); }
+        for (int s = 0; s < TS_ND; ++s) mbar_init(done + s, 1);
+        for (int s = 0; s < 32; ++s) mbar_init(b_full + s, 1);
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 4); }
+        mbar_fence_init();
+        tma_prefetch_desc(&tmap_a);
+        tma_prefetch_desc(&tmap_b);
+    }
+    if (warp == 2) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== activation producer: one halo tile per (tile, chunk[, class]) =====
+        const uint32_t a_ring = smem_u32(smem);
+        int sidx = 0;
+        for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+            const int n0 = t * IMGS;
+            for (int ck = 0; ck < ar.chunks; ++ck)
+                for (int st = 0; st < S::STAGES; ++st, ++sidx) {
+                    const int s = sidx % ar.nstg, ph = (sidx / ar.nstg) & 1;
+                    mbar_wait(empty + s, ph ^ 1);
+                    if (ar.dbg & 16) { mbar_arrive_elect(full + s); continue; }
+                    mbar_arrive_expect_tx_elect(full + s, ar.stage_tx);
+                    if (MODE == TS_FWD) tma_load_4d_elect(a_ring + s * ar.stage_bytes, &tmap_a, full + s, ck * 32, -1, -1, n0);
+                    else tma_load_4d_elect(a_ring + s * ar.stage_bytes, &tmap_a, full + s, ck * 32, -(st & 1), -(st >> 1), n0);
+                }
+        }
+    } else if (warp == 1) {
+        // ===== weight producer =====
+        const uint32_t b_ring = smem_u32(bring);
+        int itg = 0, ti = 0;
+        for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++ti) {
+            if (ar.resident && ti > 0) break;
+            for (int ck = 0; ck < ar.chunks; ++ck) {
+#pragma unroll
+                for (int i = 0; i < IPC; ++i, ++itg) {
+                    constexpr int8_t kNcls[9] = {4, 2, 2, 2, 2, 1, 1, 1, 1}, kRow[9] = {0, 4, 6, 8, 10, 12, 13, 14, 15};
+                    constexpr int8_t kBack[9] = {5, 4, 3, 3, 4, 4, 5, 5, 6};          // forward, 8 slots: see gemm_tc.cu F9_BACK
+                    const int nblk = (MODE == TS_FWD) ? kNcls[i % 9] : 1, blk0 = (MODE == TS_FWD) ? kRow[i % 9] : i;
+                    uint64_t* bar;
+                    int slot;
+                    if (ar.resident) {
+                        bar = b_full + ck * IPC + i;
+                        slot = ck * 16 + blk0;
+                    } else {
+                        const int back = (MODE == TS_FWD) ? kBack[i % 9] : ar.nbs, j = itg - back;
+                        if (j >= 0) mbar_wait(done + (j % TS_ND), (j / TS_ND) & 1);
+                        bar = b_full + (itg % TS_ND);
+                        slot = (MODE == TS_FWD) ? (blk0 & 7) : (itg % ar.nbs);
+                    }
+                    mbar_arrive_expect_tx_elect(bar, nblk * BLOCK_BYTES);
+#pragma unroll
+                    for (int q = 0; q < nblk; ++q)
+                        tma_load_2d_elect(b_ring + (slot + q) * BLOCK_BYTES, &tmap_b, bar, ck * 64, (blk0 + q) * NB);
+                }
+            }
+        }
+    } else if (warp == 2) {
+        // ===== MMA issuer (whole warp converged, one elected lane issues) =====
+        constexpr uint32_t idesc1 = umma_idesc_bf16(128, NB, 0, 0);
+        constexpr uint32_t idesc2 = umma_idesc_bf16(128, 2 * NB <= 256 ? 2 * NB : 256, 0, 0);
+        constexpr uint32_t idesc4 = umma_idesc_bf16(128, 4 * NB <= 256 ? 4 * NB : 256, 0, 0);
+        const uint64_t db0 = umma_smem_desc(smem_u32(bring), 16, 1024, 2);
+        int itg = 0, ti = 0;
+        for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++ti) {
+            const int acc = ti % NACC, use = ti / NACC;
+            mbar_wait(tempty + acc, (use & 1) ^ 1);
+            tc_fence_after_sync();
+            const uint32_t d_acc = tmem_base + acc * ACC_COLS;
+            for (int ck = 0; ck < ar.chunks; ++ck) {
+#pragma unroll
+                for (int i = 0; i < IPC; ++i, ++itg) {
+                    constexpr int8_t kRow[9] = {0, 4, 6, 8, 10, 12, 13, 14, 15};
+                    constexpr int8_t kSlot[9] = {0, 0, 2, 1, 0, 0, 1, 2, 3}, kNc[9] = {4, 2, 2, 2, 1, 1, 1, 1, 1};
+                    const int blk0 = (MODE == TS_FWD) ? kRow[i % 9] : i;
+                    mbar_wait(a_full + (itg % TS_NAS), (itg / TS_NAS) & 1);
+                    int slot;
+                    if (ar.resident) {
+                        mbar_wait(b_full + ck * IPC + i, 0);
+                        slot = ck * 16 + blk0;
+                    } else {
+                        mbar_wait(b_full + (itg % TS_ND), (itg / TS_ND) & 1);
+                        slot = (MODE == TS_FWD) ? (blk0 & 7) : (itg % ar.nbs);
+                    }
+                    tc_fence_after_sync();
+                    const uint32_t a_col = tmem_base + TS_A_COL + (itg % TS_NAS) * 32;
+                    const uint64_t db = db0 + (uint64_t)(slot * (BLOCK_BYTES >> 4));
+                    const uint32_t idesc = (MODE == TS_DGRAD) ? idesc1 : (kNc[i % 9] == 4 ? idesc4 : (kNc[i % 9] == 2 ? idesc2 : idesc1));
+#pragma unroll
+                    for (int kk = 0; kk < 2; ++kk) {
+                        if ((ar.dbg & 8) && (ck | i | kk) != 0) break;
+                        const uint32_t first = (ck | i | kk) != 0;      // the first window of a tile spans every accumulator column
+#pragma unroll
+                        for (int gi = 0; gi < ((MODE == TS_FWD && i == 4) ? 2 : 1); ++gi) {
+                            const uint32_t col = (MODE == TS_FWD) ? (gi ? 3 : kSlot[i % 9]) * NB : 0;
+                            const uint64_t dbg = db + (uint64_t)(gi * (BLOCK_BYTES >> 4) + kk * 2);
+                            umma_bf16_ts_elect(d_acc + col, a_col + kk * 8, dbg, idesc, first);             // hi  * hi
+                            umma_bf16_ts_elect(d_acc + col, a_col + kk * 8, dbg + 4, idesc, 1);             // hi  * mid
+                            umma_bf16_ts_elect(d_acc + col, a_col + 16 + kk * 8, dbg, idesc, 1);            // mid * hi
+                        }
+                    }
+                    umma_commit_elect(done + (itg % TS_ND));
+                }
+            }
+            umma_commit_elect(tfull + acc);
+        }
+    } else if (warp < 11) {
+        // ===== converters =====
+        const int ctid = threadIdx.x - 96, wset = (warp - 3) >> 2, quarter = warp & 3;
+        const int L = quarter * 32 + lane, n_l = L / HW, rem = L - n_l * HW, yy = rem / W, xx = rem - yy * W;
+        const int pitch = (MODE == TS_FWD) ? W + 2 : W + 1;
+        const int base_row = (MODE == TS_FWD) ? (n_l * (H + 2) + yy + 1) * pitch + xx + 1 : (n_l * (H + 1) + yy) * pitch + xx;
+        const int rows = ar.stage_tx >> 7;
+        const uint32_t a_ring = smem_u32(smem);
+        const uint32_t t_lane = tmem_base + ((uint32_t)(quarter * 32) << 16) + TS_A_COL;
+        int sidx = 0, itg = 0;
+        for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+            for (int ck = 0; ck < ar.chunks; ++ck)
+                for (int st = 0; st < S::STAGES; ++st, ++sidx) {
+                    const int s = sidx % ar.nstg, ph = (sidx / ar.nstg) & 1;
+                    const uint32_t base = a_ring + s * ar.stage_bytes;
+                    mbar_wait(full + s, ph);
+                    if (!(ar.dbg & 4))
+                        for (int r = ctid; r < rows; r += TS_NCONV) ts_split_row(base + r * 128, r & 7);
+                    asm volatile("bar.sync 1, 256;" ::: "memory");
+#pragma unroll
+                    for (int i = 0; i < S::WINDOWS; ++i, ++itg) {
+                        constexpr int8_t kDy[9] = {0, -1, 1, 0, 0, -1, -1, 1, 1}, kDx[9] = {0, 0, 0, 1, -1, -1, 1, 1, -1};
+                        if ((itg & 1) != wset) continue;
+                        if (itg >= TS_NAS) {
+                            const int j = itg - TS_NAS;
+                            mbar_wait(done + (j % TS_ND), (j / TS_ND) & 1);
+                        }
+                        tc_fence_after_sync();
+                        const int row = base_row + ((MODE == TS_FWD) ? kDy[i % 9] * pitch + kDx[i % 9] : (i >> 1) * pitch + (i & 1));
+                        const uint32_t addr = base + row * 128;
+                        const int sw = row & 7;
+                        if (!(ar.dbg & 2)) {
+                            uint32_t v[32];
+#pragma unroll
+                            for (int c = 0; c < 8; ++c)
+                                asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v[4 * c]), "=r"(v[4 * c + 1]), "=r"(v[4 * c + 2]), "=r"(v[4 * c + 3])
+                                             : "r"(addr + ((uint32_t)(c ^ sw) << 4)));
+                            tmem_st_32x32(t_lane + (itg % TS_NAS) * 32, v);
+                            tmem_st_wait();
+                        }
+                        tc_fence_before_sync();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(a_full + (itg % TS_NAS));
+                    }
+                    fence_proxy_async_smem();          // generic reads / writes of the tile ordered before the TMA that refills it
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(empty + s);
+                }
+        }
+    } else {
+        // ===== epilogue (warps 11..14): TMEM -> registers -> global, one thread = one pixel row =====
+        const int lane_base = (warp & 3) * 32;
+        // forward: the bias stays in registers for the whole kernel (issue slots are shared with the converter warps)
+        float bv[(MODE == TS_FWD) ? NB : 1];
+        if (MODE == TS_FWD) {
+#pragma unroll
+            for (int j = 0; j < NB; ++j) bv[j] = bias ? __ldg(bias + j) : 0.f;
+        }
+        int ti = 0;
+        for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++ti) {
+            const int acc = ti % NACC, use = ti / NACC;
+            const int row = t * 128 + lane_base + lane;
+            const uint32_t tb = tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)(acc * ACC_COLS);
+            if (MODE == TS_FWD) {
+                const int n_img = row / HW, rem = row - n_img * HW, ii = rem / W, jj = rem - ii * W;
+                float* const y00 = out + ((long)(n_img * 2 * H + 2 * ii) * (2 * W) + 2 * jj) * NB;       // class (0,0) position
+                mbar_wait(tfull + acc, use & 1);
+                tc_fence_after_sync();
+#pragma unroll 1
+                for (int slot = 0; slot < 4; ++slot) {
+                    const int py = slot >> 1, px = (slot & 1) ^ py;                  // Gray slot -> (py, px)
+                    float* p = y00 + ((long)py * (2 * W) + px) * NB;
+#pragma unroll
+                    for (int cc = 0; cc < NB; cc += 32) {
+                        float v[32];
+                        tmem_ld_32x32(tb + (uint32_t)(slot * NB + cc), v);
+                        if (slot == 3 && cc + 32 == NB) {
+                            tc_fence_before_sync();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(tempty + acc);
+                        }
+                        if (row < ar.M && !(ar.dbg & 1)) {
+#pragma unroll
+                            for (int j = 0; j < 32; j += 4) {
+                                float4 o = make_float4(v[j] + bv[cc + j], v[j + 1] + bv[cc + j + 1], v[j + 2] + bv[cc + j + 2],
+                                                       v[j + 3] + bv[cc + j + 3]);
+                                if (ar.act == MMVAE_ACT_RELU) {
+                                    o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f);
+                                } else if (ar.act == MMVAE_ACT_SIGMOID) {
+                                    o.x = 1.f / (1.f + expf(-o.x)); o.y = 1.f / (1.f + expf(-o.y));
+                                    o.z = 1.f / (1.f + expf(-o.z)); o.w = 1.f / (1.f + expf(-o.w));
+                                }
+                                __stcs(reinterpret_cast<float4*>(p + cc + j), o);
+                            }
+                        }
+                    }
+                }
+            } else {
+                float* p = out + (long)row * NB;
+                const float* mrow = mask ? mask + (long)row * NB : nullptr;
+                float4 mk[8];
+                auto load_mask = [&](int cc) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        mk[j] = (mrow && row < ar.M) ? __ldg(reinterpret_cast<const float4*>(mrow + cc + 4 * j)) : make_float4(1.f, 1.f, 1.f, 1.f);
+                };
+                load_mask(0);                             // requested before the accumulator is complete
+                mbar_wait(tfull + acc, use & 1);
+                tc_fence_after_sync();
+#pragma unroll
+                for (int cc = 0; cc < NB; cc += 32) {
+                    float v[32];
+                    tmem_ld_32x32(tb + (uint32_t)cc, v);
+                    if (cc + 32 == NB) {
+                        tc_fence_before_sync();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(tempty + acc);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        float4 o = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                        const float4 m = mk[j];
+                        o.x = m.x > 0.f ? o.x : 0.f; o.y = m.y > 0.f ? o.y : 0.f;
+                        o.z = m.z > 0.f ? o.z : 0.f; o.w = m.w > 0.f ? o.w : 0.f;
+                        if (row < ar.M && !(ar.dbg & 1)) __stcs(reinterpret_cast<float4*>(p + cc + 4 * j), o);
+                    }
+                    if (cc + 32 < NB) load_mask(cc + 32);
+                }
+            }
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem_base, 512);
+}
+
+// ------------------------------------------------------------------------------------------------------------ host side
+#define TS_SMEM_MAX 232448            // 227 KB opt-in limit per CTA
+
+static bool ts_geometry(int H, int W) {
+    const int HW = H * W;
+    return H >= 2 && W >= 2 && HW <= 128 && 128 % HW == 0 && W + 2 <= 256 && H + 2 <= 256;
+}
+
+// 1 when both directions of the layer run on the kernels of this file
+extern "C" int mmvae_convt_ts_supported(int H, int W, int Cin, int Cout) {
+    if (!mmvae_has_tcgen05() || !ts_geometry(H, W)) return 0;
+    if (Cin % 32 || Cout % 32) return 0;
+    const bool fwd_ok = (Cout == 32 || Cout == 64) && Cin <= 256;       // accumulators: 4 classes x Cout <= 256 columns
+    const bool dgrad_ok = (Cin == 32 || Cin == 64 || Cin == 128) && Cout <= 256;
+    return fwd_ok && dgrad_ok;
+}
+
+// Weights of one layer, w [Cin][Cout][4][4] (torch layout), as the two bf16 operand matrices (row = 64-element K groups of
+// [32 hi | 32 mid]):  wf [16*Cout][Cin/32 * 64]: row (kRow-ordered class row r)*Cout + co, contraction ci;
+//                     wd [16*Cin ][Cout/32 * 64]: row (cls*4 + ey*2 + ex)*Cin + ci, contraction co.
+__global__ void convt_ts_pack_kernel(const float* __restrict__ w, uint16_t* __restrict__ wf, uint16_t* __restrict__ wd, int Cin,
+                                     int Cout) {
+    const long n = 16L * Cin * Cout;
+    for (long idx = (long)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += (long)gridDim.x * blockDim.x) {
+        const int kx = (int)(idx & 3), ky = (int)((idx >> 2) & 3), co = (int)((idx >> 4) % Cout), ci = (int)(idx / (16L * Cout));
+        const float v = w[idx];
+        uint32_t hb, mb;
+        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hb) : "f"(0.f), "f"(v));
+        const float r = v - __uint_as_float(hb << 16);
+        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(mb) : "f"(0.f), "f"(r));
+        const uint16_t hi = (uint16_t)(hb & 0xffffu), mid = (uint16_t)(mb & 0xffffu);
+        // forward: output class (py,px), window shift (dy,dx): ky = 1 + py - 2*dy
+        {
+            const int py = (ky == 1 || ky == 3) ? 0 : 1, dy = (ky == 1 || ky == 2) ? 0 : (ky == 3 ? -1 : 1);
+            const int px = (kx == 1 || kx == 3) ? 0 : 1, dx = (kx == 1 || kx == 2) ? 0 : (kx == 3 ? -1 : 1);
+            // window index in the kernel's order and the rank q of the class among those the window feeds (ascending Gray slot)
+            const int8_t kDy[9] = {0, -1, 1, 0, 0, -1, -1, 1, 1}, kDx[9] = {0, 0, 0, 1, -1, -1, 1, 1, -1};
+            const int8_t kRow[9] = {0, 4, 6, 8, 10, 12, 13, 14, 15};
+            int sh = 0;
+            while (kDy[sh] != dy || kDx[sh] != dx) ++sh;
+            const int gslot = py * 2 + (px ^ py);
+            int q = 0;
+            for (int g = 0; g < gslot; ++g) {
+                const int gpy = g >> 1, gpx = (g & 1) ^ gpy;
+                const bool oky = dy == 0 || (dy < 0 ? gpy == 0 : gpy == 1), okx = dx == 0 || (dx < 0 ? gpx == 0 : gpx == 1);
+                q += (oky && okx);
+            }
+            const long row = (long)(kRow[sh] + q) * Cout + co;
+            const long col = (long)(ci >> 5) * 64 + (ci & 31);
+            const long ld = (long)(Cin >> 5) * 64;
+            wf[row * ld + col] = hi;
+            wf[row * ld + col + 32] = mid;
+        }
+        // dgrad: class py = (ky even), window ey = ky >> 1 (ky = py ? 2*ey : 1 + 2*ey)
+        {
+            const int py = (ky & 1) ? 0 : 1, ey = ky >> 1, px = (kx & 1) ? 0 : 1, ex = kx >> 1;
+            const long row = (long)((py * 2 + px) * 4 + ey * 2 + ex) * Cin + ci;
+            const long col = (long)(co >> 5) * 64 + (co & 31);
+            const long ld = (long)(Cout >> 5) * 64;
+            wd[row * ld + col] = hi;
+            wd[row * ld + col + 32] = mid;
+        }
+    }
+}
+
+extern "C" long mmvae_convt_ts_packed_elems(int Cin, int Cout) { return 16L * Cin * Cout * 2; }   // bf16 elements per matrix
+
+extern "C" int mmvae_convt_ts_pack_weights(const float* w, void* wf, void* wd, int Cin, int Cout, void* stream) {
+    MMVAE_REQUIRE(w && wf && wd && Cin > 0 && Cout > 0 && Cin % 32 == 0 && Cout % 32 == 0, "convt_ts_pack_weights: bad arguments");
+    const long n = 16L * Cin * Cout;
+    const int grid = (int)min((long)MMVAE_NUM_SMS * 4, (n + 255) / 256);
+    convt_ts_pack_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(w, (uint16_t*)wf, (uint16_t*)wd, Cin, Cout);
+    MMVAE_LAUNCH_CHECK("convt_ts_pack_weights");
+    return 0;
+}
+
+template <int MODE, int NB>
+static int ts_launch(const CUtensorMap& ta, const CUtensorMap& tb, const float* bias, const float* mask, float* out, TsArgs ar,
+                     int rows, cudaStream_t st) {
+    static bool attr_done = false;
+    auto kern = convt_ts_kernel<MODE, NB>;
+    constexpr int BLOCK_BYTES = NB * 128;
+    ar.stage_tx = rows * 128;
+    ar.dbg = mmvae_tc_dbg_bits();
+    ar.stage_bytes = (ar.stage_tx + 1023) & ~1023;
+    const long res_bytes = 16L * ar.chunks * BLOCK_BYTES;
+    ar.resident = res_bytes <= 131072;
+    ar.nbs = ar.resident ? 16 * ar.chunks : (MODE == TS_FWD ? 8 : 6);
+    const long fixed = (long)ar.nbs * BLOCK_BYTES + 1024 /*barriers*/ + 1024 /*alignment*/;
+    ar.nstg = (int)((TS_SMEM_MAX - fixed) / ar.stage_bytes);
+    if (ar.nstg > 8) ar.nstg = 8;
+    if (ar.nstg < 2) return mmvae_set_error(1, "convt_ts: shared memory plan does not fit (stage %d bytes)", ar.stage_bytes);
+    const int smem = (int)(fixed + (long)ar.nstg * ar.stage_bytes);
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM_MAX);
+        if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "convt_ts: smem attribute: %s", cudaGetErrorString(e));
+        attr_done = true;
+    }
+    const int tiles = (ar.M + 127) / 128;
+    const int grid = tiles < MMVAE_NUM_SMS ? tiles : MMVAE_NUM_SMS;
+    kern<<<grid, TS_THREADS, smem, st>>>(ta, tb, bias, mask, out, ar);
+    MMVAE_LAUNCH_CHECK("convt_ts");
+    return 0;
+}
+
+static int ts_map_b(CUtensorMap* m, const void* wb, int rows, int chunks, int NB) {
+    cuuint64_t dims[2] = {(cuuint64_t)chunks * 64, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)chunks * 64 * 2};
+    cuuint32_t box[2] = {64u, (cuuint32_t)NB}, estr[2] = {1u, 1u};
+    return mmvae_tc_encode(m, 1, 2, wb, dims, strides, box, estr);
+}
+
+// forward.  x: [Nimg,H,W,Cin] NHWC fp32; wf from mmvae_convt_ts_pack_weights; y: [Nimg,2H,2W,Cout] NHWC = act(convT(x) + bias)
+extern "C" int mmvae_convt_ts_fwd(const float* x, const void* wf, const float* bias, float* y, int Nimg, int H, int W, int Cin,
+                                  int Cout, int act, void* stream) {
+    MMVAE_REQUIRE(x && wf && y && Nimg > 0, "convt_ts_fwd: bad arguments");
+    MMVAE_REQUIRE(mmvae_convt_ts_supported(H, W, Cin, Cout), "convt_ts_fwd: unsupported shape H=%d W=%d Cin=%d Cout=%d", H, W, Cin, Cout);
+    const int IMGS = 128 / (H * W);
+    CUtensorMap ta, tb;
+    cuuint64_t dims[4] = {(cuuint64_t)Cin, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)Nimg};
+    cuuint64_t strides[3] = {(cuuint64_t)Cin * 4, (cuuint64_t)W * Cin * 4, (cuuint64_t)H * W * Cin * 4};
+    cuuint32_t box[4] = {32u, (cuuint32_t)(W + 2), (cuuint32_t)(H + 2), (cuuint32_t)IMGS}, estr[4] = {1u, 1u, 1u, 1u};
+    int rc = mmvae_tc_encode(&ta, 0, 4, x, dims, strides, box, estr);
+    if (rc) return mmvae_set_error(1, "convt_ts_fwd: tensor map (x) failed with %d", rc);
+    rc = ts_map_b(&tb, wf, 16 * Cout, Cin / 32, Cout);
+    if (rc) return mmvae_set_error(1, "convt_ts_fwd: tensor map (w) failed with %d", rc);
+    TsArgs ar{};
+    ar.M = Nimg * H * W; ar.H = H; ar.W = W; ar.chunks = Cin / 32; ar.act = act;
+    const int rows = IMGS * (H + 2) * (W + 2);
+    cudaStream_t st = (cudaStream_t)stream;
+    return Cout == 32 ? ts_launch<TS_FWD, 32>(ta, tb, bias, nullptr, y, ar, rows, st)
+                      : ts_launch<TS_FWD, 64>(ta, tb, bias, nullptr, y, ar, rows, st);
+}
+
+// dgrad.  g: [Nimg,2H,2W,Cout] NHWC gradient w.r.t. the layer's pre-activation; wd from mmvae_convt_ts_pack_weights;
+// gx: [Nimg,H,W,Cin]; x_mask: NULL or the layer input (gx zeroed where x <= 0: the ReLU backward of the layer below)
+extern "C" int mmvae_convt_ts_dgrad(const float* g, const void* wd, const float* x_mask, float* gx, int Nimg, int H, int W,
+                                    int Cin, int Cout, void* stream) {
+    MMVAE_REQUIRE(g && wd && gx && Nimg > 0, "convt_ts_dgrad: bad arguments");
+    MMVAE_REQUIRE(mmvae_convt_ts_supported(H, W, Cin, Cout), "convt_ts_dgrad: unsupported shape");
+    const int IMGS = 128 / (H * W);
+    CUtensorMap ta, tb;
+    cuuint64_t dims[4] = {(cuuint64_t)Cout, (cuuint64_t)(2 * W), (cuuint64_t)(2 * H), (cuuint64_t)Nimg};
+    cuuint64_t strides[3] = {(cuuint64_t)Cout * 4, (cuuint64_t)2 * W * Cout * 4, (cuuint64_t)4 * H * W * Cout * 4};
+    cuuint32_t box[4] = {32u, (cuuint32_t)(2 * (W + 1)), (cuuint32_t)(2 * (H + 1)), (cuuint32_t)IMGS}, estr[4] = {1u, 2u, 2u, 1u};
+    int rc = mmvae_tc_encode(&ta, 0, 4, g, dims, strides, box, estr);
+    if (rc) return mmvae_set_error(1, "convt_ts_dgrad: tensor map (g) failed with %d", rc);
+    rc = ts_map_b(&tb, wd, 16 * Cin, Cout / 32, Cin);
+    if (rc) return mmvae_set_error(1, "convt_ts_dgrad: tensor map (w) failed with %d", rc);
+    TsArgs ar{};
+    ar.M = Nimg * H * W; ar.H = H; ar.W = W; ar.chunks = Cout / 32; ar.act = 0;
+    const int rows = IMGS * (H + 1) * (W + 1);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (Cin == 32) return ts_launch<TS_DGRAD, 32>(ta, tb, nullptr, x_mask, gx, ar, rows, st);
+    if (Cin == 64) return ts_launch<TS_DGRAD, 64>(ta, tb, nullptr, x_mask, gx, ar, rows, st);
+    return ts_launch<TS_DGRAD, 128>(ta, tb, nullptr, x_mask, gx, ar, rows, st);
+}

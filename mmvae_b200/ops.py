@@ -26,6 +26,7 @@ OBJ = {"iwae": C["MMVAE_OBJ_IWAE"], "iwae_looser": C["MMVAE_OBJ_IWAE_LOOSER"], "
 # launch counter (bench.py reports gpu_launches from it); counts C-ABI calls, each >= 1 kernel launch
 N_CALLS = 0
 ALLOW_TC = True          # let mmvae_gemm pick the tcgen05 path where it supports the shape
+ALLOW_TS = True          # transposed convolutions: second-generation kernels (A operand in tensor memory, bf16x3 split)
 
 
 def _dev(t, name="tensor"):
@@ -340,6 +341,20 @@ class ConvT2dAct(torch.autograd.Function):
         x2d = _as_rows(x)
         tc = (ALLOW_TC and not small and k == 4 and stride == 2 and pad == 1 and not nchw_out and w.shape[3] == 4
               and lib.mmvae_convt_tc_supported(H, W, Cin, Cout) == 1)
+        if tc and ALLOW_TS and lib.mmvae_convt_ts_supported(H, W, Cin, Cout) == 1:
+            ne = lib.mmvae_convt_ts_packed_elems(Cin, Cout)
+            wfb = torch.empty(ne, device=x.device, dtype=torch.int16)
+            wdb = torch.empty(ne, device=x.device, dtype=torch.int16)
+            _call("mmvae_convt_ts_pack_weights", _p(w), _p(wfb), _p(wdb), Cin, Cout, _stream())
+            y = torch.empty((N, 2 * H, 2 * W, Cout), device=x.device, dtype=torch.float32)
+            _call("mmvae_convt_ts_fwd", _p(x2d), _p(wfb), _p(b), _p(y), N, H, W, Cin, Cout, ACT[act], _stream(),
+                  work=("flop", 2.0 * N * H * W * 16 * Cin * Cout))
+            keep_y = (ACT[act] != C["MMVAE_ACT_NONE"]) and not preact_grad
+            ctx.save_for_backward(x2d, w, y if keep_y else None)
+            ctx.wdb = wdb
+            ctx.cfg = (N, Cin, H, W, Cout, k, stride, pad, act, tuple(w.shape), b is not None, preact_grad,
+                       mask_input_grad, "ts")
+            return y.permute(0, 3, 1, 2)
         if tc:
             wf = torch.empty((4 * Cout, 4 * Cin), device=x.device, dtype=torch.float32)
             _call("mmvae_convt_weight_classes", _p(w), _p(wf), Cin, Cout, _stream())
@@ -384,13 +399,18 @@ class ConvT2dAct(torch.autograd.Function):
         x2d, wp, y = ctx.saved_tensors
         N, Cin, H, W, Cout, k, s, p, act, wshape, has_bias, preact_grad, mask_in, path = ctx.cfg
         small = path == "small"
-        if path == "tc":
+        if path in ("tc", "ts"):
             w = wp
             g = _as_rows(_dev(gy, "grad"))                       # [N*2H*2W, Cout], NHWC
             if y is not None:
                 g = act_bwd(g, y.view(-1, Cout), act)
             gx = gw = gb = None
-            if ctx.needs_input_grad[0]:
+            if ctx.needs_input_grad[0] and path == "ts":
+                gx2d = torch.empty_like(x2d)
+                _call("mmvae_convt_ts_dgrad", _p(g), _p(ctx.wdb), _p(x2d if mask_in else None), _p(gx2d), N, H, W, Cin, Cout,
+                      _stream(), work=("flop", 2.0 * N * H * W * 16 * Cin * Cout))
+                gx = gx2d.view(N, H, W, Cin).permute(0, 3, 1, 2)
+            elif ctx.needs_input_grad[0]:
                 wpm = permute_weight(w)                          # [Cin, 16*Cout]
                 gx2d = torch.empty_like(x2d)
                 _call("mmvae_convt_tc_dgrad", _p(g), _p(wpm), _p(x2d if mask_in else None), _p(gx2d), N, H, W, Cin, Cout,
