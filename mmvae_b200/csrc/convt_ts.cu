@@ -87,17 +87,41 @@ __device__ __forceinline__ void ts_split_row(uint32_t row_addr, int sw) {
     }
 }
 
+// Windows are handed from the converters to the issuer, and released back, in BATCHES (one mbarrier round trip per batch;
+// per-window hand-offs cost more than the 170-clock MMA work of a window: tools/ts_time.py ablation): forward 3 batches of
+// 3 windows per chunk, dgrad 2 batches of 2 windows per class tile.  The eight A slots in TMEM remain a ring of windows.
+template <int MODE> struct TsBatch;
+template <> struct TsBatch<TS_FWD> {
+    static constexpr int BW = 3, PER_STAGE = 3, PER_CHUNK = 3;
+    __host__ __device__ static constexpr int of_window(int w) { return (w / 9) * 3 + (w % 9) / 3; }
+};
+template <> struct TsBatch<TS_DGRAD> {
+    static constexpr int BW = 2, PER_STAGE = 2, PER_CHUNK = 8;
+    __host__ __device__ static constexpr int of_window(int w) { return w >> 1; }
+};
+
+__device__ __forceinline__ void tmem_st_32x8(uint32_t taddr, const uint32_t* r) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), "r"(r[0]), "r"(r[1]),
+                 "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]) : "memory");
+}
+
 // NB: rows of one weight block = MMA N of one class (forward: Cout) / of the tile (dgrad: Cin)
 template <int MODE, int NB>
 __global__ void __launch_bounds__(TS_THREADS, 1)
 convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                 const float* __restrict__ bias, const float* __restrict__ mask, float* __restrict__ out, const TsArgs ar) {
     using S = TsSched<MODE>;
+    using Bt = TsBatch<MODE>;
     constexpr int BLOCK_BYTES = NB * 128;
     constexpr int ACC_COLS = (MODE == TS_FWD) ? 4 * NB : NB;
     constexpr int NACC = (2 * ACC_COLS <= TS_A_COL) ? 2 : 1;
-    constexpr int IPC = S::STAGES * S::WINDOWS;                 // windows per chunk
+    constexpr int BW = Bt::BW;
     static_assert(ACC_COLS <= TS_A_COL, "accumulators overlap the A ring");
+    // forward: weight blocks (class rows) of the three batches of a chunk
+    constexpr int8_t kNcls[9] = {4, 2, 2, 2, 2, 1, 1, 1, 1}, kRow[9] = {0, 4, 6, 8, 10, 12, 13, 14, 15};
+    constexpr int8_t kSlot[9] = {0, 0, 2, 1, 0, 0, 1, 2, 3}, kNc[9] = {4, 2, 2, 2, 1, 1, 1, 1, 1};
+    constexpr int8_t kDy[9] = {0, -1, 1, 0, 0, -1, -1, 1, 1}, kDx[9] = {0, 0, 0, 1, -1, -1, 1, 1, -1};
+    constexpr int8_t kB0[3] = {0, 8, 13}, kBn[3] = {8, 5, 3};
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -105,21 +129,22 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     uint64_t* bars = (uint64_t*)(bring + (size_t)ar.nbs * BLOCK_BYTES);
     uint64_t* full = bars;                 // [8]  halo tile landed
     uint64_t* empty = bars + 8;            // [8]  halo tile read by all converter warps
-    uint64_t* a_full = bars + 16;          // [TS_NAS] window copied into its TMEM slot
-    uint64_t* done = bars + 24;            // [TS_ND] MMAs of a window completed (frees its A slot and weight blocks)
-    uint64_t* b_full = bars + 40;          // [32] weight blocks of a window landed
-    uint64_t* tfull = bars + 72;           // [2]
-    uint64_t* tempty = bars + 74;          // [2]
-    uint32_t* tmem_slot = (uint32_t*)(bars + 76);
+    uint64_t* a_full = bars + 16;          // [8]  a batch of windows copied into its TMEM slots
+    uint64_t* done = bars + 24;            // [8]  MMAs of a batch completed (frees its A slots and weight blocks)
+    uint64_t* b_full = bars + 32;          // [16] weight blocks of a batch landed
+    uint64_t* tfull = bars + 48;           // [2]
+    uint64_t* tempty = bars + 50;          // [2]
+    uint32_t* tmem_slot = (uint32_t*)(bars + 52);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int H = ar.H, W = ar.W, HW = H * W, IMGS = 128 / HW;
     const int tiles = (ar.M + 127) / 128;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < 8; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, TS_NCONV / 32); mbar_init(a_full + s, 4); }
-        for (int s = 0; s < TS_ND; ++s) mbar_init(done + s, 1);
-        for (int s = 0; s < 32; ++s) mbar_init(b_full + s, 1);
+        for (int s = 0; s < 8; ++s) {
+            mbar_init(full + s, 1); mbar_init(empty + s, TS_NCONV / 32); mbar_init(a_full + s, TS_NCONV / 32); mbar_init(done + s, 1);
+        }
+        for (int s = 0; s < 16; ++s) mbar_init(b_full + s, 1);
         for (int a = 0; a < 2; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 4); }
         mbar_fence_init();
         tma_prefetch_desc(&tmap_a);
@@ -148,27 +173,26 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                 }
         }
     } else if (warp == 1) {
-        // ===== weight producer =====
+        // ===== weight producer: the blocks of one batch per mbarrier =====
         const uint32_t b_ring = smem_u32(bring);
-        int itg = 0, ti = 0;
+        const int back = (MODE == TS_FWD) ? 3 : ar.nbs / 2;          // batches after which a streaming slot is reused
+        int bid = 0, ti = 0;
         for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++ti) {
             if (ar.resident && ti > 0) break;
             for (int ck = 0; ck < ar.chunks; ++ck) {
 #pragma unroll
-                for (int i = 0; i < IPC; ++i, ++itg) {
-                    constexpr int8_t kNcls[9] = {4, 2, 2, 2, 2, 1, 1, 1, 1}, kRow[9] = {0, 4, 6, 8, 10, 12, 13, 14, 15};
-                    constexpr int8_t kBack[9] = {5, 4, 3, 3, 4, 4, 5, 5, 6};          // forward, 8 slots: see gemm_tc.cu F9_BACK
-                    const int nblk = (MODE == TS_FWD) ? kNcls[i % 9] : 1, blk0 = (MODE == TS_FWD) ? kRow[i % 9] : i;
+                for (int b = 0; b < Bt::PER_CHUNK; ++b, ++bid) {
+                    const int blk0 = (MODE == TS_FWD) ? kB0[b % 3] : 2 * b, nblk = (MODE == TS_FWD) ? kBn[b % 3] : 2;
                     uint64_t* bar;
                     int slot;
                     if (ar.resident) {
-                        bar = b_full + ck * IPC + i;
+                        bar = b_full + ck * Bt::PER_CHUNK + b;
                         slot = ck * 16 + blk0;
                     } else {
-                        const int back = (MODE == TS_FWD) ? kBack[i % 9] : ar.nbs, j = itg - back;
-                        if (j >= 0) mbar_wait(done + (j % TS_ND), (j / TS_ND) & 1);
-                        bar = b_full + (itg % TS_ND);
-                        slot = (MODE == TS_FWD) ? (blk0 & 7) : (itg % ar.nbs);
+                        const int j = bid - back;
+                        if (j >= 0) mbar_wait(done + (j & 7), (j >> 3) & 1);
+                        bar = b_full + (bid & 7);
+                        slot = (MODE == TS_FWD) ? blk0 : (2 * bid) % ar.nbs;
                     }
                     mbar_arrive_expect_tx_elect(bar, nblk * BLOCK_BYTES);
 #pragma unroll
@@ -183,7 +207,7 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         constexpr uint32_t idesc2 = umma_idesc_bf16(128, 2 * NB <= 256 ? 2 * NB : 256, 0, 0);
         constexpr uint32_t idesc4 = umma_idesc_bf16(128, 4 * NB <= 256 ? 4 * NB : 256, 0, 0);
         const uint64_t db0 = umma_smem_desc(smem_u32(bring), 16, 1024, 2);
-        int itg = 0, ti = 0;
+        int bid = 0, ti = 0;
         for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++ti) {
             const int acc = ti % NACC, use = ti / NACC;
             mbar_wait(tempty + acc, (use & 1) ^ 1);
@@ -191,51 +215,56 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             const uint32_t d_acc = tmem_base + acc * ACC_COLS;
             for (int ck = 0; ck < ar.chunks; ++ck) {
 #pragma unroll
-                for (int i = 0; i < IPC; ++i, ++itg) {
-                    constexpr int8_t kRow[9] = {0, 4, 6, 8, 10, 12, 13, 14, 15};
-                    constexpr int8_t kSlot[9] = {0, 0, 2, 1, 0, 0, 1, 2, 3}, kNc[9] = {4, 2, 2, 2, 1, 1, 1, 1, 1};
-                    const int blk0 = (MODE == TS_FWD) ? kRow[i % 9] : i;
-                    mbar_wait(a_full + (itg % TS_NAS), (itg / TS_NAS) & 1);
+                for (int b = 0; b < Bt::PER_CHUNK; ++b, ++bid) {
+                    const int blk0 = (MODE == TS_FWD) ? kB0[b % 3] : 2 * b;
+                    mbar_wait(a_full + (bid & 7), (bid >> 3) & 1);
                     int slot;
                     if (ar.resident) {
-                        mbar_wait(b_full + ck * IPC + i, 0);
+                        mbar_wait(b_full + ck * Bt::PER_CHUNK + b, 0);
                         slot = ck * 16 + blk0;
                     } else {
-                        mbar_wait(b_full + (itg % TS_ND), (itg / TS_ND) & 1);
-                        slot = (MODE == TS_FWD) ? (blk0 & 7) : (itg % ar.nbs);
+                        mbar_wait(b_full + (bid & 7), (bid >> 3) & 1);
+                        slot = (MODE == TS_FWD) ? blk0 : (2 * bid) % ar.nbs;
                     }
                     tc_fence_after_sync();
-                    const uint32_t a_col = tmem_base + TS_A_COL + (itg % TS_NAS) * 32;
-                    const uint64_t db = db0 + (uint64_t)(slot * (BLOCK_BYTES >> 4));
-                    const uint32_t idesc = (MODE == TS_DGRAD) ? idesc1 : (kNc[i % 9] == 4 ? idesc4 : (kNc[i % 9] == 2 ? idesc2 : idesc1));
+                    const int w0 = bid * BW;                                 // global window index of the batch's first window
 #pragma unroll
-                    for (int kk = 0; kk < 2; ++kk) {
-                        if ((ar.dbg & 8) && (ck | i | kk) != 0) break;
-                        const uint32_t first = (ck | i | kk) != 0;      // the first window of a tile spans every accumulator column
+                    for (int wi = 0; wi < BW; ++wi) {
+                        const int i = b * BW + wi;                           // window within the chunk
+                        const uint32_t a_col = tmem_base + TS_A_COL + ((w0 + wi) & (TS_NAS - 1)) * 32;
+                        const int boff = (MODE == TS_FWD) ? kRow[i % 9] - kB0[b % 3] : wi;       // block within the batch
+                        const uint64_t db = db0 + (uint64_t)((slot + boff) * (BLOCK_BYTES >> 4));
+                        const uint32_t idesc = (MODE == TS_DGRAD) ? idesc1 : (kNc[i % 9] == 4 ? idesc4 : (kNc[i % 9] == 2 ? idesc2 : idesc1));
 #pragma unroll
-                        for (int gi = 0; gi < ((MODE == TS_FWD && i == 4) ? 2 : 1); ++gi) {
-                            const uint32_t col = (MODE == TS_FWD) ? (gi ? 3 : kSlot[i % 9]) * NB : 0;
-                            const uint64_t dbg = db + (uint64_t)(gi * (BLOCK_BYTES >> 4) + kk * 2);
-                            umma_bf16_ts_elect(d_acc + col, a_col + kk * 8, dbg, idesc, first);             // hi  * hi
-                            umma_bf16_ts_elect(d_acc + col, a_col + kk * 8, dbg + 4, idesc, 1);             // hi  * mid
-                            umma_bf16_ts_elect(d_acc + col, a_col + 16 + kk * 8, dbg, idesc, 1);            // mid * hi
+                        for (int kk = 0; kk < 2; ++kk) {
+                            if ((ar.dbg & 8) && (ck | i | kk) != 0) break;
+                            const uint32_t first = (ck | i | kk) != 0;      // the first window of a tile spans every accumulator column
+#pragma unroll
+                            for (int gi = 0; gi < ((MODE == TS_FWD && i == 4) ? 2 : 1); ++gi) {
+                                const uint32_t col = (MODE == TS_FWD) ? (gi ? 3 : kSlot[i % 9]) * NB : 0;
+                                const uint64_t dbg = db + (uint64_t)(gi * (BLOCK_BYTES >> 4) + kk * 2);
+                                umma_bf16_ts_elect(d_acc + col, a_col + kk * 8, dbg, idesc, first);             // hi  * hi
+                                umma_bf16_ts_elect(d_acc + col, a_col + kk * 8, dbg + 4, idesc, 1);             // hi  * mid
+                                umma_bf16_ts_elect(d_acc + col, a_col + 16 + kk * 8, dbg, idesc, 1);            // mid * hi
+                            }
                         }
                     }
-                    umma_commit_elect(done + (itg % TS_ND));
+                    umma_commit_elect(done + (bid & 7));
                 }
             }
             umma_commit_elect(tfull + acc);
         }
     } else if (warp < 11) {
-        // ===== converters =====
-        const int ctid = threadIdx.x - 96, wset = (warp - 3) >> 2, quarter = warp & 3;
+        // ===== converters: every warp takes part in every window; the two warps of a lane quarter split the 32 channels
+        // (half h: channels 16h..16h+15 = the MMA k-step h: hi columns 8h.., mid columns 16+8h..) =====
+        const int ctid = threadIdx.x - 96, half = (warp - 3) >> 2, quarter = warp & 3;
         const int L = quarter * 32 + lane, n_l = L / HW, rem = L - n_l * HW, yy = rem / W, xx = rem - yy * W;
         const int pitch = (MODE == TS_FWD) ? W + 2 : W + 1;
         const int base_row = (MODE == TS_FWD) ? (n_l * (H + 2) + yy + 1) * pitch + xx + 1 : (n_l * (H + 1) + yy) * pitch + xx;
         const int rows = ar.stage_tx >> 7;
         const uint32_t a_ring = smem_u32(smem);
-        const uint32_t t_lane = tmem_base + ((uint32_t)(quarter * 32) << 16) + TS_A_COL;
-        int sidx = 0, itg = 0;
+        const uint32_t t_lane = tmem_base + ((uint32_t)(quarter * 32) << 16) + TS_A_COL + 8 * half;
+        int sidx = 0, bid = 0;
         for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
             for (int ck = 0; ck < ar.chunks; ++ck)
                 for (int st = 0; st < S::STAGES; ++st, ++sidx) {
@@ -246,29 +275,40 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                         for (int r = ctid; r < rows; r += TS_NCONV) ts_split_row(base + r * 128, r & 7);
                     asm volatile("bar.sync 1, 256;" ::: "memory");
 #pragma unroll
-                    for (int i = 0; i < S::WINDOWS; ++i, ++itg) {
-                        constexpr int8_t kDy[9] = {0, -1, 1, 0, 0, -1, -1, 1, 1}, kDx[9] = {0, 0, 0, 1, -1, -1, 1, 1, -1};
-                        if ((itg & 1) != wset) continue;
-                        if (itg >= TS_NAS) {
-                            const int j = itg - TS_NAS;
-                            mbar_wait(done + (j % TS_ND), (j / TS_ND) & 1);
+                    for (int b = 0; b < Bt::PER_STAGE; ++b, ++bid) {
+                        const int w0 = bid * BW;
+                        const int jw = w0 + BW - 1 - TS_NAS;               // the window whose slot the batch's last window reuses
+                        if (jw >= 0) {
+                            const int j = Bt::of_window(jw);
+                            mbar_wait(done + (j & 7), (j >> 3) & 1);
                         }
                         tc_fence_after_sync();
-                        const int row = base_row + ((MODE == TS_FWD) ? kDy[i % 9] * pitch + kDx[i % 9] : (i >> 1) * pitch + (i & 1));
-                        const uint32_t addr = base + row * 128;
-                        const int sw = row & 7;
                         if (!(ar.dbg & 2)) {
-                            uint32_t v[32];
+                            uint32_t v[BW][16];
 #pragma unroll
-                            for (int c = 0; c < 8; ++c)
-                                asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v[4 * c]), "=r"(v[4 * c + 1]), "=r"(v[4 * c + 2]), "=r"(v[4 * c + 3])
-                                             : "r"(addr + ((uint32_t)(c ^ sw) << 4)));
-                            tmem_st_32x32(t_lane + (itg % TS_NAS) * 32, v);
+                            for (int wi = 0; wi < BW; ++wi) {
+                                const int i = b * BW + wi;                   // window within the stage
+                                const int row = base_row + ((MODE == TS_FWD) ? kDy[i % 9] * pitch + kDx[i % 9] : (i >> 1) * pitch + (i & 1));
+                                const uint32_t addr = base + row * 128;
+                                const int sw = row & 7;
+#pragma unroll
+                                for (int c = 0; c < 4; ++c) {
+                                    const int lc = (c < 2) ? 2 * half + c : 4 + 2 * half + (c - 2);      // logical 16-byte chunk
+                                    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v[wi][4 * c]), "=r"(v[wi][4 * c + 1]),
+                                                 "=r"(v[wi][4 * c + 2]), "=r"(v[wi][4 * c + 3]) : "r"(addr + ((uint32_t)(lc ^ sw) << 4)));
+                                }
+                            }
+#pragma unroll
+                            for (int wi = 0; wi < BW; ++wi) {
+                                const uint32_t ta = t_lane + ((w0 + wi) & (TS_NAS - 1)) * 32;
+                                tmem_st_32x8(ta, v[wi]);
+                                tmem_st_32x8(ta + 16, v[wi] + 8);
+                            }
                             tmem_st_wait();
                         }
                         tc_fence_before_sync();
                         __syncwarp();
-                        if (lane == 0) mbar_arrive(a_full + (itg % TS_NAS));
+                        if (lane == 0) mbar_arrive(a_full + (bid & 7));
                     }
                     fence_proxy_async_smem();          // generic reads / writes of the tile ordered before the TMA that refills it
                     __syncwarp();
@@ -449,7 +489,7 @@ static int ts_launch(const CUtensorMap& ta, const CUtensorMap& tb, const float* 
     ar.stage_bytes = (ar.stage_tx + 1023) & ~1023;
     const long res_bytes = 16L * ar.chunks * BLOCK_BYTES;
     ar.resident = res_bytes <= 131072;
-    ar.nbs = ar.resident ? 16 * ar.chunks : (MODE == TS_FWD ? 8 : 6);
+    ar.nbs = ar.resident ? 16 * ar.chunks : (MODE == TS_FWD ? 16 : 8);   // streaming: one chunk of class blocks / 4 batches
     const long fixed = (long)ar.nbs * BLOCK_BYTES + 1024 /*barriers*/ + 1024 /*alignment*/;
     ar.nstg = (int)((TS_SMEM_MAX - fixed) / ar.stage_bytes);
     if (ar.nstg > 8) ar.nstg = 8;

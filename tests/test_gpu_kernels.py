@@ -107,11 +107,15 @@ def test_convT2d_autograd(ops, cin, cout, H, s, p, act, nchw_out, N):
     yr = fn(F.conv_transpose2d(xd, wd, bd, stride=s, padding=p))
     assert y.shape == yr.shape
     assert y.is_contiguous() == nchw_out or cout == 1
-    assert rel_err(y, yr) < 2e-6
+    # shapes on the second-generation kernels (convt_ts.cu) compute hi*hi + hi*mid + mid*hi on bf16 pieces: each product is
+    # within 3 * 2^-18 = 1.1e-5 of exact (measured 3-5e-6 on the tensor); the 3xTF32 / SIMT paths are at 1e-6
+    from mmvae_b200 import _lib
+    ts = s == 2 and p == 1 and not nchw_out and _lib.load().mmvae_convt_ts_supported(H, H, cin, cout) == 1
+    assert rel_err(y, yr) < (1e-5 if ts else 2e-6)
     gy = _rand(*yr.shape, seed=4)
     gx, gw, gb = torch.autograd.grad(y, (x, w, b), gy)
     rx, rw, rb = torch.autograd.grad(yr, (xd, wd, bd), gy.double())
-    assert rel_err(gx, rx) < 5e-6 and rel_err(gw, rw) < 5e-6 and rel_err(gb, rb) < 5e-6
+    assert rel_err(gx, rx) < (1.5e-5 if ts else 5e-6) and rel_err(gw, rw) < (1.5e-5 if ts else 5e-6) and rel_err(gb, rb) < 5e-6
 
 
 def test_convT_last_layer_tensor_core_forward_is_deterministic_and_matches_simt(ops):
@@ -180,12 +184,12 @@ def test_convT2d_chain_fused_relu_backward(ops):
     r = torch.relu(F.conv_transpose2d(r, wd[1], bd[1], stride=2, padding=1))
     r = torch.relu(F.conv_transpose2d(r, wd[2], bd[2], stride=2, padding=1))
     yr = torch.sigmoid(F.conv_transpose2d(r, wd[3], bd[3], stride=2, padding=1))
-    assert rel_err(y, yr) < 2e-6
+    assert rel_err(y, yr) < 5e-6                     # two bf16x3 layers (convt_ts.cu) in the chain: 3-5e-6 each before the sigmoid
     gy = _rand(*yr.shape, seed=4)
     got = torch.autograd.grad(y, [z] + ws + bs, gy)
     ref = torch.autograd.grad(yr, [zd] + wd + bd, gy.double())
     for a, b in zip(got, ref):
-        assert rel_err(a, b) < 1e-5
+        assert rel_err(a, b) < 3e-5
 
 
 @pytest.mark.parametrize("dist,xform", [("laplace", "softmax"), ("normal", "exp_half"), ("normal", "exp_half_eps")])
