@@ -201,6 +201,13 @@ int  mmvae_convt_ts_fwd(const float* x, const void* wf, const float* bias, float
                         int Cout, int act, void* stream);
 int  mmvae_convt_ts_dgrad(const float* g, const void* wd, const float* x_mask, float* gx, int Nimg, int H, int W, int Cin,
                           int Cout, void* stream);
+/* weight AND bias gradient of the same layer in one pass over x and g (Cin <= 128): gw in the torch layout (Cin,Cout,4,4),
+ * gb [Cout] or NULL (replaces the autograd backward of ConvTranspose2d's weight / bias, encoders.py:113-124).  The pixel
+ * contraction runs on tcgen05 with g transposed into tensor memory by the converter warps and x as an MN-major bf16 operand;
+ * deterministic (partials in `workspace`, >= mmvae_convt_ts_wgrad_workspace_bytes(), added in a fixed order). */
+long mmvae_convt_ts_wgrad_workspace_bytes(int Nimg, int H, int W, int Cin, int Cout);
+int  mmvae_convt_ts_wgrad(const float* x, const float* g, float* gw, float* gb, float* workspace, long workspace_bytes,
+                          int Nimg, int H, int W, int Cin, int Cout, void* stream);
 
 /* MADE / MAF / IAF elementwise pieces (maf_model.py:62-74,91-104; iaf_model.py:60-78,94-100).  The masked-linear
  * contractions go through mmvae_gemm with the pre-masked weight (layers.py:24-25: F.linear(x, mask*W, b)). */

@@ -165,7 +165,7 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             for (int ck = 0; ck < ar.chunks; ++ck)
                 for (int st = 0; st < S::STAGES; ++st, ++sidx) {
                     const int s = sidx % ar.nstg, ph = (sidx / ar.nstg) & 1;
-                    mbar_wait(empty + s, ph ^ 1);
+                    mbar_wait_relaxed(empty + s, ph ^ 1);
                     if (ar.dbg & 16) { mbar_arrive_elect(full + s); continue; }
                     mbar_arrive_expect_tx_elect(full + s, ar.stage_tx);
                     if (MODE == TS_FWD) tma_load_4d_elect(a_ring + s * ar.stage_bytes, &tmap_a, full + s, ck * 32, -1, -1, n0);
@@ -190,7 +190,7 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                         slot = ck * 16 + blk0;
                     } else {
                         const int j = bid - back;
-                        if (j >= 0) mbar_wait(done + (j & 7), (j >> 3) & 1);
+                        if (j >= 0) mbar_wait_relaxed(done + (j & 7), (j >> 3) & 1);
                         bar = b_full + (bid & 7);
                         slot = (MODE == TS_FWD) ? blk0 : (2 * bid) % ar.nbs;
                     }
@@ -558,4 +558,441 @@ extern "C" int mmvae_convt_ts_dgrad(const float* g, const void* wd, const float*
     if (Cin == 32) return ts_launch<TS_DGRAD, 32>(ta, tb, nullptr, x_mask, gx, ar, rows, st);
     if (Cin == 64) return ts_launch<TS_DGRAD, 64>(ta, tb, nullptr, x_mask, gx, ar, rows, st);
     return ts_launch<TS_DGRAD, 128>(ta, tb, nullptr, x_mask, gx, ar, rows, st);
+}
+
+// ============================================================================================================== wgrad
+// gw[ci, co, ky, kx] = sum over coarse pixels (n,i,j) of x[n,i,j,ci] * g[n, 2i-1+ky, 2j-1+kx, co]   (the weight gradient of
+// encoders.py:113-124's ConvTranspose2d layers), and gb[co] = sum of g, in the same kernel (no extra pass over g).
+// As a GEMM the contraction runs over pixels, so both operands are "MN-major" in memory (channels contiguous):
+//   * A = g: M rows = (tap, co).  Per output-parity class of g one halo tile lands by a stride-2 TMA box (as in dgrad); a
+//     converter thread owns one TMEM lane = one (tap, co) and reads its 16 pixels of a k-block COLUMN-wise (16 conflict-free
+//     32-bit shared loads: a warp reads 32 consecutive channels of one pixel), splits them into bf16 (hi, mid) in registers,
+//     packs along k and writes 8 + 8 columns of its lane with tcgen05.st: the transposition costs no extra pass;
+//   * B = x: the landed [128 pixels x 32 ci] fp32 tile is split in place into [32 hi | 32 mid] bf16 per pixel row, which IS a
+//     valid MN-major SWIZZLE_128B operand (rows = k); the mid half is the sub-view 64 bytes into the row (tools/ts_probe.cu);
+//   * per (M tile, k-block, ci chunk) three N = 32 MMAs (hi*hi, hi*mid, mid*hi) into the same 32 accumulator columns.
+// An M tile = 128 / Cout taps; a CTA ("role") owns the M tiles whose accumulators fit 256 TMEM columns (all 16 taps when
+// Cin*Cout = 2048, one parity class when Cin = 128, Cout = 64) and a contiguous range of pixel tiles; every TW_CHAIN tiles the
+// accumulators are drained to a partial (the TMEM accumulate truncates: chains stay <= ~312 MMAs) and a second kernel adds the
+// partials in a fixed order (deterministic) straight into the torch weight layout.
+#define TW_THREADS 480
+#define TW_A_SLOTS 16                 // 16-column A slots (8 hi-pair + 8 mid-pair columns = one 16-pixel k-block of one M tile)
+#define TW_CHAIN 14                   // pixel tiles per accumulation chain (24 MMAs per tile and accumulator)
+
+struct TwArgs {
+    int M, H, W, tiles;
+    int gstage_bytes, gstage_tx, ngs, nxs;
+    int ctas_per_role, tiles_per_cta, parts_per_cta, dr;
+    float* ws;        // [partials][MTR*128][Cin]
+    float* wsb;       // [CTAs][2][128] bias partial sums
+    int dbg;
+};
+
+template <int COUT, int CIN> struct TwCfg {
+    static constexpr int TPM = 128 / COUT;                       // taps per M tile
+    static constexpr int MT = 16 / TPM;                          // M tiles of the layer
+    static constexpr int MTR = (MT < 256 / CIN) ? MT : 256 / CIN;   // M tiles per role
+    static constexpr int ROLES = MT / MTR;
+    static constexpr int COC = COUT / 32, CIC = CIN / 32;
+    static constexpr int MPC = 4 / TPM;                          // M tiles per parity class
+    static constexpr int CPR = MTR / MPC;                        // classes per role
+    static constexpr int ATILES = MTR * 8;                       // (M tile, k-block) pairs per pixel tile
+    static constexpr int NBATCH = ATILES / 4;
+    static constexpr int GST = CPR * COC;                        // g stages per pixel tile
+    static_assert(MTR >= MPC && MTR * CIN <= 256, "role does not fit");
+};
+
+// range of pixel tiles and number of partials of CTA `cr` of a role
+__host__ __device__ inline void tw_range(int cr, int tiles, int tiles_per_cta, int dr, int* t0, int* t1, int* nparts) {
+    *t0 = cr * tiles_per_cta;
+    *t1 = *t0 + tiles_per_cta < tiles ? *t0 + tiles_per_cta : tiles;
+    if (*t1 < *t0) *t1 = *t0;
+    *nparts = (*t1 - *t0 + dr - 1) / dr;
+}
+
+template <int COUT, int CIN>
+__global__ void __launch_bounds__(TW_THREADS, 1)
+convt_ts_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__ CUtensorMap tmap_x, const TwArgs ar) {
+    using C = TwCfg<COUT, CIN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* xring = smem + ar.ngs * ar.gstage_bytes;
+    // offtab[v][p]: byte offset (with the swizzle term of its row) of pixel p's row in a class tile, shifted by window v = ey*2+ex
+    uint32_t* offtab = (uint32_t*)(xring + ar.nxs * 16384);
+    uint64_t* bars = (uint64_t*)(offtab + 4 * 128);
+    uint64_t* g_full = bars;               // [8]
+    uint64_t* g_empty = bars + 8;          // [8] count 8 (converter warps)
+    uint64_t* x_full = bars + 16;          // [8]
+    uint64_t* x_ready = bars + 24;         // [8] count 8: split in place, visible to the tensor core
+    uint64_t* x_empty = bars + 32;         // [8] MMAs that read the stage completed
+    uint64_t* a_full = bars + 40;          // [4] count 8
+    uint64_t* done = bars + 44;            // [4]
+    uint64_t* tfull = bars + 48;
+    uint64_t* tempty = bars + 49;          // count 4
+    uint32_t* tmem_slot = (uint32_t*)(bars + 50);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int H = ar.H, W = ar.W, HW = H * W, IMGS = 128 / HW;
+    const int role = blockIdx.x % C::ROLES, cr = blockIdx.x / C::ROLES;
+    int t0, t1, nparts;
+    tw_range(cr, ar.tiles, ar.tiles_per_cta, ar.dr, &t0, &t1, &nparts);
+
+    for (int e = threadIdx.x; e < 4 * 128; e += TW_THREADS) {
+        const int v = e >> 7, p = e & 127, n_l = p / HW, rem = p - n_l * HW, i = rem / W, j = rem - i * W;
+        const int row = (n_l * (H + 1) + i + (v >> 1)) * (W + 1) + j + (v & 1);
+        offtab[e] = (uint32_t)(row * 128 + ((row & 7) << 4));
+    }
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < 8; ++s) {
+            mbar_init(g_full + s, 1); mbar_init(g_empty + s, 8); mbar_init(x_full + s, 1); mbar_init(x_ready + s, 8);
+            mbar_init(x_empty + s, 1);
+        }
+        for (int s = 0; s < 4; ++s) { mbar_init(a_full + s, 8); mbar_init(done + s, 1); }
+        mbar_init(tfull, 1); mbar_init(tempty, 4);
+        mbar_fence_init();
+        tma_prefetch_desc(&tmap_g);
+        tma_prefetch_desc(&tmap_x);
+    }
+    if (warp == 2) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== g producer: per pixel tile the role's parity classes, 32-channel chunk by chunk =====
+        const uint32_t g_ring = smem_u32(smem);
+        int gsi = 0;
+        for (int t = t0; t < t1; ++t)
+            for (int cl = 0; cl < C::CPR; ++cl) {
+                const int cls = role * C::CPR + cl;
+                for (int cch = 0; cch < C::COC; ++cch, ++gsi) {
+                    const int s = gsi % ar.ngs, ph = (gsi / ar.ngs) & 1;
+                    mbar_wait_relaxed(g_empty + s, ph ^ 1);
+                    mbar_arrive_expect_tx_elect(g_full + s, ar.gstage_tx);
+                    tma_load_4d_elect(g_ring + s * ar.gstage_bytes, &tmap_g, g_full + s, cch * 32, -(cls & 1), -(cls >> 1), t * IMGS);
+                }
+            }
+    } else if (warp == 1) {
+        // ===== x producer: [128 pixels x 32 ci] per chunk =====
+        const uint32_t x_ring = smem_u32(xring);
+        int xsi = 0;
+        for (int t = t0; t < t1; ++t)
+            for (int c = 0; c < C::CIC; ++c, ++xsi) {
+                const int s = xsi % ar.nxs, ph = (xsi / ar.nxs) & 1;
+                mbar_wait_relaxed(x_empty + s, ph ^ 1);
+                mbar_arrive_expect_tx_elect(x_full + s, 16384);
+                tma_load_2d_elect(x_ring + s * 16384, &tmap_x, x_full + s, c * 32, t * 128);
+            }
+    } else if (warp == 2) {
+        // ===== MMA issuer =====
+        constexpr uint32_t idesc = umma_idesc_bf16(128, 32, 0, 1);             // B MN-major
+        const uint64_t dx0 = umma_smem_desc(smem_u32(xring), 1024, 1024, 2);
+        int gb = 0, xsi = 0, ti = 0, part = 0;
+        for (int t = t0; t < t1; ++t, ++ti) {
+            const bool chain_start = (ti % ar.dr) == 0;
+            if (chain_start && part > 0) {                                    // the epilogue has drained the previous partial
+                mbar_wait(tempty, (part - 1) & 1);
+                tc_fence_after_sync();
+            }
+            uint64_t dxs[C::CIC];
+#pragma unroll
+            for (int c = 0; c < C::CIC; ++c) {
+                const int s = (xsi + c) % ar.nxs, ph = ((xsi + c) / ar.nxs) & 1;
+                mbar_wait(x_ready + s, ph);
+                dxs[c] = dx0 + (uint64_t)(s * (16384 >> 4));
+            }
+            tc_fence_after_sync();
+#pragma unroll 1
+            for (int b = 0; b < C::NBATCH; ++b, ++gb) {
+                mbar_wait(a_full + (gb & 3), (gb >> 2) & 1);
+                tc_fence_after_sync();
+#pragma unroll
+                for (int at = 0; at < 4; ++at) {
+                    const int ai = 4 * b + at, mt = ai >> 3, kb = ai & 7;
+                    const uint32_t a_col = tmem_base + 256 + ((4 * gb + at) & (TW_A_SLOTS - 1)) * 16;
+                    const uint32_t first = !(chain_start && kb == 0);
+#pragma unroll
+                    for (int c = 0; c < C::CIC; ++c) {
+                        const uint32_t d = tmem_base + mt * CIN + c * 32;
+                        const uint64_t db = dxs[c] + (uint64_t)(kb * (2048 >> 4));
+                        if (ar.dbg & 8) continue;
+                        umma_bf16_ts_elect(d, a_col, db, idesc, first);            // g_hi  * x_hi
+                        umma_bf16_ts_elect(d, a_col, db + 4, idesc, 1);            // g_hi  * x_mid
+                        umma_bf16_ts_elect(d, a_col + 8, db, idesc, 1);            // g_mid * x_hi
+                    }
+                }
+                umma_commit_elect(done + (gb & 3));
+            }
+#pragma unroll
+            for (int c = 0; c < C::CIC; ++c) umma_commit_elect(x_empty + ((xsi + c) % ar.nxs));
+            xsi += C::CIC;
+            if (((ti + 1) % ar.dr) == 0 || t + 1 == t1) { umma_commit_elect(tfull); ++part; }
+        }
+    } else if (warp < 11) {
+        // ===== converters =====
+        const int ctid = threadIdx.x - 96, wset = (warp - 3) >> 2, quarter = warp & 3;
+        const int L = quarter * 32 + lane;
+        const int tap_l = L / COUT, co = L % COUT, cch = co >> 5, w = co & 31;
+        const uint32_t g_ring = smem_u32(smem), x_ring = smem_u32(xring), tab = smem_u32(offtab);
+        const uint32_t xorc = (uint32_t)(w >> 2) << 4, addc = (uint32_t)(w & 3) << 2;
+        const uint32_t t_lane = tmem_base + ((uint32_t)(quarter * 32) << 16) + 256;
+        float bsum = 0.f;
+        int gs = 0, gph = 0;                 // g stage / phase of the current class's first chunk
+        int xs = 0, xph = 0;                 // x stage / phase of the current pixel tile's first chunk
+        int gb = 0;
+        for (int t = t0; t < t1; ++t) {
+            // x: split in place, then hand to the tensor core
+            {
+                int s = xs, ph = xph;
+#pragma unroll 1
+                for (int c = 0; c < C::CIC; ++c) {
+                    mbar_wait(x_full + s, ph);
+                    if (!(ar.dbg & 4))
+                        for (int r = ctid; r < 128; r += TS_NCONV) ts_split_row(x_ring + s * 16384 + r * 128, r & 7);
+                    if (++s == ar.nxs) { s = 0; ph ^= 1; }
+                }
+                fence_proxy_async_smem();
+                __syncwarp();
+                s = xs;
+                for (int c = 0; c < C::CIC; ++c) {
+                    if (lane == 0) mbar_arrive(x_ready + s);
+                    if (++s == ar.nxs) { s = 0; xph ^= 1; }
+                }
+                xs = s;
+            }
+            // A tiles: per class, per M tile of the class, two batches of four k-blocks; two k-blocks per warp set and batch
+#pragma unroll 1
+            for (int cl = 0; cl < C::CPR; ++cl) {
+                const int cls = role * C::CPR + cl;
+                int s = gs + cch, ph = gph;
+                if (s >= ar.ngs) { s -= ar.ngs; ph ^= 1; }
+                mbar_wait(g_full + s, ph);
+                const uint32_t gbase = g_ring + s * ar.gstage_bytes + addc;
+#pragma unroll 1
+                for (int mi = 0; mi < C::MPC; ++mi) {
+                    const int tap = (cls * C::MPC + mi) * C::TPM + tap_l;               // = cls*4 + ey*2 + ex
+                    const int v = tap & 3;
+                    const bool bias_tap = v == cls;                                       // (ey,ex) == (py,px)
+#pragma unroll 1
+                    for (int kb4 = 0; kb4 < 2; ++kb4, ++gb) {
+                        if (gb >= 4) mbar_wait(done + (gb & 3), ((gb >> 2) - 1) & 1);
+                        tc_fence_after_sync();
+#pragma unroll
+                        for (int a2 = 0; a2 < 2; ++a2) {
+                            const int at = 2 * a2 + wset, kb = kb4 * 4 + at;
+                            const uint32_t tb = tab + (uint32_t)(v * 128 + kb * 16) * 4;
+                            float f[16];
+                            if (!(ar.dbg & 2)) {
+#pragma unroll
+                                for (int k = 0; k < 16; ++k) {
+                                    uint32_t off;
+                                    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(off) : "r"(tb + k * 4));
+                                    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(f[k]) : "r"(gbase + (off ^ xorc)));
+                                }
+                            } else {
+#pragma unroll
+                                for (int k = 0; k < 16; ++k) f[k] = 0.f;
+                            }
+                            if (bias_tap) {
+#pragma unroll
+                                for (int k = 0; k < 16; ++k) bsum += f[k];
+                            }
+                            uint32_t hm[16];
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) {
+                                asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hm[j]) : "f"(f[2 * j + 1]), "f"(f[2 * j]));
+                                const float r0 = f[2 * j] - __uint_as_float(hm[j] << 16), r1 = f[2 * j + 1] - __uint_as_float(hm[j] & 0xffff0000u);
+                                asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hm[8 + j]) : "f"(r1), "f"(r0));
+                            }
+                            const uint32_t ta = t_lane + ((4 * gb + at) & (TW_A_SLOTS - 1)) * 16;
+                            tmem_st_32x8(ta, hm);
+                            tmem_st_32x8(ta + 8, hm + 8);
+                        }
+                        tmem_st_wait();
+                        tc_fence_before_sync();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(a_full + (gb & 3));
+                    }
+                }
+                // the class's g stages are free once its last k-block has been copied
+                __syncwarp();
+                s = gs;
+                for (int q = 0; q < C::COC; ++q) {
+                    if (lane == 0) mbar_arrive(g_empty + s);
+                    if (++s == ar.ngs) { s = 0; gph ^= 1; }
+                }
+                gs = s;
+            }
+        }
+        ar.wsb[((long)blockIdx.x * 2 + wset) * 128 + L] = bsum;
+    } else {
+        // ===== epilogue: drain the accumulators of a finished chain into its partial =====
+        const int lane_base = (warp & 3) * 32;
+        for (int part = 0; part < nparts; ++part) {
+            mbar_wait_relaxed(tfull, part & 1);
+            tc_fence_after_sync();
+            float* wp = ar.ws + ((long)blockIdx.x * ar.parts_per_cta + part) * (C::MTR * 128 * CIN);
+#pragma unroll 1
+            for (int mt = 0; mt < C::MTR; ++mt) {
+                float* prow = wp + (long)(mt * 128 + lane_base + lane) * CIN;
+#pragma unroll
+                for (int cc = 0; cc < CIN; cc += 32) {
+                    float v[32];
+                    tmem_ld_32x32(tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)(mt * CIN + cc), v);
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4)
+                        *reinterpret_cast<float4*>(prow + cc + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                }
+            }
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty);
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem_base, 512);
+}
+
+// partials -> gw in the torch layout [Cin][Cout][4][4] and gb[Cout], in a fixed summation order.  One block per row
+// m = tap*Cout + co of the lowered gradient (256 / Cin threads share a column and split the partials), one more for the bias.
+template <int COUT, int CIN>
+__global__ void __launch_bounds__(256) convt_ts_wgrad_reduce_kernel(const TwArgs ar, float* __restrict__ gw, float* __restrict__ gb,
+                                                                    int grid_main) {
+    using C = TwCfg<COUT, CIN>;
+    __shared__ float red[256];
+    const int tid = threadIdx.x;
+    if (blockIdx.x == 16 * COUT) {
+        if (!gb) return;
+        const int l = tid & 127, h = tid >> 7;
+        float s0 = 0.f, s1 = 0.f;
+        int b = h;
+        for (; b + 2 < grid_main * 2; b += 4) { s0 += ar.wsb[(long)b * 128 + l]; s1 += ar.wsb[(long)(b + 2) * 128 + l]; }
+        for (; b < grid_main * 2; b += 2) s0 += ar.wsb[(long)b * 128 + l];
+        red[tid] = s0 + s1;
+        __syncthreads();
+        if (tid < COUT) {
+            float t = 0.f;
+            for (int j = tid; j < 256; j += COUT) t += red[j];
+            gb[tid] = t;
+        }
+        return;
+    }
+    constexpr int NPG = 256 / CIN;
+    const int m = blockIdx.x, ci = tid % CIN, pg = tid / CIN;
+    const int tap = m / COUT, co = m % COUT;
+    const int mt = tap / C::TPM, role = mt / C::MTR, m_local = (mt % C::MTR) * 128 + (tap % C::TPM) * COUT + co;
+    const int total = ar.ctas_per_role * ar.parts_per_cta;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    int u = 0;
+    for (int q = pg; q < total; q += NPG, u = (u + 1) & 3) {
+        const int cr = q / ar.parts_per_cta, p = q - cr * ar.parts_per_cta;
+        int t0, t1, np;
+        tw_range(cr, ar.tiles, ar.tiles_per_cta, ar.dr, &t0, &t1, &np);
+        if (p < np) acc[u] += ar.ws[((long)(cr * C::ROLES + role) * ar.parts_per_cta + p) * (C::MTR * 128 * CIN) + (long)m_local * CIN + ci];
+    }
+    red[tid] = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+    __syncthreads();
+    if (pg == 0) {
+        float s = 0.f;
+#pragma unroll
+        for (int g = 0; g < NPG; ++g) s += red[g * CIN + ci];
+        const int cls = tap >> 2, ey = (tap >> 1) & 1, ex = tap & 1, py = cls >> 1, px = cls & 1;
+        const int ky = py ? 2 * ey : 1 + 2 * ey, kx = px ? 2 * ex : 1 + 2 * ex;
+        gw[(((long)ci * COUT + co) * 4 + ky) * 4 + kx] = s;
+    }
+}
+
+template <int COUT, int CIN> static void tw_plan(TwArgs* ar, int* grid, int* smem, int rows_g) {
+    using C = TwCfg<COUT, CIN>;
+    *grid = (MMVAE_NUM_SMS / C::ROLES) * C::ROLES;
+    ar->ctas_per_role = *grid / C::ROLES;
+    if (ar->ctas_per_role > ar->tiles) { ar->ctas_per_role = ar->tiles; *grid = ar->ctas_per_role * C::ROLES; }
+    ar->tiles_per_cta = (ar->tiles + ar->ctas_per_role - 1) / ar->ctas_per_role;
+    ar->parts_per_cta = (ar->tiles_per_cta + TW_CHAIN - 1) / TW_CHAIN;
+    ar->dr = (ar->tiles_per_cta + ar->parts_per_cta - 1) / ar->parts_per_cta;
+    ar->gstage_tx = rows_g * 128;
+    ar->gstage_bytes = (ar->gstage_tx + 1023) & ~1023;
+    // shared memory: x ring of up to two pixel tiles, g ring from what is left (at least one pixel tile of each)
+    const long fixed = 1024 /*align*/ + 2048 /*offtab*/ + 512 /*barriers*/;
+    ar->nxs = 2 * C::CIC > 8 ? 8 : 2 * C::CIC;
+    for (;;) {
+        ar->ngs = (int)((TS_SMEM_MAX - fixed - (long)ar->nxs * 16384) / ar->gstage_bytes);
+        if (ar->ngs >= C::GST + 1 || ar->nxs <= C::CIC) break;
+        --ar->nxs;
+    }
+    if (ar->ngs > 8) ar->ngs = 8;
+    *smem = (int)(fixed + (long)ar->nxs * 16384 + (long)ar->ngs * ar->gstage_bytes);
+}
+
+template <int COUT, int CIN> static long tw_ws_floats(int Nimg, int H, int W, long* bias_off) {
+    using C = TwCfg<COUT, CIN>;
+    TwArgs ar{};
+    ar.tiles = (Nimg * H * W + 127) / 128;
+    int grid, smem;
+    tw_plan<COUT, CIN>(&ar, &grid, &smem, (128 / (H * W)) * (H + 1) * (W + 1));
+    const long nws = (long)grid * ar.parts_per_cta * C::MTR * 128 * CIN;
+    if (bias_off) *bias_off = nws;
+    return nws + (long)grid * 2 * 128;
+}
+
+template <int COUT, int CIN>
+static int tw_launch(const float* x, const float* g, float* gw, float* gb, float* ws, long ws_bytes, int Nimg, int H, int W,
+                     cudaStream_t st) {
+    using C = TwCfg<COUT, CIN>;
+    static bool attr_done = false;
+    auto kern = convt_ts_wgrad_kernel<COUT, CIN>;
+    const int IMGS = 128 / (H * W);
+    TwArgs ar{};
+    ar.M = Nimg * H * W; ar.H = H; ar.W = W; ar.tiles = (ar.M + 127) / 128;
+    ar.dbg = mmvae_tc_dbg_bits();
+    int grid, smem;
+    const int rows_g = IMGS * (H + 1) * (W + 1);
+    tw_plan<COUT, CIN>(&ar, &grid, &smem, rows_g);
+    if (ar.ngs < C::GST || ar.nxs < C::CIC) return mmvae_set_error(1, "convt_ts_wgrad: shared memory plan does not fit");
+    long bias_off;
+    const long need = tw_ws_floats<COUT, CIN>(Nimg, H, W, &bias_off) * (long)sizeof(float);
+    if (!ws || ws_bytes < need) return mmvae_set_error(1, "convt_ts_wgrad: workspace %ld bytes, need %ld", ws_bytes, need);
+    ar.ws = ws; ar.wsb = ws + bias_off;
+    CUtensorMap tg, tx;
+    cuuint64_t dims[4] = {(cuuint64_t)COUT, (cuuint64_t)(2 * W), (cuuint64_t)(2 * H), (cuuint64_t)Nimg};
+    cuuint64_t strides[3] = {(cuuint64_t)COUT * 4, (cuuint64_t)2 * W * COUT * 4, (cuuint64_t)4 * H * W * COUT * 4};
+    cuuint32_t box[4] = {32u, (cuuint32_t)(2 * (W + 1)), (cuuint32_t)(2 * (H + 1)), (cuuint32_t)IMGS}, estr[4] = {1u, 2u, 2u, 1u};
+    int rc = mmvae_tc_encode(&tg, 0, 4, g, dims, strides, box, estr);
+    if (rc) return mmvae_set_error(1, "convt_ts_wgrad: tensor map (g) failed with %d", rc);
+    cuuint64_t xd[2] = {(cuuint64_t)CIN, (cuuint64_t)ar.M};
+    cuuint64_t xs[1] = {(cuuint64_t)CIN * 4};
+    cuuint32_t xb[2] = {32u, 128u}, xe[2] = {1u, 1u};
+    rc = mmvae_tc_encode(&tx, 0, 2, x, xd, xs, xb, xe);
+    if (rc) return mmvae_set_error(1, "convt_ts_wgrad: tensor map (x) failed with %d", rc);
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM_MAX);
+        if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "convt_ts_wgrad: smem attribute: %s", cudaGetErrorString(e));
+        attr_done = true;
+    }
+    kern<<<grid, TW_THREADS, smem, st>>>(tg, tx, ar);
+    MMVAE_LAUNCH_CHECK("convt_ts_wgrad");
+    convt_ts_wgrad_reduce_kernel<COUT, CIN><<<16 * COUT + 1, 256, 0, st>>>(ar, gw, gb, grid);
+    MMVAE_LAUNCH_CHECK("convt_ts_wgrad_reduce");
+    return 0;
+}
+
+#define TW_DISPATCH(FN, ...)                                                             \
+    (Cout == 32 ? (Cin == 32 ? FN<32, 32>(__VA_ARGS__) : Cin == 64 ? FN<32, 64>(__VA_ARGS__) : FN<32, 128>(__VA_ARGS__)) \
+                : (Cin == 32 ? FN<64, 32>(__VA_ARGS__) : Cin == 64 ? FN<64, 64>(__VA_ARGS__) : FN<64, 128>(__VA_ARGS__)))
+
+extern "C" long mmvae_convt_ts_wgrad_workspace_bytes(int Nimg, int H, int W, int Cin, int Cout) {
+    if (!mmvae_convt_ts_supported(H, W, Cin, Cout) || Cin > 128) return 0;
+    return TW_DISPATCH(tw_ws_floats, Nimg, H, W, nullptr) * (long)sizeof(float);
+}
+
+// wgrad.  x: [Nimg,H,W,Cin]; g: [Nimg,2H,2W,Cout] (gradient w.r.t. the pre-activation), NHWC fp32; gw: torch layout
+// (Cin,Cout,4,4); gb: [Cout] or NULL.  workspace >= mmvae_convt_ts_wgrad_workspace_bytes().
+extern "C" int mmvae_convt_ts_wgrad(const float* x, const float* g, float* gw, float* gb, float* workspace, long workspace_bytes,
+                                    int Nimg, int H, int W, int Cin, int Cout, void* stream) {
+    MMVAE_REQUIRE(x && g && gw && Nimg > 0, "convt_ts_wgrad: bad arguments");
+    MMVAE_REQUIRE(mmvae_convt_ts_supported(H, W, Cin, Cout) && Cin <= 128, "convt_ts_wgrad: unsupported shape");
+    cudaStream_t st = (cudaStream_t)stream;
+    return TW_DISPATCH(tw_launch, x, g, gw, gb, workspace, workspace_bytes, Nimg, H, W, st);
 }

@@ -418,9 +418,21 @@ class ConvT2dAct(torch.autograd.Function):
                 gx = gx2d.view(N, H, W, Cin).permute(0, 3, 1, 2)
             need_w, need_b = ctx.needs_input_grad[1], has_bias and ctx.needs_input_grad[2]
             dw, db, sunk = _sinks(ctx.leaves, need_w, need_b)
+            lib = _lib.load()
+            ts_w = path == "ts" and need_w and Cin <= 128
+            if ts_w:
+                with _wgrad_side(sunk, g, x2d):
+                    nb = lib.mmvae_convt_ts_wgrad_workspace_bytes(N, H, W, Cin, Cout)
+                    ws = torch.empty(nb // 4, device=g.device, dtype=torch.float32)
+                    gw = torch.empty(wshape, device=g.device, dtype=torch.float32) if dw is None else dw
+                    gb = (torch.empty(Cout, device=g.device, dtype=torch.float32) if db is None else db) if need_b else None
+                    _call("mmvae_convt_ts_wgrad", _p(x2d), _p(g), _p(gw), _p(gb), _p(ws), nb, N, H, W, Cin, Cout, _stream(),
+                          work=("flop", 2.0 * N * H * W * 16 * Cin * Cout))
+                    gw = None if dw is not None else gw
+                    gb = None if db is not None else gb
+                return gx, gw, gb, None, None, None, None, None, None
             with _wgrad_side(sunk, g, x2d):
                 if need_w:
-                    lib = _lib.load()
                     nb = lib.mmvae_convt_tc_wgrad_workspace_bytes(N, H, W, Cin, Cout)
                     ws = torch.empty(nb // 4, device=g.device, dtype=torch.float32) if nb else None
                     gwp = torch.empty((Cin, 16 * Cout), device=g.device, dtype=torch.float32)

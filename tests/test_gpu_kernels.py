@@ -114,8 +114,18 @@ def test_convT2d_autograd(ops, cin, cout, H, s, p, act, nchw_out, N):
     assert rel_err(y, yr) < (1e-5 if ts else 2e-6)
     gy = _rand(*yr.shape, seed=4)
     gx, gw, gb = torch.autograd.grad(y, (x, w, b), gy)
-    rx, rw, rb = torch.autograd.grad(yr, (xd, wd, bd), gy.double())
-    assert rel_err(gx, rx) < (1.5e-5 if ts else 5e-6) and rel_err(gw, rw) < (1.5e-5 if ts else 5e-6) and rel_err(gb, rb) < 5e-6
+    if act == "relu":
+        # branch-consistent reference: the ReLU mask is the kernel's own (a unit whose pre-activation is within the forward
+        # error of zero may land on either side of the kink; each such flip moves the gradient by an O(1) term, 1e-3 of the
+        # norm at N = 77, which says nothing about the arithmetic being compared)
+        pre = F.conv_transpose2d(xd, wd, bd, stride=s, padding=p)
+        rx, rw, rb = torch.autograd.grad(pre, (xd, wd, bd), gy.double() * (y.detach() > 0))
+    else:
+        rx, rw, rb = torch.autograd.grad(yr, (xd, wd, bd), gy.double())
+    tol = 1.5e-5 if ts else 5e-6
+    assert rel_err(gx, rx) < tol, "gx"
+    assert rel_err(gw, rw) < tol, "gw"
+    assert rel_err(gb, rb) < 5e-6, "gb"
 
 
 def test_convT_last_layer_tensor_core_forward_is_deterministic_and_matches_simt(ops):

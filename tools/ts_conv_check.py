@@ -52,7 +52,7 @@ def case(N, cin, cout, H, check=True, relu_in=True):
             rx = rx * (xd > 0)
         for ts in (True, False):
             y, gx, gw, gb = out[ts]
-            print(f"  N={N} {cin}->{cout} H={H} {'TS ' if ts else 'old'}: y {rel(y, yr):.2e}  gx {rel(gx, rx):.2e}  gw {rel(gw, rw):.2e}  "
+            print(f"  N={N} {cin}->{cout} H={H} {'TS ' if ts else 'old'}: y {rel(y, yr):.2e}  gx {rel(gx, rx):.2e}  gw {rel(gw, rw):.2e}  gb {rel(gb, rb):.2e}  "
                   f"max|y-yr| {(y.double() - yr).abs().max().item():.2e}", flush=True)
     for ts in (True, False):
         ops.ALLOW_TS = ts

@@ -36,7 +36,6 @@ __device__ __forceinline__ void tmem_st_x16(uint32_t taddr, const uint32_t* r) {
                  ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
                  "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]) : "memory");
 }
-__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 // ---- 1. numerics.  K = 32 (bf16: 2 MMAs of K=16, 16 TMEM columns; tf32: 4 MMAs of K=8, 32 columns), N = 64.
 template <bool BF16>
@@ -188,7 +187,89 @@ template <bool BF16, int mode, int R> static void timing(long long* d, const cha
     }
 }
 
+
+// ---- 3. B operand MN-major (rows = k, 64 bf16 of n contiguous = 128 bytes, SWIZZLE_128B), A in TMEM.  K = 16 per MMA, two
+// MMAs (32 k rows).  n_off = first n column (0 or 32: a descriptor that starts 64 bytes into the swizzled row), N = 32 or 64.
+__global__ void __launch_bounds__(128, 1) numerics_mn(const float* A, const float* B, float* D, int N, int n_off, int sbo, int lbo) {
+    constexpr int K = 32;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    __shared__ uint64_t bar;
+    __shared__ uint32_t slot;
+    const int warp = threadIdx.x >> 5, t = threadIdx.x;
+    if (t == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
+    if (warp == 0) { tmem_alloc(&slot, 128); tmem_relinquish(); }
+    for (int i = t; i < K * 64; i += 128) {                      // B[k][n], n < 64
+        const int k = i / 64, n = i % 64, byte = n * 2, c = byte >> 4;
+        *(__nv_bfloat16*)(smem + k * 128 + ((c ^ (k & 7)) << 4) + (byte & 15)) = __float2bfloat16(B[i]);
+    }
+    fence_proxy_async_smem();
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tm = slot;
+    {
+        uint32_t r[16];
+        for (int j = 0; j < 16; ++j) {
+            const __nv_bfloat16 lo = __float2bfloat16(A[t * K + 2 * j]), hi = __float2bfloat16(A[t * K + 2 * j + 1]);
+            r[j] = (uint32_t)__bfloat16_as_ushort(lo) | ((uint32_t)__bfloat16_as_ushort(hi) << 16);
+        }
+        tmem_st_x16(tm + ((uint32_t)(warp * 32) << 16) + 64, r);
+        tmem_st_wait();
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    if (warp == 0) {
+        const uint32_t idesc = idesc_bf16(128, N) | (1u << 16);                  // B MN-major
+        for (int kk = 0; kk < 2; ++kk) {
+            const uint64_t db = umma_smem_desc(smem_u32(smem) + kk * 2048 + n_off * 2, lbo, sbo, 2);
+            umma_ts_elect<true>(tm, tm + 64 + kk * 8, db, idesc, kk != 0);
+        }
+        umma_commit_elect(&bar);
+    }
+    mbar_wait(&bar, 0);
+    tc_fence_after_sync();
+    float v[32];
+    for (int c = 0; c < N; c += 32) {
+        tmem_ld_32x32(tm + ((uint32_t)(warp * 32) << 16) + c, v);
+        for (int j = 0; j < 32; ++j) D[t * 64 + c + j] = v[j];
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tm, 128);
+}
+static int check_mn(int N, int n_off, int sbo, int lbo) {
+    const int K = 32;
+    float *hA = (float*)malloc(128 * K * 4), *hB = (float*)malloc(64 * K * 4), *hD = (float*)malloc(128 * 64 * 4);
+    srand(2);
+    for (int i = 0; i < 128 * K; ++i) hA[i] = (float)((rand() % 17) - 8) / 8.f;
+    for (int i = 0; i < 64 * K; ++i) hB[i] = (float)((rand() % 17) - 8) / 4.f;
+    float *dA, *dB, *dD;
+    cudaMalloc(&dA, 128 * K * 4); cudaMalloc(&dB, 64 * K * 4); cudaMalloc(&dD, 128 * 64 * 4);
+    cudaMemcpy(dA, hA, 128 * K * 4, cudaMemcpyHostToDevice);
+    cudaMemcpy(dB, hB, 64 * K * 4, cudaMemcpyHostToDevice);
+    cudaMemset(dD, 0, 128 * 64 * 4);
+    cudaFuncSetAttribute(numerics_mn, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * 1024);
+    numerics_mn<<<1, 128, 32 * 1024>>>(dA, dB, dD, N, n_off, sbo, lbo);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { printf("MN-major numerics: %s\n", cudaGetErrorString(e)); return 1; }
+    cudaMemcpy(hD, dD, 128 * 64 * 4, cudaMemcpyDeviceToHost);
+    double maxerr = 0;
+    for (int m = 0; m < 128; ++m)
+        for (int n = 0; n < N; ++n) {
+            double s = 0;
+            for (int k = 0; k < K; ++k) s += (double)hA[m * K + k] * hB[k * 64 + n_off + n];
+            maxerr = fmax(maxerr, fabs(s - hD[m * 64 + n]));
+        }
+    printf("B MN-major SW128 bf16, N=%d starting at column %d, SBO=%d LBO=%d: max |err| = %g  %s\n", N, n_off, sbo, lbo, maxerr,
+           maxerr == 0 ? "EXACT" : "MISMATCH");
+    return maxerr != 0;
+}
+
 int main() {
+    for (int sbo : {1024, 2048}) for (int lbo : {1024, 2048, 4096}) { check_mn(64, 0, sbo, lbo); check_mn(32, 0, sbo, lbo); check_mn(32, 32, sbo, lbo); }
+    if (getenv("TS_PROBE_MN_ONLY")) return 0;
     int bad = check<true>("bf16") + check<false>("tf32");
     long long* d;
     cudaMalloc(&d, 8);

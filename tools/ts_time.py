@@ -31,6 +31,10 @@ def run(N, cin, cout, H, bits_list):
     ne = lib.mmvae_convt_ts_packed_elems(cin, cout)
     wf = torch.empty(ne, device="cuda", dtype=torch.int16)
     wd = torch.empty(ne, device="cuda", dtype=torch.int16)
+    nb = lib.mmvae_convt_ts_wgrad_workspace_bytes(N, H, H, cin, cout)
+    ws = torch.empty(nb // 4, device="cuda")
+    gw = torch.empty_like(w)
+    gb = torch.empty_like(b)
     _lib.check(lib.mmvae_convt_ts_pack_weights(P(w), P(wf), P(wd), cin, cout, None))
     tp = timeit(lambda: lib.mmvae_convt_ts_pack_weights(P(w), P(wf), P(wd), cin, cout, None))
     print(f"{cin}->{cout} H={H} N={N}: pack {tp:.1f} us")
@@ -38,12 +42,13 @@ def run(N, cin, cout, H, bits_list):
         lib.mmvae_gemm_tc_set_mode(bits << 8)
         tf = timeit(lambda: _lib.check(lib.mmvae_convt_ts_fwd(P(x), P(wf), P(b), P(y), N, H, H, cin, cout, 1, None)))
         td = timeit(lambda: _lib.check(lib.mmvae_convt_ts_dgrad(P(g), P(wd), P(x), P(gx), N, H, H, cin, cout, None)))
+        tw = timeit(lambda: _lib.check(lib.mmvae_convt_ts_wgrad(P(x), P(g), P(gw), P(gb), P(ws), nb, N, H, H, cin, cout, None)))
         lib.mmvae_gemm_tc_set_mode(0)
-        print(f"  dbg {bits:2d}: fwd {tf:7.1f} us   dgrad {td:7.1f} us", flush=True)
+        print(f"  dbg {bits:2d}: fwd {tf:7.1f} us   dgrad {td:7.1f} us   wgrad+bias {tw:7.1f} us", flush=True)
 
 
 if __name__ == "__main__":
     N = int(sys.argv[1]) if len(sys.argv) > 1 else 7680
-    bl = [0, 1, 2, 4, 8, 16, 2 | 4, 2 | 4 | 16, 1 | 2 | 4 | 16, 1 | 8, 1 | 2 | 4 | 8 | 16]
+    bl = [0, 2, 4, 8, 2 | 4 | 8] if len(sys.argv) < 3 else [0, 1, 2, 4, 8, 16, 2 | 4, 2 | 4 | 16, 1 | 2 | 4 | 16, 1 | 8, 31]
     run(N, 64, 32, 8, bl)
     run(N, 128, 64, 4, bl)
