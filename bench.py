@@ -240,6 +240,7 @@ def profile_step(trainer, x, peak, detail=False):
         trainer.step(x)
     torch.cuda.synchronize()
     ops.PROFILE = []
+    ops.GEMM_LOG = [] if detail else None
     n0 = ops.N_CALLS
     trainer.step(x)
     torch.cuda.synchronize()
@@ -251,6 +252,9 @@ def profile_step(trainer, x, peak, detail=False):
     if detail:
         for name, work, e0, e1 in rec:
             sys.stderr.write(f"{name:32s} {e0.elapsed_time(e1) * 1e3:9.1f} us  {work}\n")
+        for tag, e0, e1 in ops.GEMM_LOG or []:
+            sys.stderr.write(f"gemm {tag}  {e0.elapsed_time(e1) * 1e3:9.1f} us\n")
+        ops.GEMM_LOG = None
     for name, work, e0, e1 in rec:
         a = agg.setdefault(name, {"ms": 0.0, "n": 0, "flop": 0.0, "byte": 0.0})
         a["ms"] += e0.elapsed_time(e1)

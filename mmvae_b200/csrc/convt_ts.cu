@@ -410,13 +410,31 @@ static bool ts_geometry(int H, int W) {
     return H >= 2 && W >= 2 && HW <= 128 && 128 % HW == 0 && W + 2 <= 256 && H + 2 <= 256;
 }
 
-// 1 when both directions of the layer run on the kernels of this file
+// shared-memory plan of convt_ts_kernel: weight slots (resident or streaming) + at least two halo tiles
+static bool ts_plan(int mode, int NB, int chunks, int rows, int* nbs, int* resident, int* nstg, int* stage_bytes) {
+    const int block = NB * 128;
+    *stage_bytes = (rows * 128 + 1023) & ~1023;
+    *resident = 16L * chunks * block <= 131072;
+    *nbs = *resident ? 16 * chunks : (mode == TS_FWD ? 16 : 8);
+    const long fixed = (long)*nbs * block + 1024 /*barriers*/ + 1024 /*alignment*/;
+    long n = (TS_SMEM_MAX - fixed) / *stage_bytes;
+    *nstg = (int)(n > 8 ? 8 : n);
+    return *nstg >= 2;
+}
+static bool tw_fits(int H, int W, int Cin, int Cout);
+
+// 1 when forward, data gradient and weight gradient of the layer all run on the kernels of this file
 extern "C" int mmvae_convt_ts_supported(int H, int W, int Cin, int Cout) {
     if (!mmvae_has_tcgen05() || !ts_geometry(H, W)) return 0;
     if (Cin % 32 || Cout % 32) return 0;
     const bool fwd_ok = (Cout == 32 || Cout == 64) && Cin <= 256;       // accumulators: 4 classes x Cout <= 256 columns
     const bool dgrad_ok = (Cin == 32 || Cin == 64 || Cin == 128) && Cout <= 256;
-    return fwd_ok && dgrad_ok;
+    if (!fwd_ok || !dgrad_ok) return 0;
+    const int IMGS = 128 / (H * W);
+    int a, b, c, d;
+    if (!ts_plan(TS_FWD, Cout, Cin / 32, IMGS * (H + 2) * (W + 2), &a, &b, &c, &d)) return 0;
+    if (!ts_plan(TS_DGRAD, Cin, Cout / 32, IMGS * (H + 1) * (W + 1), &a, &b, &c, &d)) return 0;
+    return tw_fits(H, W, Cin, Cout) ? 1 : 0;
 }
 
 // Weights of one layer, w [Cin][Cout][4][4] (torch layout), as the two bf16 operand matrices (row = 64-element K groups of
@@ -486,15 +504,9 @@ static int ts_launch(const CUtensorMap& ta, const CUtensorMap& tb, const float* 
     constexpr int BLOCK_BYTES = NB * 128;
     ar.stage_tx = rows * 128;
     ar.dbg = mmvae_tc_dbg_bits();
-    ar.stage_bytes = (ar.stage_tx + 1023) & ~1023;
-    const long res_bytes = 16L * ar.chunks * BLOCK_BYTES;
-    ar.resident = res_bytes <= 131072;
-    ar.nbs = ar.resident ? 16 * ar.chunks : (MODE == TS_FWD ? 16 : 8);   // streaming: one chunk of class blocks / 4 batches
-    const long fixed = (long)ar.nbs * BLOCK_BYTES + 1024 /*barriers*/ + 1024 /*alignment*/;
-    ar.nstg = (int)((TS_SMEM_MAX - fixed) / ar.stage_bytes);
-    if (ar.nstg > 8) ar.nstg = 8;
-    if (ar.nstg < 2) return mmvae_set_error(1, "convt_ts: shared memory plan does not fit (stage %d bytes)", ar.stage_bytes);
-    const int smem = (int)(fixed + (long)ar.nstg * ar.stage_bytes);
+    if (!ts_plan(MODE, NB, ar.chunks, rows, &ar.nbs, &ar.resident, &ar.nstg, &ar.stage_bytes))
+        return mmvae_set_error(1, "convt_ts: shared memory plan does not fit (stage %d bytes)", ar.stage_bytes);
+    const int smem = (int)((long)ar.nbs * BLOCK_BYTES + 2048 + (long)ar.nstg * ar.stage_bytes);
     if (!attr_done) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM_MAX);
         if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "convt_ts: smem attribute: %s", cudaGetErrorString(e));
@@ -740,7 +752,7 @@ convt_ts_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_c
         float bsum = 0.f;
         int gs = 0, gph = 0;                 // g stage / phase of the current class's first chunk
         int xs = 0, xph = 0;                 // x stage / phase of the current pixel tile's first chunk
-        int gb = 0;
+        int gb = 0, pending = -1;
         for (int t = t0; t < t1; ++t) {
             // x: split in place, then hand to the tensor core
             {
@@ -776,43 +788,53 @@ convt_ts_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_c
                     const bool bias_tap = v == cls;                                       // (ey,ex) == (py,px)
 #pragma unroll 1
                     for (int kb4 = 0; kb4 < 2; ++kb4, ++gb) {
+                        // loads of this batch are issued before the previous batch's tcgen05.st are waited for and handed
+                        // over: the TMEM-store latency and the shared-memory round trips overlap
+                        float f[2][16];
+#pragma unroll
+                        for (int a2 = 0; a2 < 2; ++a2) {
+                            const int kb = kb4 * 4 + 2 * a2 + wset;
+                            const uint32_t tb = tab + (uint32_t)(v * 128 + kb * 16) * 4;
+                            if (!(ar.dbg & 2)) {
+                                uint32_t off[16];
+#pragma unroll
+                                for (int k = 0; k < 16; ++k) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(off[k]) : "r"(tb + k * 4));
+#pragma unroll
+                                for (int k = 0; k < 16; ++k)
+                                    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(f[a2][k]) : "r"(gbase + (off[k] ^ xorc)));
+                            } else {
+#pragma unroll
+                                for (int k = 0; k < 16; ++k) f[a2][k] = 0.f;
+                            }
+                        }
+                        if (pending >= 0) {
+                            tmem_st_wait();
+                            tc_fence_before_sync();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(a_full + (pending & 3));
+                        }
                         if (gb >= 4) mbar_wait(done + (gb & 3), ((gb >> 2) - 1) & 1);
                         tc_fence_after_sync();
 #pragma unroll
                         for (int a2 = 0; a2 < 2; ++a2) {
-                            const int at = 2 * a2 + wset, kb = kb4 * 4 + at;
-                            const uint32_t tb = tab + (uint32_t)(v * 128 + kb * 16) * 4;
-                            float f[16];
-                            if (!(ar.dbg & 2)) {
-#pragma unroll
-                                for (int k = 0; k < 16; ++k) {
-                                    uint32_t off;
-                                    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(off) : "r"(tb + k * 4));
-                                    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(f[k]) : "r"(gbase + (off ^ xorc)));
-                                }
-                            } else {
-#pragma unroll
-                                for (int k = 0; k < 16; ++k) f[k] = 0.f;
-                            }
+                            const int at = 2 * a2 + wset;
                             if (bias_tap) {
 #pragma unroll
-                                for (int k = 0; k < 16; ++k) bsum += f[k];
+                                for (int k = 0; k < 16; ++k) bsum += f[a2][k];
                             }
                             uint32_t hm[16];
 #pragma unroll
                             for (int j = 0; j < 8; ++j) {
-                                asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hm[j]) : "f"(f[2 * j + 1]), "f"(f[2 * j]));
-                                const float r0 = f[2 * j] - __uint_as_float(hm[j] << 16), r1 = f[2 * j + 1] - __uint_as_float(hm[j] & 0xffff0000u);
+                                asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hm[j]) : "f"(f[a2][2 * j + 1]), "f"(f[a2][2 * j]));
+                                const float r0 = f[a2][2 * j] - __uint_as_float(hm[j] << 16);
+                                const float r1 = f[a2][2 * j + 1] - __uint_as_float(hm[j] & 0xffff0000u);
                                 asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hm[8 + j]) : "f"(r1), "f"(r0));
                             }
                             const uint32_t ta = t_lane + ((4 * gb + at) & (TW_A_SLOTS - 1)) * 16;
                             tmem_st_32x8(ta, hm);
                             tmem_st_32x8(ta + 8, hm + 8);
                         }
-                        tmem_st_wait();
-                        tc_fence_before_sync();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(a_full + (gb & 3));
+                        pending = gb;
                     }
                 }
                 // the class's g stages are free once its last k-block has been copied
@@ -824,6 +846,12 @@ convt_ts_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_c
                 }
                 gs = s;
             }
+        }
+        if (pending >= 0) {
+            tmem_st_wait();
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(a_full + (pending & 3));
         }
         ar.wsb[((long)blockIdx.x * 2 + wset) * 128 + L] = bsum;
     } else {
@@ -848,6 +876,11 @@ convt_ts_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_c
             tc_fence_before_sync();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty);
+        }
+        // partials this CTA's (shorter) range does not produce are zero, so that the reduction needs no range logic
+        for (int part = nparts; part < ar.parts_per_cta; ++part) {
+            float4* wp = reinterpret_cast<float4*>(ar.ws + ((long)blockIdx.x * ar.parts_per_cta + part) * (C::MTR * 128 * CIN));
+            for (int i = threadIdx.x - 352; i < C::MTR * 128 * CIN / 4; i += 128) wp[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
     }
     tc_fence_before_sync();
@@ -883,15 +916,20 @@ __global__ void __launch_bounds__(256) convt_ts_wgrad_reduce_kernel(const TwArgs
     const int m = blockIdx.x, ci = tid % CIN, pg = tid / CIN;
     const int tap = m / COUT, co = m % COUT;
     const int mt = tap / C::TPM, role = mt / C::MTR, m_local = (mt % C::MTR) * 128 + (tap % C::TPM) * COUT + co;
-    const int total = ar.ctas_per_role * ar.parts_per_cta;
-    float acc[4] = {0.f, 0.f, 0.f, 0.f};
-    int u = 0;
-    for (int q = pg; q < total; q += NPG, u = (u + 1) & 3) {
+    const int total = ar.ctas_per_role * ar.parts_per_cta;              // partial q of the role belongs to CTA q / parts_per_cta
+    const long pstride = (long)C::MTR * 128 * CIN;
+    const float* base = ar.ws + (long)m_local * CIN + ci;
+    auto paddr = [&](int q) {
         const int cr = q / ar.parts_per_cta, p = q - cr * ar.parts_per_cta;
-        int t0, t1, np;
-        tw_range(cr, ar.tiles, ar.tiles_per_cta, ar.dr, &t0, &t1, &np);
-        if (p < np) acc[u] += ar.ws[((long)(cr * C::ROLES + role) * ar.parts_per_cta + p) * (C::MTR * 128 * CIN) + (long)m_local * CIN + ci];
+        return base + ((long)(cr * C::ROLES + role) * ar.parts_per_cta + p) * pstride;
+    };
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    int q = pg;
+    for (; q + 3 * NPG < total; q += 4 * NPG) {                          // four independent loads in flight
+        const float a0 = __ldg(paddr(q)), a1 = __ldg(paddr(q + NPG)), a2 = __ldg(paddr(q + 2 * NPG)), a3 = __ldg(paddr(q + 3 * NPG));
+        acc[0] += a0; acc[1] += a1; acc[2] += a2; acc[3] += a3;
     }
+    for (; q < total; q += NPG) acc[0] += __ldg(paddr(q));
     red[tid] = (acc[0] + acc[1]) + (acc[2] + acc[3]);
     __syncthreads();
     if (pg == 0) {
@@ -976,6 +1014,20 @@ static int tw_launch(const float* x, const float* g, float* gw, float* gb, float
     convt_ts_wgrad_reduce_kernel<COUT, CIN><<<16 * COUT + 1, 256, 0, st>>>(ar, gw, gb, grid);
     MMVAE_LAUNCH_CHECK("convt_ts_wgrad_reduce");
     return 0;
+}
+
+template <int COUT, int CIN> static int tw_fits_t(int H, int W) {
+    using C = TwCfg<COUT, CIN>;
+    TwArgs ar{};
+    ar.tiles = 1;
+    int grid, smem;
+    tw_plan<COUT, CIN>(&ar, &grid, &smem, (128 / (H * W)) * (H + 1) * (W + 1));
+    return ar.ngs >= C::GST && ar.nxs >= C::CIC;
+}
+static bool tw_fits(int H, int W, int Cin, int Cout) {
+    if (Cin > 128 || (Cout != 32 && Cout != 64)) return false;
+    return (Cout == 32 ? (Cin == 32 ? tw_fits_t<32, 32>(H, W) : Cin == 64 ? tw_fits_t<32, 64>(H, W) : tw_fits_t<32, 128>(H, W))
+                       : (Cin == 32 ? tw_fits_t<64, 32>(H, W) : Cin == 64 ? tw_fits_t<64, 64>(H, W) : tw_fits_t<64, 128>(H, W))) != 0;
 }
 
 #define TW_DISPATCH(FN, ...)                                                             \

@@ -107,6 +107,16 @@ def _sinks(ctx_leaves, need_w, need_b):
     return dw, db, (dw is not None or not need_w) and (db is not None or not need_b) and (need_w or need_b)
 
 
+RELU_TAP = None          # test hook: set to a dict to record, per weight (data_ptr), the sign pattern y > 0 of every fused-ReLU
+                         # output in call order -- lets the fp64 oracle be evaluated on the SAME side of each kink (tests only)
+
+
+def _tap_relu(w, y, act):
+    if RELU_TAP is not None and act == "relu":
+        RELU_TAP.setdefault(w.data_ptr(), []).append((y.detach() > 0))
+
+
+GEMM_LOG = None          # set to a list (with PROFILE) to record ("M N K a_kmajor b_kmajor act", start, end) per GEMM
 PROFILE = None           # set to a list to record (name, work, start_event, end_event) per C-ABI call (bench.py)
 
 
@@ -134,6 +144,9 @@ def gemm(a, b, bias, M, N, K, a_kmajor, b_kmajor, act=None, out=None):
     ws = torch.empty(ws_bytes // 4, device=a.device, dtype=torch.float32) if ws_bytes else None
     _call("mmvae_gemm", _p(a), _p(b), _p(bias), _p(out), M, N, K, int(a_kmajor), int(b_kmajor), ACT[act], _p(ws),
           ws_bytes, int(ALLOW_TC), _stream(), work=("flop", 2.0 * M * N * K))
+    if GEMM_LOG is not None and PROFILE:
+        GEMM_LOG.append((f"M={M} N={N} K={K} a_k={int(a_kmajor)} b_k={int(b_kmajor)} bias={bias is not None} act={act}",
+                         PROFILE[-1][2], PROFILE[-1][3]))
     return out
 
 
@@ -227,6 +240,7 @@ class LinearAct(torch.autograd.Function):
         ctx.save_for_backward(x, w, y if ACT[act] != C["MMVAE_ACT_NONE"] else None)
         ctx.has_bias = b is not None
         ctx.leaves = (w, b)
+        _tap_relu(w, y, act)
         return y
 
     @staticmethod
@@ -297,6 +311,7 @@ class Conv2dAct(torch.autograd.Function):
         ctx.cfg = (N, Cin, H, W, Cout, k, stride, pad, Ho, Wo, act, tuple(w.shape), b is not None,
                    x.is_contiguous() and Cin > 1)
         ctx.leaves = (w, b)
+        _tap_relu(w, y2d.view(N, Ho, Wo, Cout).permute(0, 3, 1, 2), act)
         return y2d.view(N, Ho, Wo, Cout).permute(0, 3, 1, 2)
 
     @staticmethod
@@ -330,6 +345,12 @@ class ConvT2dAct(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, w, b, stride, pad, act, nchw_out, preact_grad, mask_input_grad=False):
+        y = ConvT2dAct._forward(ctx, x, w, b, stride, pad, act, nchw_out, preact_grad, mask_input_grad)
+        _tap_relu(w, y, act)
+        return y
+
+    @staticmethod
+    def _forward(ctx, x, w, b, stride, pad, act, nchw_out, preact_grad, mask_input_grad):
         x = _dev(x, "x")
         ctx.leaves = (w, b)
         w = _c(w, "weight")

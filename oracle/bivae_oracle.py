@@ -96,17 +96,44 @@ def spec_jnf_mnist_svhn(latent_dim=20, flow="maf", no_nf=False, dcca=True, dim_d
 # ----------------------------------------------------------------------------------------------------------
 # networks (L0)
 # ----------------------------------------------------------------------------------------------------------
+# Test hook for branch-consistent comparisons.  The gradient of a ReLU network is ill-conditioned at the kinks: a unit whose
+# pre-activation is within the forward error of zero lands on either side, and each such flip moves the gradient by an O(1)
+# term (at C2 size ~1e-6 of 10^8 units flip between ANY two fp32 evaluations, ~1e-3 of a gradient's norm).  With RELU_MASKS =
+# {weight key: bool tensor [rows, ...]} the oracle takes the sign pattern of the layer fed by that weight from the
+# implementation under test (rows consumed in call order), so what is compared is the arithmetic, not the coin flips.
+RELU_MASKS = None
+_relu_cursor = {}
+
+
+def relu_masks(masks):
+    """Install (or clear with None) the sign patterns; resets the per-key row cursors."""
+    global RELU_MASKS
+    RELU_MASKS = masks
+    _relu_cursor.clear()
+
+
+def _relu(x, key):
+    if RELU_MASKS is None or key not in RELU_MASKS:
+        return F.relu(x)
+    m = RELU_MASKS[key]
+    c = _relu_cursor.get(key, 0)
+    n = x.shape[0]
+    assert c + n <= m.shape[0] and tuple(m.shape[1:]) == tuple(x.shape[1:]), (key, c, n, tuple(m.shape), tuple(x.shape))
+    _relu_cursor[key] = c + n
+    return x * m[c:c + n].to(x.dtype)
+
+
 def enc_mlp(sd, p, x):
     """pythae 0.0.8 Encoder_VAE_MLP: flatten → Linear(D,512)+ReLU → {embedding, log_var}: Linear(512,L)."""
     h = x.reshape(x.shape[0], -1)
-    h = F.relu(F.linear(h, sd[p + "layers.0.0.weight"], sd[p + "layers.0.0.bias"]))
+    h = _relu(F.linear(h, sd[p + "layers.0.0.weight"], sd[p + "layers.0.0.bias"]), p + "layers.0.0.weight")
     return (F.linear(h, sd[p + "embedding.weight"], sd[p + "embedding.bias"]),
             F.linear(h, sd[p + "log_var.weight"], sd[p + "log_var.bias"]))
 
 
 def dec_mlp(sd, p, z, shape):
     """pythae 0.0.8 Decoder_AE_MLP: Linear(L,512)+ReLU → Linear(512,D)+Sigmoid → reshape (·,C,H,W)."""
-    h = F.relu(F.linear(z, sd[p + "layers.0.0.weight"], sd[p + "layers.0.0.bias"]))
+    h = _relu(F.linear(z, sd[p + "layers.0.0.weight"], sd[p + "layers.0.0.bias"]), p + "layers.0.0.weight")
     h = torch.sigmoid(F.linear(h, sd[p + "layers.1.0.weight"], sd[p + "layers.1.0.bias"]))
     return h.reshape((z.shape[0],) + tuple(shape))
 
@@ -115,7 +142,7 @@ def enc_svhn(sd, p, x, L):
     """models/nn/encoders.py:72-105."""
     e = x
     for i in (0, 2, 4):
-        e = F.relu(F.conv2d(e, sd[p + f"enc.{i}.weight"], sd[p + f"enc.{i}.bias"], stride=2, padding=1))
+        e = _relu(F.conv2d(e, sd[p + f"enc.{i}.weight"], sd[p + f"enc.{i}.bias"], stride=2, padding=1), p + f"enc.{i}.weight")
     mu = F.conv2d(e, sd[p + "c1.weight"], sd[p + "c1.bias"], stride=2, padding=0).reshape(-1, L)
     lv = F.conv2d(e, sd[p + "c2.weight"], sd[p + "c2.bias"], stride=2, padding=0).reshape(-1, L)
     return mu, lv
@@ -124,9 +151,9 @@ def enc_svhn(sd, p, x, L):
 def dec_svhn(sd, p, z):
     """models/nn/encoders.py:108-136 (leading dims flattened by the caller)."""
     h = z.reshape(-1, z.shape[-1], 1, 1)
-    h = F.relu(F.conv_transpose2d(h, sd[p + "dec.0.weight"], sd[p + "dec.0.bias"], stride=1, padding=0))
-    h = F.relu(F.conv_transpose2d(h, sd[p + "dec.2.weight"], sd[p + "dec.2.bias"], stride=2, padding=1))
-    h = F.relu(F.conv_transpose2d(h, sd[p + "dec.4.weight"], sd[p + "dec.4.bias"], stride=2, padding=1))
+    h = _relu(F.conv_transpose2d(h, sd[p + "dec.0.weight"], sd[p + "dec.0.bias"], stride=1, padding=0), p + "dec.0.weight")
+    h = _relu(F.conv_transpose2d(h, sd[p + "dec.2.weight"], sd[p + "dec.2.bias"], stride=2, padding=1), p + "dec.2.weight")
+    h = _relu(F.conv_transpose2d(h, sd[p + "dec.4.weight"], sd[p + "dec.4.bias"], stride=2, padding=1), p + "dec.4.weight")
     h = torch.sigmoid(F.conv_transpose2d(h, sd[p + "dec.6.weight"], sd[p + "dec.6.bias"], stride=2, padding=1))
     return h
 
@@ -142,7 +169,7 @@ def enc_twostep(sd, p, x, first_kind, dcca_latent, dim_dcca):
             h, _ = enc_svhn(sd, fp + "encoder.", x, dcca_latent)
         h = torch.matmul(h - sd[fp + "m"], sd[fp + "w"])[:, :dim_dcca]
     for i in (0, 2, 4):
-        h = F.relu(F.linear(h, sd[p + f"sec_encoder.{i}.weight"], sd[p + f"sec_encoder.{i}.bias"]))
+        h = _relu(F.linear(h, sd[p + f"sec_encoder.{i}.weight"], sd[p + f"sec_encoder.{i}.bias"]), p + f"sec_encoder.{i}.weight")
     return (F.linear(h, sd[p + "embedding.weight"], sd[p + "embedding.bias"]),
             F.linear(h, sd[p + "log_var.weight"], sd[p + "log_var.bias"]))
 
@@ -178,7 +205,7 @@ def joint_encode(spec: Spec, sd, x):
             hs.append(enc_svhn(sd, p, x[m], spec.joint_head_latent)[0])
     e = torch.cat(hs, dim=1)
     for j in range(spec.num_hidden_layers):
-        e = F.relu(F.linear(e, sd[f"joint_encoder.enc.{j}.0.weight"], sd[f"joint_encoder.enc.{j}.0.bias"]))
+        e = _relu(F.linear(e, sd[f"joint_encoder.enc.{j}.0.weight"], sd[f"joint_encoder.enc.{j}.0.bias"]), f"joint_encoder.enc.{j}.0.weight")
     mu = F.linear(e, sd["joint_encoder.fc21.weight"], sd["joint_encoder.fc21.bias"])
     std = torch.exp(0.5 * F.linear(e, sd["joint_encoder.fc22.weight"], sd["joint_encoder.fc22.bias"])) + ETA
     return mu, std

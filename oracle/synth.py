@@ -156,10 +156,11 @@ def make_noise(kind, shape, rs):
     return _t(rs.standard_normal(shape))
 
 
-def grad_digest(g: torch.Tensor):
-    """Compact, order-sensitive fingerprint of a gradient tensor for golden fixtures."""
+def grad_digest(g: torch.Tensor, keep64=False):
+    """Compact, order-sensitive fingerprint of a gradient tensor for golden fixtures (keep64: sampled values stay fp64,
+    for the fixtures produced by running the reference in double precision)."""
     f = g.detach().reshape(-1).double()
     n = f.numel()
     idx = torch.linspace(0, n - 1, steps=min(n, 48)).long()
-    return {"norm": f.norm().item(), "sum": f.sum().item(), "idx": idx, "vals": f[idx].float().clone(),
-            "numel": n}
+    return {"norm": f.norm().item(), "sum": f.sum().item(), "idx": idx,
+            "vals": f[idx].clone() if keep64 else f[idx].float().clone(), "numel": n}

@@ -26,6 +26,24 @@ def test_objectives_match_reference(name):
         check_digests({k: v.grad for k, v in lsd.items()}, res["grads"], GRAD_RTOL, f"{name}:{oname}")
 
 
+@pytest.mark.parametrize("name", OBJ_CASES)
+def test_fp64_oracle_matches_fp64_reference(name):
+    """The pin proper: the fixtures also hold the UNMODIFIED reference run in double precision
+    (model.double(), same noise tape).  In fp64 neither side has rounding noise to hide behind: loss to 5e-9 (measured 1e-10,
+    1.2e-9 with the Bernoulli likelihood, whose torch kernel differs in the last bits), every gradient tensor (norm and 48
+    sampled entries) to 1e-7.  A 3e-4 formula error in an encoder-gradient path, which the
+    5e-4 fp32 comparison above could not see, fails here."""
+    g, spec, sd = load_golden(name)
+    assert set(g["results64"]) == set(g["results"])
+    for oname, res in g["results64"].items():
+        lsd = leaf_sd(sd, dtype=torch.float64)
+        loss = O.OBJECTIVES[oname](spec, lsd, [t.double() for t in g["x"]], g["K"], [n.double() for n in g["noise"]])
+        loss.backward()
+        ref = res["loss"].item()
+        assert abs(loss.item() - ref) <= 5e-9 * abs(ref), (name, oname, loss.item(), ref)
+        check_digests({k: v.grad for k, v in lsd.items()}, res["grads"], 1e-7, f"{name}:{oname}:fp64")
+
+
 @pytest.mark.parametrize("name", ["eval_ms_laplace", "eval_ms_tail", "eval_msf"])
 def test_evaluators_match_reference(name):
     g, spec, sd = load_golden(name)
