@@ -128,6 +128,8 @@ long mmvae_gemm_workspace_bytes(int M, int N, int K, int a_kmajor, int b_kmajor)
 /* debug / speed probe of the tensor-core path: 0 = 3xTF32 split (fp32 accuracy, default), 1 = single TF32 pass.
  * Returns the previous mode. */
 int mmvae_gemm_tc_set_mode(int mode);
+/* number of tcgen05 GEMM launches (gemm_tc_kernel) this process has made: lets a test assert which kernel a shape ran on */
+long mmvae_gemm_tc_launch_count(void);
 /* column sums: out[n] = sum_m A[m,n]  (bias gradients); workspace >= mmvae_colsum_workspace_bytes(M,N) */
 int  mmvae_colsum(const float* A, float* out, float* workspace, int M, int N, void* stream);
 long mmvae_colsum_workspace_bytes(int M, int N);

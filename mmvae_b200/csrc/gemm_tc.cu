@@ -27,6 +27,7 @@
 #define TC_MAX_CHAIN 32                // k-blocks accumulated in one TMEM chain when split-K is available
 
 static int g_tc_dbg = 0;
+static long g_tc_launches = 0;         // launches of gemm_tc_kernel (tests assert that a shape really ran on tcgen05)
 static int g_tc_mode = 0;              // 0 = 3xTF32 (fp32 accuracy), 1 = single TF32 pass (debug / speed probe)
 
 template <int BN> struct TcCfg {
@@ -417,6 +418,7 @@ static int tc_init() {
 }
 
 extern "C" int mmvae_has_tcgen05(void) { return tc_init(); }
+extern "C" long mmvae_gemm_tc_launch_count(void) { return g_tc_launches; }
 extern "C" int mmvae_gemm_tc_set_mode(int mode) {
     const int old = g_tc_mode;
     g_tc_mode = (mode & 0xff) == 1 ? 1 : 0;
@@ -506,8 +508,10 @@ static bool tc_shape_ok(int M, int N, int K, int a_k, int b_k) {
 
 long mmvae_gemm_tc_workspace_bytes(int M, int N, int K, int a_k, int b_k) {
     if (!tc_shape_ok(M, N, K, a_k, b_k)) return 0;
-    const TcPlan p = tc_plan(M, N, K, true);
-    return p.S > 1 ? (long)p.S * M * N * (long)sizeof(float) : 0;
+    // the launch plans with can_swap = (no bias, no activation), which this query does not know: cover both plans
+    const TcPlan p = tc_plan(M, N, K, true), q = tc_plan(M, N, K, false);
+    const int S = p.S > q.S ? p.S : q.S;
+    return S > 1 ? (long)S * M * N * (long)sizeof(float) : 0;
 }
 
 void mmvae_splitk_reduce(const float* ws, const float* bias, float* C, long MN, int N, int S, int act, cudaStream_t st);
@@ -529,6 +533,7 @@ static int tc_launch(const CUtensorMap& ta, const CUtensorMap& tb, const float* 
     kern<<<grid, TC_THREADS, TcCfg<BN>::SMEM, st>>>(ta, tb, bias, C, ws, M, N, K, act, p.kb_per, p.S, transposed,
                                                     (g_tc_mode == 1 ? 1 : 3) | (g_tc_dbg << 8), cv, mask);
     MMVAE_LAUNCH_CHECK("gemm_tc");
+    ++g_tc_launches;
     return 0;
 }
 

@@ -145,6 +145,7 @@ def run_training(args, out_dir, synthetic=None, max_steps=None, log=print):
     best, bad, steps = float("inf"), 0, 0
     for epoch in range(1, args.epochs + 1):
         model.train()
+        trainer.set_schedule(epoch, args.warmup, args.beta_prior)       # main.py:155: objective(model, data, K, epoch, warmup, beta_prior)
         b_loss = torch.zeros((), device=device)
         n_seen, t0 = 0, time.perf_counter()
         for x in train_loader:
@@ -162,6 +163,8 @@ def run_training(args, out_dir, synthetic=None, max_steps=None, log=print):
                 break
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
+        if hasattr(model, "step"):
+            model.step(epoch)                                # main.py:171: the model's own per-epoch schedule (beta_kl decay, ...)
         tot = torch.stack([b_loss, torch.tensor(float(n_seen), device=device)])
         P.allreduce_sum_(tot)
         train_loss = (tot[0] / tot[1]).item()

@@ -61,6 +61,10 @@ def _sink(p):
         return None
     key = p.data_ptr()
     if key in GRAD_SINK:
+        # second use of the parameter in this backward pass: autograd adds this gradient to p.grad on the current stream,
+        # while the first one may still be being WRITTEN by a kernel on the weight-gradient stream -- order them
+        if WGRAD_STREAM is not None and WGRAD_USED:
+            torch.cuda.current_stream().wait_stream(WGRAD_STREAM)
         return None
     GRAD_SINK.add(key)
     return p.grad
@@ -108,12 +112,15 @@ def _sinks(ctx_leaves, need_w, need_b):
 
 
 RELU_TAP = None          # test hook: set to a dict to record, per weight (data_ptr), the sign pattern y > 0 of every fused-ReLU
-                         # output in call order -- lets the fp64 oracle be evaluated on the SAME side of each kink (tests only)
+                         # output in call order -- lets a double-precision checker be evaluated on the SAME side of each kink (tests only)
 
 
-def _tap_relu(w, y, act):
+def _tap_relu(w, b, y, act):
     if RELU_TAP is not None and act == "relu":
-        RELU_TAP.setdefault(w.data_ptr(), []).append((y.detach() > 0))
+        m = y.detach() > 0
+        RELU_TAP.setdefault(w.data_ptr(), []).append(m)
+        if b is not None:                       # masked (MADE) weights are temporaries: the bias identifies the layer
+            RELU_TAP.setdefault(b.data_ptr(), []).append(m)
 
 
 GEMM_LOG = None          # set to a list (with PROFILE) to record ("M N K a_kmajor b_kmajor act", start, end) per GEMM
@@ -240,7 +247,7 @@ class LinearAct(torch.autograd.Function):
         ctx.save_for_backward(x, w, y if ACT[act] != C["MMVAE_ACT_NONE"] else None)
         ctx.has_bias = b is not None
         ctx.leaves = (w, b)
-        _tap_relu(w, y, act)
+        _tap_relu(w, b, y, act)
         return y
 
     @staticmethod
@@ -311,7 +318,7 @@ class Conv2dAct(torch.autograd.Function):
         ctx.cfg = (N, Cin, H, W, Cout, k, stride, pad, Ho, Wo, act, tuple(w.shape), b is not None,
                    x.is_contiguous() and Cin > 1)
         ctx.leaves = (w, b)
-        _tap_relu(w, y2d.view(N, Ho, Wo, Cout).permute(0, 3, 1, 2), act)
+        _tap_relu(w, b, y2d.view(N, Ho, Wo, Cout).permute(0, 3, 1, 2), act)
         return y2d.view(N, Ho, Wo, Cout).permute(0, 3, 1, 2)
 
     @staticmethod
@@ -346,7 +353,7 @@ class ConvT2dAct(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, b, stride, pad, act, nchw_out, preact_grad, mask_input_grad=False):
         y = ConvT2dAct._forward(ctx, x, w, b, stride, pad, act, nchw_out, preact_grad, mask_input_grad)
-        _tap_relu(w, y, act)
+        _tap_relu(w, b, y, act)
         return y
 
     @staticmethod

@@ -46,6 +46,9 @@ class Trainer:
         self.pg = process_group
         self.distributed = dist.is_initialized() and dist.get_world_size() > 1 if distributed is None else distributed
         self._graph = None
+        # objective(model, x, K, epoch, warmup, beta_prior) as main.py:155 calls it; set_schedule() updates these per epoch
+        self.epoch, self.warmup, self.beta_prior = 1, 0, 1
+        self._sched_key = None
         self.grad_sink = grad_sink
         self._wgrad_stream = torch.cuda.Stream(device=dev) if (wgrad_stream and grad_sink) else None
         if branch_streams and hasattr(model, "_run_branches"):
@@ -55,9 +58,23 @@ class Trainer:
         if self.distributed:
             dist.broadcast(self.fp.flat, src, group=self.pg)
 
+    def set_schedule(self, epoch, warmup=0, beta_prior=1):
+        """The positional arguments the reference passes to every objective (main.py:155: epoch, args.warmup,
+        args.beta_prior).  m_jmvae_nf turns them into its two training phases, the frozen sub-modules of the second one and
+        the beta schedules, all of which a captured graph bakes in (requires_grad pattern, Python scalars): when anything the
+        objective can see changes, the graph is dropped and the caller re-captures on its next full batch."""
+        self.epoch, self.warmup, self.beta_prior = epoch, warmup, beta_prior
+        key = (epoch >= warmup, epoch if getattr(self.model, "linear_warmup", False) else None, beta_prior,
+               getattr(self.model, "beta_kl", None))
+        if key != self._sched_key:
+            if self._sched_key is not None:
+                self._graph = None
+                self._graph_upd = None
+            self._sched_key = key
+
     def _fwd_bwd(self, x, noise=None):
         self.fp.grad.zero_()
-        loss, _ = self.objective(self.model, x, self.K, 1, 0, 1, noise=noise)
+        loss, _ = self.objective(self.model, x, self.K, self.epoch, self.warmup, self.beta_prior, noise=noise)
         ops.GRAD_SINK = set() if self.grad_sink else None    # weight/bias gradients land in the flat buffer directly
         ops.WGRAD_STREAM = self._wgrad_stream if self.grad_sink else None   # ... computed off the data-gradient chain
         try:
@@ -76,9 +93,33 @@ class Trainer:
         if self.distributed:                                 # ONE collective per step: the flat gradient bucket
             dist.all_reduce(self.fp.grad, op=dist.ReduceOp.SUM, group=self.pg)
 
+    def _active_segments(self):
+        """Contiguous ranges of the flat buffer whose parameters currently require a gradient.  torch.optim.Adam skips a
+        parameter whose .grad is None (the frozen joint encoder / decoders of m_jmvae_nf's second phase, objectives.py:180-183):
+        its moments and the parameter stay put; updating it with a zero gradient would keep moving it along its momentum."""
+        flags = tuple(p.requires_grad for p in self.fp.params)
+        if getattr(self, "_seg_flags", None) != flags:
+            segs, o, start = [], 0, None
+            for p, f in zip(self.fp.params, flags):
+                if f and start is None:
+                    start = o
+                if not f and start is not None:
+                    segs.append((start, o))
+                    start = None
+                o += p.numel()
+            if start is not None:
+                segs.append((start, o))
+            self._seg_flags, self._segs = flags, segs
+        return self._segs
+
     def _update(self):
-        ops.adam_amsgrad_(self.fp.flat, self.fp.grad, self.m, self.v, self.vmax, self.step_dev, lr=self.lr,
-                          amsgrad=self.amsgrad)
+        segs = self._active_segments()
+        for i, (a, b) in enumerate(segs):
+            step = self.step_dev
+            if i > 0:                                        # the kernel increments the step counter it is given: once per step
+                step = self.step_dev - 1.0
+            ops.adam_amsgrad_(self.fp.flat[a:b], self.fp.grad[a:b], self.m[a:b], self.v[a:b], self.vmax[a:b], step, lr=self.lr,
+                              amsgrad=self.amsgrad)
 
     def _step_impl(self, x, noise=None):
         loss = self._fwd_bwd(x, noise)
@@ -96,12 +137,17 @@ class Trainer:
     # around it are replayed.
     def capture(self, x_example, warmup=3):
         self._static_x = [t.clone() for t in x_example]
+        # the warm-up iterations run real steps (allocator and lazy initialisations must happen before capture): parameters,
+        # moments and the step counter are put back afterwards, so capturing is invisible to the optimisation trajectory
+        saved = [t.clone() for t in (self.fp.flat, self.m, self.v, self.vmax, self.step_dev)]
         s = torch.cuda.Stream()
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
             for _ in range(warmup):
                 self._step_impl(self._static_x)
         torch.cuda.current_stream().wait_stream(s)
+        for dst, src in zip((self.fp.flat, self.m, self.v, self.vmax, self.step_dev), saved):
+            dst.copy_(src)
         self._graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self._graph):
             self._static_loss = self._fwd_bwd(self._static_x)

@@ -231,14 +231,14 @@ def made(sd, p, x, n_hidden):
         w = sd[p + f"net.{2 * i}.mask"].to(h.dtype) * sd[p + f"net.{2 * i}.weight"]
         h = F.linear(h, w, sd[p + f"net.{2 * i}.bias"])
         if i < n_hidden:
-            h = F.relu(h)
+            h = _relu(h, p + f"net.{2 * i}.bias")
     L = x.shape[1]
     return h[:, :L], h[:, L:]
 
 
 def maf_forward(spec: Spec, sd, p, x):
     """maf/maf_model.py:49-76 (data → prior): one MADE pass per block."""
-    ladj = torch.zeros(x.shape[0], dtype=x.dtype)
+    ladj = x.new_zeros(x.shape[0])
     for b in range(spec.n_made_blocks):
         mu, lv = made(sd, p + f"net.{b}.", x, spec.n_hidden_in_made)
         x = (x - mu) * (-lv).exp()
@@ -249,7 +249,7 @@ def maf_forward(spec: Spec, sd, p, x):
 
 def maf_inverse(spec: Spec, sd, p, y):
     """maf/maf_model.py:78-110 (prior → data): L sequential MADE passes per block, blocks reversed."""
-    ladj = torch.zeros(y.shape[0], dtype=y.dtype)
+    ladj = y.new_zeros(y.shape[0])
     L = y.shape[1]
     for b in reversed(range(spec.n_made_blocks)):
         y = y.flip(dims=(1,))
@@ -267,7 +267,7 @@ def maf_inverse(spec: Spec, sd, p, y):
 
 def iaf_forward(spec: Spec, sd, p, x):
     """iaf/iaf_model.py:48-80: the sequential direction."""
-    ladj = torch.zeros(x.shape[0], dtype=x.dtype)
+    ladj = x.new_zeros(x.shape[0])
     L = x.shape[1]
     for b in range(spec.n_made_blocks):
         cols = []
@@ -283,7 +283,7 @@ def iaf_forward(spec: Spec, sd, p, x):
 
 def iaf_inverse(spec: Spec, sd, p, y):
     """iaf/iaf_model.py:82-107: one pass per block, blocks reversed."""
-    ladj = torch.zeros(y.shape[0], dtype=y.dtype)
+    ladj = y.new_zeros(y.shape[0])
     for b in reversed(range(spec.n_made_blocks)):
         y = y.flip(dims=(1,))
         m, s = made(sd, p + f"net.{b}.", y, spec.n_hidden_in_made)
@@ -299,7 +299,7 @@ def flow_forward(spec, sd, m, z):
         return maf_forward(spec, sd, p, z)
     if spec.vae == "my_VAE_IAF":
         return iaf_forward(spec, sd, p, z)
-    return z, torch.zeros(z.shape[0], dtype=z.dtype)
+    return z, z.new_zeros(z.shape[0])
 
 
 def flow_inverse(spec, sd, m, z0):
@@ -308,7 +308,7 @@ def flow_inverse(spec, sd, m, z0):
         return maf_inverse(spec, sd, p, z0)
     if spec.vae == "my_VAE_IAF":
         return iaf_inverse(spec, sd, p, z0)
-    return z0, torch.zeros(z0.shape[0], dtype=z0.dtype)
+    return z0, z0.new_zeros(z0.shape[0])
 
 
 # ----------------------------------------------------------------------------------------------------------
@@ -363,7 +363,7 @@ def posterior_std(spec: Spec, log_var):
 def pz_params(spec: Spec, sd, like):
     if "_pz_params.0" in sd:
         return sd["_pz_params.0"].to(like.dtype), sd["_pz_params.1"].to(like.dtype)
-    return torch.zeros(1, spec.latent_dim, dtype=like.dtype), torch.ones(1, spec.latent_dim, dtype=like.dtype)
+    return like.new_zeros(1, spec.latent_dim), like.new_ones(1, spec.latent_dim)
 
 
 # ----------------------------------------------------------------------------------------------------------
@@ -461,7 +461,7 @@ def m_elbo(spec, sd, x, K, noise):
         for d in range(M):
             lpx_z = _lpx(spec, recon[d][d], x[d], d)
             if d == r:
-                lwt = torch.zeros((), dtype=lpx_z.dtype)
+                lwt = lpx_z.new_zeros(())
             else:
                 zs = zss[d].detach()
                 lwt = (lat_log_prob(spec.dist, zs, mus[r].unsqueeze(0), stds[r].unsqueeze(0))

@@ -29,8 +29,47 @@ def leaf_sd(sd, dtype=torch.float32, frozen_prefixes=()):
     return out
 
 
-def check_digests(grads, digests, rtol, what=""):
-    """grads: name → tensor (or None).  digests: from synth.grad_digest on the reference's .grad."""
+class relu_tap:
+    """with relu_tap(model) as tap: <forward + backward on the CUDA path>;  tap.masks = {parameter name: sign pattern of the
+    ReLU layer fed by that weight / bias, rows in call order} (ops.RELU_TAP), for oracle.relu_masks()."""
+
+    def __init__(self, model):
+        self.model, self.masks = model, None
+
+    def __enter__(self):
+        from mmvae_b200 import ops
+        ops.RELU_TAP = {}
+        return self
+
+    def __exit__(self, *exc):
+        from mmvae_b200 import ops
+        torch.cuda.synchronize()
+        tap, ops.RELU_TAP = ops.RELU_TAP, None
+        names = {p.data_ptr(): k for k, p in self.model.named_parameters()}
+        self.masks = {names[ptr]: torch.cat(ms).cpu() for ptr, ms in tap.items() if ptr in names}
+        return False
+
+
+def branch_consistent(run_oracle, masks):
+    """run_oracle() -> (loss, {name: grad}) evaluates the fp64 oracle (fresh leaves each call).  Returns
+    (loss_b, grads_b, delta): the oracle on the ReLU branches of the implementation under test, and
+    delta[name] = grads_b[name] - grads_plain[name] -- exactly zero unless some unit's pre-activation is within the
+    implementation's forward error of zero, in which case it is the (O(1) per unit) amount by which ANY two finite-precision
+    evaluations may legitimately differ; the comparisons against the reference's fixtures widen by it and by nothing else."""
+    O.relu_masks(None)
+    l_plain, g_plain = run_oracle()
+    O.relu_masks(masks)
+    try:
+        l_b, g_b = run_oracle()
+    finally:
+        O.relu_masks(None)
+    delta = {k: (g_b[k] - g_plain[k]) for k in g_b if g_b[k] is not None and g_plain.get(k) is not None}
+    return l_b, g_b, delta, abs(l_b - l_plain)
+
+
+def check_digests(grads, digests, rtol, what="", delta=None):
+    """grads: name → tensor (or None).  digests: from synth.grad_digest on the reference's .grad.  delta: see
+    branch_consistent (slack for units on the other side of a ReLU kink; zero when there are none)."""
     for k, d in digests.items():
         g = grads.get(k)
         assert g is not None, f"{what}: no gradient for {k}"
@@ -42,8 +81,11 @@ def check_digests(grads, digests, rtol, what=""):
         if ref_norm == 0.0:
             assert f.norm().item() == 0.0, f"{what}: {k} should have zero grad"
             continue
-        assert abs(f.norm().item() - ref_norm) <= rtol * ref_norm, f"{what}: {k} norm {f.norm().item()} vs {ref_norm}"
-        assert err <= rtol * max(scale, 1e-3 * ref_norm), f"{what}: {k} sampled values off by {err / scale:.3e}"
+        dk = delta.get(k) if delta else None
+        slack_n = dk.norm().item() if dk is not None else 0.0
+        slack_i = dk.reshape(-1).double().cpu()[d["idx"]].norm().item() if dk is not None else 0.0
+        assert abs(f.norm().item() - ref_norm) <= rtol * ref_norm + slack_n, f"{what}: {k} norm {f.norm().item()} vs {ref_norm}"
+        assert err <= rtol * max(scale, 1e-3 * ref_norm) + 1.05 * slack_i, f"{what}: {k} sampled values off by {err / scale:.3e}"
 
 
 # ------------------------------------------------------------------------------------------------ GPU helpers

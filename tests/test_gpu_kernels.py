@@ -41,6 +41,27 @@ def test_gemm_layouts(ops, M, N, K, a_k, b_k):
     assert rel_err(out, torch.sigmoid(ref + bias.double())) < 2e-6
 
 
+@pytest.mark.parametrize("M,N,K", [(7680, 784, 512), (7680, 512, 784), (512, 784, 7680), (7680, 512, 512)])
+@pytest.mark.parametrize("a_k,b_k", [(1, 1), (1, 0), (0, 1), (0, 0)])
+def test_gemm_tensor_core_path_with_epilogue(ops, M, N, K, a_k, b_k):
+    """The MLP-decoder shapes of C2 (above the 0.4 GMAC gate of gemm_tc.cu) in all four operand layouts, with the bias + ReLU /
+    Sigmoid epilogue and without: these must run on gemm_tc_kernel (BN = 128 tiles, split-K for the K = 7680 one), which the
+    launch counter asserts, and match fp64."""
+    from mmvae_b200 import _lib
+    lib = _lib.load()
+    A, B = _rand(M, K, seed=1, scale=K ** -0.5), _rand(N, K, seed=2)      # unit-scale pre-activations: no saturated sigmoids
+    bias = _rand(N, seed=3)
+    a_s = A if a_k else A.t().contiguous()
+    b_s = B if b_k else B.t().contiguous()
+    ref = A.double() @ B.double().t()
+    for act, fn in ((None, None), ("relu", torch.relu), ("sigmoid", torch.sigmoid)):
+        n0 = lib.mmvae_gemm_tc_launch_count()
+        out = ops.gemm(a_s, b_s, bias if act else None, M, N, K, a_k, b_k, act)
+        assert lib.mmvae_gemm_tc_launch_count() == n0 + 1, "shape did not run on the tcgen05 kernel"
+        r = fn(ref + bias.double()) if act else ref
+        assert rel_err(out, r) < 2e-6, (act, rel_err(out, r))
+
+
 def test_colsum_and_act_bwd(ops):
     A = _rand(1000, 77, seed=4)
     assert rel_err(ops.colsum(A), A.double().sum(0)) < 1e-6

@@ -117,3 +117,51 @@ def test_every_model_family_captures_after_eager_steps(family, objective, K, dis
     assert all(map(math.isfinite, first + later))
     if objective != "m_elbo":                                    # m_elbo's exp(log q_r - log q_d) weights are heavy-tailed at K=3
         assert sum(later[-5:]) / 5 > sum(first) / 3
+
+
+def test_trainer_passes_the_schedule_and_freezes_like_the_reference():
+    """main.py:155,171: objective(model, data, K, epoch, warmup, beta_prior) and model.step(epoch).  m_jmvae_nf trains the joint
+    ELBO while epoch < warmup; from epoch >= warmup the joint encoder and the decoders are frozen (objectives.py:180-183) and
+    torch's Adam skips them (grad None): they must not move, not even along their momentum; a captured graph is dropped when
+    the phase changes; capturing does not advance the optimiser."""
+    import numpy as np
+    from oracle import bivae_oracle as O
+    from oracle import synth
+    from tests.helpers import build_jmvae_nf
+    from mmvae_b200.train import Trainer
+    spec = O.spec_jnf_mnist_svhn(20, "maf", dcca=False)
+    sd = synth.make_state_dict(spec, 5)
+    model = build_jmvae_nf(spec, sd, flow="maf", fix_jencoder=True, fix_decoders=True, warmup=2)
+    tr = Trainer(model, "m_jmvae_nf", K=1, distributed=False)
+    x = [t.cuda() for t in synth.make_inputs(spec, 32, seed=6)]
+    snap = lambda mod: torch.cat([p.detach().reshape(-1).clone() for p in mod.parameters()])
+    # phase 1 (epoch 1 < warmup 2): everything trains, eagerly and through a captured graph
+    tr.set_schedule(1, warmup=2, beta_prior=1)
+    j0, d0, e0 = snap(model.joint_encoder), snap(model.vaes[1].decoder), snap(model.vaes[0].encoder)
+    tr.step(x)
+    j1 = snap(model.joint_encoder)
+    assert (j1 - j0).abs().max().item() > 0 and (snap(model.vaes[1].decoder) - d0).abs().max().item() > 0
+    before, steps_before = tr.fp.flat.clone(), tr.step_dev.item()
+    tr.capture(x, warmup=2)
+    torch.cuda.synchronize()
+    assert torch.equal(tr.fp.flat, before) and tr.step_dev.item() == steps_before       # capture is invisible
+    assert tr.graph_ready(x)
+    tr.step_graph(x)
+    torch.cuda.synchronize()
+    assert (snap(model.joint_encoder) - j1).abs().max().item() > 0
+    # phase 2 (epoch 2 >= warmup): the graph of phase 1 is gone; joint encoder and decoders stay bit-identical
+    tr.set_schedule(2, warmup=2, beta_prior=1)
+    assert not tr.graph_ready(x)
+    j2, d2, e2 = snap(model.joint_encoder), snap(model.vaes[1].decoder), snap(model.vaes[0].encoder)
+    for _ in range(2):
+        tr.step(x)
+    tr.capture(x, warmup=1)
+    tr.step_graph(x)
+    torch.cuda.synchronize()
+    assert torch.equal(snap(model.joint_encoder), j2) and torch.equal(snap(model.vaes[1].decoder), d2)
+    assert (snap(model.vaes[0].encoder) - e2).abs().max().item() > 0                    # the unimodal encoders train
+    # the model's own per-epoch schedule reaches the next capture
+    model.decrease_beta_kl = 0.5
+    model.step(2)
+    tr.set_schedule(3, warmup=2, beta_prior=1)
+    assert not tr.graph_ready(x)
