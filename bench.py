@@ -26,6 +26,7 @@ import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
 METRIC = "MNIST-SVHN MMVAE K=30 DReG train samples/s"
+EVAL_METRIC = "K=1000 NLL eval samples/s (joint + both conditionals)"
 B_PER_GPU, K_TRAIN, LATENT = 128, 30, 20
 FLOP_PER_SAMPLE = 1.845e9          # necessary fwd+bwd work per training sample at C2
 EVAL_FLOP_PER_DATAPOINT = 20.2e9   # joint + both conditionals at K=1000
@@ -40,12 +41,20 @@ def parse():
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of CUDA-graph replay")
     ap.add_argument("--no-eval", action="store_true", help="skip the K=1000 evaluator leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--eval-datapoints", type=int, default=64)
+    ap.add_argument("--eval-datapoints", type=int, default=500, help="per rank; C4 = the loader batch of compute_likelihoods.py:82")
     ap.add_argument("--detail", action="store_true", help="print every C-ABI call of the profiled step to stderr")
     return ap.parse_args()
 
 
-TC_FAMILY = ("mmvae_gemm", "mmvae_convt_tc_fwd", "mmvae_convt_tc_dgrad", "mmvae_convt_tc_wgrad")
+# C-ABI entry point -> the kernel it launches (the roofline is reported per KERNEL; mmvae_gemm is a dispatcher and is split by
+# the kernel it picked, see ops.gemm)
+KERNEL_OF = {
+    "mmvae_convt_ts_fwd": "convt_ts_kernel<FWD>", "mmvae_convt_ts_dgrad": "convt_ts_kernel<DGRAD>",
+    "mmvae_convt_ts_wgrad": "convt_ts_wgrad_kernel", "mmvae_gemm[tcgen05]": "gemm_tc_kernel", "mmvae_gemm[simt]": "gemm_simt_kernel",
+    "mmvae_convt_tc_fwd": "convt_fwd9_kernel", "mmvae_convt_tc_dgrad": "gemm_tc_kernel(dgrad)", "mmvae_convt_tc_wgrad": "gemm_tc_kernel(wgrad)",
+    "mmvae_convt_small_fwd": "convt_l4_fwd_tc_kernel", "mmvae_convt_small_dgrad": "convt_l4_dgrad_tc_kernel",
+    "mmvae_convt_small_wgrad": "convt_small_wgrad_kernel", "mmvae_loglik_fwd": "loglik_fwd_kernel", "mmvae_loglik_bwd": "loglik_bwd_kernel",
+}
 
 
 def load_traffic():
@@ -93,36 +102,67 @@ def cpu_port_step_rate(steps, warmup, B=B_PER_GPU, K=K_TRAIN):
     return B / dt, cores, dt * 1e3
 
 
-def port_eager_gpu_rate(dev, steps=5, warmup=3, B=B_PER_GPU, K=K_TRAIN):
-    """The same port (torch ops, fp32, the reference's op sequence incl. its K-fold encoder-free restatement) run
-    EAGERLY on the B200 — the reference's real deployment mode is `model.to('cuda')` (main.py:64-71), so this, not the
-    CPU figure, is the number the kernels have to beat.  Reported inside cpu_baseline as `eager_b200`."""
+def port_eager_gpu_rate(dev, strict_fp32, steps=5, warmup=3, B=B_PER_GPU, K=K_TRAIN):
+    """The CPU port's op sequence (torch ops; it already encodes once instead of K times, so it is FASTER than the reference's
+    own forward) run eagerly on the B200 through cuDNN / cuBLAS -- the reference's deployment mode is `model.to('cuda')` with
+    `cudnn.benchmark = True` (main.py:47,64-71).  strict_fp32 = False: torch's defaults as the reference runs them (cuDNN
+    convolutions may use TF32, matmuls fp32); strict_fp32 = True: TF32 off everywhere, the accuracy class this repo's kernels
+    are held to.  Returns (samples/s, ms/step)."""
     from oracle import bivae_oracle as O
     from oracle import synth
-    spec = O.spec_mnist_svhn(LATENT, "laplace")
-    sd = {k: v.to(dev) for k, v in synth.make_state_dict(spec, 1).items()}
-    leaves = {k: v.clone().requires_grad_(k.endswith(("weight", "bias"))) for k, v in sd.items()}
-    opt = torch.optim.Adam([v for v in leaves.values() if v.requires_grad], lr=1e-3, amsgrad=True)
-    x = [t.to(dev) for t in synth.make_inputs(spec, B, seed=2)]
-    rs = np.random.RandomState(3)
-    noises = [[synth.make_noise("laplace", (K, B, LATENT), rs).to(dev) for _ in range(2)] for _ in range(2)]
+    saved = (torch.backends.cudnn.benchmark, torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.benchmark = True
+    torch.backends.cudnn.allow_tf32 = not strict_fp32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        spec = O.spec_mnist_svhn(LATENT, "laplace")
+        sd = {k: v.to(dev) for k, v in synth.make_state_dict(spec, 1).items()}
+        leaves = {k: v.clone().requires_grad_(k.endswith(("weight", "bias"))) for k, v in sd.items()}
+        opt = torch.optim.Adam([v for v in leaves.values() if v.requires_grad], lr=1e-3, amsgrad=True)
+        x = [t.to(dev) for t in synth.make_inputs(spec, B, seed=2)]
+        rs = np.random.RandomState(3)
+        noises = [[synth.make_noise("laplace", (K, B, LATENT), rs).to(dev) for _ in range(2)] for _ in range(2)]
 
-    def step(i):
-        opt.zero_grad(set_to_none=True)
-        loss = O.m_dreg_looser(spec, leaves, x, K, noises[i % 2])
-        (-loss).backward()
-        opt.step()
-    for i in range(warmup):
-        step(i)
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(steps):
-        step(i)
-    e1.record()
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / steps
+        def step(i):
+            opt.zero_grad(set_to_none=True)
+            loss = O.m_dreg_looser(spec, leaves, x, K, noises[i % 2])
+            (-loss).backward()
+            opt.step()
+        for i in range(warmup):
+            step(i)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            step(i)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+    finally:
+        torch.backends.cudnn.benchmark, torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
     return B / (ms * 1e-3), ms
+
+
+def cpu_port_eval_rate(n=4, K=1000, bs=100):
+    """The CPU port's three K-sample evaluators (oracle/bivae_oracle.py: joint + both conditionals, the calls of
+    compute_likelihoods.py:106-107) on n datapoints on the host cores.  Returns (datapoints/s, cores, seconds)."""
+    from oracle import bivae_oracle as O
+    from oracle import synth
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    spec = O.spec_mnist_svhn(LATENT, "laplace")
+    sd = synth.make_state_dict(spec, 1)
+    data = synth.make_inputs(spec, n, seed=4)
+    rs = np.random.RandomState(5)
+    nz = lambda *shape: synth.make_noise("laplace", shape, rs)
+    mask = torch.from_numpy(rs.binomial(1, 0.5, (K, n))).float()
+    with torch.no_grad():
+        t0 = time.perf_counter()
+        O.conditional_likelihood(spec, sd, data, 0, 1, K, bs, nz(n, K, LATENT))
+        O.conditional_likelihood(spec, sd, data, 1, 0, K, bs, nz(n, K, LATENT))
+        O.mmvae_joint_likelihood(spec, sd, data, K, bs, mask, [nz(K, n, LATENT), nz(K, n, LATENT)])
+        dt = time.perf_counter() - t0
+    return n / dt, cores, dt
 
 
 def run_reference(args):
@@ -130,6 +170,7 @@ def run_reference(args):
     if rank != 0:
         return
     val, cores, ms = cpu_port_step_rate(max(1, args.steps), max(0, args.warmup))
+    ev, _, ev_s = cpu_port_eval_rate(4)
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": "samples/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
@@ -141,6 +182,9 @@ def run_reference(args):
         "cpu_baseline": {"value": val, "unit": "samples/s", "cores": cores, "kind": "port",
                          "sample": f"{args.steps} full C2 steps (B=128,K=30) fwd+bwd+Adam after {args.warmup} warm-up"},
         "e2e": {"value": val, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "eval": {"metric": EVAL_METRIC, "value": ev, "unit": "samples/s", "datapoints": 4, "K": 1000, "batch_size_K": 100,
+                 "s_per_pass": ev_s, "cores": cores, "kind": "port",
+                 "sample": "4 datapoints x (joint + both conditionals) at K=1000 on the host cores"},
     }
     _OUT.write(json.dumps(line) + "\n")
     _OUT.flush()
@@ -229,6 +273,55 @@ def timed(fn, steps, dist_on):
     return ms.item()
 
 
+def roofline_of(agg, total, peak):
+    """The roofline object of the dominant KERNEL of a profiled pass: the entry point with the largest summed CUDA-event time
+    among those that launch one kernel.  achieved = ALGORITHMIC flops (2MNK of the contraction; tensor-bound kernels) or
+    bytes (HBM-bound ones) of its launches / their summed time; peak = MEASURED_PEAKS.json (sustained bf16 / copy)."""
+    traffic = load_traffic()
+    cand = {k: a for k, a in agg.items() if k in KERNEL_OF and (a["flop"] > 0 or a["byte"] > 0)}
+    if not cand:
+        return None
+    top = max(cand, key=lambda k: cand[k]["ms"])
+    a, kern = cand[top], KERNEL_OF[top]
+    tr = traffic.get(kern, {}) if isinstance(traffic.get(kern), dict) else {}
+    if a["flop"] > 0:
+        ach = a["flop"] / (a["ms"] * 1e-3) / 1e12
+        roof = {"kernel": kern, "entry_point": top, "bound": "tensor", "achieved": ach, "peak": peak["tflops"], "unit": "TFLOP/s",
+                "frac": ach / peak["tflops"]}
+        note = ("algorithmic 2MNK of the kernel's launches in one pass / their summed CUDA-event time; peak = "
+                f"{peak['which']} dense bf16 (sustained). The kernel computes hi*hi + hi*mid + mid*hi on bf16 pieces (3 MMAs per "
+                "algorithmic MMA), so its MMA-work fraction is 3 x frac")
+    else:
+        ach = a["byte"] / (a["ms"] * 1e-3) / 1e9
+        roof = {"kernel": kern, "entry_point": top, "bound": "hbm", "achieved": ach, "peak": peak["hbm_gbs"], "unit": "GB/s",
+                "frac": ach / peak["hbm_gbs"]}
+        note = f"algorithmic bytes of the kernel's launches in one pass / their summed CUDA-event time; peak = {peak['which']} copy bandwidth"
+    roof.update({"traffic": tr.get("dram_bytes_per_launch"), "launches": a["n"], "us_per_launch": round(1e3 * a["ms"] / a["n"], 1),
+                 "share_of_pass": round(a["ms"] / total, 4), "tensor_pipe_active_ncu_pct": tr.get("tensor_pipe_active_pct"),
+                 "note": note + "; traffic / tensor_pipe_active_ncu_pct: ncu --set full of the same kernel (profiles/traffic.json), null if absent"})
+    return roof
+
+
+def profile_pass(fn):
+    """Runs fn() with CUDA events around every C-ABI call -> ({entry: {ms, n, flop, byte}}, total ms, records)."""
+    from mmvae_b200 import ops
+    torch.cuda.synchronize()
+    ops.PROFILE = []
+    try:
+        fn()
+        torch.cuda.synchronize()
+    finally:
+        rec, ops.PROFILE = ops.PROFILE, None
+    agg = {}
+    for name, work, e0, e1 in rec:
+        a = agg.setdefault(name, {"ms": 0.0, "n": 0, "flop": 0.0, "byte": 0.0})
+        a["ms"] += e0.elapsed_time(e1)
+        a["n"] += 1
+        if work is not None:
+            a[work[0]] += work[1]
+    return agg, sum(a["ms"] for a in agg.values()), rec
+
+
 def profile_step(trainer, x, peak, detail=False):
     """One instrumented eager step: CUDA events around every C-ABI call -> per-kernel time shares and the roofline
     figures of the dominant kernel (algorithmic work / measured time)."""
@@ -264,35 +357,7 @@ def profile_step(trainer, x, peak, detail=False):
     total = sum(a["ms"] for a in agg.values())
     shares = {k: {"ms": round(a["ms"], 4), "launches": a["n"], "share": round(a["ms"] / total, 4)}
               for k, a in sorted(agg.items(), key=lambda kv: -kv[1]["ms"])}
-    # the dominant KERNEL: gemm_tc_kernel (tcgen05 3xTF32) is launched through four C-ABI entry points
-    fam = {"ms": 0.0, "n": 0, "flop": 0.0}
-    for k in TC_FAMILY:
-        if k in agg:
-            for f in fam:
-                fam[f] += agg[k][f]
-    rest = {k: a for k, a in agg.items() if k not in TC_FAMILY}
-    top_rest = max(rest, key=lambda k: rest[k]["ms"]) if rest else None
-    traffic = load_traffic()
-    if fam["ms"] >= (rest[top_rest]["ms"] if top_rest else 0.0):
-        ach = fam["flop"] / (fam["ms"] * 1e-3) / 1e12
-        roof = {"kernel": "gemm_tc_kernel (tcgen05 3xTF32 GEMM / implicit-GEMM convT; entry points " + ", ".join(
-                    k for k in TC_FAMILY if k in agg) + ")",
-                "bound": "tensor", "achieved": ach, "peak": peak["tflops"], "unit": "TFLOP/s",
-                "frac": ach / peak["tflops"], "traffic": traffic.get("gemm_tc_kernel"),
-                "launches": fam["n"], "share_of_step": round(fam["ms"] / total, 4),
-                "tensor_pipe_frac": 6.0 * ach / peak["tflops"],
-                "note": f"algorithmic 2MNK of the {fam['n']} launches of one step / their summed CUDA-event time; peak = "
-                        f"{peak['which']} dense bf16 (sustained). The path computes fp32-accurate 3xTF32: 3 tf32 MMAs per "
-                        "algorithmic MMA on a pipe whose tf32 rate is half the bf16 rate, so tensor_pipe_frac = 6 x frac; "
-                        "traffic = mean ncu dram bytes per launch (profiles/traffic.json) or null"}
-    else:
-        a = rest[top_rest]
-        ach = a["byte"] / (a["ms"] * 1e-3) / 1e9
-        roof = {"kernel": top_rest, "bound": "hbm", "achieved": ach, "peak": peak["hbm_gbs"], "unit": "GB/s",
-                "frac": ach / peak["hbm_gbs"], "traffic": traffic.get(top_rest), "launches": a["n"],
-                "share_of_step": round(a["ms"] / total, 4),
-                "note": f"algorithmic bytes of the {a['n']} {top_rest} launches of one step / their summed CUDA-event "
-                        f"time; peak = {peak['which']} copy bandwidth"}
+    roof = roofline_of(agg, total, peak)
     return roof, shares, calls, total
 
 
@@ -395,13 +460,23 @@ def run_b200(args):
                                     "sample": "2 full C2 steps (B=128,K=30) fwd+bwd+Adam after 1 warm-up",
                                     "ms_per_step": cms}
             try:
-                gv, gms = port_eager_gpu_rate(dev)
+                gv, gms = port_eager_gpu_rate(dev, strict_fp32=False)
+                sv, sms = port_eager_gpu_rate(dev, strict_fp32=True)
                 line["cpu_baseline"]["eager_b200"] = {
-                    "value": gv, "unit": "samples/s", "ms_per_step": gms,
-                    "what": "the same port (torch eager ops, cuDNN/cuBLAS, TF32 off) on this B200: the reference's own "
-                            "deployment mode; 5 steps after 3 warm-up"}
+                    "reference_settings": {"value": gv, "unit": "samples/s", "ms_per_step": gms,
+                                           "what": "cudnn.benchmark=True, torch's default TF32 policy (cuDNN may use TF32, "
+                                                   "matmuls fp32): how main.py:47,64-71 runs on a GPU"},
+                    "strict_fp32": {"value": sv, "unit": "samples/s", "ms_per_step": sms,
+                                    "what": "cudnn.benchmark=True, TF32 disabled for cuDNN and cuBLAS: the accuracy class of "
+                                            "this repo's kernels"},
+                    "what": "the CPU port's op sequence (it encodes once, i.e. it is faster than the reference's own "
+                            "K-tiled forward) run eagerly with torch/cuDNN/cuBLAS on this B200; 5 steps after 3 warm-up"}
             except Exception as e:                  # informational only
                 line["cpu_baseline"]["eager_b200"] = {"error": f"{type(e).__name__}: {e}"[:200]}
+            if ev is not None:
+                ev_v, ev_c, ev_s = cpu_port_eval_rate(4)
+                line["eval"]["cpu_baseline"] = {"value": ev_v, "unit": "samples/s", "cores": ev_c, "kind": "port",
+                                                "sample": "4 datapoints x (joint + both conditionals) at K=1000", "seconds": ev_s}
         _OUT.write(json.dumps(line) + "\n")
         _OUT.flush()
     if dist_on:
@@ -410,34 +485,64 @@ def run_b200(args):
 
 
 def run_eval(model, dev, n, peak, dist_on=False):
-    """K=1000 NLL evaluator (compute_likelihoods.py:106-107): joint + both conditionals per datapoint; n datapoints in
-    total, sharded over the ranks by batch (mmvae_b200.parallel)."""
+    """K=1000 NLL evaluator (compute_likelihoods.py:82,106-107: batches of 500 datapoints, K=1000, batch_size_K=100): joint +
+    both conditionals per datapoint; n datapoints in total.  Timed (a) batch-sharded over the ranks with the data resident in
+    HBM (`value`), (b) the same through host buffers (`e2e`: H2D of the batch inside the timed region, per-datapoint results
+    read back), (c) sharded over the K importance samples with the (max, sum-exp) combine (`samples_axis`; equal to (a) on one
+    GPU).  Every rank runs it; rank 0 reports."""
     import torch.distributed as dist
     from mmvae_b200 import parallel as P
     data = synth_batch(n, seed=999, device=dev)
+    host = synth_batch(n, seed=999, pin=True)
 
-    def once():
+    def once(axis="batch", src=None):
+        d = data if src is None else [t.to(dev, non_blocking=True) for t in src]
         for c, g in ((0, 1), (1, 0)):
-            P.conditional_likelihood(model, data, c, g, K=1000, batch_size_K=100, axis="batch")
-        return P.joint_likelihood(model, data, K=1000, batch_size_K=100, axis="batch")[0]["likelihood"]
-    once()
-    if dist_on:
-        dist.barrier()
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    reps = 2
-    for _ in range(reps):
-        ll = once()
-    e1.record()
-    torch.cuda.synchronize()
-    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-    if dist_on:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    s = ms.item() * 1e-3 / reps
-    return {"metric": "K=1000 NLL eval samples/s (joint + both conditionals)", "value": n / s, "unit": "samples/s",
-            "datapoints": n, "K": 1000, "batch_size_K": 100, "s_per_pass": s, "joint_ll": float(ll),
-            "sharding": "batch", "achieved_tflops_algorithmic": n * EVAL_FLOP_PER_DATAPOINT / s / 1e12}
+            _, per = P.conditional_likelihood(model, d, c, g, K=1000, batch_size_K=100, axis=axis)
+        out, perj = P.joint_likelihood(model, d, K=1000, batch_size_K=100, axis=axis)
+        if src is not None:
+            perj.cpu()                                      # the per-datapoint log-likelihoods go back to the host
+        return out["likelihood"]
+
+    def clock(fn, reps=2):
+        fn()
+        if dist_on:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            ll = fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if dist_on:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return ms.item() * 1e-3 / reps, float(ll)
+
+    s, ll = clock(once)
+    s_e2e, _ = clock(lambda: once(src=host))
+    s_k, ll_k = clock(lambda: once(axis="samples")) if dist_on else (s, ll)
+    ev = {"metric": EVAL_METRIC, "value": n / s, "unit": "samples/s", "datapoints": n, "K": 1000, "batch_size_K": 100,
+          "s_per_pass": s, "joint_ll": ll, "sharding": "batch",
+          "config": {"workload": "C4: K=1000 importance-sampled joint + conditional log-likelihoods, MNIST-SVHN MMVAE, "
+                                 f"{n} datapoints (loader batch 500 per GPU), batch_size_K=100"},
+          "e2e": {"value": n / s_e2e, "unit": "samples/s", "h2d_bytes_per_step": sum(t.numel() * 4 for t in host),
+                  "d2h_bytes_per_step": 4 * n},
+          "samples_axis": {"value": n / s_k, "unit": "samples/s", "joint_ll": ll_k,
+                           "what": "the same pass sharded over the K importance samples (every rank sees all datapoints, "
+                                   "K/N samples each), combined with one MAX + one SUM all-reduce per evaluator"},
+          "achieved_tflops_algorithmic": n * EVAL_FLOP_PER_DATAPOINT / s / 1e12}
+    # per-kernel accounting of one evaluator pass on a slice (the pass is a loop over datapoint chunks of identical launches)
+    m = min(n, 32)
+    small = [t[:m] for t in data]
+    agg, total, _ = profile_pass(lambda: [P.conditional_likelihood(model, small, 0, 1, K=1000, batch_size_K=100, axis="batch"),
+                                          P.conditional_likelihood(model, small, 1, 0, K=1000, batch_size_K=100, axis="batch"),
+                                          P.joint_likelihood(model, small, K=1000, batch_size_K=100, axis="batch")])
+    ev["roofline"] = roofline_of(agg, total, peak)
+    ev["kernel_shares"] = {k: {"ms": round(a["ms"], 4), "launches": a["n"], "share": round(a["ms"] / total, 4)}
+                           for k, a in sorted(agg.items(), key=lambda kv: -kv[1]["ms"])[:12]}
+    return ev
 
 
 def run_eval_jmvae_nf(dev, n_per_rank, dist_on=False):

@@ -229,3 +229,72 @@ int mmvae_gemm_simt(const float* A, const float* B, const float* bias, float* C,
     }
     return 0;
 }
+
+// ---- skinny-K rows x wide-N: y[R,N] = act(x[R,K] * W + b) with K <= 32 (the latent dimension) ----------------------------------
+// The first layer of every decoder (pythae Decoder_AE_MLP Linear(L,512); Decoder_VAE_SVHN's ConvTranspose2d(L,128,4,1,0) on a
+// 1x1 input = Linear(L, 2048), encoders.py:116-118) at M*K*B rows: 20 FMAs per output, i.e. a STORE-bound kernel (63 MB out at
+// C2) that the tiled GEMM above ran at 1 TB/s.  Here a thread keeps its 4 columns of W (K float4) in registers, the block's x
+// rows sit in shared memory and are read as broadcasts, and every warp store covers 512 contiguous bytes.
+#define SK_ROWS 64
+#define SK_THREADS 256
+template <int KMAX, bool B_KMAJOR>
+__global__ void __launch_bounds__(SK_THREADS)
+gemm_skinny_kernel(const float* __restrict__ X, const float* __restrict__ W, const float* __restrict__ bias, float* __restrict__ Y, int R,
+                   int N, int K, int act) {
+    __shared__ __align__(16) float xs[SK_ROWS][KMAX];
+    const int n = (blockIdx.x * SK_THREADS + threadIdx.x) * 4;
+    const int r0 = blockIdx.y * SK_ROWS;
+    for (int i = threadIdx.x; i < SK_ROWS * KMAX; i += SK_THREADS) {
+        const int r = i / KMAX, k = i - r * KMAX;
+        xs[r][k] = (r0 + r < R && k < K) ? X[(long)(r0 + r) * K + k] : 0.f;
+    }
+    float4 w[KMAX];
+    float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (n < N) {
+#pragma unroll
+        for (int k = 0; k < KMAX; ++k) {
+            if (k < K) {
+                if (B_KMAJOR) w[k] = make_float4(W[(long)n * K + k], W[(long)(n + 1) * K + k], W[(long)(n + 2) * K + k], W[(long)(n + 3) * K + k]);
+                else w[k] = __ldg(reinterpret_cast<const float4*>(W + (long)k * N + n));
+            } else {
+                w[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+        if (bias) b4 = make_float4(bias[n], bias[n + 1], bias[n + 2], bias[n + 3]);
+    }
+    __syncthreads();
+    if (n >= N) return;
+    const int rows = min(SK_ROWS, R - r0);
+#pragma unroll 2
+    for (int r = 0; r < rows; ++r) {
+        float4 a = b4;
+#pragma unroll
+        for (int k = 0; k < KMAX; k += 4) {
+            const float4 xv = *reinterpret_cast<const float4*>(&xs[r][k]);          // same address in every lane: broadcast
+            a.x = fmaf(xv.x, w[k].x, a.x); a.y = fmaf(xv.x, w[k].y, a.y); a.z = fmaf(xv.x, w[k].z, a.z); a.w = fmaf(xv.x, w[k].w, a.w);
+            a.x = fmaf(xv.y, w[k + 1].x, a.x); a.y = fmaf(xv.y, w[k + 1].y, a.y); a.z = fmaf(xv.y, w[k + 1].z, a.z); a.w = fmaf(xv.y, w[k + 1].w, a.w);
+            a.x = fmaf(xv.z, w[k + 2].x, a.x); a.y = fmaf(xv.z, w[k + 2].y, a.y); a.z = fmaf(xv.z, w[k + 2].z, a.z); a.w = fmaf(xv.z, w[k + 2].w, a.w);
+            a.x = fmaf(xv.w, w[k + 3].x, a.x); a.y = fmaf(xv.w, w[k + 3].y, a.y); a.z = fmaf(xv.w, w[k + 3].z, a.z); a.w = fmaf(xv.w, w[k + 3].w, a.w);
+        }
+        a.x = apply_act(a.x, act); a.y = apply_act(a.y, act); a.z = apply_act(a.z, act); a.w = apply_act(a.w, act);
+        __stcs(reinterpret_cast<float4*>(Y + (long)(r0 + r) * N + n), a);
+    }
+}
+
+// returns -1 when the shape is not for this kernel
+int mmvae_gemm_skinny(const float* A, const float* B, const float* bias, float* C, int M, int N, int K, int a_kmajor, int b_kmajor,
+                      int act, cudaStream_t st) {
+    if (!a_kmajor || K > 32 || K < 1 || (N & 3) || M < 512 || N < 256) return -1;
+    if (((uintptr_t)C & 15) || (!b_kmajor && ((uintptr_t)B & 15))) return -1;
+    const dim3 grid((N / 4 + SK_THREADS - 1) / SK_THREADS, (M + SK_ROWS - 1) / SK_ROWS);
+    if (grid.y > 65535) return -1;
+    if (K <= 20) {
+        if (b_kmajor) gemm_skinny_kernel<20, true><<<grid, SK_THREADS, 0, st>>>(A, B, bias, C, M, N, K, act);
+        else gemm_skinny_kernel<20, false><<<grid, SK_THREADS, 0, st>>>(A, B, bias, C, M, N, K, act);
+    } else {
+        if (b_kmajor) gemm_skinny_kernel<32, true><<<grid, SK_THREADS, 0, st>>>(A, B, bias, C, M, N, K, act);
+        else gemm_skinny_kernel<32, false><<<grid, SK_THREADS, 0, st>>>(A, B, bias, C, M, N, K, act);
+    }
+    MMVAE_LAUNCH_CHECK("gemm_skinny");
+    return 0;
+}

@@ -7,6 +7,7 @@ need no transpose pass.
 """
 import ctypes
 import math
+import weakref
 
 import torch
 
@@ -149,8 +150,12 @@ def gemm(a, b, bias, M, N, K, a_kmajor, b_kmajor, act=None, out=None):
     ws_bytes = lib.mmvae_gemm_workspace_bytes(M, N, K, int(a_kmajor), int(b_kmajor)) if ALLOW_TC else \
         lib.mmvae_gemm_workspace_bytes(M, N, K, -1, -1)
     ws = torch.empty(ws_bytes // 4, device=a.device, dtype=torch.float32) if ws_bytes else None
+    n_tc = lib.mmvae_gemm_tc_launch_count() if PROFILE is not None else 0
     _call("mmvae_gemm", _p(a), _p(b), _p(bias), _p(out), M, N, K, int(a_kmajor), int(b_kmajor), ACT[act], _p(ws),
           ws_bytes, int(ALLOW_TC), _stream(), work=("flop", 2.0 * M * N * K))
+    if PROFILE:                                   # which kernel the dispatcher picked: the per-kernel accounting of bench.py
+        on_tc = lib.mmvae_gemm_tc_launch_count() != n_tc
+        PROFILE[-1] = ("mmvae_gemm[tcgen05]" if on_tc else "mmvae_gemm[simt]",) + PROFILE[-1][1:]
     if GEMM_LOG is not None and PROFILE:
         GEMM_LOG.append((f"M={M} N={N} K={K} a_k={int(a_kmajor)} b_k={int(b_kmajor)} bias={bias is not None} act={act}",
                          PROFILE[-1][2], PROFILE[-1][3]))
@@ -174,12 +179,46 @@ def act_bwd(g, y, act):
     return out
 
 
+# Derived weight layouts (lowered / class-major / bf16-packed copies of a conv weight) are pure functions of the weight.  The
+# K=1000 evaluators call each decoder ~10 times per batch with frozen weights (12 permute + 4 pack launches per pass, 6 % of
+# it): under torch.no_grad() a layout is built once per weight VALUE and reused while the SAME tensor object is unchanged --
+# tracked by a weak reference to the object (a new model at a recycled address is a different object), its version counter
+# (any torch in-place update) and WEIGHT_EPOCH (bumped by the fused optimizer and by graph replays, which write through raw
+# pointers).  With gradients enabled nothing is cached: a training step uses each layout once.
+WEIGHT_EPOCH = 0
+_LAYOUTS = {}
+
+
+def weights_changed():
+    """Call after writing parameters behind torch's back (fused optimizer kernel, CUDA-graph replay)."""
+    global WEIGHT_EPOCH
+    WEIGHT_EPOCH += 1
+
+
+def _layout(w, kind, build):
+    if torch.is_grad_enabled() or torch.cuda.is_current_stream_capturing():
+        return build()
+    key = (id(w), kind)
+    stamp = (w._version, WEIGHT_EPOCH, w.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    hit = _LAYOUTS.get(key)
+    if hit is not None and hit[0]() is w and hit[1] == stamp:
+        return hit[2]
+    out = build()
+    if len(_LAYOUTS) > 64:
+        for k in [k for k, v in _LAYOUTS.items() if v[0]() is None]:
+            del _LAYOUTS[k]
+    _LAYOUTS[key] = (weakref.ref(w), stamp, out)
+    return out
+
+
 def permute_weight(w):
     """torch conv weight [C0,C1,kh,kw] -> lowered 2-D [C0, kh*kw*C1] (tap-major, C1 fastest)."""
-    C0, C1, kh, kw = w.shape
-    out = torch.empty((C0, kh * kw * C1), device=w.device, dtype=torch.float32)
-    _call("mmvae_permute_weight", _p(w), _p(out), C0, C1, kh * kw, 1, _stream())
-    return out
+    def build():
+        C0, C1, kh, kw = w.shape
+        out = torch.empty((C0, kh * kw * C1), device=w.device, dtype=torch.float32)
+        _call("mmvae_permute_weight", _p(w), _p(out), C0, C1, kh * kw, 1, _stream())
+        return out
+    return _layout(w, "permuted", build)
 
 
 def unpermute_weight(wp, shape, out=None):
@@ -370,10 +409,13 @@ class ConvT2dAct(torch.autograd.Function):
         tc = (ALLOW_TC and not small and k == 4 and stride == 2 and pad == 1 and not nchw_out and w.shape[3] == 4
               and lib.mmvae_convt_tc_supported(H, W, Cin, Cout) == 1)
         if tc and ALLOW_TS and lib.mmvae_convt_ts_supported(H, W, Cin, Cout) == 1:
-            ne = lib.mmvae_convt_ts_packed_elems(Cin, Cout)
-            wfb = torch.empty(ne, device=x.device, dtype=torch.int16)
-            wdb = torch.empty(ne, device=x.device, dtype=torch.int16)
-            _call("mmvae_convt_ts_pack_weights", _p(w), _p(wfb), _p(wdb), Cin, Cout, _stream())
+            def build():
+                ne = lib.mmvae_convt_ts_packed_elems(Cin, Cout)
+                wf_ = torch.empty(ne, device=x.device, dtype=torch.int16)
+                wd_ = torch.empty(ne, device=x.device, dtype=torch.int16)
+                _call("mmvae_convt_ts_pack_weights", _p(w), _p(wf_), _p(wd_), Cin, Cout, _stream())
+                return wf_, wd_
+            wfb, wdb = _layout(w, "ts_bf16", build)
             y = torch.empty((N, 2 * H, 2 * W, Cout), device=x.device, dtype=torch.float32)
             _call("mmvae_convt_ts_fwd", _p(x2d), _p(wfb), _p(b), _p(y), N, H, W, Cin, Cout, ACT[act], _stream(),
                   work=("flop", 2.0 * N * H * W * 16 * Cin * Cout))
@@ -800,6 +842,7 @@ def mask_weight(w, mask):
 
 def adam_amsgrad_(p, g, m, v, vmax, step_dev, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, amsgrad=True):
     """in-place fused Adam(amsgrad) on flat buffers (main.py:114-115)."""
+    weights_changed()
     _call("mmvae_adam_amsgrad", _p(p), _p(g), _p(m), _p(v), _p(vmax), p.numel(), float(lr), float(betas[0]),
           float(betas[1]), float(eps), _p(step_dev), int(amsgrad), _stream())
 

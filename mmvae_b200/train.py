@@ -148,6 +148,7 @@ class Trainer:
         torch.cuda.current_stream().wait_stream(s)
         for dst, src in zip((self.fp.flat, self.m, self.v, self.vmax, self.step_dev), saved):
             dst.copy_(src)
+        ops.weights_changed()                                # derived weight layouts must be rebuilt INSIDE the graph
         self._graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self._graph):
             self._static_loss = self._fwd_bwd(self._static_x)
@@ -175,6 +176,7 @@ class Trainer:
     def step_graph(self, x):
         for dst, src in zip(self._static_x, x):
             dst.copy_(src, non_blocking=True)
+        ops.weights_changed()                                # the replayed optimizer writes the parameters in place
         self._graph.replay()
         if self._graph_upd is not None:
             self._reduce()
