@@ -38,6 +38,9 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: B=128 per GPU (default, the driver's contract); strong: the reference config's GLOBAL B=128 split over the GPUs")
+    ap.add_argument("--one-graph", action="store_true", help="capture the NCCL all-reduce inside the step graph (opt-in, see train.py)")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of CUDA-graph replay")
     ap.add_argument("--no-eval", action="store_true", help="skip the K=1000 evaluator leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -382,7 +385,7 @@ def run_b200(args):
     model = make_model(dev)
     trainer = Trainer(model, "m_dreg_looser", K=K_TRAIN, lr=1e-3, amsgrad=True)
     trainer.broadcast_parameters(0)
-    B = B_PER_GPU
+    B = B_PER_GPU if args.scaling == "weak" else max(1, B_PER_GPU // world)
     batches = [synth_batch(B, seed=100 + rank * 17 + i, device=dev) for i in range(4)]
     host_batches = [synth_batch(B, seed=100 + rank * 17 + i, pin=True) for i in range(4)]
 
@@ -396,7 +399,7 @@ def run_b200(args):
     graph_err = None
     if use_graph:
         try:
-            trainer.capture(batches[0], warmup=2)
+            trainer.capture(batches[0], warmup=2, capture_collective=args.one_graph)
         except Exception as e:                      # same kernels, launched eagerly instead of replayed
             graph_err = f"{type(e).__name__}: {e}"[:200]
             use_graph = False
@@ -426,12 +429,13 @@ def run_b200(args):
 
     line = {
         "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
-        "warmup": max(3, args.warmup), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+        "warmup": max(3, args.warmup), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": args.scaling,
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": "C2: MNIST-SVHN MMVAE m_dreg_looser K=30 L=20 laplace posterior, Normal likelihood, "
                                "Adam(amsgrad) step included", "batch_per_gpu": B, "global_batch": B * world, "K": K_TRAIN,
                    "parallelism": f"dp{world} batch-sharded, one flat NCCL all-reduce(SUM) of 1289507 fp32 gradients",
                    "cuda_graph": use_graph, "graph_error": graph_err,
+                   "collective_in_graph": bool(use_graph and dist_on and args.one_graph),
                    "l2": "per-step working set (decoder activations of 7680 latent rows, ~2 GB) exceeds the 126 MB L2; "
                          "4 input batches rotate"},
         "clocks": clk,

@@ -132,10 +132,11 @@ class Trainer:
         return self._step_impl(x, noise)
 
     # ---- CUDA-graph replay: static input buffers, RNG inside the graph -------------------------------------------
-    # Two graphs (forward+backward, optimizer) with the NCCL all-reduce issued between them on the same stream: the
-    # collective stays an ordinary stream-ordered launch (no capture of communicator state), the ~100 kernel launches
-    # around it are replayed.
-    def capture(self, x_example, warmup=3):
+    # Two graphs (forward+backward, optimizer) with the NCCL all-reduce issued between them on the same stream: the collective
+    # stays an ordinary stream-ordered launch, the ~100 kernel launches around it are replayed.  capture_collective=True puts
+    # the all-reduce INSIDE one graph (no host gap around it); measured once at N=2 (2.231 ms/step) but two of three further
+    # multi-rank runs with it hung on this stack (the communicator's watchdog thread and global-mode capture), so it is opt-in.
+    def capture(self, x_example, warmup=3, capture_collective=False):
         self._static_x = [t.clone() for t in x_example]
         # the warm-up iterations run real steps (allocator and lazy initialisations must happen before capture): parameters,
         # moments and the step counter are put back afterwards, so capturing is invisible to the optimisation trajectory
@@ -149,13 +150,15 @@ class Trainer:
         for dst, src in zip((self.fp.flat, self.m, self.v, self.vmax, self.step_dev), saved):
             dst.copy_(src)
         ops.weights_changed()                                # derived weight layouts must be rebuilt INSIDE the graph
+        one_graph = capture_collective or not self.distributed
         self._graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self._graph):
             self._static_loss = self._fwd_bwd(self._static_x)
-            if not self.distributed:
+            if one_graph:
+                self._reduce()
                 self._update()
         self._graph_upd = None
-        if self.distributed:
+        if not one_graph:
             self._graph_upd = torch.cuda.CUDAGraph()
             with torch.cuda.graph(self._graph_upd):
                 self._update()

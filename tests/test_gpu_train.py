@@ -165,3 +165,18 @@ def test_trainer_passes_the_schedule_and_freezes_like_the_reference():
     model.step(2)
     tr.set_schedule(3, warmup=2, beta_prior=1)
     assert not tr.graph_ready(x)
+
+
+def test_two_rank_nccl_step_equals_one_rank():
+    """The N-rank step on the CUDA path with the NCCL all-reduce (eager and captured in the step graph) against the 1-rank
+    step on the concatenated batch (tools/nccl_equality.py).  Needs two GPUs on the box."""
+    import os
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29541", os.path.join(root, "tools", "nccl_equality.py")], capture_output=True, text=True,
+                       timeout=600, cwd=root)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
