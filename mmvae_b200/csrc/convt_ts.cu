@@ -316,18 +316,19 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                 }
         }
     } else {
-        // ===== epilogue (warps 11..14): TMEM -> registers -> global, one thread = one pixel row =====
+        // ===== epilogue (warps 11..14): TMEM -> registers -> (transposition pad) -> global =====
+        // A thread reads its pixel's 32 accumulator columns; stored directly that is 32 different 128-byte lines per store
+        // instruction (the LSU walks 32 tags: ~40 us of the kernel, tools/ts_time.py bit 1).  Each warp therefore transposes
+        // its 32 x 32 block through a private 4 KB pad (128-byte rows, 16-byte chunks XOR-swizzled by the row: conflict-free
+        // both ways) so that one store instruction covers 4 rows x 128 contiguous bytes.
         const int lane_base = (warp & 3) * 32;
-        // forward: the bias stays in registers for the whole kernel (issue slots are shared with the converter warps)
-        float bv[(MODE == TS_FWD) ? NB : 1];
-        if (MODE == TS_FWD) {
-#pragma unroll
-            for (int j = 0; j < NB; ++j) bv[j] = bias ? __ldg(bias + j) : 0.f;
-        }
+        const uint32_t pad = smem_u32(bars) + 1024 + (uint32_t)(warp & 3) * 4096;
+        const uint32_t my_row = pad + lane * 128, my_sw = lane & 7;
+        const int tr_c = lane & 7, tr_r0 = lane >> 3;                    // transposed role: chunk tr_c of rows tr_r0 + 4k
         int ti = 0;
         for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++ti) {
             const int acc = ti % NACC, use = ti / NACC;
-            const int row = t * 128 + lane_base + lane;
+            const int row0 = t * 128 + lane_base, row = row0 + lane;
             const uint32_t tb = tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)(acc * ACC_COLS);
             if (MODE == TS_FWD) {
                 const int n_img = row / HW, rem = row - n_img * HW, ii = rem / W, jj = rem - ii * W;
@@ -337,7 +338,7 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
 #pragma unroll 1
                 for (int slot = 0; slot < 4; ++slot) {
                     const int py = slot >> 1, px = (slot & 1) ^ py;                  // Gray slot -> (py, px)
-                    float* p = y00 + ((long)py * (2 * W) + px) * NB;
+                    const unsigned long long p = (unsigned long long)(y00 + ((long)py * (2 * W) + px) * NB);
 #pragma unroll
                     for (int cc = 0; cc < NB; cc += 32) {
                         float v[32];
@@ -347,30 +348,43 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                             __syncwarp();
                             if (lane == 0) mbar_arrive(tempty + acc);
                         }
-                        if (row < ar.M && !(ar.dbg & 1)) {
 #pragma unroll
-                            for (int j = 0; j < 32; j += 4) {
-                                float4 o = make_float4(v[j] + bv[cc + j], v[j + 1] + bv[cc + j + 1], v[j + 2] + bv[cc + j + 2],
-                                                       v[j + 3] + bv[cc + j + 3]);
-                                if (ar.act == MMVAE_ACT_RELU) {
-                                    o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f);
-                                } else if (ar.act == MMVAE_ACT_SIGMOID) {
-                                    o.x = 1.f / (1.f + expf(-o.x)); o.y = 1.f / (1.f + expf(-o.y));
-                                    o.z = 1.f / (1.f + expf(-o.z)); o.w = 1.f / (1.f + expf(-o.w));
-                                }
-                                __stcs(reinterpret_cast<float4*>(p + cc + j), o);
+                        for (int c = 0; c < 8; ++c)
+                            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((uint32_t)(c ^ my_sw) << 4)), "f"(v[4 * c]),
+                                         "f"(v[4 * c + 1]), "f"(v[4 * c + 2]), "f"(v[4 * c + 3]) : "memory");
+                        __syncwarp();
+                        const float4 b4 = bias ? make_float4(__ldg(bias + cc + 4 * tr_c), __ldg(bias + cc + 4 * tr_c + 1),
+                                                             __ldg(bias + cc + 4 * tr_c + 2), __ldg(bias + cc + 4 * tr_c + 3))
+                                               : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) {
+                            const int r = 4 * k + tr_r0;
+                            float4 o;
+                            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(o.x), "=f"(o.y), "=f"(o.z), "=f"(o.w)
+                                         : "r"(pad + r * 128 + ((uint32_t)(tr_c ^ (r & 7)) << 4)));
+                            o.x += b4.x; o.y += b4.y; o.z += b4.z; o.w += b4.w;
+                            if (ar.act == MMVAE_ACT_RELU) {
+                                o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f);
+                            } else if (ar.act == MMVAE_ACT_SIGMOID) {
+                                o.x = 1.f / (1.f + expf(-o.x)); o.y = 1.f / (1.f + expf(-o.y));
+                                o.z = 1.f / (1.f + expf(-o.z)); o.w = 1.f / (1.f + expf(-o.w));
                             }
+                            float* pr = reinterpret_cast<float*>(__shfl_sync(0xffffffffu, p, r));       // row r's output pixel
+                            if (row0 + r < ar.M && !(ar.dbg & 1)) __stcs(reinterpret_cast<float4*>(pr + cc + 4 * tr_c), o);
                         }
+                        __syncwarp();                                     // the pad is rewritten by the next chunk
                     }
                 }
             } else {
-                float* p = out + (long)row * NB;
-                const float* mrow = mask ? mask + (long)row * NB : nullptr;
+                const bool use_mask = mask != nullptr;
                 float4 mk[8];
                 auto load_mask = [&](int cc) {
 #pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        mk[j] = (mrow && row < ar.M) ? __ldg(reinterpret_cast<const float4*>(mrow + cc + 4 * j)) : make_float4(1.f, 1.f, 1.f, 1.f);
+                    for (int k = 0; k < 8; ++k) {
+                        const int r = 4 * k + tr_r0;
+                        mk[k] = (use_mask && row0 + r < ar.M) ? __ldg(reinterpret_cast<const float4*>(mask + (long)(row0 + r) * NB + cc + 4 * tr_c))
+                                                              : make_float4(1.f, 1.f, 1.f, 1.f);
+                    }
                 };
                 load_mask(0);                             // requested before the accumulator is complete
                 mbar_wait(tfull + acc, use & 1);
@@ -385,13 +399,23 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                         if (lane == 0) mbar_arrive(tempty + acc);
                     }
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        float4 o = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-                        const float4 m = mk[j];
+                    for (int c = 0; c < 8; ++c)
+                        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((uint32_t)(c ^ my_sw) << 4)), "f"(v[4 * c]),
+                                     "f"(v[4 * c + 1]), "f"(v[4 * c + 2]), "f"(v[4 * c + 3]) : "memory");
+                    __syncwarp();
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const int r = 4 * k + tr_r0;
+                        float4 o;
+                        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(o.x), "=f"(o.y), "=f"(o.z), "=f"(o.w)
+                                     : "r"(pad + r * 128 + ((uint32_t)(tr_c ^ (r & 7)) << 4)));
+                        const float4 m = mk[k];
                         o.x = m.x > 0.f ? o.x : 0.f; o.y = m.y > 0.f ? o.y : 0.f;
                         o.z = m.z > 0.f ? o.z : 0.f; o.w = m.w > 0.f ? o.w : 0.f;
-                        if (row < ar.M && !(ar.dbg & 1)) __stcs(reinterpret_cast<float4*>(p + cc + 4 * j), o);
+                        if (row0 + r < ar.M && !(ar.dbg & 1))
+                            __stcs(reinterpret_cast<float4*>(out + (long)(row0 + r) * NB + cc + 4 * tr_c), o);
                     }
+                    __syncwarp();
                     if (cc + 32 < NB) load_mask(cc + 32);
                 }
             }
@@ -416,7 +440,7 @@ static bool ts_plan(int mode, int NB, int chunks, int rows, int* nbs, int* resid
     *stage_bytes = (rows * 128 + 1023) & ~1023;
     *resident = 16L * chunks * block <= 131072;
     *nbs = *resident ? 16 * chunks : (mode == TS_FWD ? 16 : 8);
-    const long fixed = (long)*nbs * block + 1024 /*barriers*/ + 1024 /*alignment*/;
+    const long fixed = (long)*nbs * block + 1024 /*barriers*/ + 16384 /*epilogue pads*/ + 1024 /*alignment*/;
     long n = (TS_SMEM_MAX - fixed) / *stage_bytes;
     *nstg = (int)(n > 8 ? 8 : n);
     return *nstg >= 2;
@@ -506,7 +530,7 @@ static int ts_launch(const CUtensorMap& ta, const CUtensorMap& tb, const float* 
     ar.dbg = mmvae_tc_dbg_bits();
     if (!ts_plan(MODE, NB, ar.chunks, rows, &ar.nbs, &ar.resident, &ar.nstg, &ar.stage_bytes))
         return mmvae_set_error(1, "convt_ts: shared memory plan does not fit (stage %d bytes)", ar.stage_bytes);
-    const int smem = (int)((long)ar.nbs * BLOCK_BYTES + 2048 + (long)ar.nstg * ar.stage_bytes);
+    const int smem = (int)((long)ar.nbs * BLOCK_BYTES + 2048 + 16384 + (long)ar.nstg * ar.stage_bytes);
     if (!attr_done) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM_MAX);
         if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "convt_ts: smem attribute: %s", cudaGetErrorString(e));
