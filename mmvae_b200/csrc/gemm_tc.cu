@@ -58,6 +58,31 @@ __device__ __forceinline__ void tf32_split_tile(uint32_t hi_addr, uint32_t lo_ad
     }
 }
 
+// bf16x3 mode (passes == 2; K-major x K-major operands): a landed row of 32 fp32 (128 bytes, 16-byte chunks XOR-swizzled by the
+// row) is split IN PLACE into 16 words of packed bf16 hi pairs | 16 words of packed bf16 mid pairs -- the same 128 bytes are then
+// a K-major bf16 operand row whose hi half starts at byte 0 and whose mid half at byte 64 (convt_ts.cu uses the same split).
+__device__ __forceinline__ void bf16_split_row(uint32_t row_addr, int sw) {
+    float f[32];
+#pragma unroll
+    for (int c = 0; c < 8; ++c)
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(f[4 * c]), "=f"(f[4 * c + 1]), "=f"(f[4 * c + 2]), "=f"(f[4 * c + 3])
+                     : "r"(row_addr + ((uint32_t)(c ^ sw) << 4)));
+    uint32_t hp[16], mp[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hp[j]) : "f"(f[2 * j + 1]), "f"(f[2 * j]));
+        const float r0 = f[2 * j] - __uint_as_float(hp[j] << 16), r1 = f[2 * j + 1] - __uint_as_float(hp[j] & 0xffff0000u);
+        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(mp[j]) : "f"(r1), "f"(r0));
+    }
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row_addr + ((uint32_t)(c ^ sw) << 4)), "r"(hp[4 * c]), "r"(hp[4 * c + 1]),
+                     "r"(hp[4 * c + 2]), "r"(hp[4 * c + 3]) : "memory");
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row_addr + ((uint32_t)((4 + c) ^ sw) << 4)), "r"(mp[4 * c]), "r"(mp[4 * c + 1]),
+                     "r"(mp[4 * c + 2]), "r"(mp[4 * c + 3]) : "memory");
+    }
+}
+
 __device__ __forceinline__ float apply_act_tc(float v, int act) {
     if (act == MMVAE_ACT_RELU) return fmaxf(v, 0.f);
     if (act == MMVAE_ACT_SIGMOID) return 1.f / (1.f + expf(-v));
@@ -214,10 +239,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             tc_fence_after_sync();
             const uint32_t d_big = tmem_base + acc * (2 * BN), d_small = d_big + BN;
             for (int i = 0; i < tl.nk; ++i) {
-                mbar_wait(passes == 3 ? conv + s : full + s, ph);
+                mbar_wait(passes >= 2 ? conv + s : full + s, ph);
                 tc_fence_after_sync();
                 const uint64_t dah = da0 + (uint64_t)(s * (Cfg::STAGE >> 4)), dal = dah + (TC_A_TILE >> 4);
                 const uint64_t dbh = db0 + (uint64_t)(s * (Cfg::STAGE >> 4)), dbl = dbh + (Cfg::B_TILE >> 4);
+                if (!A_MN && !B_MN && passes == 2) {
+                    // bf16x3: hi*hi + hi*mid + mid*hi, K = 16 per MMA (two k-steps per 32-float k-block); hi / mid halves of the
+                    // split rows are 64 bytes apart, a k-step 32 bytes
+                    constexpr uint32_t idesc_bf = umma_idesc_bf16(TC_BM, BN, 0, 0);
+#pragma unroll
+                    for (int kk = 0; kk < 2; ++kk) {
+                        const uint32_t first = (i | kk) != 0;
+                        umma_bf16_ss_elect(d_big, dah + kk * 2, dbh + kk * 2, idesc_bf, first);
+                        umma_bf16_ss_elect(d_big, dah + kk * 2, dbh + 4 + kk * 2, idesc_bf, 1);
+                        umma_bf16_ss_elect(d_big, dah + 4 + kk * 2, dbh + kk * 2, idesc_bf, 1);
+                    }
+                    umma_commit_elect(empty + s);
+                    if (++s == STAGES) { s = 0; ph ^= 1; }
+                    continue;
+                }
 #pragma unroll
                 for (int kk = 0; kk < TC_BK / 8; ++kk) {
                     if ((dbg & 16) && (i | kk) != 0) break;
@@ -245,7 +285,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     } else if (warp < 6) {
         // ===== converter (warps 2..5): lo = rn_tf32(a - trunc_tf32(a)), same swizzled position in the lo tile =====
         const int tq = threadIdx.x - 64;               // 0..127
-        if (passes == 3) {
+        if (!A_MN && !B_MN && passes == 2) {
+            int it = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                const TcTile tl = tc_tile(t, tiles_m, tiles_n, BN, nkb, kb_per_split);
+                for (int i = 0; i < tl.nk; ++i, ++it) {
+                    const int s = it % STAGES, ph = (it / STAGES) & 1;
+                    mbar_wait(full + s, ph);
+                    const uint32_t st = smem_u32(smem) + s * Cfg::STAGE;
+                    bf16_split_row(st + tq * 128, tq & 7);                                  // A: one row per thread
+                    if (tq < BN) bf16_split_row(st + 2 * TC_A_TILE + tq * 128, tq & 7);      // B: BN rows
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(conv + s);
+                }
+            }
+        } else if (passes == 3) {
             int it = 0;
             for (int t = blockIdx.x; t < total; t += gridDim.x) {
                 const TcTile tl = tc_tile(t, tiles_m, tiles_n, BN, nkb, kb_per_split);
@@ -530,8 +585,12 @@ static int tc_launch(const CUtensorMap& ta, const CUtensorMap& tb, const float* 
     }
     const long total = (long)((N + BN - 1) / BN) * ((M + TC_BM - 1) / TC_BM) * p.S;
     const int grid = (int)(total < MMVAE_NUM_SMS ? total : MMVAE_NUM_SMS);      // persistent: one CTA per SM
+    // Debug bit 65536 runs K-major x K-major plain GEMMs with the bf16x3 split of convt_ts.cu (hi*hi + hi*mid + mid*hi, half the
+    // MMA instructions of 3xTF32).  Measured (tools/gemm_bf16_ab.py): 7680x784x512 54.1 -> 48.9 us, 122880x128x512 107 -> 93 us
+    // at 3.3e-6 instead of 9e-7 relative error -- this kernel is not bound by MMA issue, so 3xTF32 stays the default.
+    const int passes = g_tc_mode == 1 ? 1 : ((!A_MN && !B_MN && cv.mode == 0 && (g_tc_dbg & 65536)) ? 2 : 3);
     kern<<<grid, TC_THREADS, TcCfg<BN>::SMEM, st>>>(ta, tb, bias, C, ws, M, N, K, act, p.kb_per, p.S, transposed,
-                                                    (g_tc_mode == 1 ? 1 : 3) | (g_tc_dbg << 8), cv, mask);
+                                                    passes | (g_tc_dbg << 8), cv, mask);
     MMVAE_LAUNCH_CHECK("gemm_tc");
     ++g_tc_launches;
     return 0;
