@@ -165,6 +165,14 @@ int mmvae_col2im(const float* col, const float* bias, float* y, int N, int C, in
 int  mmvae_convt_small_supported(int H, int W, int Cin, int Cout);
 int  mmvae_convt_small_fwd(const float* x, const float* w, const float* bias, float* y, int N, int H, int W, int Cin,
                            int Cout, int act, void* stream);
+/* Evaluator form of the same forward (no gradient): the image is never written; lp[n] (+ lp_lo[n], the residual of the fp64
+ * row sum, or NULL) = lik_scaling * sum_pix log p(xdata[(n / x_div) % B] | y_n) for the Normal / Laplace unit-scale likelihoods
+ * (mmvae.py:154-156, multi_vaes.py:306-311 on the decoder output of encoders.py:125-128).  tcgen05 path only (H = W = 16,
+ * Cin = 32): check _supported() first. */
+int  mmvae_convt_small_fwd_loglik_supported(int H, int W, int Cin, int Cout, int lik);
+int  mmvae_convt_small_fwd_loglik(const float* x, const float* w, const float* bias, const float* xdata, float* lp, float* lp_lo,
+                                  int N, int H, int W, int Cin, int Cout, int act, int B, int x_div, int lik, float lik_scaling,
+                                  void* stream);
 /* g: gradient w.r.t. y; if y_act != NULL it is multiplied by act'(y_act) on the fly (g is then post-activation).
  * x_mask: NULL or the layer's input x (N,H,W,Cin): gx is zeroed where x <= 0 (fused ReLU backward of the layer below). */
 int  mmvae_convt_small_dgrad(const float* g, const float* y_act, const float* w, const float* x_mask, float* gx,

@@ -56,10 +56,23 @@ __device__ __forceinline__ void l4_tmem_ld16_nowait(uint32_t taddr, uint32_t* r)
 }
 __device__ __forceinline__ void l4_tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// Evaluator mode (no gradient): the finished image never reaches HBM.  The finalize warps, which hold every output pixel of an
+// image after bias + sigmoid, reduce log p(x | image) on the spot (mmvae.py:154-156, multi_vaes.py:306-311: Normal / Laplace
+// with unit scale) and write one (hi, lo) pair per image: 12 KB of stores and the 12 KB re-read of loglik_fwd_kernel per latent
+// row are gone (at K = 1000 that is a quarter of the decoder's HBM traffic).  lp == NULL: plain forward.
+struct L4LogLik {
+    const float* x;          // [B, COUT*32*32] data, row (img / x_div) % B
+    float* lp;               // [n_img] or NULL
+    float* lp_lo;            // [n_img] residual of the fp64 row sum, or NULL
+    int B, x_div, lik;
+    float scale;
+    double row_const;        // -D * log sqrt(2 pi)  /  -D * log 2
+};
+
 template <int COUT>
 __global__ void __launch_bounds__(L4_THREADS, 1)
 convt_l4_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float* __restrict__ w,
-                       const float* __restrict__ bias, float* __restrict__ y, int n_img, int act, int dbg) {
+                       const float* __restrict__ bias, float* __restrict__ y, int n_img, int act, int dbg, const L4LogLik ll) {
     constexpr int NB = 16 * COUT;                 // UMMA N
     constexpr int OUT_FLOATS = COUT * 32 * 32;
     constexpr int OUT_SMEM = COUT * 32 * L4_PITCH;     // floats of the padded smem image
@@ -145,6 +158,7 @@ convt_l4_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float* 
         // scattered (bias + activation + NCHW store + re-zero), one image behind, so that the scatter of image n+1
         // overlaps the store of image n (two smem images; img_full / img_empty hand them over) =====
         const int tq = threadIdx.x - 64;
+        __shared__ double ll_red[2][4];
         float bv[COUT];
 #pragma unroll
         for (int c = 0; c < COUT; ++c) bv[c] = bias ? __ldg(bias + c) : 0.f;
@@ -157,6 +171,13 @@ convt_l4_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float* 
                 // at positions 4j..4j+3 = columns 4j-1..4j+2 and takes column 4j+3 from its right neighbour's first
                 // element (the lane above; position 32 for the last float4 of a row) -> aligned 128-bit global stores
                 float4* dst = reinterpret_cast<float4*>(y + (long)img * OUT_FLOATS);
+                const float4* xr = ll.lp ? reinterpret_cast<const float4*>(ll.x + (long)((img / ll.x_div) % ll.B) * OUT_FLOATS) : nullptr;
+                float part = 0.f;                              // this thread's 24 pixel terms (fp32, as the reference's)
+                float4 xv[OUT_FLOATS / 4 / 128];
+                if (ll.lp) {                                   // all data loads in flight before the first use
+#pragma unroll
+                    for (int i = 0; i < OUT_FLOATS / 4 / 128; ++i) xv[i] = __ldg(xr + tq + i * 128);
+                }
 #pragma unroll
                 for (int i = 0; i < OUT_FLOATS / 4 / 128; ++i) {
                     const int q = tq + i * 128;                // float4 of the NCHW image: 256 per channel -> channel = i >> 1
@@ -169,9 +190,27 @@ convt_l4_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float* 
                     float4 o;
                     o.x = l4_act_fast(m.y + b, act); o.y = l4_act_fast(m.z + b, act);
                     o.z = l4_act_fast(m.w + b, act); o.w = l4_act_fast(nx + b, act);
-                    __stcs(dst + q, o);
+                    if (ll.lp) {
+                        const float d0 = xv[i].x - o.x, d1 = xv[i].y - o.y, d2 = xv[i].z - o.z, d3 = xv[i].w - o.w;
+                        if (ll.lik == MMVAE_LIK_NORMAL) part += -0.5f * ((d0 * d0 + d1 * d1) + (d2 * d2 + d3 * d3));
+                        else part += -((fabsf(d0) + fabsf(d1)) + (fabsf(d2) + fabsf(d3)));
+                    } else {
+                        __stcs(dst + q, o);
+                    }
                     *src = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (j == 7) out[row * L4_PITCH + 32] = 0.f;
+                }
+                if (ll.lp) {                                   // 128 partial sums of 24 terms -> fp64 total (ll_red alternates per image)
+                    const float ws = warp_sum(part);
+                    if (lane == 0) ll_red[n & 1][warp - 2] = (double)ws;
+                    asm volatile("bar.sync 3, 128;" ::: "memory");
+                    if (tq == 0) {
+                        const double* r = ll_red[n & 1];
+                        const double v = (double)ll.scale * (((r[0] + r[1]) + (r[2] + r[3])) + ll.row_const);
+                        const float hi = (float)v;
+                        ll.lp[img] = hi;
+                        if (ll.lp_lo) ll.lp_lo[img] = (float)(v - (double)hi);
+                    }
                 }
             }
             __syncwarp();
@@ -286,7 +325,8 @@ convt_l4_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float* 
 }
 
 template <int COUT>
-static int l4_launch(const CUtensorMap& tm, const float* w, const float* bias, float* y, int N, int act, cudaStream_t st) {
+static int l4_launch(const CUtensorMap& tm, const float* w, const float* bias, float* y, int N, int act, cudaStream_t st,
+                     const L4LogLik& ll = L4LogLik{nullptr, nullptr, nullptr, 1, 1, 0, 1.f, 0.0}) {
     static bool attr_done = false;
     constexpr int SMEM = L4_STAGES * 2 * L4_TILE + 2 * L4_BROWS * 128 + 2 * COUT * 32 * L4_PITCH * 4 + 256 + 1024;
     auto kern = convt_l4_fwd_tc_kernel<COUT>;
@@ -296,7 +336,7 @@ static int l4_launch(const CUtensorMap& tm, const float* w, const float* bias, f
         attr_done = true;
     }
     const int grid = N < MMVAE_NUM_SMS ? N : MMVAE_NUM_SMS;
-    kern<<<grid, L4_THREADS, SMEM, st>>>(tm, w, bias, y, N, act, (mmvae_tc_dbg_bits() >> 10) & 7);   // ablation bits, 0 in production
+    kern<<<grid, L4_THREADS, SMEM, st>>>(tm, w, bias, y, N, act, (mmvae_tc_dbg_bits() >> 10) & 7, ll);   // ablation bits, 0 in production
     MMVAE_LAUNCH_CHECK("convt_l4_fwd_tc");
     return 0;
 }
@@ -311,6 +351,27 @@ int mmvae_convt_l4_fwd_tc(const float* x, const float* w, const float* bias, flo
     if (rc < 0) return -1;                                   // no tcgen05 / TMA on this device
     if (rc) return mmvae_set_error(1, "convt_l4_fwd_tc: cuTensorMapEncodeTiled failed with %d", rc);
     return Cout == 3 ? l4_launch<3>(tm, w, bias, y, N, act, st) : l4_launch<1>(tm, w, bias, y, N, act, st);
+}
+
+// forward fused with the pixel log-likelihood (evaluators): lp[img] (+ lp_lo) = scale * sum_pix log p(xdata[(img / x_div) % B] | y_img)
+extern "C" int mmvae_convt_small_fwd_loglik_supported(int H, int W, int Cin, int Cout, int lik) {
+    return H == 16 && W == 16 && Cin == 32 && (Cout == 3 || Cout == 1) && (lik == MMVAE_LIK_NORMAL || lik == MMVAE_LIK_LAPLACE) &&
+           mmvae_has_tcgen05() && !(mmvae_tc_dbg_bits() & 512);
+}
+extern "C" int mmvae_convt_small_fwd_loglik(const float* x, const float* w, const float* bias, const float* xdata, float* lp,
+                                            float* lp_lo, int N, int H, int W, int Cin, int Cout, int act, int B, int x_div, int lik,
+                                            float lik_scaling, void* stream) {
+    MMVAE_REQUIRE(x && w && xdata && lp && N > 0 && B > 0 && x_div > 0, "convt_small_fwd_loglik: bad arguments");
+    MMVAE_REQUIRE(mmvae_convt_small_fwd_loglik_supported(H, W, Cin, Cout, lik), "convt_small_fwd_loglik: unsupported shape / likelihood");
+    MMVAE_REQUIRE((((uintptr_t)x | (uintptr_t)xdata) & 15) == 0, "convt_small_fwd_loglik: unaligned pointer");
+    CUtensorMap tm;
+    const int rc = mmvae_tc_tmap_rows(&tm, x, (long)N * 256, 32, 128);
+    if (rc) return mmvae_set_error(1, "convt_small_fwd_loglik: cuTensorMapEncodeTiled failed with %d", rc);
+    const int D = Cout * 32 * 32;
+    const L4LogLik ll{xdata, lp, lp_lo, B, x_div, lik, lik_scaling,
+                      lik == MMVAE_LIK_NORMAL ? -(double)D * (double)MMVAE_LOG_SQRT_2PI : -(double)D * (double)MMVAE_LOG2};
+    cudaStream_t st = (cudaStream_t)stream;
+    return Cout == 3 ? l4_launch<3>(tm, w, bias, nullptr, N, act, st, ll) : l4_launch<1>(tm, w, bias, nullptr, N, act, st, ll);
 }
 
 // =====================================================================================================================

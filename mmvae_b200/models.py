@@ -103,9 +103,14 @@ class Multi_VAES(nn.Module):
 
     def _lpx_rows(self, d, z_rows, x_d, x_div, scaled):
         """sum_pix log p(x_d | decoder_d(z)) for z_rows [R,L] -> [R]."""
-        recon = self.vaes[d].decoder(z_rows)["reconstruction"]
-        R = recon.shape[0]
         c = self.lik_scaling[d] if scaled else 1.0
+        dec = self.vaes[d].decoder
+        if not torch.is_grad_enabled() and hasattr(dec, "loglik_rows"):        # evaluators: the image never reaches HBM
+            lp = dec.loglik_rows(z_rows, self._flat_x(x_d), x_div, self.params.recon_losses[d], c)
+            if lp is not None:
+                return lp
+        recon = dec(z_rows)["reconstruction"]
+        R = recon.shape[0]
         return ops.LogLik.apply(recon.reshape(R, -1), self._flat_x(x_d), x_div, self.params.recon_losses[d], c, False)[0]
 
     def _is_loglik(self, z, data, mods, qmode, mu=None, std=None, lq_ext=None, K_total=None, with_prior=True,

@@ -171,6 +171,24 @@ def colsum(a2d, out=None):
     return out
 
 
+def convt_fwd_loglik_supported(w, H, W, lik):
+    Cin, Cout = w.shape[0], w.shape[1]
+    return w.shape[2] == 4 and w.shape[3] == 4 and lik in LIK and \
+        _lib.load().mmvae_convt_small_fwd_loglik_supported(H, W, Cin, Cout, LIK[lik]) == 1
+
+
+def convt_small_fwd_loglik(x, w, b, act, x_flat, x_div, lik, scale):
+    """-> lp [N]: the image-producing ConvTranspose2d + activation fused with sum_pix log p(x_flat[(n / x_div) % B] | y_n)."""
+    N, Cin, H, W = x.shape
+    Cout = w.shape[1]
+    x2d = _as_rows(_dev(x, "x"))
+    xf = _c(x_flat, "x")
+    lp = torch.empty(N, device=x.device, dtype=torch.float32)
+    _call("mmvae_convt_small_fwd_loglik", _p(x2d), _p(_c(w, "weight")), _p(b), _p(xf), _p(lp), None, N, H, W, Cin, Cout, ACT[act],
+          xf.shape[0], int(x_div), LIK[lik], float(scale), _stream(), work=("byte", 4.0 * x2d.numel()))
+    return lp
+
+
 def act_bwd(g, y, act):
     if ACT[act] == C["MMVAE_ACT_NONE"]:
         return g

