@@ -533,7 +533,7 @@ def run_eval(model, dev, n, peak, dist_on=False):
                                  f"{n} datapoints (loader batch 500 per GPU), batch_size_K=100"},
           "e2e": {"value": n / s_e2e, "unit": "samples/s", "h2d_bytes_per_step": sum(t.numel() * 4 for t in host),
                   "d2h_bytes_per_step": 4 * n},
-          "samples_axis": {"value": n / s_k, "unit": "samples/s", "joint_ll": ll_k,
+          "samples_axis": {"value": n / s_k, "unit": "datapoints/s", "joint_ll": ll_k,
                            "what": "the same pass sharded over the K importance samples (every rank sees all datapoints, "
                                    "K/N samples each), combined with one MAX + one SUM all-reduce per evaluator"},
           "achieved_tflops_algorithmic": n * EVAL_FLOP_PER_DATAPOINT / s / 1e12}

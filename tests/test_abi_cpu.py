@@ -66,3 +66,38 @@ def test_microbatch_split_matches_reference_rule():
     from mmvae_b200.objectives import compute_microbatch_split
     x = [torch.zeros(128, 1, 28, 28), torch.zeros(128, 3, 32, 32)]
     assert compute_microbatch_split(x, 30) == 128 and compute_microbatch_split(x, 2000) == 80
+
+
+@pytest.mark.ref
+def test_reference_checkpoints_load_strict_into_every_model_class(tmp_path):
+    """Build container only (needs /root/reference): a checkpoint SAVED by the unmodified reference model (through
+    oracle/ref_shim.py) loads with strict=True into the matching mmvae_b200 VAE_* class, and round-trips back into the
+    reference (main.py:70, 240-246: `torch.save(model.state_dict())` / `load_state_dict`)."""
+    import argparse
+    import importlib.util
+    import mmvae_b200
+    from oracle import bivae_oracle as O
+    from oracle import synth
+    spec_ = importlib.util.spec_from_file_location("make_golden", os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "make_golden.py"))
+    MG = importlib.util.module_from_spec(spec_)
+    spec_.loader.exec_module(MG)
+    ns = lambda **kw: argparse.Namespace(**{**dict(latent_dim=20, dist="laplace", recon_losses=["normal", "normal"], llik_scaling=0.0,
+                                                    device="cpu", data_path="", epochs=1, beta_kl=1.0, decrease_beta_kl=1.0,
+                                                    fix_jencoder=True, fix_decoders=True, no_recon=True, no_nf=False, flow="maf",
+                                                    dcca=False, dim_dcca=9, num_hidden_layers=1, warmup=0), **kw})
+    cases = [
+        ("VAE_mnist_svhn", O.spec_mnist_svhn(20, "laplace"), MG.ref_mmvae, ns()),
+        ("VAE_mmvae_msf", O.spec_msf(30, "normal"), MG.ref_mmvae, ns(latent_dim=30, dist="normal", recon_losses=["normal"] * 3)),
+        ("VAE_circles_squares", O.spec_circles(2, "normal"), MG.ref_mmvae, ns(latent_dim=2, dist="normal")),
+        ("VAE_mvae_mnist_svhn", O.spec_mnist_svhn(20, "normal"), MG.ref_mvae, ns(dist="normal")),
+    ]
+    for cls, spec, build_ref, params in cases:
+        ref = build_ref(spec, synth.make_state_dict(spec, 3))
+        path = tmp_path / f"{cls}.pt"
+        torch.save(ref.state_dict(), path)
+        ours = getattr(mmvae_b200, cls)(params)
+        missing = ours.load_state_dict(torch.load(path), strict=True)
+        assert not missing.missing_keys and not missing.unexpected_keys, cls
+        for k, v in ref.state_dict().items():
+            assert torch.equal(ours.state_dict()[k].cpu(), v), (cls, k)
+        ref.load_state_dict(ours.state_dict(), strict=True)              # and back
