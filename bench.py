@@ -365,6 +365,53 @@ def profile_step(trainer, x, peak, detail=False):
 
 
 # --------------------------------------------------------------------------------------------------------- main
+def other_config_steps(dev, reps=10):
+    """Training step (forward + backward + AMSGrad, CUDA-graph replay through train.Trainer) of the other BASELINE configs on
+    one GPU: extra keys of the line, not the metric.  C1 circles-squares m_iwae K=10 B=64 (mmvae_circles.py defaults), C3
+    JMVAE-NF MAF + DCCA m_jmvae_nf B=128 (decoders and joint encoder frozen: its second training phase), C5 trimodal
+    m_dreg_looser K=30 B=64."""
+    import mmvae_b200
+    from mmvae_b200 import ops
+    from mmvae_b200.train import Trainer
+    out = {}
+
+    def ns(**kw):
+        base = dict(latent_dim=LATENT, dist="laplace", recon_losses=["normal", "normal"], llik_scaling=0.0, device=str(dev),
+                    data_path="", epochs=1)
+        base.update(kw)
+        return argparse.Namespace(**base)
+    cases = {
+        "C1 circles-squares m_iwae K=10 B=64 L=4": (lambda: mmvae_b200.VAE_circles_squares(ns(latent_dim=4, dist="normal")), "m_iwae", 10,
+                                                [(64, 1, 32, 32), (64, 1, 32, 32)]),
+        "C3 JMVAE-NF MAF+DCCA m_jmvae_nf B=128 (flows phase)": (
+            lambda: mmvae_b200.VAE_jnf_mnist_svhn_dcca(ns(dist="normal", num_hidden_layers=1, beta_kl=1.0, decrease_beta_kl=1.0,
+                                                          fix_jencoder=True, fix_decoders=True, no_recon=True, warmup=0, dcca=True,
+                                                          dim_dcca=9, flow="maf", no_nf=False)), "m_jmvae_nf", 1,
+            [(128, 1, 28, 28), (128, 3, 32, 32)]),
+        "C5 trimodal MNIST-SVHN-Fashion m_dreg_looser K=30 B=64": (
+            lambda: mmvae_b200.VAE_mmvae_msf(ns(latent_dim=30, dist="normal", recon_losses=["normal"] * 3)), "m_dreg_looser", 30,
+            [(64, 1, 28, 28), (64, 3, 32, 32), (64, 1, 28, 28)]),
+    }
+    for name, (build, objective, K, shapes) in cases.items():
+        try:
+            torch.manual_seed(1)
+            model = build().to(dev)
+            tr = Trainer(model, objective, K=K, lr=1e-3, distributed=False)
+            g = torch.Generator().manual_seed(3)
+            x = [torch.rand(*s, generator=g).to(dev) for s in shapes]
+            n0 = ops.N_CALLS
+            tr.step(x)
+            torch.cuda.synchronize()
+            calls = ops.N_CALLS - n0
+            tr.capture(x, warmup=2)
+            ms = timed(lambda i: tr.step_graph(x), reps, False) / reps
+            out[name] = {"ms_per_step": ms, "samples_per_s": shapes[0][0] / (ms * 1e-3), "launches_per_step": calls}
+            del tr, model
+        except Exception as e:                              # informational keys only
+            out[name] = {"error": f"{type(e).__name__}: {e}"[:200]}
+    return out
+
+
 def run_b200(args):
     import torch.distributed as dist
     rank = int(os.environ.get("RANK", "0"))
@@ -458,6 +505,8 @@ def run_b200(args):
         if ev is not None:
             line["eval"] = ev
             line["eval_jmvae_nf"] = ev_jnf
+        if world == 1 and not args.no_eval:
+            line["other_configs"] = other_config_steps(dev)
         if world == 1 and not args.no_cpu_baseline:
             v, cores, cms = cpu_port_step_rate(2, 1)
             line["cpu_baseline"] = {"value": v, "unit": "samples/s", "cores": cores, "kind": "port",
@@ -533,7 +582,7 @@ def run_eval(model, dev, n, peak, dist_on=False):
                                  f"{n} datapoints (loader batch 500 per GPU), batch_size_K=100"},
           "e2e": {"value": n / s_e2e, "unit": "samples/s", "h2d_bytes_per_step": sum(t.numel() * 4 for t in host),
                   "d2h_bytes_per_step": 4 * n},
-          "samples_axis": {"value": n / s_k, "unit": "datapoints/s", "joint_ll": ll_k,
+          "samples_axis": {"value": n / s_k, "unit": "samples/s", "joint_ll": ll_k,
                            "what": "the same pass sharded over the K importance samples (every rank sees all datapoints, "
                                    "K/N samples each), combined with one MAX + one SUM all-reduce per evaluator"},
           "achieved_tflops_algorithmic": n * EVAL_FLOP_PER_DATAPOINT / s / 1e12}

@@ -130,6 +130,10 @@ long mmvae_gemm_workspace_bytes(int M, int N, int K, int a_kmajor, int b_kmajor)
 int mmvae_gemm_tc_set_mode(int mode);
 /* number of tcgen05 GEMM launches (gemm_tc_kernel) this process has made: lets a test assert which kernel a shape ran on */
 long mmvae_gemm_tc_launch_count(void);
+/* contractions of at most this many multiply-adds (M*N*K) run on the one-launch cluster split-K kernel (gemm_small_kernel:
+ * K split over the CTAs of a thread-block cluster, partials reduced through distributed shared memory, exact fp32);
+ * 0 switches it off.  Returns the previous limit.  Tuning / test hook. */
+long mmvae_gemm_small_set_limit(long macs);
 /* column sums: out[n] = sum_m A[m,n]  (bias gradients); workspace >= mmvae_colsum_workspace_bytes(M,N) */
 int  mmvae_colsum(const float* A, float* out, float* workspace, int M, int N, void* stream);
 long mmvae_colsum_workspace_bytes(int M, int N);

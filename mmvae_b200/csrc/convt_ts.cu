@@ -35,6 +35,8 @@
 int mmvae_tc_dbg_bits();
 int mmvae_tc_encode(CUtensorMap* m, int is_bf16, int rank, const void* base, const cuuint64_t* dims, const cuuint64_t* strides,
                     const cuuint32_t* box, const cuuint32_t* estr);
+int mmvae_tc_encode_linear(CUtensorMap* m, int is_bf16, int rank, const void* base, const cuuint64_t* dims,
+                           const cuuint64_t* strides, const cuuint32_t* box, const cuuint32_t* estr);
 
 // ---- window schedule ----------------------------------------------------------------------------------------------------
 // forward: one halo tile per chunk, 9 windows (dy,dx); window s feeds kNcls[s] output-parity classes whose accumulators are
@@ -646,14 +648,16 @@ __host__ __device__ inline void tw_range(int cr, int tiles, int tiles_per_cta, i
     *nparts = (*t1 - *t0 + dr - 1) / dr;
 }
 
-template <int COUT, int CIN>
+// WT: H == W == WT known at compile time (the rows of a k-block's 16 pixels are then immediates off one base), 0 = any geometry
+template <int COUT, int CIN, int WT>
 __global__ void __launch_bounds__(TW_THREADS, 1)
 convt_ts_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__ CUtensorMap tmap_x, const TwArgs ar) {
     using C = TwCfg<COUT, CIN>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* xring = smem + ar.ngs * ar.gstage_bytes;
-    // offtab[v][p]: byte offset (with the swizzle term of its row) of pixel p's row in a class tile, shifted by window v = ey*2+ex
+    // offtab[v][p]: byte offset of pixel p's row in a class tile (linear rows of 128 B: the g tiles are read by threads only,
+    // 32 consecutive channels of one row per warp instruction, so they need no swizzle), shifted by window v = ey*2+ex
     uint32_t* offtab = (uint32_t*)(xring + ar.nxs * 16384);
     uint64_t* bars = (uint64_t*)(offtab + 4 * 128);
     uint64_t* g_full = bars;               // [8]
@@ -676,7 +680,7 @@ convt_ts_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_c
     for (int e = threadIdx.x; e < 4 * 128; e += TW_THREADS) {
         const int v = e >> 7, p = e & 127, n_l = p / HW, rem = p - n_l * HW, i = rem / W, j = rem - i * W;
         const int row = (n_l * (H + 1) + i + (v >> 1)) * (W + 1) + j + (v & 1);
-        offtab[e] = (uint32_t)(row * 128 + ((row & 7) << 4));
+        offtab[e] = (uint32_t)(row * 128);
     }
     if (threadIdx.x == 0) {
         for (int s = 0; s < 8; ++s) {
@@ -771,7 +775,7 @@ convt_ts_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_c
         const int L = quarter * 32 + lane;
         const int tap_l = L / COUT, co = L % COUT, cch = co >> 5, w = co & 31;
         const uint32_t g_ring = smem_u32(smem), x_ring = smem_u32(xring), tab = smem_u32(offtab);
-        const uint32_t xorc = (uint32_t)(w >> 2) << 4, addc = (uint32_t)(w & 3) << 2;
+        const uint32_t addc = (uint32_t)w << 2;
         const uint32_t t_lane = tmem_base + ((uint32_t)(quarter * 32) << 16) + 256;
         float bsum = 0.f;
         int gs = 0, gph = 0;                 // g stage / phase of the current class's first chunk
@@ -820,12 +824,24 @@ convt_ts_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_c
                             const int kb = kb4 * 4 + 2 * a2 + wset;
                             const uint32_t tb = tab + (uint32_t)(v * 128 + kb * 16) * 4;
                             if (!(ar.dbg & 2)) {
-                                uint32_t off[16];
+                                if (WT) {
+                                    uint32_t b0;
+                                    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(b0) : "r"(tb));
+                                    b0 += gbase;
 #pragma unroll
-                                for (int k = 0; k < 16; ++k) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(off[k]) : "r"(tb + k * 4));
+                                    for (int k = 0; k < 16; ++k)
+                                        asm volatile("ld.shared.f32 %0, [%1];" : "=f"(f[a2][k])
+                                                     : "r"(b0 + (uint32_t)(((k / (WT ? WT : 1)) * (WT + 1) + (k % (WT ? WT : 1))) * 128)));
+                                } else {
+                                    uint32_t off[16];
 #pragma unroll
-                                for (int k = 0; k < 16; ++k)
-                                    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(f[a2][k]) : "r"(gbase + (off[k] ^ xorc)));
+                                    for (int k = 0; k < 16; k += 4)
+                                        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                                                     : "=r"(off[k]), "=r"(off[k + 1]), "=r"(off[k + 2]), "=r"(off[k + 3]) : "r"(tb + k * 4));
+#pragma unroll
+                                    for (int k = 0; k < 16; ++k)
+                                        asm volatile("ld.shared.f32 %0, [%1];" : "=f"(f[a2][k]) : "r"(gbase + off[k]));
+                                }
                             } else {
 #pragma unroll
                                 for (int k = 0; k < 16; ++k) f[a2][k] = 0.f;
@@ -1003,8 +1019,10 @@ template <int COUT, int CIN>
 static int tw_launch(const float* x, const float* g, float* gw, float* gb, float* ws, long ws_bytes, int Nimg, int H, int W,
                      cudaStream_t st) {
     using C = TwCfg<COUT, CIN>;
-    static bool attr_done = false;
-    auto kern = convt_ts_wgrad_kernel<COUT, CIN>;
+    static bool attr_done[2] = {false, false};
+    constexpr int WF = (COUT == 32 && CIN == 64) ? 8 : ((COUT == 64 && CIN == 128) ? 4 : 0);      // the layers of the SVHN decoder
+    const int fast = WF && H == WF && W == WF;
+    auto kern = fast ? convt_ts_wgrad_kernel<COUT, CIN, WF> : convt_ts_wgrad_kernel<COUT, CIN, 0>;
     const int IMGS = 128 / (H * W);
     TwArgs ar{};
     ar.M = Nimg * H * W; ar.H = H; ar.W = W; ar.tiles = (ar.M + 127) / 128;
@@ -1021,17 +1039,17 @@ static int tw_launch(const float* x, const float* g, float* gw, float* gb, float
     cuuint64_t dims[4] = {(cuuint64_t)COUT, (cuuint64_t)(2 * W), (cuuint64_t)(2 * H), (cuuint64_t)Nimg};
     cuuint64_t strides[3] = {(cuuint64_t)COUT * 4, (cuuint64_t)2 * W * COUT * 4, (cuuint64_t)4 * H * W * COUT * 4};
     cuuint32_t box[4] = {32u, (cuuint32_t)(2 * (W + 1)), (cuuint32_t)(2 * (H + 1)), (cuuint32_t)IMGS}, estr[4] = {1u, 2u, 2u, 1u};
-    int rc = mmvae_tc_encode(&tg, 0, 4, g, dims, strides, box, estr);
+    int rc = mmvae_tc_encode_linear(&tg, 0, 4, g, dims, strides, box, estr);
     if (rc) return mmvae_set_error(1, "convt_ts_wgrad: tensor map (g) failed with %d", rc);
     cuuint64_t xd[2] = {(cuuint64_t)CIN, (cuuint64_t)ar.M};
     cuuint64_t xs[1] = {(cuuint64_t)CIN * 4};
     cuuint32_t xb[2] = {32u, 128u}, xe[2] = {1u, 1u};
     rc = mmvae_tc_encode(&tx, 0, 2, x, xd, xs, xb, xe);
     if (rc) return mmvae_set_error(1, "convt_ts_wgrad: tensor map (x) failed with %d", rc);
-    if (!attr_done) {
+    if (!attr_done[fast]) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM_MAX);
         if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "convt_ts_wgrad: smem attribute: %s", cudaGetErrorString(e));
-        attr_done = true;
+        attr_done[fast] = true;
     }
     kern<<<grid, TW_THREADS, smem, st>>>(tg, tx, ar);
     MMVAE_LAUNCH_CHECK("convt_ts_wgrad");

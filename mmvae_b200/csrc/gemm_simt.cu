@@ -298,3 +298,243 @@ int mmvae_gemm_skinny(const float* A, const float* B, const float* bias, float* 
     MMVAE_LAUNCH_CHECK("gemm_skinny");
     return 0;
 }
+
+// ---- small GEMMs: one launch, split-K inside a thread-block cluster ---------------------------------------------------------
+// The encoders at batch 128, every MADE layer and every weight gradient of a 128-row layer are contractions of 10^6..10^8 MACs:
+// latency-bound, 8-14 us each through the kernels above (a K loop on a few CTAs, or a split-K pass plus its reduce launch).
+// Here the K range of one 64x64 output tile is split over the S <= 16 CTAs of a cluster (grid z = cluster z = S); each CTA
+// leaves its partial tile in its own shared memory, and after one cluster barrier CTA r sums rows [r*64/S, (r+1)*64/S) of the S
+// partials through distributed shared memory in rank order (deterministic), applies bias + activation and stores.  No
+// workspace, no counters, no second launch.  Exact fp32 FMA arithmetic.
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
+
+#define GS_BM 64
+#define GS_BN 64
+#define GS_BKG 128                     // k per shared-memory group: everything a CTA needs for 8 k-tiles is in flight at once
+#define GS_LD (GS_BM + G_PAD)          // row stride of an operand group s[k][row]
+#define GS_SMEM (2 * GS_BKG * GS_LD * (int)sizeof(float))
+
+// One 64 x GS_BKG operand group in registers (8 float4 per thread), zero-filled outside [0,rows_total) x [k0,k_end).
+// KMAJOR (src[row*ld + k]): a warp takes 8 rows x 64 contiguous bytes (whole sectors); the transposing store is 2-way conflicted.
+template <bool KMAJOR>
+struct GroupLoader {
+    static constexpr int NV = GS_BM * GS_BKG / 4 / G_THREADS;
+    float4 v[NV];
+    __device__ __forceinline__ void load(const float* __restrict__ src, int ld, int row0, int rows_total, int k0, int k_end, bool vec_ok) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int f = threadIdx.x + i * G_THREADS;
+            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (KMAJOR) {
+                const int row = (f / 4) % GS_BM, kq = ((f / (4 * GS_BM)) * 4 + (f % 4)) * 4;
+                const int gr = row0 + row, gk = k0 + kq;
+                if (gr < rows_total && gk < k_end) {
+                    const float* p = src + (long)gr * ld + gk;
+                    if (vec_ok && gk + 3 < k_end) t = __ldg(reinterpret_cast<const float4*>(p));
+                    else {
+                        t.x = p[0];
+                        if (gk + 1 < k_end) t.y = p[1];
+                        if (gk + 2 < k_end) t.z = p[2];
+                        if (gk + 3 < k_end) t.w = p[3];
+                    }
+                }
+            } else {
+                const int k = f / (GS_BM / 4), rq = (f % (GS_BM / 4)) * 4;
+                const int gk = k0 + k, gr = row0 + rq;
+                if (gk < k_end && gr < rows_total) {
+                    const float* p = src + (long)gk * ld + gr;
+                    if (vec_ok && gr + 3 < rows_total) t = __ldg(reinterpret_cast<const float4*>(p));
+                    else {
+                        t.x = p[0];
+                        if (gr + 1 < rows_total) t.y = p[1];
+                        if (gr + 2 < rows_total) t.z = p[2];
+                        if (gr + 3 < rows_total) t.w = p[3];
+                    }
+                }
+            }
+            v[i] = t;
+        }
+    }
+    __device__ __forceinline__ void store(float* __restrict__ s) const {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int f = threadIdx.x + i * G_THREADS;
+            if (KMAJOR) {
+                const int row = (f / 4) % GS_BM, kq = ((f / (4 * GS_BM)) * 4 + (f % 4)) * 4;
+                s[(kq + 0) * GS_LD + row] = v[i].x;
+                s[(kq + 1) * GS_LD + row] = v[i].y;
+                s[(kq + 2) * GS_LD + row] = v[i].z;
+                s[(kq + 3) * GS_LD + row] = v[i].w;
+            } else {
+                const int k = f / (GS_BM / 4), rq = (f % (GS_BM / 4)) * 4;
+                *reinterpret_cast<float4*>(&s[k * GS_LD + rq]) = v[i];
+            }
+        }
+    }
+};
+
+// grid (N tiles, M tiles, S), cluster (1, 1, S).  CTA z contracts k in [z*k_per, (z+1)*k_per) (k_per a multiple of 16).
+template <bool A_KMAJOR, bool B_KMAJOR>
+__global__ void __launch_bounds__(G_THREADS, 2)
+gemm_small_kernel(const float* __restrict__ A, const float* __restrict__ Bm, const float* __restrict__ bias, float* __restrict__ C,
+                  int M, int N, int K, int act, int k_per) {
+    extern __shared__ __align__(16) float sm[];                           // As[128][68] | Bs[128][68]; later red[64][64]
+    float* As = sm;
+    float* Bs = sm + GS_BKG * GS_LD;
+    const int m0 = blockIdx.y * GS_BM, n0 = blockIdx.x * GS_BN;
+    const int k_begin = min(K, (int)blockIdx.z * k_per), k_end = min(K, k_begin + k_per);
+    const int lda = A_KMAJOR ? K : M, ldb = B_KMAJOR ? K : N;
+    const bool a_vec = (((uintptr_t)A & 15) == 0) && (lda % 4 == 0);
+    const bool b_vec = (((uintptr_t)Bm & 15) == 0) && (ldb % 4 == 0);
+    const int ty = threadIdx.x / 16, tx = threadIdx.x % 16;
+
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+    GroupLoader<A_KMAJOR> la;
+    GroupLoader<B_KMAJOR> lb;
+    if (k_begin < k_end) {
+        la.load(A, lda, m0, M, k_begin, k_end, a_vec);
+        lb.load(Bm, ldb, n0, N, k_begin, k_end, b_vec);
+        la.store(As);
+        lb.store(Bs);
+    }
+    __syncthreads();
+    for (int k0 = k_begin; k0 < k_end; k0 += GS_BKG) {
+        const bool more = (k0 + GS_BKG < k_end);
+        if (more) {                                                      // the next group's loads fly under this group's FMAs
+            la.load(A, lda, m0, M, k0 + GS_BKG, k_end, a_vec);
+            lb.load(Bm, ldb, n0, N, k0 + GS_BKG, k_end, b_vec);
+        }
+        const int kn = min(GS_BKG, (k_end - k0 + 15) & ~15);
+        const float* as = As + ty * 4;
+        const float* bs = Bs + tx * 4;
+#pragma unroll 1
+        for (int kb = 0; kb < kn; kb += 16) {
+#pragma unroll
+            for (int kk = 0; kk < 16; ++kk) {
+                const float4 a = *reinterpret_cast<const float4*>(as + (kb + kk) * GS_LD);
+                const float4 b = *reinterpret_cast<const float4*>(bs + (kb + kk) * GS_LD);
+                const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+            }
+        }
+        __syncthreads();
+        if (more) {
+            la.store(As);
+            lb.store(Bs);
+            __syncthreads();
+        }
+    }
+
+    const int S = gridDim.z;
+    const bool c_vec = (((uintptr_t)C & 15) == 0) && (N % 4 == 0);
+    if (S == 1) {
+        const int gn = n0 + tx * 4;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int gm = m0 + ty * 4 + i;
+            if (gm >= M) continue;
+            float r[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) r[j] = (gn + j < N) ? apply_act(acc[i][j] + (bias ? bias[gn + j] : 0.f), act) : 0.f;
+            float* p = C + (long)gm * N + gn;
+            if (c_vec && gn + 3 < N) *reinterpret_cast<float4*>(p) = make_float4(r[0], r[1], r[2], r[3]);
+            else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (gn + j < N) p[j] = r[j];
+            }
+        }
+        return;
+    }
+    // the loop's trailing __syncthreads() has retired every read of the operand groups: reuse them for the partial tile
+    cg::cluster_group cluster = cg::this_cluster();
+    float4* red = reinterpret_cast<float4*>(sm);                         // [64 rows][16 float4]
+#pragma unroll
+    for (int i = 0; i < 4; ++i) red[(ty * 4 + i) * 16 + tx] = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+    cluster.sync();
+    const int rank = (int)cluster.block_rank(), rows_per = GS_BM / S;
+    for (int e = threadIdx.x; e < rows_per * 16; e += G_THREADS) {
+        const int row = rank * rows_per + e / 16, c4 = e % 16;
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int z = 0; z < S; ++z) {
+            const float4 v = cluster.map_shared_rank(red, z)[row * 16 + c4];
+            s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
+        const int gm = m0 + row, gn = n0 + c4 * 4;
+        if (gm < M && gn < N) {
+            float r[4] = {s.x, s.y, s.z, s.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) r[j] = (gn + j < N) ? apply_act(r[j] + (bias ? bias[gn + j] : 0.f), act) : 0.f;
+            float* p = C + (long)gm * N + gn;
+            if (c_vec && gn + 3 < N) *reinterpret_cast<float4*>(p) = make_float4(r[0], r[1], r[2], r[3]);
+            else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (gn + j < N) p[j] = r[j];
+            }
+        }
+    }
+    cluster.sync();                                                       // nobody leaves while a peer may still read its partial
+}
+
+static int g_small_max_split = 16;
+static long g_small_max_macs = 64L << 20;                                 // above this the tensor-core / tiled kernels win (measured)
+extern "C" long mmvae_gemm_small_set_limit(long macs) { const long o = g_small_max_macs; g_small_max_macs = macs; return o; }
+extern "C" int mmvae_gemm_small_set_max_split(int s) { const int o = g_small_max_split; g_small_max_split = s; return o; }
+
+// S: power of two <= 16, enough CTAs to fill the machine twice, at least two k-tiles per CTA
+static int small_splits(long tiles, int nk) {
+    const int cap = tiles <= 4 ? g_small_max_split : (g_small_max_split < 8 ? g_small_max_split : 8);   // 16-CTA clusters pay only for 1-4 tiles (measured)
+    int S = 1;
+    while (S < cap && tiles * S < 2L * MMVAE_NUM_SMS && nk / (2 * S) >= 2) S *= 2;
+    return S;
+}
+
+template <bool AK, bool BK>
+static int small_launch(const float* A, const float* B, const float* bias, float* C, int M, int N, int K, int act, dim3 grid, int k_per,
+                        cudaStream_t st) {
+    static bool attr_done = false;
+    auto kern = gemm_small_kernel<AK, BK>;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GS_SMEM);
+        if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "gemm_small: kernel attributes: %s", cudaGetErrorString(e));
+        attr_done = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = dim3(G_THREADS); cfg.dynamicSmemBytes = GS_SMEM; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 1; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = grid.z;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, A, B, bias, C, M, N, K, act, k_per);
+    if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "gemm_small: launch: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+// returns -1 when the shape is not for this kernel
+int mmvae_gemm_small(const float* A, const float* B, const float* bias, float* C, int M, int N, int K, int a_kmajor, int b_kmajor,
+                     int act, cudaStream_t st) {
+    if ((long)M * N * K > g_small_max_macs) return -1;
+    const long tm = (M + GS_BM - 1) / GS_BM, tn = (N + GS_BN - 1) / GS_BN;
+    if (tm * tn > MMVAE_NUM_SMS && g_small_max_macs < (1L << 40)) return -1;    // enough tiles to fill the machine: the tiled kernels
+    if (tm > 65535 || tn > 65535) return -1;
+    const int nk = (K + G_BK - 1) / G_BK;
+    const int S = small_splits(tm * tn, nk);
+    const int tps = ((nk + S - 1) / S) * G_BK;                             // k per CTA
+    if (tps > 4 * GS_BKG && g_small_max_macs < (1L << 40)) return -1;      // a long serial K loop on a few CTAs: the split-K kernels
+    const dim3 grid((unsigned)tn, (unsigned)tm, (unsigned)S);
+    if (a_kmajor && b_kmajor) return small_launch<true, true>(A, B, bias, C, M, N, K, act, grid, tps, st);
+    if (a_kmajor && !b_kmajor) return small_launch<true, false>(A, B, bias, C, M, N, K, act, grid, tps, st);
+    if (!a_kmajor && b_kmajor) return small_launch<false, true>(A, B, bias, C, M, N, K, act, grid, tps, st);
+    return small_launch<false, false>(A, B, bias, C, M, N, K, act, grid, tps, st);
+}

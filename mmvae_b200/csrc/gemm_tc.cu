@@ -503,19 +503,28 @@ int mmvae_tc_tmap_rows(CUtensorMap* m, const float* base, long rows, long cols, 
 int mmvae_tc_dbg_bits() { return g_tc_dbg; }
 // used by convt_ts.cu: any tiled map with 128-byte swizzle.  dims/box/estr: `rank` entries, innermost first; strides:
 // rank-1 byte pitches.  is_bf16: element type (else fp32).  -1 = no tcgen05/TMA on this device, else the CUresult.
-int mmvae_tc_encode(CUtensorMap* m, int is_bf16, int rank, const void* base, const cuuint64_t* dims, const cuuint64_t* strides,
-                    const cuuint32_t* box, const cuuint32_t* estr) {
+static int tc_encode_impl(CUtensorMap* m, int is_bf16, int rank, const void* base, const cuuint64_t* dims, const cuuint64_t* strides,
+                          const cuuint32_t* box, const cuuint32_t* estr, CUtensorMapSwizzle swz) {
     if (!tc_init()) return -1;
     CUresult r = CUDA_SUCCESS;
     for (int attempt = 0; attempt < 2; ++attempt) {
         r = g_encode(m, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, rank, (void*)base,
-                     dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                     dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
                      CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         // a thread whose first CUDA call is this driver entry point (an autograd worker) has no context bound yet
         if (r != CUDA_ERROR_INVALID_CONTEXT) break;
         (void)cudaFree(nullptr);
     }
     return (int)r;
+}
+int mmvae_tc_encode(CUtensorMap* m, int is_bf16, int rank, const void* base, const cuuint64_t* dims, const cuuint64_t* strides,
+                    const cuuint32_t* box, const cuuint32_t* estr) {
+    return tc_encode_impl(m, is_bf16, rank, base, dims, strides, box, estr, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+// same, rows of the box laid out linearly in shared memory (no swizzle): tiles that only threads read, channel-contiguous
+int mmvae_tc_encode_linear(CUtensorMap* m, int is_bf16, int rank, const void* base, const cuuint64_t* dims,
+                           const cuuint64_t* strides, const cuuint32_t* box, const cuuint32_t* estr) {
+    return tc_encode_impl(m, is_bf16, rank, base, dims, strides, box, estr, CU_TENSOR_MAP_SWIZZLE_NONE);
 }
 // MN-major operand [krows, ncols] (ncols contiguous), box = 32 columns x box_rows k-rows, SWIZZLE_128B_ATOM_32B
 int mmvae_tc_tmap_mn(CUtensorMap* m, const float* base, long krows, long ncols, int box_rows) {

@@ -23,6 +23,8 @@ int mmvae_gemm_tc(const float* A, const float* B, const float* bias, float* C, i
                   int b_kmajor, int act, float* workspace, long workspace_bytes, cudaStream_t st);
 int mmvae_gemm_skinny(const float* A, const float* B, const float* bias, float* C, int M, int N, int K, int a_kmajor, int b_kmajor,
                       int act, cudaStream_t st);
+int mmvae_gemm_small(const float* A, const float* B, const float* bias, float* C, int M, int N, int K, int a_kmajor, int b_kmajor,
+                     int act, cudaStream_t st);
 long mmvae_gemm_simt_workspace_bytes(int M, int N, int K);
 long mmvae_gemm_tc_workspace_bytes(int M, int N, int K, int a_k, int b_k);
 
@@ -40,6 +42,10 @@ extern "C" int mmvae_gemm(const float* A, const float* B, const float* bias, flo
     cudaStream_t st = (cudaStream_t)stream;
     {
         const int rc = mmvae_gemm_skinny(A, B, bias, C, M, N, K, a_kmajor, b_kmajor, act, st);     // K = latent dimension
+        if (rc != -1) return rc;
+    }
+    {
+        const int rc = mmvae_gemm_small(A, B, bias, C, M, N, K, a_kmajor, b_kmajor, act, st);      // latency-bound sizes
         if (rc != -1) return rc;
     }
     if (allow_tc) {

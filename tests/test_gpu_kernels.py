@@ -42,6 +42,36 @@ def test_gemm_layouts(ops, M, N, K, a_k, b_k):
     assert rel_err(out, torch.sigmoid(ref + bias.double())) < tol
 
 
+@pytest.mark.parametrize("M,N,K", [(128, 512, 784), (128, 20, 2048), (20, 512, 128), (77, 53, 131), (1, 1, 1), (64, 64, 16),
+                                   (65, 129, 33), (2048, 128, 1024), (128, 128, 128), (40, 128, 128), (3, 1000, 515)])
+@pytest.mark.parametrize("a_k,b_k", [(1, 1), (1, 0), (0, 1), (0, 0)])
+def test_gemm_small_cluster_split_k(ops, M, N, K, a_k, b_k):
+    """The one-launch cluster split-K kernel (gemm_small_kernel: K split over the CTAs of a thread-block cluster, partials
+    reduced through distributed shared memory): every split factor 1..16, ragged M / N / K, unaligned leading dimensions, all
+    four operand layouts, bias + activation; exact fp32 FMA against fp64; bit-identical on a second call (fixed reduction
+    order); and the same shapes with the kernel switched off (limit 0) agree to rounding."""
+    from mmvae_b200 import _lib
+    lib = _lib.load()
+    A, B, bias = _rand(M, K, seed=1, scale=K ** -0.5), _rand(N, K, seed=2), _rand(N, seed=3)
+    a_s = A.contiguous() if a_k else A.t().contiguous()
+    b_s = B.contiguous() if b_k else B.t().contiguous()
+    ref = A.double() @ B.double().t()
+    for act, fn in ((None, None), ("relu", torch.relu), ("sigmoid", torch.sigmoid)):
+        n0 = lib.mmvae_gemm_tc_launch_count()
+        out = ops.gemm(a_s, b_s, bias if act else None, M, N, K, a_k, b_k, act)
+        want = fn(ref + bias.double()) if act else ref
+        assert (out.double() - want).abs().max().item() <= 2e-6 * max(1.0, want.abs().max().item())
+        again = ops.gemm(a_s, b_s, bias if act else None, M, N, K, a_k, b_k, act)
+        assert torch.equal(out, again)
+        assert lib.mmvae_gemm_tc_launch_count() == n0                     # neither call went to the tensor-core kernel
+        old = lib.mmvae_gemm_small_set_limit(0)
+        try:
+            other = ops.gemm(a_s, b_s, bias if act else None, M, N, K, a_k, b_k, act)
+        finally:
+            lib.mmvae_gemm_small_set_limit(old)
+        assert (out - other).abs().max().item() <= 4e-6 * max(1.0, want.abs().max().item())
+
+
 @pytest.mark.parametrize("M,N,K", [(7680, 784, 512), (7680, 512, 784), (512, 784, 7680), (7680, 512, 512)])
 @pytest.mark.parametrize("a_k,b_k", [(1, 1), (1, 0), (0, 1), (0, 0)])
 def test_gemm_tensor_core_path_with_epilogue(ops, M, N, K, a_k, b_k):
