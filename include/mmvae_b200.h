@@ -226,6 +226,21 @@ int  mmvae_convt_ts_wgrad(const float* x, const float* g, float* gw, float* gb, 
 /* MADE / MAF / IAF elementwise pieces (maf_model.py:62-74,91-104; iaf_model.py:60-78,94-100).  The masked-linear
  * contractions go through mmvae_gemm with the pre-masked weight (layers.py:24-25: F.linear(x, mask*W, b)). */
 int mmvae_mask_weight(const float* w, const float* mask, float* out, long n, void* stream);
+/* One MADE (made_model.py:21-111: masked Linear layers layers.py:14-25 with ReLU between them) on R rows as three kernels
+ * instead of ~27 launches per training step -- the parallel direction of a flow block (MAF.forward maf_model.py:62-74,
+ * IAF.inverse iaf_model.py:94-100) and its autograd backward.  dims: host array of n_layers+1 widths (input, hidden..., output;
+ * multiples of 4, at most 128, equal hidden widths, 2 <= n_layers <= 5); ptrs: host array of 3*n_layers device pointers
+ * {W_l [out,in], mask_l [out,in], bias_l [out] or NULL}; the masked weight mask*W is formed inside the kernels.
+ * fwd: x [R,dims[0]] -> y [R,dims[n_layers]], h [n_layers-1][R][dims[1]] = the hidden activations (kept for backward).
+ * bwd_data: gy -> gx (or NULL) and gpre [n_layers-1][R][dims[1]], the gradients w.r.t. the hidden pre-activations.
+ * bwd_weights: grads = host array of 2*n_layers device pointers {gW_l, gb_l} (NULL = skip), each OVERWRITTEN with
+ * mask_l * (gpre_l^T input_l) and the column sums of gpre_l (gpre of the last layer is gy); fixed summation order. */
+int mmvae_made_supported(int n_layers, const int* dims);
+int mmvae_made_fwd(const float* x, const void* ptrs, const int* dims, int n_layers, float* h, float* y, int R, void* stream);
+int mmvae_made_bwd_data(const float* gy, const void* ptrs, const int* dims, int n_layers, const float* h, float* gpre,
+                        float* gx, int R, void* stream);
+int mmvae_made_bwd_weights(const float* x, const float* gy, const void* ptrs, const void* grads, const int* dims,
+                           int n_layers, const float* h, const float* gpre, int R, void* stream);
 /* The sequential direction of one MADE flow block (MAF.inverse maf_model.py:91-104; IAF.forward iaf_model.py:60-78; MADE
  * made_model.py:21-111) as ONE kernel: replaces L MADE passes (4 masked GEMMs each) + L affine steps.  Every hidden unit
  * is evaluated once, when the last column it depends on is produced.  y [R,L] block input (read at column L-1-i when

@@ -65,8 +65,10 @@ class MADE(nn.Module):
 
     def raw(self, x, mw=None):
         """-> h [R, 2L] = (mu | log_var)."""
-        mw = self.masked_weights() if mw is None else mw
         lay = self.layers()
+        if mw is None and x.is_cuda and ops.made_fused_ok([(l.weight, l.mask, l.bias) for l in lay], x.shape[0]):
+            return ops.MadeFused.apply(x, *[t for l in lay for t in (l.weight, l.mask, l.bias)])
+        mw = self.masked_weights() if mw is None else mw
         h = x
         for i, (l, w) in enumerate(zip(lay, mw)):
             h = ops.LinearAct.apply(h, w, l.bias, "relu" if i < len(lay) - 1 else None)

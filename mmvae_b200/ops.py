@@ -739,6 +739,80 @@ class MaskWeight(torch.autograd.Function):
         return mask_weight(_c(g, "grad"), mask), None
 
 
+MADE_FUSED = True         # tests switch it off to compare with the per-layer formulation
+MADE_FUSED_MAX_ROWS = 1024   # above this the per-layer GEMMs (tensor cores) win
+
+
+def _made_arrays(layers):
+    """-> (dims int array, [W, mask, b]*n pointer array) for mmvae_made_*: `layers` = [(W, mask, bias or None), ...]."""
+    dims = [layers[0][0].shape[1]] + [w.shape[0] for w, _, _ in layers]
+    ptrs = []
+    for w, m, b in layers:
+        ptrs += [w.data_ptr(), m.data_ptr(), b.data_ptr() if b is not None else None]
+    return (ctypes.c_int * len(dims))(*dims), (ctypes.c_void_p * len(ptrs))(*ptrs), dims
+
+
+def made_fused_ok(layers, rows):
+    if not MADE_FUSED or rows > MADE_FUSED_MAX_ROWS or any(b is None for _, _, b in layers):
+        return False
+    dims = [layers[0][0].shape[1]] + [w.shape[0] for w, _, _ in layers]
+    return _lib.load().mmvae_made_supported(len(layers), (ctypes.c_int * len(dims))(*dims)) == 1
+
+
+class MadeFused(torch.autograd.Function):
+    """h = MADE(x) with every masked layer in one kernel (csrc/made_train.cu); args: x, then (W, mask, bias) per layer."""
+
+    @staticmethod
+    def forward(ctx, x, *params):
+        n = len(params) // 3
+        x = _c(x, "x")
+        layers = [(_c(params[3 * l], "weight"), _c(params[3 * l + 1], "mask"), _c(params[3 * l + 2], "bias")) for l in range(n)]
+        dims_c, ptrs_c, dims = _made_arrays(layers)
+        R, H = x.shape[0], dims[1]
+        h = torch.empty((n - 1, R, H), device=x.device, dtype=torch.float32)
+        y = torch.empty((R, dims[-1]), device=x.device, dtype=torch.float32)
+        _call("mmvae_made_fwd", _p(x), ptrs_c, dims_c, n, _p(h), _p(y), R, _stream(),
+              work=("flop", 2.0 * R * sum(a * b for a, b in zip(dims[:-1], dims[1:]))))
+        if RELU_TAP is not None:
+            for l in range(n - 1):
+                RELU_TAP.setdefault(layers[l][2].data_ptr(), []).append(h[l].detach() > 0)
+        ctx.save_for_backward(x, h, *[t for lay in layers for t in lay])
+        ctx.leaves = params
+        ctx.n = n
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, h = ctx.saved_tensors[:2]
+        flat = ctx.saved_tensors[2:]
+        n = ctx.n
+        layers = [(flat[3 * l], flat[3 * l + 1], flat[3 * l + 2]) for l in range(n)]
+        dims_c, ptrs_c, dims = _made_arrays(layers)
+        R = x.shape[0]
+        gy = _c(gy, "grad")
+        gpre = torch.empty_like(h)
+        gx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+        _call("mmvae_made_bwd_data", _p(gy), ptrs_c, dims_c, n, _p(h), _p(gpre), _p(gx), R, _stream(),
+              work=("flop", 2.0 * R * sum(a * b for a, b in zip(dims[:-1], dims[1:]))))
+        out, dst, sunk_all, any_need = [gx], [], True, False
+        for l in range(n):
+            need_w, need_b = ctx.needs_input_grad[1 + 3 * l], ctx.needs_input_grad[3 + 3 * l]
+            dw = _sink(ctx.leaves[3 * l]) if need_w else None
+            db = _sink(ctx.leaves[3 * l + 2]) if need_b else None
+            gw = dw if dw is not None else (torch.empty_like(layers[l][0]) if need_w else None)
+            gb = db if db is not None else (torch.empty_like(layers[l][2]) if need_b else None)
+            sunk_all = sunk_all and (dw is not None or not need_w) and (db is not None or not need_b)
+            any_need = any_need or need_w or need_b
+            dst += [gw, gb]
+            out += [None if dw is not None else gw, None, None if db is not None else gb]
+        if any_need:
+            grads_c = (ctypes.c_void_p * len(dst))(*[t.data_ptr() if t is not None else None for t in dst])
+            with _wgrad_side(sunk_all, gy, gpre, h, x):
+                _call("mmvae_made_bwd_weights", _p(x), _p(gy), ptrs_c, grads_c, dims_c, n, _p(h), _p(gpre), R, _stream(),
+                      work=("flop", 2.0 * R * sum(a * b for a, b in zip(dims[:-1], dims[1:]))))
+        return tuple(out)
+
+
 class FlowAffine(torch.autograd.Function):
     """Affine coupling + log|det J| update (mmvae_flow_affine_fwd).  -> (out [R,L], ladj_out [R])."""
 

@@ -518,3 +518,59 @@ def test_fused_sequential_made_rejects_unsupported_shapes(ops):
     m = flows.MADE(20, [128] * 3)
     m.net[0].mask.zero_()
     assert not ops.made_seq_plan(m).ok                                  # masks that are not the sequential ones
+
+
+@pytest.mark.parametrize("R", [1, 16, 17, 128, 300, 1024])
+@pytest.mark.parametrize("L,H,n_hidden", [(20, 128, 3), (8, 64, 1), (12, 32, 2)])
+def test_made_fused_training_kernels(ops, R, L, H, n_hidden):
+    """csrc/made_train.cu (one forward kernel, one data-gradient kernel, one weight-gradient kernel per MADE) against the
+    per-layer formulation of the same module (mask, GEMM, activation backward, column sums) and against fp64 torch: output,
+    gradient w.r.t. the input and every masked weight / bias gradient; ragged row counts; bit-identical on a second pass."""
+    from mmvae_b200 import flows
+    torch.manual_seed(R + L)
+    made = flows.MADE(L, [H] * n_hidden).cuda()
+    if R == 17:                                                   # parameters as views at odd offsets of one flat buffer (train.Trainer)
+        ps = list(made.parameters())
+        flat = torch.empty(sum(p.numel() + 1 for p in ps) + 1, device="cuda")
+        off = 1
+        for p in ps:
+            flat[off:off + p.numel()].copy_(p.data.reshape(-1))
+            p.data = flat[off:off + p.numel()].view_as(p)
+            off += p.numel() + 1
+    x = _rand(R, L, seed=5).requires_grad_()
+    gy = _rand(R, 2 * L, seed=6)
+    params = [p for p in made.parameters()]
+
+    def run(fused):
+        ops.MADE_FUSED = fused
+        try:
+            y = made.raw(x)
+            grads = torch.autograd.grad(y, [x] + params, gy)
+        finally:
+            ops.MADE_FUSED = True
+        return y.detach(), grads
+    n0 = ops.N_CALLS
+    y1, g1 = run(True)
+    assert ops.N_CALLS - n0 == 3                                   # forward, data gradient, weight gradients
+    y2, g2 = run(False)
+    y3, g3 = run(True)
+    assert torch.equal(y1, y3) and all(torch.equal(a, b) for a, b in zip(g1, g3))
+    # fp64 reference of the module
+    h = x.detach().double()
+    h.requires_grad_()
+    lay = made.layers()
+    ws = [l.weight.detach().double().requires_grad_() for l in lay]
+    bs = [l.bias.detach().double().requires_grad_() for l in lay]
+    z = h
+    for i, l in enumerate(lay):
+        z = torch.nn.functional.linear(z, ws[i] * l.mask.double(), bs[i])
+        if i < len(lay) - 1:
+            z = z.relu()
+    ref = torch.autograd.grad(z, [h] + [t for wb in zip(ws, bs) for t in wb], gy.double())
+    assert rel_err(y1, z) < 2e-6 and rel_err(y2, z) < 2e-6
+    for a, b, r in zip(g1, g2, ref):
+        if r.abs().max().item() == 0.0:
+            assert a.abs().max().item() == 0.0
+            continue
+        assert rel_err(a, r) < 5e-6, (a.shape, rel_err(a, r))
+        assert rel_err(b, r) < 5e-6

@@ -56,7 +56,7 @@ for fixed in (True, False):
             a[1] += 1
         tot = sum(a[0] for a in agg.values())
         print(f"  kernel time {tot:.3f} ms over {len(rec)} calls")
-        for k, a in sorted(agg.items(), key=lambda kv: -kv[1][0])[:12]:
+        for k, a in sorted(agg.items(), key=lambda kv: -kv[1][0])[:30]:
             print(f"  {k:30s} {a[0] * 1e3:8.1f} us {a[1]:4d} calls")
     eager = timed(lambda: tr.step(x), 30)
     tr.capture(x)
