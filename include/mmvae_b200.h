@@ -130,6 +130,10 @@ long mmvae_gemm_workspace_bytes(int M, int N, int K, int a_kmajor, int b_kmajor)
 int mmvae_gemm_tc_set_mode(int mode);
 /* number of tcgen05 GEMM launches (gemm_tc_kernel) this process has made: lets a test assert which kernel a shape ran on */
 long mmvae_gemm_tc_launch_count(void);
+/* which kernel the most recent mmvae_gemm call of this process ran on: 0 gemm_simt_kernel (tiled SIMT, exact fp32),
+ * 1 gemm_tc_kernel (tcgen05), 2 gemm_skinny_kernel (K <= 32), 3 gemm_small_kernel (cluster split-K); -1 before the first call.
+ * Accounting hook of bench.py / the tests. */
+int mmvae_gemm_last_kernel(void);
 /* contractions of at most this many multiply-adds (M*N*K) run on the one-launch cluster split-K kernel (gemm_small_kernel:
  * K split over the CTAs of a thread-block cluster, partials reduced through distributed shared memory, exact fp32);
  * 0 switches it off.  Returns the previous limit.  Tuning / test hook. */

@@ -61,6 +61,7 @@ struct TsArgs {
     int nstg;         // halo tiles in flight
     int nbs;          // weight-block slots (streaming) / 16*chunks (resident)
     int resident;
+    unsigned long long* trace;   // tools/ts_trace.py: per-role clock accounting of CTA 0 (TRACE instantiation only), else NULL
     int dbg;          // ablation bits (tools/ts_time.py), 0 in production: 1 no global stores, 2 no window copies, 4 no split,
                       // 8 no MMAs, 16 no activation loads
 };
@@ -108,10 +109,16 @@ __device__ __forceinline__ void tmem_st_32x8(uint32_t taddr, const uint32_t* r) 
 }
 
 // NB: rows of one weight block = MMA N of one class (forward: Cout) / of the tile (dgrad: Cin)
-template <int MODE, int NB>
+#define TS_T0() const long long _c0 = TRACE ? clock64() : 0
+#define TS_T1(slot) do { if (TRACE) tacc[slot] += clock64() - _c0; } while (0)
+#define TS_TRACE_OUT(role) do { if (TRACE && blockIdx.x == 0 && lane == 0) { tacc[7] = clock64() - t_role; \
+        for (int k = 0; k < 8; ++k) ar.trace[(role) * 8 + k] = (unsigned long long)tacc[k]; } } while (0)
+
+template <int MODE, int NB, bool TRACE = false>
 __global__ void __launch_bounds__(TS_THREADS, 1)
 convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                const float* __restrict__ bias, const float* __restrict__ mask, float* __restrict__ out, const TsArgs ar) {
+                const __grid_constant__ CUtensorMap tmap_y, const float* __restrict__ bias, const float* __restrict__ mask,
+                float* __restrict__ out, const TsArgs ar) {
     using S = TsSched<MODE>;
     using Bt = TsBatch<MODE>;
     constexpr int BLOCK_BYTES = NB * 128;
@@ -152,11 +159,15 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         tma_prefetch_desc(&tmap_a);
         tma_prefetch_desc(&tmap_b);
     }
+    float* bias_s = reinterpret_cast<float*>(bars) + 128;                     // bytes 512..1023 of the barrier block
+    if (MODE == TS_FWD && threadIdx.x < NB) bias_s[threadIdx.x] = bias ? bias[threadIdx.x] : 0.f;
     if (warp == 2) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
+    long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const long long t_role = TRACE ? clock64() : 0;
 
     if (warp == 0) {
         // ===== activation producer: one halo tile per (tile, chunk[, class]) =====
@@ -167,13 +178,14 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             for (int ck = 0; ck < ar.chunks; ++ck)
                 for (int st = 0; st < S::STAGES; ++st, ++sidx) {
                     const int s = sidx % ar.nstg, ph = (sidx / ar.nstg) & 1;
-                    mbar_wait_relaxed(empty + s, ph ^ 1);
+                    { TS_T0(); mbar_wait_relaxed(empty + s, ph ^ 1); TS_T1(0); }
                     if (ar.dbg & 16) { mbar_arrive_elect(full + s); continue; }
                     mbar_arrive_expect_tx_elect(full + s, ar.stage_tx);
                     if (MODE == TS_FWD) tma_load_4d_elect(a_ring + s * ar.stage_bytes, &tmap_a, full + s, ck * 32, -1, -1, n0);
                     else tma_load_4d_elect(a_ring + s * ar.stage_bytes, &tmap_a, full + s, ck * 32, -(st & 1), -(st >> 1), n0);
                 }
         }
+        TS_TRACE_OUT(0);
     } else if (warp == 1) {
         // ===== weight producer: the blocks of one batch per mbarrier =====
         const uint32_t b_ring = smem_u32(bring);
@@ -212,15 +224,16 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         int bid = 0, ti = 0;
         for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++ti) {
             const int acc = ti % NACC, use = ti / NACC;
-            mbar_wait(tempty + acc, (use & 1) ^ 1);
+            { TS_T0(); mbar_wait(tempty + acc, (use & 1) ^ 1); TS_T1(0); }
             tc_fence_after_sync();
             const uint32_t d_acc = tmem_base + acc * ACC_COLS;
             for (int ck = 0; ck < ar.chunks; ++ck) {
 #pragma unroll
                 for (int b = 0; b < Bt::PER_CHUNK; ++b, ++bid) {
                     const int blk0 = (MODE == TS_FWD) ? kB0[b % 3] : 2 * b;
-                    mbar_wait(a_full + (bid & 7), (bid >> 3) & 1);
+                    { TS_T0(); mbar_wait(a_full + (bid & 7), (bid >> 3) & 1); TS_T1(1); }
                     int slot;
+                    const long long _cb = TRACE ? clock64() : 0;
                     if (ar.resident) {
                         mbar_wait(b_full + ck * Bt::PER_CHUNK + b, 0);
                         slot = ck * 16 + blk0;
@@ -228,7 +241,9 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                         mbar_wait(b_full + (bid & 7), (bid >> 3) & 1);
                         slot = (MODE == TS_FWD) ? blk0 : (2 * bid) % ar.nbs;
                     }
+                    if (TRACE) tacc[2] += clock64() - _cb;
                     tc_fence_after_sync();
+                    const long long _ci = TRACE ? clock64() : 0;
                     const int w0 = bid * BW;                                 // global window index of the batch's first window
 #pragma unroll
                     for (int wi = 0; wi < BW; ++wi) {
@@ -245,17 +260,17 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                             for (int gi = 0; gi < ((MODE == TS_FWD && i == 4) ? 2 : 1); ++gi) {
                                 const uint32_t col = (MODE == TS_FWD) ? (gi ? 3 : kSlot[i % 9]) * NB : 0;
                                 const uint64_t dbg = db + (uint64_t)(gi * (BLOCK_BYTES >> 4) + kk * 2);
-                                umma_bf16_ts_elect(d_acc + col, a_col + kk * 8, dbg, idesc, first);             // hi  * hi
-                                umma_bf16_ts_elect(d_acc + col, a_col + kk * 8, dbg + 4, idesc, 1);             // hi  * mid
-                                umma_bf16_ts_elect(d_acc + col, a_col + 16 + kk * 8, dbg, idesc, 1);            // mid * hi
+                                umma_bf16_ts3_elect(d_acc + col, a_col + kk * 8, a_col + 16 + kk * 8, dbg, idesc, first);   // hi*hi, hi*mid, mid*hi
                             }
                         }
                     }
                     umma_commit_elect(done + (bid & 7));
+                    if (TRACE) tacc[3] += clock64() - _ci;
                 }
             }
             umma_commit_elect(tfull + acc);
         }
+        TS_TRACE_OUT(2);
     } else if (warp < 11) {
         // ===== converters: every warp takes part in every window; the two warps of a lane quarter split the 32 channels
         // (half h: channels 16h..16h+15 = the MMA k-step h: hi columns 8h.., mid columns 16+8h..) =====
@@ -272,19 +287,26 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                 for (int st = 0; st < S::STAGES; ++st, ++sidx) {
                     const int s = sidx % ar.nstg, ph = (sidx / ar.nstg) & 1;
                     const uint32_t base = a_ring + s * ar.stage_bytes;
-                    mbar_wait(full + s, ph);
-                    if (!(ar.dbg & 4))
-                        for (int r = ctid; r < rows; r += TS_NCONV) ts_split_row(base + r * 128, r & 7);
-                    asm volatile("bar.sync 1, 256;" ::: "memory");
+                    { TS_T0(); mbar_wait(full + s, ph); TS_T1(0); }
+                    {
+                        TS_T0();
+                        if (!(ar.dbg & 4))
+                            for (int r = ctid; r < rows; r += TS_NCONV) ts_split_row(base + r * 128, r & 7);
+                        TS_T1(1);
+                    }
+                    { TS_T0(); asm volatile("bar.sync 1, 256;" ::: "memory"); TS_T1(2); }
 #pragma unroll
                     for (int b = 0; b < Bt::PER_STAGE; ++b, ++bid) {
                         const int w0 = bid * BW;
                         const int jw = w0 + BW - 1 - TS_NAS;               // the window whose slot the batch's last window reuses
                         if (jw >= 0) {
                             const int j = Bt::of_window(jw);
-                            mbar_wait(done + (j & 7), (j >> 3) & 1);
+                            TS_T0(); mbar_wait(done + (j & 7), (j >> 3) & 1); TS_T1(3);
                         }
                         tc_fence_after_sync();
+                        // (issuing the shared-memory reads before this wait, or waiting per window, measured slower: 132 / 152 us
+                        // against 111 us for the 64->32 layer, tools/ts_trace.py)
+                        const long long _cc = TRACE ? clock64() : 0;
                         if (!(ar.dbg & 2)) {
                             uint32_t v[BW][16];
 #pragma unroll
@@ -306,17 +328,23 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                                 tmem_st_32x8(ta, v[wi]);
                                 tmem_st_32x8(ta + 16, v[wi] + 8);
                             }
-                            tmem_st_wait();
                         }
+                        if (!(ar.dbg & 2)) tmem_st_wait();
                         tc_fence_before_sync();
                         __syncwarp();
                         if (lane == 0) mbar_arrive(a_full + (bid & 7));
+                        if (TRACE) tacc[4] += clock64() - _cc;
                     }
-                    fence_proxy_async_smem();          // generic reads / writes of the tile ordered before the TMA that refills it
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(empty + s);
+                    {
+                        TS_T0();
+                        fence_proxy_async_smem();      // generic reads / writes of the tile ordered before the TMA that refills it
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(empty + s);
+                        TS_T1(5);
+                    }
                 }
         }
+        if (warp == 3) TS_TRACE_OUT(3);
     } else {
         // ===== epilogue (warps 11..14): TMEM -> registers -> (transposition pad) -> global =====
         // A thread reads its pixel's 32 accumulator columns; stored directly that is 32 different 128-byte lines per store
@@ -333,14 +361,16 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             const int row0 = t * 128 + lane_base, row = row0 + lane;
             const uint32_t tb = tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)(acc * ACC_COLS);
             if (MODE == TS_FWD) {
-                const int n_img = row / HW, rem = row - n_img * HW, ii = rem / W, jj = rem - ii * W;
-                float* const y00 = out + ((long)(n_img * 2 * H + 2 * ii) * (2 * W) + 2 * jj) * NB;       // class (0,0) position
-                mbar_wait(tfull + acc, use & 1);
+                // Each 32-channel chunk of a parity class leaves as ONE TMA store: the four warps write their pixels' rows
+                // (128 bytes, 16-byte chunks XOR-swizzled by the row = SWIZZLE_128B) into one 16 KB tile, and the tensor map
+                // of y scatters it to the class's pixels (2i+py, 2j+px).  No transposition reads, shuffles or global store
+                // instructions in the warps (they were the bottleneck of the kernel: tools/ts_trace.py).
+                { TS_T0(); mbar_wait(tfull + acc, use & 1); TS_T1(0); }
                 tc_fence_after_sync();
+                const bool issuer = (warp == 11 && lane == 0);
 #pragma unroll 1
                 for (int slot = 0; slot < 4; ++slot) {
                     const int py = slot >> 1, px = (slot & 1) ^ py;                  // Gray slot -> (py, px)
-                    const unsigned long long p = (unsigned long long)(y00 + ((long)py * (2 * W) + px) * NB);
 #pragma unroll
                     for (int cc = 0; cc < NB; cc += 32) {
                         float v[32];
@@ -351,30 +381,29 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                             if (lane == 0) mbar_arrive(tempty + acc);
                         }
 #pragma unroll
+                        for (int c = 0; c < 8; ++c) {
+                            const float4 b4 = *reinterpret_cast<const float4*>(bias_s + cc + 4 * c);        // broadcast
+                            v[4 * c] += b4.x; v[4 * c + 1] += b4.y; v[4 * c + 2] += b4.z; v[4 * c + 3] += b4.w;
+                        }
+                        if (ar.act == MMVAE_ACT_RELU) {
+#pragma unroll
+                            for (int c = 0; c < 32; ++c) v[c] = fmaxf(v[c], 0.f);
+                        } else if (ar.act == MMVAE_ACT_SIGMOID) {
+#pragma unroll
+                            for (int c = 0; c < 32; ++c) v[c] = 1.f / (1.f + expf(-v[c]));
+                        }
+                        if (issuer) bulk_wait_group_read0();                 // the previous store has read the tile
+                        asm volatile("bar.sync 2, 128;" ::: "memory");
+#pragma unroll
                         for (int c = 0; c < 8; ++c)
                             asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((uint32_t)(c ^ my_sw) << 4)), "f"(v[4 * c]),
                                          "f"(v[4 * c + 1]), "f"(v[4 * c + 2]), "f"(v[4 * c + 3]) : "memory");
-                        __syncwarp();
-                        const float4 b4 = bias ? make_float4(__ldg(bias + cc + 4 * tr_c), __ldg(bias + cc + 4 * tr_c + 1),
-                                                             __ldg(bias + cc + 4 * tr_c + 2), __ldg(bias + cc + 4 * tr_c + 3))
-                                               : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-                        for (int k = 0; k < 8; ++k) {
-                            const int r = 4 * k + tr_r0;
-                            float4 o;
-                            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(o.x), "=f"(o.y), "=f"(o.z), "=f"(o.w)
-                                         : "r"(pad + r * 128 + ((uint32_t)(tr_c ^ (r & 7)) << 4)));
-                            o.x += b4.x; o.y += b4.y; o.z += b4.z; o.w += b4.w;
-                            if (ar.act == MMVAE_ACT_RELU) {
-                                o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f);
-                            } else if (ar.act == MMVAE_ACT_SIGMOID) {
-                                o.x = 1.f / (1.f + expf(-o.x)); o.y = 1.f / (1.f + expf(-o.y));
-                                o.z = 1.f / (1.f + expf(-o.z)); o.w = 1.f / (1.f + expf(-o.w));
-                            }
-                            float* pr = reinterpret_cast<float*>(__shfl_sync(0xffffffffu, p, r));       // row r's output pixel
-                            if (row0 + r < ar.M && !(ar.dbg & 1)) __stcs(reinterpret_cast<float4*>(pr + cc + 4 * tr_c), o);
+                        fence_proxy_async_smem();
+                        asm volatile("bar.sync 3, 128;" ::: "memory");
+                        if (issuer && !(ar.dbg & 1)) {
+                            tma_store_5d(&tmap_y, smem_u32(bars) + 1024, px * NB + cc, 0, py, 0, t * IMGS);
+                            bulk_commit_group();
                         }
-                        __syncwarp();                                     // the pad is rewritten by the next chunk
                     }
                 }
             } else {
@@ -389,7 +418,7 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                     }
                 };
                 load_mask(0);                             // requested before the accumulator is complete
-                mbar_wait(tfull + acc, use & 1);
+                { TS_T0(); mbar_wait(tfull + acc, use & 1); TS_T1(0); }
                 tc_fence_after_sync();
 #pragma unroll
                 for (int cc = 0; cc < NB; cc += 32) {
@@ -422,6 +451,8 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                 }
             }
         }
+        if (MODE == TS_FWD && warp == 11 && lane == 0) bulk_wait_group0();
+        if (warp == 11) TS_TRACE_OUT(4);
     }
     tc_fence_before_sync();
     __syncthreads();
@@ -522,25 +553,31 @@ extern "C" int mmvae_convt_ts_pack_weights(const float* w, void* wf, void* wd, i
     return 0;
 }
 
+// tools/ts_trace.py: a device buffer of 5 roles x 8 counters (clocks of CTA 0: producer, -, issuer, converter warp, epilogue warp)
+static unsigned long long* g_ts_trace = nullptr;
+extern "C" void mmvae_convt_ts_set_trace(void* buf) { g_ts_trace = (unsigned long long*)buf; }
+
 template <int MODE, int NB>
-static int ts_launch(const CUtensorMap& ta, const CUtensorMap& tb, const float* bias, const float* mask, float* out, TsArgs ar,
-                     int rows, cudaStream_t st) {
-    static bool attr_done = false;
-    auto kern = convt_ts_kernel<MODE, NB>;
+static int ts_launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ty, const float* bias, const float* mask,
+                     float* out, TsArgs ar, int rows, cudaStream_t st) {
+    static bool attr_done[2] = {false, false};
+    const int tr = g_ts_trace != nullptr;
+    auto kern = tr ? convt_ts_kernel<MODE, NB, true> : convt_ts_kernel<MODE, NB, false>;
+    ar.trace = g_ts_trace;
     constexpr int BLOCK_BYTES = NB * 128;
     ar.stage_tx = rows * 128;
     ar.dbg = mmvae_tc_dbg_bits();
     if (!ts_plan(MODE, NB, ar.chunks, rows, &ar.nbs, &ar.resident, &ar.nstg, &ar.stage_bytes))
         return mmvae_set_error(1, "convt_ts: shared memory plan does not fit (stage %d bytes)", ar.stage_bytes);
     const int smem = (int)((long)ar.nbs * BLOCK_BYTES + 2048 + 16384 + (long)ar.nstg * ar.stage_bytes);
-    if (!attr_done) {
+    if (!attr_done[tr]) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM_MAX);
         if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "convt_ts: smem attribute: %s", cudaGetErrorString(e));
-        attr_done = true;
+        attr_done[tr] = true;
     }
     const int tiles = (ar.M + 127) / 128;
     const int grid = tiles < MMVAE_NUM_SMS ? tiles : MMVAE_NUM_SMS;
-    kern<<<grid, TS_THREADS, smem, st>>>(ta, tb, bias, mask, out, ar);
+    kern<<<grid, TS_THREADS, smem, st>>>(ta, tb, ty, bias, mask, out, ar);
     MMVAE_LAUNCH_CHECK("convt_ts");
     return 0;
 }
@@ -570,8 +607,19 @@ extern "C" int mmvae_convt_ts_fwd(const float* x, const void* wf, const float* b
     ar.M = Nimg * H * W; ar.H = H; ar.W = W; ar.chunks = Cin / 32; ar.act = act;
     const int rows = IMGS * (H + 2) * (W + 2);
     cudaStream_t st = (cudaStream_t)stream;
-    return Cout == 32 ? ts_launch<TS_FWD, 32>(ta, tb, bias, nullptr, y, ar, rows, st)
-                      : ts_launch<TS_FWD, 64>(ta, tb, bias, nullptr, y, ar, rows, st);
+    // y as a rank-5 tensor [Nimg][H][py][W][px*Cout + co]: one parity class x 32 channels of a pixel tile is the box
+    // {32, W, 1, H, IMGS} at {px*Cout + c0, 0, py, 0, n0}; images past Nimg are clipped by the TMA
+    CUtensorMap ty;
+    {
+        cuuint64_t yd[5] = {(cuuint64_t)2 * Cout, (cuuint64_t)W, 2u, (cuuint64_t)H, (cuuint64_t)Nimg};
+        cuuint64_t ys[4] = {(cuuint64_t)2 * Cout * 4, (cuuint64_t)2 * W * Cout * 4, (cuuint64_t)4 * W * Cout * 4,
+                            (cuuint64_t)4 * H * W * Cout * 4};
+        cuuint32_t yb[5] = {32u, (cuuint32_t)W, 1u, (cuuint32_t)H, (cuuint32_t)IMGS}, ye[5] = {1u, 1u, 1u, 1u, 1u};
+        rc = mmvae_tc_encode(&ty, 0, 5, y, yd, ys, yb, ye);
+        if (rc) return mmvae_set_error(1, "convt_ts_fwd: tensor map (y) failed with %d", rc);
+    }
+    return Cout == 32 ? ts_launch<TS_FWD, 32>(ta, tb, ty, bias, nullptr, y, ar, rows, st)
+                      : ts_launch<TS_FWD, 64>(ta, tb, ty, bias, nullptr, y, ar, rows, st);
 }
 
 // dgrad.  g: [Nimg,2H,2W,Cout] NHWC gradient w.r.t. the layer's pre-activation; wd from mmvae_convt_ts_pack_weights;
@@ -593,9 +641,9 @@ extern "C" int mmvae_convt_ts_dgrad(const float* g, const void* wd, const float*
     ar.M = Nimg * H * W; ar.H = H; ar.W = W; ar.chunks = Cout / 32; ar.act = 0;
     const int rows = IMGS * (H + 1) * (W + 1);
     cudaStream_t st = (cudaStream_t)stream;
-    if (Cin == 32) return ts_launch<TS_DGRAD, 32>(ta, tb, nullptr, x_mask, gx, ar, rows, st);
-    if (Cin == 64) return ts_launch<TS_DGRAD, 64>(ta, tb, nullptr, x_mask, gx, ar, rows, st);
-    return ts_launch<TS_DGRAD, 128>(ta, tb, nullptr, x_mask, gx, ar, rows, st);
+    if (Cin == 32) return ts_launch<TS_DGRAD, 32>(ta, tb, ta, nullptr, x_mask, gx, ar, rows, st);
+    if (Cin == 64) return ts_launch<TS_DGRAD, 64>(ta, tb, ta, nullptr, x_mask, gx, ar, rows, st);
+    return ts_launch<TS_DGRAD, 128>(ta, tb, ta, nullptr, x_mask, gx, ar, rows, st);
 }
 
 // ============================================================================================================== wgrad
@@ -757,9 +805,7 @@ convt_ts_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_c
                         const uint32_t d = tmem_base + mt * CIN + c * 32;
                         const uint64_t db = dxs[c] + (uint64_t)(kb * (2048 >> 4));
                         if (ar.dbg & 8) continue;
-                        umma_bf16_ts_elect(d, a_col, db, idesc, first);            // g_hi  * x_hi
-                        umma_bf16_ts_elect(d, a_col, db + 4, idesc, 1);            // g_hi  * x_mid
-                        umma_bf16_ts_elect(d, a_col + 8, db, idesc, 1);            // g_mid * x_hi
+                        umma_bf16_ts3_elect(d, a_col, a_col + 8, db, idesc, first);       // g_hi*x_hi, g_hi*x_mid, g_mid*x_hi
                     }
                 }
                 umma_commit_elect(done + (gb & 3));

@@ -33,6 +33,9 @@ extern "C" long mmvae_gemm_workspace_bytes(int M, int N, int K, int a_kmajor, in
     return a > b ? a : b;
 }
 
+static int g_last_gemm_kernel = -1;
+extern "C" int mmvae_gemm_last_kernel(void) { return g_last_gemm_kernel; }
+
 extern "C" int mmvae_gemm(const float* A, const float* B, const float* bias, float* C, int M, int N, int K,
                           int a_kmajor, int b_kmajor, int act, float* workspace, long workspace_bytes, int allow_tc,
                           void* stream) {
@@ -42,16 +45,17 @@ extern "C" int mmvae_gemm(const float* A, const float* B, const float* bias, flo
     cudaStream_t st = (cudaStream_t)stream;
     {
         const int rc = mmvae_gemm_skinny(A, B, bias, C, M, N, K, a_kmajor, b_kmajor, act, st);     // K = latent dimension
-        if (rc != -1) return rc;
+        if (rc != -1) { g_last_gemm_kernel = 2; return rc; }
     }
     {
         const int rc = mmvae_gemm_small(A, B, bias, C, M, N, K, a_kmajor, b_kmajor, act, st);      // latency-bound sizes
-        if (rc != -1) return rc;
+        if (rc != -1) { g_last_gemm_kernel = 3; return rc; }
     }
     if (allow_tc) {
         const int rc = mmvae_gemm_tc(A, B, bias, C, M, N, K, a_kmajor, b_kmajor, act, workspace, workspace_bytes, st);
-        if (rc != -1) return rc;
+        if (rc != -1) { g_last_gemm_kernel = 1; return rc; }
     }
+    g_last_gemm_kernel = 0;
     return mmvae_gemm_simt(A, B, bias, C, M, N, K, a_kmajor, b_kmajor, act, workspace, workspace_bytes, st);
 }
 

@@ -73,6 +73,16 @@ __device__ __forceinline__ void tma_load_4d(void* smem_dst, const void* tmap, ui
         : "memory");
 }
 
+// TMA store of a 5-D box shared -> global (bulk async-group completion); smem source written by generic stores must be made
+// visible with fence.proxy.async by the writing threads first
+__device__ __forceinline__ void tma_store_5d(const void* tmap, uint32_t smem_src, int c0, int c1, int c2, int c3, int c4) {
+    asm volatile("cp.async.bulk.tensor.5d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5, %6}], [%1];" ::"l"((uint64_t)tmap),
+                 "r"(smem_src), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4) : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_group_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_group0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 // 1-D bulk copy global -> shared (bytes and both addresses multiples of 16), completion counted on an mbarrier
 __device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
@@ -198,6 +208,20 @@ __device__ __forceinline__ void umma_bf16_ts_elect(uint32_t tmem_d, uint32_t tme
         "{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %4, 0;\n\telect.sync _|q, 0xffffffff;\n\t"
         "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}\n" ::"r"(tmem_d),
         "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// The three MMAs of one bf16x3 product (hi*hi, hi*mid, mid*hi) under ONE election: the operands reach the uniform datapath
+// once (R2UR) instead of once per instruction -- the issuing thread was spending ~40 clocks per MMA on them, more than the
+// 16..64 clocks the tensor core needs (tools/ts_trace.py).  b_mid_off: descriptor offset (16-byte units) of the mid half of B.
+__device__ __forceinline__ void umma_bf16_ts3_elect(uint32_t tmem_d, uint32_t tmem_a_hi, uint32_t tmem_a_mid, uint64_t desc_b,
+                                                    uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p, q, t;\n\t.reg .b64 dm;\n\tsetp.ne.b32 p, %5, 0;\n\tsetp.eq.u32 t, 0, 0;\n\tadd.s64 dm, %3, 4;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %3, %4, p;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], dm, %4, t;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [%2], %3, %4, t;\n\t}\n" ::"r"(tmem_d),
+        "r"(tmem_a_hi), "r"(tmem_a_mid), "l"(desc_b), "r"(idesc), "r"(accumulate)
         : "memory");
 }
 // the shared-memory ("SS") form of the same instruction

@@ -124,6 +124,7 @@ def _tap_relu(w, b, y, act):
             RELU_TAP.setdefault(b.data_ptr(), []).append(m)
 
 
+GEMM_KERNELS = {0: "simt", 1: "tcgen05", 2: "skinny", 3: "small"}
 GEMM_LOG = None          # set to a list (with PROFILE) to record ("M N K a_kmajor b_kmajor act", start, end) per GEMM
 PROFILE = None           # set to a list to record (name, work, start_event, end_event) per C-ABI call (bench.py)
 
@@ -150,12 +151,10 @@ def gemm(a, b, bias, M, N, K, a_kmajor, b_kmajor, act=None, out=None):
     ws_bytes = lib.mmvae_gemm_workspace_bytes(M, N, K, int(a_kmajor), int(b_kmajor)) if ALLOW_TC else \
         lib.mmvae_gemm_workspace_bytes(M, N, K, -1, -1)
     ws = torch.empty(ws_bytes // 4, device=a.device, dtype=torch.float32) if ws_bytes else None
-    n_tc = lib.mmvae_gemm_tc_launch_count() if PROFILE is not None else 0
     _call("mmvae_gemm", _p(a), _p(b), _p(bias), _p(out), M, N, K, int(a_kmajor), int(b_kmajor), ACT[act], _p(ws),
           ws_bytes, int(ALLOW_TC), _stream(), work=("flop", 2.0 * M * N * K))
     if PROFILE:                                   # which kernel the dispatcher picked: the per-kernel accounting of bench.py
-        on_tc = lib.mmvae_gemm_tc_launch_count() != n_tc
-        PROFILE[-1] = ("mmvae_gemm[tcgen05]" if on_tc else "mmvae_gemm[simt]",) + PROFILE[-1][1:]
+        PROFILE[-1] = ("mmvae_gemm[%s]" % GEMM_KERNELS[lib.mmvae_gemm_last_kernel()],) + PROFILE[-1][1:]
     if GEMM_LOG is not None and PROFILE:
         GEMM_LOG.append((f"M={M} N={N} K={K} a_k={int(a_kmajor)} b_k={int(b_kmajor)} bias={bias is not None} act={act}",
                          PROFILE[-1][2], PROFILE[-1][3]))

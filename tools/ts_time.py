@@ -49,6 +49,6 @@ def run(N, cin, cout, H, bits_list):
 
 if __name__ == "__main__":
     N = int(sys.argv[1]) if len(sys.argv) > 1 else 7680
-    bl = [0, 2, 4, 8, 2 | 4 | 8] if len(sys.argv) < 3 else [0, 1, 2, 4, 8, 16, 2 | 4, 2 | 4 | 16, 1 | 2 | 4 | 16, 1 | 8, 31]
+    bl = [0, 2, 4, 8, 2 | 4 | 8] if len(sys.argv) < 3 else [0, 1, 16, 14, 15, 30, 31, 1 | 16, 8 | 16, 2 | 4]
     run(N, 64, 32, 8, bl)
     run(N, 128, 64, 4, bl)
