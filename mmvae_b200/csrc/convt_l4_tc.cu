@@ -91,7 +91,7 @@ convt_l4_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float* 
     uint64_t* img_full = tempty + L4_NACC;        // [2] scattered image complete (epilogue -> converter warps)
     uint64_t* img_empty = img_full + 2;           // [2] image stored and zeroed again (converter -> epilogue warps)
     uint32_t* tmem_slot = (uint32_t*)(img_empty + 2);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;      // warp-uniform for the compiler: the single-warp roles run on the uniform datapath
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < L4_STAGES; ++s) { mbar_init(full + s, 1); mbar_init(conv + s, 4); mbar_init(empty + s, 1); }
@@ -418,7 +418,7 @@ convt_l4_dgrad_tc_kernel(const float* __restrict__ g, const float* __restrict__ 
     uint64_t* tfull = bars + 8;           // [NACC]
     uint64_t* tempty = bars + 8 + L4D_NACC;
     uint32_t* tmem_slot = (uint32_t*)(tempty + L4D_NACC);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;      // warp-uniform for the compiler: the single-warp roles run on the uniform datapath
     const bool has_y = y_act != nullptr && act != MMVAE_ACT_NONE;
 
     if (threadIdx.x == 0) {
@@ -675,7 +675,7 @@ convt_l4_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float
     uint64_t* tfull = bars + 4 + 3 * L4W_STAGES;        // [2]
     uint64_t* tempty = tfull + 2;                       // [2] count 4
     uint32_t* tmem_slot = (uint32_t*)(tempty + 2);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;      // warp-uniform for the compiler: the single-warp roles run on the uniform datapath
     const bool has_y = y_act != nullptr && act != MMVAE_ACT_NONE;
 
     if (threadIdx.x == 0) {

@@ -125,6 +125,10 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     constexpr int ACC_COLS = (MODE == TS_FWD) ? 4 * NB : NB;
     constexpr int NACC = (2 * ACC_COLS <= TS_A_COL) ? 2 : 1;
     constexpr int BW = Bt::BW;
+    // forward: a landed row is split into bf16 (hi | mid) IN PLACE once and copied by 9 windows.  dgrad: 4 windows per class
+    // tile; splitting in the copy costs the same ALU work as the separate pass and saves the pass's shared-memory write-back,
+    // its barrier and the proxy fence (tools/ts_trace.py: 2.3 of 8.4 k clocks per tile at 64->32 channels)
+    constexpr bool INPLACE = (MODE == TS_FWD);
     static_assert(ACC_COLS <= TS_A_COL, "accumulators overlap the A ring");
     // forward: weight blocks (class rows) of the three batches of a chunk
     constexpr int8_t kNcls[9] = {4, 2, 2, 2, 2, 1, 1, 1, 1}, kRow[9] = {0, 4, 6, 8, 10, 12, 13, 14, 15};
@@ -145,7 +149,7 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     uint64_t* tempty = bars + 50;          // [2]
     uint32_t* tmem_slot = (uint32_t*)(bars + 52);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;      // warp-uniform for the compiler (uniform registers / branches in the single-warp roles)
     const int H = ar.H, W = ar.W, HW = H * W, IMGS = 128 / HW;
     const int tiles = (ar.M + 127) / 128;
 
@@ -168,6 +172,11 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     const uint32_t tmem_base = *tmem_slot;
     long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     const long long t_role = TRACE ? clock64() : 0;
+    if (TRACE && threadIdx.x == 64) {                       // every CTA: wall-clock (ns) of its start, at [64 + 2*cta]
+        unsigned long long ns;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+        ar.trace[64 + 2 * blockIdx.x] = ns;
+    }
 
     if (warp == 0) {
         // ===== activation producer: one halo tile per (tile, chunk[, class]) =====
@@ -221,12 +230,17 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         constexpr uint32_t idesc2 = umma_idesc_bf16(128, 2 * NB <= 256 ? 2 * NB : 256, 0, 0);
         constexpr uint32_t idesc4 = umma_idesc_bf16(128, 4 * NB <= 256 ? 4 * NB : 256, 0, 0);
         const uint64_t db0 = umma_smem_desc(smem_u32(bring), 16, 1024, 2);
+        // The CTA owns all 512 columns, so the allocation starts at column 0, lane 0: with the base a literal the operand
+        // addresses of every MMA are functions of uniform loop counters only and stay in uniform registers (with the loaded
+        // base the issuing lane spent ~40 clocks per MMA moving them there: tools/ts_trace.py, SASS R2UR chains).
+        if (tmem_base != 0) __trap();
+        constexpr uint32_t tmem_base_u = 0;
         int bid = 0, ti = 0;
         for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++ti) {
             const int acc = ti % NACC, use = ti / NACC;
             { TS_T0(); mbar_wait(tempty + acc, (use & 1) ^ 1); TS_T1(0); }
             tc_fence_after_sync();
-            const uint32_t d_acc = tmem_base + acc * ACC_COLS;
+            const uint32_t d_acc = tmem_base_u + acc * ACC_COLS;
             for (int ck = 0; ck < ar.chunks; ++ck) {
 #pragma unroll
                 for (int b = 0; b < Bt::PER_CHUNK; ++b, ++bid) {
@@ -248,7 +262,7 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
 #pragma unroll
                     for (int wi = 0; wi < BW; ++wi) {
                         const int i = b * BW + wi;                           // window within the chunk
-                        const uint32_t a_col = tmem_base + TS_A_COL + ((w0 + wi) & (TS_NAS - 1)) * 32;
+                        const uint32_t a_col = tmem_base_u + TS_A_COL + ((w0 + wi) & (TS_NAS - 1)) * 32;
                         const int boff = (MODE == TS_FWD) ? kRow[i % 9] - kB0[b % 3] : wi;       // block within the batch
                         const uint64_t db = db0 + (uint64_t)((slot + boff) * (BLOCK_BYTES >> 4));
                         const uint32_t idesc = (MODE == TS_DGRAD) ? idesc1 : (kNc[i % 9] == 4 ? idesc4 : (kNc[i % 9] == 2 ? idesc2 : idesc1));
@@ -271,6 +285,11 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             umma_commit_elect(tfull + acc);
         }
         TS_TRACE_OUT(2);
+        if (TRACE && lane == 0) {
+            unsigned long long ns;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+            ar.trace[64 + 2 * blockIdx.x + 1] = ns;
+        }
     } else if (warp < 11) {
         // ===== converters: every warp takes part in every window; the two warps of a lane quarter split the 32 channels
         // (half h: channels 16h..16h+15 = the MMA k-step h: hi columns 8h.., mid columns 16+8h..) =====
@@ -288,13 +307,15 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                     const int s = sidx % ar.nstg, ph = (sidx / ar.nstg) & 1;
                     const uint32_t base = a_ring + s * ar.stage_bytes;
                     { TS_T0(); mbar_wait(full + s, ph); TS_T1(0); }
-                    {
-                        TS_T0();
-                        if (!(ar.dbg & 4))
-                            for (int r = ctid; r < rows; r += TS_NCONV) ts_split_row(base + r * 128, r & 7);
-                        TS_T1(1);
+                    if (INPLACE) {
+                        {
+                            TS_T0();
+                            if (!(ar.dbg & 4))
+                                for (int r = ctid; r < rows; r += TS_NCONV) ts_split_row(base + r * 128, r & 7);
+                            TS_T1(1);
+                        }
+                        { TS_T0(); asm volatile("bar.sync 1, 256;" ::: "memory"); TS_T1(2); }
                     }
-                    { TS_T0(); asm volatile("bar.sync 1, 256;" ::: "memory"); TS_T1(2); }
 #pragma unroll
                     for (int b = 0; b < Bt::PER_STAGE; ++b, ++bid) {
                         const int w0 = bid * BW;
@@ -315,11 +336,32 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                                 const int row = base_row + ((MODE == TS_FWD) ? kDy[i % 9] * pitch + kDx[i % 9] : (i >> 1) * pitch + (i & 1));
                                 const uint32_t addr = base + row * 128;
                                 const int sw = row & 7;
+                                if (INPLACE) {
 #pragma unroll
-                                for (int c = 0; c < 4; ++c) {
-                                    const int lc = (c < 2) ? 2 * half + c : 4 + 2 * half + (c - 2);      // logical 16-byte chunk
-                                    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v[wi][4 * c]), "=r"(v[wi][4 * c + 1]),
-                                                 "=r"(v[wi][4 * c + 2]), "=r"(v[wi][4 * c + 3]) : "r"(addr + ((uint32_t)(lc ^ sw) << 4)));
+                                    for (int c = 0; c < 4; ++c) {
+                                        const int lc = (c < 2) ? 2 * half + c : 4 + 2 * half + (c - 2);      // logical 16-byte chunk
+                                        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v[wi][4 * c]), "=r"(v[wi][4 * c + 1]),
+                                                     "=r"(v[wi][4 * c + 2]), "=r"(v[wi][4 * c + 3]) : "r"(addr + ((uint32_t)(lc ^ sw) << 4)));
+                                    }
+                                } else {
+                                    // the warp's 16 channels of the fp32 row, split into bf16 (hi, mid) pairs on the way
+                                    float f[16];
+#pragma unroll
+                                    for (int c = 0; c < 4; ++c)
+                                        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(f[4 * c]), "=f"(f[4 * c + 1]), "=f"(f[4 * c + 2]),
+                                                     "=f"(f[4 * c + 3]) : "r"(addr + ((uint32_t)((4 * half + c) ^ sw) << 4)));
+#pragma unroll
+                                    for (int j = 0; j < 8; ++j) {
+                                        uint32_t hp;
+                                        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hp) : "f"(f[2 * j + 1]), "f"(f[2 * j]));
+                                        const float r0 = f[2 * j] - __uint_as_float(hp << 16), r1 = f[2 * j + 1] - __uint_as_float(hp & 0xffff0000u);
+                                        v[wi][j] = hp;
+                                        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(v[wi][8 + j]) : "f"(r1), "f"(r0));
+                                    }
+                                    if (ar.dbg & 4) {
+#pragma unroll
+                                        for (int j = 0; j < 16; ++j) v[wi][j] = __float_as_uint(f[j]);
+                                    }
                                 }
                             }
 #pragma unroll
@@ -337,7 +379,7 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                     }
                     {
                         TS_T0();
-                        fence_proxy_async_smem();      // generic reads / writes of the tile ordered before the TMA that refills it
+                        if (INPLACE) fence_proxy_async_smem();      // generic WRITES to the tile ordered before the TMA that refills it
                         __syncwarp();
                         if (lane == 0) mbar_arrive(empty + s);
                         TS_T1(5);
@@ -719,7 +761,7 @@ convt_ts_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_c
     uint64_t* tempty = bars + 49;          // count 4
     uint32_t* tmem_slot = (uint32_t*)(bars + 50);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;      // warp-uniform for the compiler (uniform registers / branches in the single-warp roles)
     const int H = ar.H, W = ar.W, HW = H * W, IMGS = 128 / HW;
     const int role = blockIdx.x % C::ROLES, cr = blockIdx.x / C::ROLES;
     int t0, t1, nparts;

@@ -141,7 +141,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     uint32_t* tmem_slot = (uint32_t*)(bars + 3 * STAGES + 4);
     float* epi = (float*)(smem + STAGES * Cfg::STAGE + 256);          // epilogue transposition pads (16-byte aligned)
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;      // warp-uniform for the compiler: the single-warp roles run on the uniform datapath
     const int nkb = (K + TC_BK - 1) / TC_BK;
     const int tiles_m = (M + TC_BM - 1) / TC_BM, tiles_n = (N + BN - 1) / BN;
     const int total = tiles_m * tiles_n * splits;
@@ -744,7 +744,7 @@ convt_fwd9_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     uint64_t* tfull = bars + 3 * NT;
     uint64_t* tempty = bars + 3 * NT + 2;
     uint32_t* tmem_slot = (uint32_t*)(bars + 3 * NT + 4);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;      // warp-uniform for the compiler: the single-warp roles run on the uniform datapath
     const int tiles = (M + TC_BM - 1) / TC_BM, nk = 9 * chunks, HW = H * W;
 
     if (threadIdx.x == 0) {

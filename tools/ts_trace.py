@@ -24,16 +24,23 @@ for cin, cout, H in ((64, 32, 8), (128, 64, 4)):
     wf = torch.empty(ne, device="cuda", dtype=torch.int16)
     wd = torch.empty(ne, device="cuda", dtype=torch.int16)
     _lib.check(lib.mmvae_convt_ts_pack_weights(P(w), P(wf), P(wd), cin, cout, None))
-    tr = torch.zeros(64, device="cuda", dtype=torch.int64)
+    tr = torch.zeros(64 + 2 * 148, device="cuda", dtype=torch.int64)
     lib.mmvae_gemm_tc_set_mode(bits << 8)
     for name, fn in (("fwd", lambda: lib.mmvae_convt_ts_fwd(P(x), P(wf), P(b), P(y), N, H, H, cin, cout, 1, None)),
                      ("dgrad", lambda: lib.mmvae_convt_ts_dgrad(P(g), P(wd), P(x), P(gx), N, H, H, cin, cout, None))):
         fn(); torch.cuda.synchronize()
         lib.mmvae_convt_ts_set_trace(ctypes.c_void_p(tr.data_ptr()))
         tr.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         _lib.check(fn()); torch.cuda.synchronize()
+        e0.record(); _lib.check(fn()); e1.record(); torch.cuda.synchronize()
         lib.mmvae_convt_ts_set_trace(None)
         t = tr.cpu().tolist()
+        st, en = t[64::2], t[65::2]
+        t0 = min(st)
+        dur = sorted(e - s for s, e in zip(st, en))
+        print(f"   traced kernel {e0.elapsed_time(e1) * 1e3:.1f} us by events; CTA starts {min(st) - t0}..{max(st) - t0} ns, issuer ends "
+              f"{min(en) - t0}..{max(en) - t0} ns; per-CTA busy ns min/median/max {dur[0]}/{dur[len(dur) // 2]}/{dur[-1]}")
         tiles = (N * H * H // 128 + 147) // 148
         print(f"{cin}->{cout} H={H} {name} (dbg {bits}), CTA 0, {tiles} tiles: clocks per tile")
         for r in (0, 2, 3, 4):
