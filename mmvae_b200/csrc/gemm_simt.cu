@@ -169,15 +169,60 @@ gemm_simt_kernel(const float* __restrict__ A, const float* __restrict__ Bm, cons
     }
 }
 
+// C = act(sum_z ws[z] + bias), partials added in the order z = 0..S-1 (deterministic).  Eight loads are in flight before the
+// first add: the S loads of an element are independent, only the adds are ordered (the plain loop paid one L2 round trip per
+// partial: 9 us per launch, 11 launches per C2 step).  VEC: 4 consecutive elements per thread (MN, N multiples of 4).
+template <bool VEC>
 __global__ void __launch_bounds__(256)
 splitk_reduce_kernel(const float* __restrict__ ws, const float* __restrict__ bias, float* __restrict__ C, long MN,
                      int N, int S, int act) {
-    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < MN; i += (long)gridDim.x * blockDim.x) {
-        float s = 0.f;
-        for (int z = 0; z < S; ++z) s += ws[(long)z * MN + i];
-        if (bias) s += bias[i % N];
-        C[i] = apply_act(s, act);
+    if (VEC) {
+        const long MN4 = MN >> 2;
+        const float4* w4 = reinterpret_cast<const float4*>(ws);
+        for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < MN4; i += (long)gridDim.x * blockDim.x) {
+            float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+            int z = 0;
+            for (; z + 8 <= S; z += 8) {
+                float4 v[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) v[u] = __ldcs(w4 + (long)(z + u) * MN4 + i);
+#pragma unroll
+                for (int u = 0; u < 8; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
+            }
+            for (; z < S; ++z) {
+                const float4 v = __ldcs(w4 + (long)z * MN4 + i);
+                s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+            }
+            if (bias) {
+                const int n = (int)((i * 4) % N);
+                s.x += bias[n]; s.y += bias[n + 1]; s.z += bias[n + 2]; s.w += bias[n + 3];
+            }
+            reinterpret_cast<float4*>(C)[i] = make_float4(apply_act(s.x, act), apply_act(s.y, act), apply_act(s.z, act), apply_act(s.w, act));
+        }
+    } else {
+        for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < MN; i += (long)gridDim.x * blockDim.x) {
+            float s = 0.f;
+            int z = 0;
+            for (; z + 8 <= S; z += 8) {
+                float v[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) v[u] = __ldcs(ws + (long)(z + u) * MN + i);
+#pragma unroll
+                for (int u = 0; u < 8; ++u) s += v[u];
+            }
+            for (; z < S; ++z) s += __ldcs(ws + (long)z * MN + i);
+            if (bias) s += bias[i % N];
+            C[i] = apply_act(s, act);
+        }
     }
+}
+
+static void splitk_reduce_launch(const float* ws, const float* bias, float* C, long MN, int N, int S, int act, cudaStream_t st) {
+    const bool vec = (N % 4 == 0) && ((((uintptr_t)ws | (uintptr_t)C) & 15) == 0);
+    const long work = vec ? MN / 4 : MN;
+    const int grid = (int)min((long)MMVAE_NUM_SMS * 8, (work + 255) / 256);
+    if (vec) splitk_reduce_kernel<true><<<grid, 256, 0, st>>>(ws, bias, C, MN, N, S, act);
+    else splitk_reduce_kernel<false><<<grid, 256, 0, st>>>(ws, bias, C, MN, N, S, act);
 }
 
 static int pick_splits(int M, int N, int K, int BN) {
@@ -197,8 +242,7 @@ long mmvae_gemm_simt_workspace_bytes(int M, int N, int K) {
 }
 
 void mmvae_splitk_reduce(const float* ws, const float* bias, float* C, long MN, int N, int S, int act, cudaStream_t st) {
-    const int grid = (int)min((long)MMVAE_NUM_SMS * 4, (MN + 255) / 256);
-    splitk_reduce_kernel<<<grid, 256, 0, st>>>(ws, bias, C, MN, N, S, act);
+    splitk_reduce_launch(ws, bias, C, MN, N, S, act, st);
 }
 
 template <int BN>
@@ -222,9 +266,7 @@ int mmvae_gemm_simt(const float* A, const float* B, const float* bias, float* C,
     else launch_simt<128>(A, B, bias, C, workspace, M, N, K, a_kmajor, b_kmajor, act, S, st);
     MMVAE_LAUNCH_CHECK("gemm_simt");
     if (S > 1) {
-        const long MN = (long)M * N;
-        const int grid = (int)min((long)MMVAE_NUM_SMS * 4, (MN + 255) / 256);
-        splitk_reduce_kernel<<<grid, 256, 0, st>>>(workspace, bias, C, MN, N, S, act);
+        splitk_reduce_launch(workspace, bias, C, (long)M * N, N, S, act, st);
         MMVAE_LAUNCH_CHECK("splitk_reduce");
     }
     return 0;
