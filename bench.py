@@ -277,33 +277,39 @@ def timed(fn, steps, dist_on):
     return ms.item()
 
 
-def roofline_of(agg, total, peak):
-    """The roofline object of the dominant KERNEL of a profiled pass: the entry point with the largest summed CUDA-event time
-    among those that launch one kernel.  achieved = ALGORITHMIC flops (2MNK of the contraction; tensor-bound kernels) or
-    bytes (HBM-bound ones) of its launches / their summed time; peak = MEASURED_PEAKS.json (sustained bf16 / copy)."""
+def roofline_of(agg, total, peak, top_n=6):
+    """Roofline objects of the KERNELS of a profiled pass (entry points that launch one kernel), largest summed CUDA-event time
+    first; the first one is the line's `roofline`, the list its `rooflines`.  achieved = ALGORITHMIC flops (2MNK of the
+    contraction; tensor-bound kernels) or bytes (HBM-bound ones) of its launches / their summed time; peak =
+    MEASURED_PEAKS.json (sustained bf16 / copy)."""
     traffic = load_traffic()
     cand = {k: a for k, a in agg.items() if k in KERNEL_OF and (a["flop"] > 0 or a["byte"] > 0)}
-    if not cand:
-        return None
-    top = max(cand, key=lambda k: cand[k]["ms"])
-    a, kern = cand[top], KERNEL_OF[top]
-    tr = traffic.get(kern, {}) if isinstance(traffic.get(kern), dict) else {}
-    if a["flop"] > 0:
-        ach = a["flop"] / (a["ms"] * 1e-3) / 1e12
-        roof = {"kernel": kern, "entry_point": top, "bound": "tensor", "achieved": ach, "peak": peak["tflops"], "unit": "TFLOP/s",
-                "frac": ach / peak["tflops"]}
-        note = ("algorithmic 2MNK of the kernel's launches in one pass / their summed CUDA-event time; peak = "
-                f"{peak['which']} dense bf16 (sustained). The kernel computes hi*hi + hi*mid + mid*hi on bf16 pieces (3 MMAs per "
-                "algorithmic MMA), so its MMA-work fraction is 3 x frac")
-    else:
-        ach = a["byte"] / (a["ms"] * 1e-3) / 1e9
-        roof = {"kernel": kern, "entry_point": top, "bound": "hbm", "achieved": ach, "peak": peak["hbm_gbs"], "unit": "GB/s",
-                "frac": ach / peak["hbm_gbs"]}
-        note = f"algorithmic bytes of the kernel's launches in one pass / their summed CUDA-event time; peak = {peak['which']} copy bandwidth"
-    roof.update({"traffic": tr.get("dram_bytes_per_launch"), "launches": a["n"], "us_per_launch": round(1e3 * a["ms"] / a["n"], 1),
-                 "share_of_pass": round(a["ms"] / total, 4), "tensor_pipe_active_ncu_pct": tr.get("tensor_pipe_active_pct"),
-                 "note": note + "; traffic / tensor_pipe_active_ncu_pct: ncu --set full of the same kernel (profiles/traffic.json), null if absent"})
-    return roof
+    out = []
+    for top in sorted(cand, key=lambda k: -cand[k]["ms"])[:top_n]:
+        a, kern = cand[top], KERNEL_OF[top]
+        tr = traffic.get(kern, {}) if isinstance(traffic.get(kern), dict) else {}
+        if a["flop"] > 0:
+            ach = a["flop"] / (a["ms"] * 1e-3) / 1e12
+            roof = {"kernel": kern, "entry_point": top, "bound": "tensor", "achieved": ach, "peak": peak["tflops"], "unit": "TFLOP/s",
+                    "frac": ach / peak["tflops"]}
+            how = {"gemm_tc_kernel": "3xTF32: three tf32 MMAs per algorithmic MMA, and tf32 runs at half the bf16 rate, so its "
+                                     "MMA-work fraction is 6 x frac",
+                   "gemm_simt_kernel": "exact fp32 on the FMA pipes (no tensor cores): the tensor peak is only the common scale",
+                   "gemm_small_kernel": "exact fp32 on the FMA pipes, latency-bound sizes: the tensor peak is only the common scale",
+                   "gemm_skinny_kernel": "K <= 32: store-bound, the tensor peak is only the common scale"}.get(
+                kern, "bf16x3: hi*hi + hi*mid + mid*hi on bf16 pieces (3 MMAs per algorithmic MMA), so its MMA-work fraction is 3 x frac")
+            note = ("algorithmic 2MNK of the kernel's launches in one pass / their summed CUDA-event time; peak = "
+                    f"{peak['which']} dense bf16 (sustained). " + how)
+        else:
+            ach = a["byte"] / (a["ms"] * 1e-3) / 1e9
+            roof = {"kernel": kern, "entry_point": top, "bound": "hbm", "achieved": ach, "peak": peak["hbm_gbs"], "unit": "GB/s",
+                    "frac": ach / peak["hbm_gbs"]}
+            note = f"algorithmic bytes of the kernel's launches in one pass / their summed CUDA-event time; peak = {peak['which']} copy bandwidth"
+        roof.update({"traffic": tr.get("dram_bytes_per_launch"), "launches": a["n"], "us_per_launch": round(1e3 * a["ms"] / a["n"], 1),
+                     "share_of_pass": round(a["ms"] / total, 4), "tensor_pipe_active_ncu_pct": tr.get("tensor_pipe_active_pct"),
+                     "note": note + "; traffic / tensor_pipe_active_ncu_pct: ncu --set full of the same kernel (profiles/traffic.json), null if absent"})
+        out.append(roof)
+    return out
 
 
 def profile_pass(fn):
@@ -494,8 +500,9 @@ def run_b200(args):
     }
     prof = profile_step(trainer, batches[0], peak, args.detail)      # every rank: the step contains the all-reduce
     if rank == 0:
-        roof, shares, calls, prof_ms = prof
-        line["roofline"] = roof
+        roofs, shares, calls, prof_ms = prof
+        line["roofline"] = roofs[0] if roofs else None
+        line["rooflines"] = roofs
         line["kernel_shares"] = shares
         line["profiled_step_ms"] = prof_ms
     ev = None
@@ -593,7 +600,9 @@ def run_eval(model, dev, n, peak, dist_on=False):
     agg, total, _ = profile_pass(lambda: [P.conditional_likelihood(model, small, 0, 1, K=1000, batch_size_K=100, axis="batch"),
                                           P.conditional_likelihood(model, small, 1, 0, K=1000, batch_size_K=100, axis="batch"),
                                           P.joint_likelihood(model, small, K=1000, batch_size_K=100, axis="batch")])
-    ev["roofline"] = roofline_of(agg, total, peak)
+    roofs = roofline_of(agg, total, peak)
+    ev["roofline"] = roofs[0] if roofs else None
+    ev["rooflines"] = roofs
     ev["kernel_shares"] = {k: {"ms": round(a["ms"], 4), "launches": a["n"], "share": round(a["ms"] / total, 4)}
                            for k, a in sorted(agg.items(), key=lambda kv: -kv[1]["ms"])[:12]}
     return ev

@@ -409,44 +409,57 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                 // instructions in the warps (they were the bottleneck of the kernel: tools/ts_trace.py).
                 { TS_T0(); mbar_wait(tfull + acc, use & 1); TS_T1(0); }
                 tc_fence_after_sync();
-                const bool issuer = (warp == 11 && lane == 0);
-#pragma unroll 1
-                for (int slot = 0; slot < 4; ++slot) {
+                // every warp stores its own 32 pixels (4 KB, one box of the per-warp tensor map): no barrier between the warps
+                const int R0 = lane_base, n_w = t * IMGS + R0 / HW, i_w = (R0 % HW) / W;
+                // chunk j = 32 accumulator columns: slot j / (NB/32), channels (j % (NB/32))*32.  The load of chunk j+1 is in
+                // flight while chunk j is processed (tensor memory reads run at 64 B/clk: 256 clocks per chunk).
+                constexpr int CPS = NB / 32, NCH = 4 * CPS;
+                auto process = [&](uint32_t* r, int j) {
+                    const int slot = j / CPS, cc = (j % CPS) * 32;
                     const int py = slot >> 1, px = (slot & 1) ^ py;                  // Gray slot -> (py, px)
+                    float v[32];
 #pragma unroll
-                    for (int cc = 0; cc < NB; cc += 32) {
-                        float v[32];
-                        tmem_ld_32x32(tb + (uint32_t)(slot * NB + cc), v);
-                        if (slot == 3 && cc + 32 == NB) {
-                            tc_fence_before_sync();
-                            __syncwarp();
-                            if (lane == 0) mbar_arrive(tempty + acc);
-                        }
-#pragma unroll
-                        for (int c = 0; c < 8; ++c) {
-                            const float4 b4 = *reinterpret_cast<const float4*>(bias_s + cc + 4 * c);        // broadcast
-                            v[4 * c] += b4.x; v[4 * c + 1] += b4.y; v[4 * c + 2] += b4.z; v[4 * c + 3] += b4.w;
-                        }
-                        if (ar.act == MMVAE_ACT_RELU) {
-#pragma unroll
-                            for (int c = 0; c < 32; ++c) v[c] = fmaxf(v[c], 0.f);
-                        } else if (ar.act == MMVAE_ACT_SIGMOID) {
-#pragma unroll
-                            for (int c = 0; c < 32; ++c) v[c] = 1.f / (1.f + expf(-v[c]));
-                        }
-                        if (issuer) bulk_wait_group_read0();                 // the previous store has read the tile
-                        asm volatile("bar.sync 2, 128;" ::: "memory");
-#pragma unroll
-                        for (int c = 0; c < 8; ++c)
-                            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((uint32_t)(c ^ my_sw) << 4)), "f"(v[4 * c]),
-                                         "f"(v[4 * c + 1]), "f"(v[4 * c + 2]), "f"(v[4 * c + 3]) : "memory");
-                        fence_proxy_async_smem();
-                        asm volatile("bar.sync 3, 128;" ::: "memory");
-                        if (issuer && !(ar.dbg & 1)) {
-                            tma_store_5d(&tmap_y, smem_u32(bars) + 1024, px * NB + cc, 0, py, 0, t * IMGS);
-                            bulk_commit_group();
-                        }
+                    for (int c = 0; c < 8; ++c) {
+                        const float4 b4 = *reinterpret_cast<const float4*>(bias_s + cc + 4 * c);        // broadcast
+                        v[4 * c] = __uint_as_float(r[4 * c]) + b4.x; v[4 * c + 1] = __uint_as_float(r[4 * c + 1]) + b4.y;
+                        v[4 * c + 2] = __uint_as_float(r[4 * c + 2]) + b4.z; v[4 * c + 3] = __uint_as_float(r[4 * c + 3]) + b4.w;
                     }
+                    if (ar.act == MMVAE_ACT_RELU) {
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) v[c] = fmaxf(v[c], 0.f);
+                    } else if (ar.act == MMVAE_ACT_SIGMOID) {
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) v[c] = 1.f / (1.f + expf(-v[c]));
+                    }
+                    if (lane == 0) bulk_wait_group_read0();              // the warp's previous store has read its rows
+                    __syncwarp();
+#pragma unroll
+                    for (int c = 0; c < 8; ++c)
+                        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((uint32_t)(c ^ my_sw) << 4)), "f"(v[4 * c]),
+                                     "f"(v[4 * c + 1]), "f"(v[4 * c + 2]), "f"(v[4 * c + 3]) : "memory");
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0 && !(ar.dbg & 1)) {
+                        tma_store_5d(&tmap_y, pad, px * NB + cc, 0, py, i_w, n_w);
+                        bulk_commit_group();
+                    }
+                };
+                uint32_t ra[32], rb[32];
+                tmem_ld_32x32_nowait(tb, ra);
+#pragma unroll 1
+                for (int j = 0; j < NCH; j += 2) {
+                    tmem_ld_wait_regs(ra);
+                    tmem_ld_32x32_nowait(tb + (uint32_t)((j + 1) * 32), rb);
+                    process(ra, j);
+                    tmem_ld_wait_regs(rb);
+                    if (j + 2 < NCH) {
+                        tmem_ld_32x32_nowait(tb + (uint32_t)((j + 2) * 32), ra);
+                    } else {                                             // every column of the accumulator is in registers
+                        tc_fence_before_sync();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(tempty + acc);
+                    }
+                    process(rb, j + 1);
                 }
             } else {
                 const bool use_mask = mask != nullptr;
@@ -493,7 +506,7 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                 }
             }
         }
-        if (MODE == TS_FWD && warp == 11 && lane == 0) bulk_wait_group0();
+        if (MODE == TS_FWD && lane == 0) bulk_wait_group0();
         if (warp == 11) TS_TRACE_OUT(4);
     }
     tc_fence_before_sync();
@@ -506,7 +519,7 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
 
 static bool ts_geometry(int H, int W) {
     const int HW = H * W;
-    return H >= 2 && W >= 2 && HW <= 128 && 128 % HW == 0 && W + 2 <= 256 && H + 2 <= 256;
+    return H >= 2 && W >= 2 && W <= 32 && HW <= 128 && 128 % HW == 0 && W + 2 <= 256 && H + 2 <= 256;
 }
 
 // shared-memory plan of convt_ts_kernel: weight slots (resident or streaming) + at least two halo tiles
@@ -650,13 +663,16 @@ extern "C" int mmvae_convt_ts_fwd(const float* x, const void* wf, const float* b
     const int rows = IMGS * (H + 2) * (W + 2);
     cudaStream_t st = (cudaStream_t)stream;
     // y as a rank-5 tensor [Nimg][H][py][W][px*Cout + co]: one parity class x 32 channels of a pixel tile is the box
-    // {32, W, 1, H, IMGS} at {px*Cout + c0, 0, py, 0, n0}; images past Nimg are clipped by the TMA
+    // {32, W, 1, rows, images} of ONE WARP's 32 pixels at {px*Cout + c0, 0, py, i0, n}; images past Nimg are clipped by the TMA
     CUtensorMap ty;
     {
         cuuint64_t yd[5] = {(cuuint64_t)2 * Cout, (cuuint64_t)W, 2u, (cuuint64_t)H, (cuuint64_t)Nimg};
         cuuint64_t ys[4] = {(cuuint64_t)2 * Cout * 4, (cuuint64_t)2 * W * Cout * 4, (cuuint64_t)4 * W * Cout * 4,
                             (cuuint64_t)4 * H * W * Cout * 4};
-        cuuint32_t yb[5] = {32u, (cuuint32_t)W, 1u, (cuuint32_t)H, (cuuint32_t)IMGS}, ye[5] = {1u, 1u, 1u, 1u, 1u};
+        // per-warp box: 32 consecutive pixels of the tile = 32/W image rows of one image, or 32/(H*W) whole images
+        const int HWp = H * W;
+        cuuint32_t yb[5] = {32u, (cuuint32_t)W, 1u, (cuuint32_t)(HWp >= 32 ? 32 / W : H), (cuuint32_t)(HWp >= 32 ? 1 : 32 / HWp)};
+        cuuint32_t ye[5] = {1u, 1u, 1u, 1u, 1u};
         rc = mmvae_tc_encode(&ty, 0, 5, y, yd, ys, yb, ye);
         if (rc) return mmvae_set_error(1, "convt_ts_fwd: tensor map (y) failed with %d", rc);
     }
