@@ -180,3 +180,55 @@ def test_two_rank_nccl_step_equals_one_rank():
                         "--master-port", "29541", os.path.join(root, "tools", "nccl_equality.py")], capture_output=True, text=True,
                        timeout=600, cwd=root)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_sink_with_parameters_used_twice_in_one_pass():
+    """m_jmvae_nf with a trainable joint encoder and the reconstruction terms on (fix_jencoder = fix_decoders = False,
+    no_recon = False): the joint encoder runs in objective() AND compute_kld(), every unimodal encoder in encode_raw() and
+    vae(x), every MADE once per flow call.  The first gradient of such a parameter is written by its kernel on the
+    weight-gradient stream into p.grad, the second comes back through autograd's `+=` on another stream: the two must be
+    ordered (ops._sink).  Gradients and parameters after three steps against plain autograd accumulation on one stream: equal
+    to rounding (a parameter with three uses is summed as g1 + (g2 + g3) instead of (g1 + g2) + g3; a LOST contribution would be
+    an O(1) error), and identical from run to run; then the same through graph replay."""
+    from tests.helpers import build_jmvae_nf
+    from mmvae_b200.train import Trainer
+    spec = O.spec_jnf_mnist_svhn(20, "maf", dcca=False)
+    sd = synth.make_state_dict(spec, 21)
+    B = 64
+    x = [t.cuda() for t in synth.make_inputs(spec, B, seed=22)]
+    rs = np.random.RandomState(23)
+    nz = lambda: synth.make_noise("normal", (B, 20), rs).cuda()
+    noises = [{"eps1": nz(), "eps2": nz(), "eps_uni": [nz(), nz()]} for _ in range(3)]
+
+    def run(sink, streams):
+        model = build_jmvae_nf(spec, sd, flow="maf", fix_jencoder=False, fix_decoders=False, no_recon=False, warmup=0)
+        tr = Trainer(model, "m_jmvae_nf", K=1, lr=1e-3, branch_streams=streams, grad_sink=sink, wgrad_stream=streams,
+                     distributed=False)
+        losses, g0 = [], None
+        for nz in noises:
+            losses.append(tr.step(x, noise=nz).item())
+            if g0 is None:
+                torch.cuda.synchronize()
+                g0 = tr.fp.grad.clone()
+        torch.cuda.synchronize()
+        return losses, g0, tr.fp.flat.clone(), tr
+    l0, g0, p0, _ = run(False, False)
+    assert g0.abs().max().item() > 0
+    prev = None
+    for rep in range(3):
+        l1, g1, p1, tr = run(True, True)
+        assert l1[0] == l0[0] and max(abs(a - b) / abs(b) for a, b in zip(l1, l0)) < 1e-6
+        assert rel_err(g1, g0) < 1e-7, rel_err(g1, g0)
+        assert rel_err(p1, p0) < 1e-6, rel_err(p1, p0)
+        assert prev is None or (torch.equal(g1, prev[0]) and torch.equal(p1, prev[1]))       # no race: run-to-run identical
+        prev = (g1, p1)
+    # graph replay of the same schedule: two replays on the same state as two eager steps of the plain trainer
+    _, _, _, plain = run(False, False)
+    tr.capture(x, warmup=1)
+    for _ in range(2):
+        tr.step_graph(x)
+        plain.step(x)
+    torch.cuda.synchronize()
+    assert np.isfinite(float(tr._static_loss))
+    # the RNG streams of the two trainers differ (graph-captured noise), so compare the update sizes, not the bits
+    assert rel_err(tr.fp.flat, plain.fp.flat) < 5e-2
