@@ -108,6 +108,12 @@ __device__ __forceinline__ void tmem_st_32x8(uint32_t taddr, const uint32_t* r) 
                  "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]) : "memory");
 }
 
+__device__ __forceinline__ void tmem_zero_32x32(uint32_t taddr) {          // 32 lanes x 32 columns of zeros
+    const uint32_t z = 0;
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, "
+                 "%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1};" ::"r"(taddr), "r"(z) : "memory");
+}
+
 // NB: rows of one weight block = MMA N of one class (forward: Cout) / of the tile (dgrad: Cin)
 #define TS_T0() const long long _c0 = TRACE ? clock64() : 0
 #define TS_T1(slot) do { if (TRACE) tacc[slot] += clock64() - _c0; } while (0)
@@ -131,10 +137,23 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     constexpr bool INPLACE = (MODE == TS_FWD);
     static_assert(ACC_COLS <= TS_A_COL, "accumulators overlap the A ring");
     // forward: weight blocks (class rows) of the three batches of a chunk
-    constexpr int8_t kNcls[9] = {4, 2, 2, 2, 2, 1, 1, 1, 1}, kRow[9] = {0, 4, 6, 8, 10, 12, 13, 14, 15};
-    constexpr int8_t kSlot[9] = {0, 0, 2, 1, 0, 0, 1, 2, 3}, kNc[9] = {4, 2, 2, 2, 1, 1, 1, 1, 1};
-    constexpr int8_t kDy[9] = {0, -1, 1, 0, 0, -1, -1, 1, 1}, kDx[9] = {0, 0, 0, 1, -1, -1, 1, 1, -1};
-    constexpr int8_t kB0[3] = {0, 8, 13}, kBn[3] = {8, 5, 3};
+    // Window order.  With two accumulator buffers (4*NB <= 128 columns) the centre window comes first: its MMA spans all four
+    // classes and initialises them.  With ONE buffer (NB = 64) the windows are ordered by the highest class slot they touch
+    // and every MMA accumulates: the epilogue zero-fills a class slot as soon as it has read it and releases it on its own
+    // barrier, so the next tile's first batch (slots 0, 1) starts while slots 2, 3 are still being drained (the issuer was
+    // waiting 5 of 25 k clocks per tile for the whole accumulator, tools/ts_trace.py).
+    constexpr bool SLOTREL = (MODE == TS_FWD) && NACC == 1;
+    constexpr int TWO = SLOTREL ? 7 : 4;                       // the dx = -1 window: classes in slots 0 and 3, two MMA groups
+    constexpr int8_t kRow[9] = {SLOTREL ? 0 : 0, SLOTREL ? 1 : 4, SLOTREL ? 3 : 6, SLOTREL ? 4 : 8, SLOTREL ? 6 : 10,
+                                SLOTREL ? 7 : 12, SLOTREL ? 9 : 13, SLOTREL ? 10 : 14, SLOTREL ? 12 : 15};
+    constexpr int8_t kSlot[9] = {0, 0, SLOTREL ? 1 : 2, 1, SLOTREL ? 2 : 0, SLOTREL ? 2 : 0, SLOTREL ? 3 : 1, SLOTREL ? 0 : 2,
+                                 SLOTREL ? 0 : 3};
+    constexpr int8_t kNc[9] = {SLOTREL ? 1 : 4, 2, SLOTREL ? 1 : 2, 2, 1, SLOTREL ? 2 : 1, 1, 1, SLOTREL ? 4 : 1};
+    constexpr int8_t kDy[9] = {SLOTREL ? -1 : 0, -1, SLOTREL ? -1 : 1, 0, SLOTREL ? 1 : 0, SLOTREL ? 1 : -1, SLOTREL ? 1 : -1,
+                               SLOTREL ? 0 : 1, SLOTREL ? 0 : 1};
+    constexpr int8_t kDx[9] = {SLOTREL ? -1 : 0, 0, SLOTREL ? 1 : 0, 1, SLOTREL ? 1 : -1, SLOTREL ? 0 : -1, SLOTREL ? -1 : 1,
+                               SLOTREL ? -1 : 1, SLOTREL ? 0 : -1};
+    constexpr int8_t kB0[3] = {0, SLOTREL ? 4 : 8, SLOTREL ? 9 : 13}, kBn[3] = {SLOTREL ? 4 : 8, 5, SLOTREL ? 7 : 3};
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -146,8 +165,8 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     uint64_t* done = bars + 24;            // [8]  MMAs of a batch completed (frees its A slots and weight blocks)
     uint64_t* b_full = bars + 32;          // [16] weight blocks of a batch landed
     uint64_t* tfull = bars + 48;           // [2]
-    uint64_t* tempty = bars + 50;          // [2]
-    uint32_t* tmem_slot = (uint32_t*)(bars + 52);
+    uint64_t* tempty = bars + 50;          // [2] per accumulator buffer, or [4] per class slot (SLOTREL)
+    uint32_t* tmem_slot = (uint32_t*)(bars + 56);
 
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;      // warp-uniform for the compiler (uniform registers / branches in the single-warp roles)
     const int H = ar.H, W = ar.W, HW = H * W, IMGS = 128 / HW;
@@ -158,7 +177,8 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             mbar_init(full + s, 1); mbar_init(empty + s, TS_NCONV / 32); mbar_init(a_full + s, TS_NCONV / 32); mbar_init(done + s, 1);
         }
         for (int s = 0; s < 16; ++s) mbar_init(b_full + s, 1);
-        for (int a = 0; a < 2; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 4); }
+        for (int a = 0; a < 2; ++a) mbar_init(tfull + a, 1);
+        for (int a = 0; a < 4; ++a) mbar_init(tempty + a, 4);
         mbar_fence_init();
         tma_prefetch_desc(&tmap_a);
         tma_prefetch_desc(&tmap_b);
@@ -238,13 +258,22 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         int bid = 0, ti = 0;
         for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++ti) {
             const int acc = ti % NACC, use = ti / NACC;
-            { TS_T0(); mbar_wait(tempty + acc, (use & 1) ^ 1); TS_T1(0); }
-            tc_fence_after_sync();
+            if (!SLOTREL) {
+                TS_T0(); mbar_wait(tempty + acc, (use & 1) ^ 1); TS_T1(0);
+                tc_fence_after_sync();
+            }
             const uint32_t d_acc = tmem_base_u + acc * ACC_COLS;
             for (int ck = 0; ck < ar.chunks; ++ck) {
 #pragma unroll
                 for (int b = 0; b < Bt::PER_CHUNK; ++b, ++bid) {
                     const int blk0 = (MODE == TS_FWD) ? kB0[b % 3] : 2 * b;
+                    if (SLOTREL && ck == 0 && b < 2) {          // batch 0 touches class slots 0, 1; batch 1 adds 2, 3 (zero-filled)
+                        TS_T0();
+                        mbar_wait(tempty + 2 * b, ti & 1);
+                        mbar_wait(tempty + 2 * b + 1, ti & 1);
+                        TS_T1(0);
+                        tc_fence_after_sync();
+                    }
                     { TS_T0(); mbar_wait(a_full + (bid & 7), (bid >> 3) & 1); TS_T1(1); }
                     int slot;
                     const long long _cb = TRACE ? clock64() : 0;
@@ -269,9 +298,9 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
 #pragma unroll
                         for (int kk = 0; kk < 2; ++kk) {
                             if ((ar.dbg & 8) && (ck | i | kk) != 0) break;
-                            const uint32_t first = (ck | i | kk) != 0;      // the first window of a tile spans every accumulator column
+                            const uint32_t first = SLOTREL ? 1u : (uint32_t)((ck | i | kk) != 0);      // the first window of a tile spans every accumulator column
 #pragma unroll
-                            for (int gi = 0; gi < ((MODE == TS_FWD && i == 4) ? 2 : 1); ++gi) {
+                            for (int gi = 0; gi < ((MODE == TS_FWD && i == TWO) ? 2 : 1); ++gi) {
                                 const uint32_t col = (MODE == TS_FWD) ? (gi ? 3 : kSlot[i % 9]) * NB : 0;
                                 const uint64_t dbg = db + (uint64_t)(gi * (BLOCK_BYTES >> 4) + kk * 2);
                                 umma_bf16_ts3_elect(d_acc + col, a_col + kk * 8, a_col + 16 + kk * 8, dbg, idesc, first);   // hi*hi, hi*mid, mid*hi
@@ -398,6 +427,16 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         const uint32_t my_row = pad + lane * 128, my_sw = lane & 7;
         const int tr_c = lane & 7, tr_r0 = lane >> 3;                    // transposed role: chunk tr_c of rows tr_r0 + 4k
         int ti = 0;
+        if (SLOTREL) {                                           // every MMA accumulates: the accumulator starts at zero
+            const uint32_t tz = tmem_base + ((uint32_t)lane_base << 16);
+#pragma unroll
+            for (int c = 0; c < ACC_COLS; c += 32) tmem_zero_32x32(tz + (uint32_t)c);
+            tmem_st_wait();
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0)
+                for (int sl = 0; sl < 4; ++sl) mbar_arrive(tempty + sl);
+        }
         for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++ti) {
             const int acc = ti % NACC, use = ti / NACC;
             const int row0 = t * 128 + lane_base, row = row0 + lane;
@@ -445,6 +484,24 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                     }
                 };
                 uint32_t ra[32], rb[32];
+                if (SLOTREL) {
+                    // a class slot = CPS = 2 chunks: both into registers, the slot zero-filled and released, then processed
+#pragma unroll 1
+                    for (int sl = 0; sl < 4; ++sl) {
+                        tmem_ld_32x32_nowait(tb + (uint32_t)(sl * NB), ra);
+                        tmem_ld_32x32_nowait(tb + (uint32_t)(sl * NB + 32), rb);
+                        tmem_ld_wait_regs(ra);
+                        tmem_ld_wait_regs(rb);
+                        tmem_zero_32x32(tb + (uint32_t)(sl * NB));
+                        tmem_zero_32x32(tb + (uint32_t)(sl * NB + 32));
+                        tmem_st_wait();
+                        tc_fence_before_sync();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(tempty + sl);
+                        process(ra, 2 * sl);
+                        process(rb, 2 * sl + 1);
+                    }
+                } else {
                 tmem_ld_32x32_nowait(tb, ra);
 #pragma unroll 1
                 for (int j = 0; j < NCH; j += 2) {
@@ -460,6 +517,7 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                         if (lane == 0) mbar_arrive(tempty + acc);
                     }
                     process(rb, j + 1);
+                }
                 }
             } else {
                 const bool use_mask = mask != nullptr;
@@ -568,8 +626,14 @@ __global__ void convt_ts_pack_kernel(const float* __restrict__ w, uint16_t* __re
             const int py = (ky == 1 || ky == 3) ? 0 : 1, dy = (ky == 1 || ky == 2) ? 0 : (ky == 3 ? -1 : 1);
             const int px = (kx == 1 || kx == 3) ? 0 : 1, dx = (kx == 1 || kx == 2) ? 0 : (kx == 3 ? -1 : 1);
             // window index in the kernel's order and the rank q of the class among those the window feeds (ascending Gray slot)
-            const int8_t kDy[9] = {0, -1, 1, 0, 0, -1, -1, 1, 1}, kDx[9] = {0, 0, 0, 1, -1, -1, 1, 1, -1};
-            const int8_t kRow[9] = {0, 4, 6, 8, 10, 12, 13, 14, 15};
+            const bool slotrel = Cout > 32;                  // the window order of convt_ts_kernel's single-accumulator form
+            const int8_t kDyA[9] = {0, -1, 1, 0, 0, -1, -1, 1, 1}, kDxA[9] = {0, 0, 0, 1, -1, -1, 1, 1, -1};
+            const int8_t kRowA[9] = {0, 4, 6, 8, 10, 12, 13, 14, 15};
+            const int8_t kDyB[9] = {-1, -1, -1, 0, 1, 1, 1, 0, 0}, kDxB[9] = {-1, 0, 1, 1, 1, 0, -1, -1, 0};
+            const int8_t kRowB[9] = {0, 1, 3, 4, 6, 7, 9, 10, 12};
+            const int8_t* kDy = slotrel ? kDyB : kDyA;
+            const int8_t* kDx = slotrel ? kDxB : kDxA;
+            const int8_t* kRow = slotrel ? kRowB : kRowA;
             int sh = 0;
             while (kDy[sh] != dy || kDx[sh] != dx) ++sh;
             const int gslot = py * 2 + (px ^ py);
