@@ -20,7 +20,7 @@ from .networks import Decoder_AE_MLP, Decoder_VAE_SVHN, Encoder_VAE_MLP, Encoder
 from .vaes import VAEConfig, draw_noise, laplace_VAE, my_VAE
 
 dist_dict = {"normal": dist.Normal, "laplace": dist.Laplace, "bernoulli": dist.Bernoulli}
-EVAL_MAX_ROWS = 32768          # decoder rows per evaluator chunk (bounds the lowering buffers to a few GB)
+EVAL_MAX_ROWS = 65536          # decoder rows per evaluator chunk (bounds the activation buffers to ~5 GB; 32768 measured 1.5 % slower at C4)
 
 
 class Multi_VAES(nn.Module):
