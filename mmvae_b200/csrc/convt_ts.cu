@@ -10,15 +10,21 @@
 //     clocks tf32 needs for K = 8; the dropped terms (mid*mid, hi*lo, lo*hi) are <= 3 * 2^-18 of |a||b| per product;
 //   * ONE halo tile per 128-pixel tile and 32-channel chunk arrives by TMA (out-of-image rows / columns = the unit's zero fill);
 //     the 9 (forward) or 4x4 (dgrad, per output-parity class) shifted windows are sub-views of it;
-//   * eight converter warps split the landed fp32 tile IN PLACE into packed bf16 pairs (row = 32 fp32 -> 16 hi words | 16 mid
-//     words, same 128 bytes, same 128-byte swizzle) and then copy, per shifted window, each pixel's row into the TMEM lane that
-//     owns the pixel (8 conflict-free 128-bit shared loads + one tcgen05.st of 32 columns): no conversion arithmetic per window;
+//   * eight converter warps copy, per shifted window, each pixel's row into the TMEM lane that owns the pixel (conflict-free
+//     128-bit shared loads + tcgen05.st).  Forward: the landed fp32 tile is first split IN PLACE into packed bf16 pairs (row =
+//     32 fp32 -> 16 hi words | 16 mid words, same 128 bytes, same swizzle), so the 9 window copies carry no arithmetic; dgrad
+//     (4 windows per class tile): the split happens inside the copy -- no write-back, barrier or proxy fence;
 //   * weights are prepared once per step as bf16 (hi | mid) K-major rows (mmvae_convt_ts_pack_weights) and stay RESIDENT in
-//     shared memory when they fit (128 KB: the Cin*Cout = 2048 layer), else stream through a block ring.
+//     shared memory when they fit (128 KB: the Cin*Cout = 2048 layer), else stream through a block ring;
+//   * the issuing warp runs on the UNIFORM datapath (warp index through a lane-0 shuffle, TMEM addresses off a literal base):
+//     one UTCHMMA per MMA, no election / R2UR chain per instruction;
+//   * forward epilogue: TMEM -> registers -> bias + activation -> the warp's swizzled 4 KB tile -> one TMA store per 32-channel
+//     chunk of a parity class (y as a rank-5 tensor); dgrad epilogue: warp-private transposition pads, ReLU mask fused.
 // Warp roles (480 threads): 0 = activation (A) TMA producer, 1 = weight (B) TMA producer, 2 = TMEM owner + MMA issuer,
-// 3-10 = converters (two warps per TMEM lane quarter, alternating windows), 11-14 = epilogue.
-// TMEM: columns 0..255 accumulators (double-buffered when they need <= 128 columns), 256..511 a ring of eight A slots
-// (32 columns: 16 hi-pair + 16 mid-pair columns = 32 channels).
+// 3-10 = converters (two warps per TMEM lane quarter, each half of the 32 channels), 11-14 = epilogue.
+// TMEM: columns 0..255 accumulators (double-buffered when they need <= 128 columns; otherwise released per class slot),
+// 256..511 a ring of eight A slots (32 columns: 16 hi-pair + 16 mid-pair columns = 32 channels).
+// Where the clocks of a tile go: tools/ts_trace.py (TRACE instantiation, clock64 around every wait of every role).
 #include <cuda.h>
 #include <cudaTypedefs.h>
 #include "common.cuh"
