@@ -431,6 +431,8 @@ int mmvae_convt_l4_fwd_tc(const float* x, const float* w, const float* bias, flo
 int mmvae_convt_l4_dgrad_tc(const float* g, const float* y_act, const float* w, const float* x_mask, float* gx, int N,
                             int H, int W, int Cin, int Cout, int act, cudaStream_t st);          // convt_l4_tc.cu
 
+int mmvae_convt_l4_wgrad_ts(const float* x, const float* g, const float* y_act, float* part, int P, int N, int H, int W, int Cin,
+                            int Cout, int act, cudaStream_t st);
 int mmvae_convt_l4_wgrad_tc(const float* x, const float* g, const float* y_act, float* part, int P, int N, int H, int W,
                             int Cin, int Cout, int act, cudaStream_t st);                        // convt_l4_tc.cu
 int mmvae_tc_dbg_bits();                                                                         // gemm_tc.cu
@@ -531,7 +533,10 @@ extern "C" int mmvae_convt_small_wgrad(const float* x, const float* g, const flo
     MMVAE_REQUIRE(mmvae_convt_small_supported(H, W, Cin, Cout) == 2, "convt_small_wgrad: unsupported shape (needs Cin == 32)");
     const size_t smem = csw_smem_bytes(H, W, Cin, Cout, y_act != nullptr);
     const int P = cs_wgrad_ctas(N);
-    int rc = (mmvae_tc_dbg_bits_() & 16384) ? mmvae_convt_l4_wgrad_tc(x, g, y_act, workspace, P, N, H, W, Cin, Cout, act, (cudaStream_t)stream) : -1;
+    // the tensor-memory kernel of convt_ts.cu (bf16x3) unless debug bit 32 asks for the fp32-FMA kernel; bit 16384: the
+    // first-generation shared-memory-operand tcgen05 kernel (slower than either, kept for comparison)
+    int rc = (mmvae_tc_dbg_bits_() & 16384) ? mmvae_convt_l4_wgrad_tc(x, g, y_act, workspace, P, N, H, W, Cin, Cout, act, (cudaStream_t)stream)
+             : ((mmvae_tc_dbg_bits_() & 32) ? -1 : mmvae_convt_l4_wgrad_ts(x, g, y_act, workspace, P, N, H, W, Cin, Cout, act, (cudaStream_t)stream));
     if (rc > 0) return rc;
     if (rc < 0) {
         rc = CS_SWITCH(Cout, cs_wgrad, x, g, y_act, workspace, P, N, H, W, act, smem, (cudaStream_t)stream);

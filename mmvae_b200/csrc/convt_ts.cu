@@ -1264,3 +1264,294 @@ extern "C" int mmvae_convt_ts_wgrad(const float* x, const float* g, float* gw, f
     cudaStream_t st = (cudaStream_t)stream;
     return TW_DISPATCH(tw_launch, x, g, gw, gb, workspace, workspace_bytes, Nimg, H, W, st);
 }
+
+// ============================================================================================== last-layer weight gradient
+// ConvTranspose2d(32, Cout <= 8, 4, 2, 1) on a 16x16 grid (encoders.py:124-128, the image-producing layer): weight + bias
+// gradient with the same operand scheme as convt_ts_wgrad_kernel -- g transposed into TENSOR MEMORY by converter threads (one
+// TMEM lane = one (tap, co) row of the lowered gradient, 16*Cout = 48 of 128 rows used, 12 per lane quarter so that every
+// converter warp has work), x split in place into a bf16 MN-major operand, three N = 32 MMAs per 16-pixel k-block -- but with g
+// as the NCHW image gradient: per image g (and the layer output y) arrive by two bulk copies, the converter warps form the
+// pre-activation gradient g * act'(y) once into a zero-bordered shared-memory image (and the bias gradient from it), and a lane
+// reads its 16 pixels of a k-block (one row of the 16x16 grid) at stride 2 from that image.  Replaces the fp32-FMA kernel of
+// convt_small.cu (154 us at 7680 images, the largest kernel of the C2 step) for this shape; partials are written in the
+// layout of convt_small_wgrad_reduce (one per CTA: chains of 12 pixel tiles are drained into registers, the TMEM accumulate
+// truncates), so the fixed-order reduction is shared.
+#define L4W_NXS 6                      // x tiles (128 pixels x 32 ci, 16 KB) in flight
+#define L4W_GP 36                      // pitch of the bordered pre-activation-gradient image (34 rows x 36 floats per channel)
+#define L4W_CHAIN 12                   // pixel tiles per TMEM accumulation chain (24 MMAs each)
+#define L4W_NGB 4                      // g / y images in flight
+
+struct L4wArgs {
+    const float* g;
+    const float* y;
+    float* part;
+    int n_img, act, imgs_per_cta, dbg;
+};
+
+__device__ __forceinline__ float l4w_dact(float y, int act) {
+    if (act == MMVAE_ACT_RELU) return y > 0.f ? 1.f : 0.f;
+    if (act == MMVAE_ACT_SIGMOID) return y * (1.f - y);
+    return 1.f;
+}
+
+template <int COUT>
+__global__ void __launch_bounds__(TW_THREADS, 1)
+convt_l4w_ts_kernel(const __grid_constant__ CUtensorMap tmap_x, const L4wArgs ar) {
+    constexpr int ROWS = 16 * COUT, RPQ = (ROWS + 3) / 4, IMG = COUT * 1024, PLANE = 34 * L4W_GP, TOT = 32 * COUT * 16;
+    static_assert(RPQ <= 32, "too many output channels");
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* xring = smem;                                           // [L4W_NXS][16384]
+    float* graw = (float*)(xring + L4W_NXS * 16384);                 // [L4W_NGB][g IMG | y IMG]
+    float* gs = graw + L4W_NGB * 2 * IMG;                            // [COUT][34][L4W_GP], border stays zero
+    uint64_t* bars = (uint64_t*)(gs + ((COUT * PLANE + 3) & ~3));
+    uint64_t* graw_full = bars;            // [4]
+    uint64_t* graw_empty = bars + 4;       // [4] count 8
+    uint64_t* x_full = bars + 8;           // [8]
+    uint64_t* x_ready = bars + 16;         // [8] count 4: split in place by the epilogue warps
+    uint64_t* x_empty = bars + 24;         // [8]
+    uint64_t* a_full = bars + 32;          // [4] count 8
+    uint64_t* done = bars + 36;            // [4]
+    uint64_t* tfull = bars + 40;           // [2]
+    uint64_t* tempty = bars + 42;          // [2] count 4
+    uint32_t* tmem_slot = (uint32_t*)(bars + 44);
+
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+    const int n0 = min(ar.n_img, (int)blockIdx.x * ar.imgs_per_cta), n1 = min(ar.n_img, n0 + ar.imgs_per_cta);
+    const int ntiles = 2 * (n1 - n0), nparts = (ntiles + L4W_CHAIN - 1) / L4W_CHAIN;
+
+    for (int e = threadIdx.x; e < COUT * PLANE; e += TW_THREADS) gs[e] = 0.f;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < 2; ++s) { mbar_init(tfull + s, 1); mbar_init(tempty + s, 4); }
+        for (int s = 0; s < L4W_NGB; ++s) { mbar_init(graw_full + s, 1); mbar_init(graw_empty + s, 8); }
+        for (int s = 0; s < 8; ++s) { mbar_init(x_full + s, 1); mbar_init(x_ready + s, 4); mbar_init(x_empty + s, 1); }
+        for (int s = 0; s < 4; ++s) { mbar_init(a_full + s, 8); mbar_init(done + s, 1); }
+        mbar_fence_init();
+        tma_prefetch_desc(&tmap_x);
+    }
+    if (warp == 2) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== g / y producer: one image = two bulk copies =====
+        const uint32_t bytes = (uint32_t)(IMG * 4 * (ar.y ? 2 : 1));
+        for (int n = n0, it = 0; n < n1; ++n, ++it) {
+            const int buf = it % L4W_NGB;
+            mbar_wait_relaxed(graw_empty + buf, ((it / L4W_NGB) & 1) ^ 1);
+            if (ar.dbg & 16) { if (lane == 0) mbar_arrive(graw_full + buf); __syncwarp(); continue; }
+            if (lane == 0) {
+                mbar_arrive_expect_tx(graw_full + buf, bytes);
+                bulk_load_1d(graw + buf * 2 * IMG, ar.g + (long)n * IMG, IMG * 4, graw_full + buf);
+                if (ar.y) bulk_load_1d(graw + buf * 2 * IMG + IMG, ar.y + (long)n * IMG, IMG * 4, graw_full + buf);
+            }
+            __syncwarp();
+        }
+    } else if (warp == 1) {
+        // ===== x producer: [128 pixels x 32 ci] per tile, two tiles per image =====
+        const uint32_t x_ring = smem_u32(xring);
+        for (int ti = 0; ti < ntiles; ++ti) {
+            const int s = ti % L4W_NXS, ph = (ti / L4W_NXS) & 1;
+            mbar_wait_relaxed(x_empty + s, ph ^ 1);
+            mbar_arrive_expect_tx_elect(x_full + s, 16384);
+            tma_load_2d_elect(x_ring + s * 16384, &tmap_x, x_full + s, 0, (n0 + (ti >> 1)) * 256 + (ti & 1) * 128);
+        }
+    } else if (warp == 2) {
+        // ===== MMA issuer (uniform datapath, literal TMEM base: see convt_ts_kernel) =====
+        if (tmem_base != 0) __trap();
+        constexpr uint32_t idesc = umma_idesc_bf16(128, 32, 0, 1);             // B MN-major
+        const uint64_t dx0 = umma_smem_desc(smem_u32(xring), 1024, 1024, 2);
+        int gb = 0, part = 0;
+        for (int ti = 0; ti < ntiles; ++ti) {
+            const bool chain_start = (ti % L4W_CHAIN) == 0;
+            const int acc = part & 1;
+            if (chain_start && part >= 2) {                                    // the epilogue has drained this buffer's previous chain
+                mbar_wait(tempty + acc, ((part >> 1) - 1) & 1);
+                tc_fence_after_sync();
+            }
+            const int s = ti % L4W_NXS, ph = (ti / L4W_NXS) & 1;
+            mbar_wait(x_ready + s, ph);
+            tc_fence_after_sync();
+            const uint64_t dx = dx0 + (uint64_t)(s * (16384 >> 4));
+#pragma unroll 1
+            for (int b = 0; b < 2; ++b, ++gb) {
+                mbar_wait(a_full + (gb & 3), (gb >> 2) & 1);
+                tc_fence_after_sync();
+#pragma unroll
+                for (int at = 0; at < 4; ++at) {
+                    const int kb = 4 * b + at;
+                    const uint32_t a_col = 256u + (uint32_t)(((4 * gb + at) & (TW_A_SLOTS - 1)) * 16);
+                    const uint32_t first = !(chain_start && kb == 0);
+                    if (ar.dbg & 8) continue;
+                    umma_bf16_ts3_elect((uint32_t)(acc * 32), a_col, a_col + 8, dx + (uint64_t)(kb * (2048 >> 4)), idesc, first);
+                }
+                umma_commit_elect(done + (gb & 3));
+            }
+            umma_commit_elect(x_empty + s);
+            if (((ti + 1) % L4W_CHAIN) == 0 || ti + 1 == ntiles) { umma_commit_elect(tfull + acc); ++part; }
+        }
+    } else if (warp < 11) {
+        // ===== converters: build the pre-activation gradient image, split x, transpose g into tensor memory =====
+        const int ctid = threadIdx.x - 96, wset = (warp - 3) >> 2, quarter = warp & 3;
+        const int r = quarter * RPQ + lane;                                    // row of the lowered gradient owned by this lane
+        const bool live = lane < RPQ && r < ROWS;
+        const int tap = live ? r / COUT : 0, co = live ? r % COUT : 0, ky = tap >> 2, kx = tap & 3;
+        const uint32_t g_lane = smem_u32(gs) + (uint32_t)((co * PLANE + ky * L4W_GP + kx) * 4);
+        const uint32_t t_lane = tmem_base + ((uint32_t)(quarter * 32) << 16) + 256;
+        float bsum[COUT];
+#pragma unroll
+        for (int c = 0; c < COUT; ++c) bsum[c] = 0.f;
+        int gb = 0, pending = -1;
+        for (int n = n0, it = 0; n < n1; ++n, ++it) {
+            const int buf = it % L4W_NGB;
+            asm volatile("bar.sync 1, 256;" ::: "memory");                   // every read of the previous image's gs is done
+            mbar_wait(graw_full + buf, (it / L4W_NGB) & 1);
+            {
+                const float4* g4 = reinterpret_cast<const float4*>(graw + buf * 2 * IMG);
+                const float4* y4 = reinterpret_cast<const float4*>(graw + buf * 2 * IMG + IMG);
+                for (int i = ctid; i < IMG / 4 && !(ar.dbg & 64); i += TS_NCONV) {
+                    const int e = 4 * i, xx = e & 31, yy = (e >> 5) & 31, c = e >> 10;
+                    float4 v = g4[i];
+                    if (ar.y) {
+                        const float4 yv = y4[i];
+                        v.x *= l4w_dact(yv.x, ar.act); v.y *= l4w_dact(yv.y, ar.act); v.z *= l4w_dact(yv.z, ar.act); v.w *= l4w_dact(yv.w, ar.act);
+                    }
+                    float* d = gs + c * PLANE + (yy + 1) * L4W_GP + xx + 1;
+                    d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+                    const float sv = (v.x + v.y) + (v.z + v.w);
+#pragma unroll
+                    for (int cc = 0; cc < COUT; ++cc) bsum[cc] += (cc == c) ? sv : 0.f;
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(graw_empty + buf);
+            asm volatile("bar.sync 1, 256;" ::: "memory");                   // gs of this image is complete
+            for (int h = 0; h < 2; ++h) {
+#pragma unroll 1
+                for (int b = 0; b < 2; ++b, ++gb) {
+                    float f[2][16];
+#pragma unroll
+                    for (int a2 = 0; a2 < 2; ++a2) {
+                        const int kb = 4 * b + 2 * a2 + wset, irow = 8 * h + kb;               // row i of the 16x16 grid
+                        const uint32_t base = g_lane + (uint32_t)(2 * irow * L4W_GP * 4);
+#pragma unroll
+                        for (int k = 0; k < 16; ++k) {
+                            if (live && !(ar.dbg & 2)) asm volatile("ld.shared.f32 %0, [%1];" : "=f"(f[a2][k]) : "r"(base + (uint32_t)(8 * k)));
+                            else f[a2][k] = 0.f;
+                        }
+                    }
+                    if (pending >= 0) {
+                        tmem_st_wait();
+                        tc_fence_before_sync();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(a_full + (pending & 3));
+                    }
+                    if (gb >= 4) mbar_wait(done + (gb & 3), ((gb >> 2) - 1) & 1);
+                    tc_fence_after_sync();
+#pragma unroll
+                    for (int a2 = 0; a2 < 2; ++a2) {
+                        const int at = 2 * a2 + wset;
+                        uint32_t hm[16];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hm[j]) : "f"(f[a2][2 * j + 1]), "f"(f[a2][2 * j]));
+                            const float r0 = f[a2][2 * j] - __uint_as_float(hm[j] << 16);
+                            const float r1 = f[a2][2 * j + 1] - __uint_as_float(hm[j] & 0xffff0000u);
+                            asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hm[8 + j]) : "f"(r1), "f"(r0));
+                        }
+                        const uint32_t ta = t_lane + ((4 * gb + at) & (TW_A_SLOTS - 1)) * 16;
+                        tmem_st_32x8(ta, hm);
+                        tmem_st_32x8(ta + 8, hm + 8);
+                    }
+                    pending = gb;
+                }
+            }
+        }
+        if (pending >= 0) {
+            tmem_st_wait();
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(a_full + (pending & 3));
+        }
+        // bias partials of the 256 converter threads -> shared memory (the g staging area is free now)
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+#pragma unroll
+        for (int c = 0; c < COUT; ++c) graw[c * TS_NCONV + ctid] = bsum[c];
+    } else {
+        // ===== epilogue: chains are drained into registers; one partial per CTA at the end =====
+        const int quarter = warp & 3, r = quarter * RPQ + lane;
+        const bool live = lane < RPQ && r < ROWS;
+        float accr[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) accr[j] = 0.f;
+        // these warps also split every landed x tile in place (one row per thread) and hand it to the tensor core
+        const uint32_t x_ring = smem_u32(xring);
+        const int xrow = quarter * 32 + lane;
+        int part = 0;
+        for (int ti = 0; ti < ntiles; ++ti) {
+            const int s = ti % L4W_NXS, ph = (ti / L4W_NXS) & 1;
+            mbar_wait(x_full + s, ph);
+            if (!(ar.dbg & 4)) ts_split_row(x_ring + s * 16384 + xrow * 128, xrow & 7);
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(x_ready + s);
+            if (((ti + 1) % L4W_CHAIN) == 0 || ti + 1 == ntiles) {
+                const int acc = part & 1;
+                mbar_wait_relaxed(tfull + acc, (part >> 1) & 1);
+                tc_fence_after_sync();
+                float v[32];
+                tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * 32), v);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) accr[j] += v[j];
+                tc_fence_before_sync();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(tempty + acc);
+                ++part;
+            }
+        }
+        if (live) {
+            const int tap = r / COUT, co = r % COUT;
+            float* out = ar.part + (long)blockIdx.x * (TOT + COUT);
+#pragma unroll
+            for (int ci = 0; ci < 32; ++ci) out[(ci * COUT + co) * 16 + tap] = accr[ci];
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem_base, 512);
+    if (threadIdx.x < COUT) {                                                  // bias: fixed order over the converter threads
+        float s = 0.f;
+        for (int i = 0; i < TS_NCONV; ++i) s += graw[threadIdx.x * TS_NCONV + i];
+        ar.part[(long)blockIdx.x * (TOT + COUT) + TOT + threadIdx.x] = s;
+    }
+}
+
+// partials [P][Cin*Cout*16 + Cout] in the layout of convt_small_wgrad_reduce.  -1: not this kernel's shape.
+int mmvae_convt_l4_wgrad_ts(const float* x, const float* g, const float* y_act, float* part, int P, int N, int H, int W, int Cin,
+                            int Cout, int act, cudaStream_t st) {
+    if (!mmvae_has_tcgen05() || H != 16 || W != 16 || Cin != 32 || Cout != 3 || P < 1) return -1;
+    if ((((uintptr_t)g | (uintptr_t)x | (uintptr_t)y_act) & 15) != 0) return -1;
+    constexpr int COUT = 3;
+    CUtensorMap tx;
+    cuuint64_t xd[2] = {32u, (cuuint64_t)N * 256};
+    cuuint64_t xs[1] = {128u};
+    cuuint32_t xb[2] = {32u, 128u}, xe[2] = {1u, 1u};
+    int rc = mmvae_tc_encode(&tx, 0, 2, x, xd, xs, xb, xe);
+    if (rc) return mmvae_set_error(1, "convt_l4_wgrad_ts: tensor map (x) failed with %d", rc);
+    L4wArgs ar{};
+    ar.g = g; ar.y = y_act; ar.part = part; ar.n_img = N; ar.act = act; ar.imgs_per_cta = (N + P - 1) / P;
+    ar.dbg = mmvae_tc_dbg_bits();
+    const int smem = 1024 + L4W_NXS * 16384 + L4W_NGB * 2 * COUT * 1024 * 4 + ((COUT * 34 * L4W_GP + 3) & ~3) * 4 + 512;
+    static bool attr_done = false;
+    auto kern = convt_l4w_ts_kernel<COUT>;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return mmvae_set_error(1000 + (int)e, "convt_l4_wgrad_ts: smem attribute: %s", cudaGetErrorString(e));
+        attr_done = true;
+    }
+    kern<<<P, TW_THREADS, smem, st>>>(tx, ar);
+    MMVAE_LAUNCH_CHECK("convt_l4_wgrad_ts");
+    return 0;
+}

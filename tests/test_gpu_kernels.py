@@ -182,8 +182,9 @@ def test_convT2d_autograd(ops, cin, cout, H, s, p, act, nchw_out, N):
     else:
         rx, rw, rb = torch.autograd.grad(yr, (xd, wd, bd), gy.double())
     tol = 1.5e-5 if ts else 5e-6
+    l4w = (cin, cout, H, s, p) == (32, 3, 16, 2, 1) and nchw_out        # the image layer's weight gradient: bf16x3 (convt_l4w_ts_kernel)
     assert rel_err(gx, rx) < tol, "gx"
-    assert rel_err(gw, rw) < tol, "gw"
+    assert rel_err(gw, rw) < (1.5e-5 if l4w else tol), "gw"
     assert rel_err(gb, rb) < 5e-6, "gb"
 
 
@@ -210,8 +211,9 @@ def test_convT_last_layer_tensor_core_forward_is_deterministic_and_matches_simt(
 
 @pytest.mark.parametrize("N", [1, 7, 333, 1200])
 def test_convT_last_layer_tensor_core_wgrad(ops, N):
-    """convt_l4_wgrad_tc_kernel against fp64 autograd and the SIMT kernel (chains of 4 images per accumulator, several
-    chains per CTA at N = 1200)."""
+    """The image layer's weight gradient: convt_l4w_ts_kernel (default: g transposed into tensor memory, bf16x3, chains of 12
+    pixel tiles drained into registers), the fp32-FMA kernel (debug bit 32) and the first-generation tcgen05 kernel (bit 16384)
+    against fp64 autograd and each other; ragged image counts per CTA at N = 333, several chains per CTA at N = 1200."""
     from mmvae_b200 import _lib
     lib = _lib.load()
     x = _rand(N, 16, 16, 32, seed=5).relu().permute(0, 3, 1, 2).requires_grad_()
@@ -222,7 +224,8 @@ def test_convT_last_layer_tensor_core_wgrad(ops, N):
     yr = torch.sigmoid(F.conv_transpose2d(xd, wd, bd, stride=2, padding=1))
     rw, rb = torch.autograd.grad(yr, (wd, bd), gy.double())
     res = {}
-    for bit in (0, 16384):
+    tols = {0: 1.5e-5, 32: 5e-6, 16384: 5e-6}          # 0: tensor-memory bf16x3 kernel (convt_ts.cu), 32: fp32 FMA, 16384: first-generation tcgen05
+    for bit in (0, 32, 16384):
         old = lib.mmvae_gemm_tc_set_mode(bit << 8)
         try:
             y = ops.ConvT2dAct.apply(x, w, b, 2, 1, "sigmoid", True, False)
@@ -231,8 +234,8 @@ def test_convT_last_layer_tensor_core_wgrad(ops, N):
             assert torch.equal(res[bit][0], again[0]) and torch.equal(res[bit][1], again[1])     # deterministic
         finally:
             lib.mmvae_gemm_tc_set_mode(old)
-        assert rel_err(res[bit][0], rw) < 5e-6 and rel_err(res[bit][1], rb) < 5e-6, bit
-    assert rel_err(res[16384][0], res[0][0]) < 5e-6
+        assert rel_err(res[bit][0], rw) < tols[bit] and rel_err(res[bit][1], rb) < 5e-6, bit
+    assert rel_err(res[16384][0], res[32][0]) < 5e-6 and rel_err(res[0][0], res[32][0]) < 1.5e-5
 
 
 def test_convT2d_chain_fused_relu_backward(ops):

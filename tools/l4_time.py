@@ -42,7 +42,9 @@ for N in (7680, 32768):
     gw = torch.empty_like(w); gb = torch.empty(3, device="cuda")
     ws = torch.empty(lib.mmvae_convt_small_wgrad_workspace_bytes(N, 32, 3) // 4, device="cuda")
     mb = (2 * y.numel() + x.numel()) * 4 / 1e6
-    for dbg, tag in ((0, "wgrad SIMT direct"), (16384, "wgrad tcgen05"), (16384 | 1024, "wgrad tc, no gather"),
+    for dbg, tag in ((32, "wgrad SIMT direct"), (0, "wgrad tensor-memory (bf16x3)"), (2, "wgrad ts, no g reads"), (4, "wgrad ts, no x split"),
+                     (8, "wgrad ts, no MMAs"), (14, "wgrad ts, skeleton"), (14 | 16, "wgrad ts, skeleton, no g/y loads"), (14 | 64, "wgrad ts, skeleton, no build"),
+                     (14 | 16 | 64, "wgrad ts, skeleton, neither"), (16384, "wgrad tcgen05 (1st gen)"), (16384 | 1024, "wgrad tc, no gather"),
                      (16384 | 2048, "wgrad tc, no g_pre image"), (16384 | 4096, "wgrad tc, 1/4 of the UMMAs"),
                      (16384 | 7168, "wgrad tc, skeleton")):
         lib.mmvae_gemm_tc_set_mode(dbg << 8)
