@@ -1294,36 +1294,43 @@ __device__ __forceinline__ float l4w_dact(float y, int act) {
     return 1.f;
 }
 
+// Warp roles (480 threads).  A TMEM lane belongs to the warps with (warp % 4) == lane / 32, and the 48 rows sit in lanes 0..23 and
+// 32..55 (24 per quarter), so the EIGHT warps with warp % 4 in {0, 1} are the converters: four sets of two, one 16-pixel k-block
+// per set and batch.  2 = TMEM owner + MMA issuer, 3 = g / y producer, 6 = x producer, 7 / 10 / 11 / 14 = builders: they form the
+// pre-activation-gradient image of the next image (and the bias gradient) and split every landed x tile in place.  The accumulation chains are drained by converter set 0 (its warps own the lanes of the rows).
 template <int COUT>
 __global__ void __launch_bounds__(TW_THREADS, 1)
 convt_l4w_ts_kernel(const __grid_constant__ CUtensorMap tmap_x, const L4wArgs ar) {
-    constexpr int ROWS = 16 * COUT, RPQ = (ROWS + 3) / 4, IMG = COUT * 1024, PLANE = 34 * L4W_GP, TOT = 32 * COUT * 16;
+    constexpr int ROWS = 16 * COUT, RPQ = (ROWS + 1) / 2, IMG = COUT * 1024, PLANE = 34 * L4W_GP, TOT = 32 * COUT * 16;
     static_assert(RPQ <= 32, "too many output channels");
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* xring = smem;                                           // [L4W_NXS][16384]
     float* graw = (float*)(xring + L4W_NXS * 16384);                 // [L4W_NGB][g IMG | y IMG]
-    float* gs = graw + L4W_NGB * 2 * IMG;                            // [COUT][34][L4W_GP], border stays zero
-    uint64_t* bars = (uint64_t*)(gs + ((COUT * PLANE + 3) & ~3));
+    float* gs = graw + L4W_NGB * 2 * IMG;                            // [2][COUT][34][L4W_GP], borders stay zero
+    constexpr int GSZ = (COUT * PLANE + 3) & ~3;
+    uint64_t* bars = (uint64_t*)(gs + 2 * GSZ);
     uint64_t* graw_full = bars;            // [4]
-    uint64_t* graw_empty = bars + 4;       // [4] count 8
+    uint64_t* graw_empty = bars + 4;       // [4] count 4 (builder warps)
     uint64_t* x_full = bars + 8;           // [8]
-    uint64_t* x_ready = bars + 16;         // [8] count 4: split in place by the epilogue warps
+    uint64_t* x_ready = bars + 16;         // [8] count 4: split in place by the splitter warps
     uint64_t* x_empty = bars + 24;         // [8]
     uint64_t* a_full = bars + 32;          // [4] count 8
     uint64_t* done = bars + 36;            // [4]
     uint64_t* tfull = bars + 40;           // [2]
-    uint64_t* tempty = bars + 42;          // [2] count 4
-    uint32_t* tmem_slot = (uint32_t*)(bars + 44);
+    uint64_t* tempty = bars + 42;          // [2] count 2 (the two warps of converter set 0)
+    uint64_t* gs_full = bars + 44;         // [2] count 4: image built
+    uint64_t* gs_empty = bars + 46;        // [2] count 8: every converter warp has read it
+    uint32_t* tmem_slot = (uint32_t*)(bars + 48);
 
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int n0 = min(ar.n_img, (int)blockIdx.x * ar.imgs_per_cta), n1 = min(ar.n_img, n0 + ar.imgs_per_cta);
-    const int ntiles = 2 * (n1 - n0), nparts = (ntiles + L4W_CHAIN - 1) / L4W_CHAIN;
+    const int ntiles = 2 * (n1 - n0);
 
-    for (int e = threadIdx.x; e < COUT * PLANE; e += TW_THREADS) gs[e] = 0.f;
+    for (int e = threadIdx.x; e < 2 * GSZ; e += TW_THREADS) gs[e] = 0.f;
     if (threadIdx.x == 0) {
-        for (int s = 0; s < 2; ++s) { mbar_init(tfull + s, 1); mbar_init(tempty + s, 4); }
-        for (int s = 0; s < L4W_NGB; ++s) { mbar_init(graw_full + s, 1); mbar_init(graw_empty + s, 8); }
+        for (int s = 0; s < 2; ++s) { mbar_init(tfull + s, 1); mbar_init(tempty + s, 2); mbar_init(gs_full + s, 4); mbar_init(gs_empty + s, 8); }
+        for (int s = 0; s < L4W_NGB; ++s) { mbar_init(graw_full + s, 1); mbar_init(graw_empty + s, 4); }
         for (int s = 0; s < 8; ++s) { mbar_init(x_full + s, 1); mbar_init(x_ready + s, 4); mbar_init(x_empty + s, 1); }
         for (int s = 0; s < 4; ++s) { mbar_init(a_full + s, 8); mbar_init(done + s, 1); }
         mbar_fence_init();
@@ -1334,8 +1341,9 @@ convt_l4w_ts_kernel(const __grid_constant__ CUtensorMap tmap_x, const L4wArgs ar
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
+    const bool is_conv = (warp & 3) < 2 && warp < 14;                // warps 0,1,4,5,8,9,12,13
 
-    if (warp == 0) {
+    if (warp == 3) {
         // ===== g / y producer: one image = two bulk copies =====
         const uint32_t bytes = (uint32_t)(IMG * 4 * (ar.y ? 2 : 1));
         for (int n = n0, it = 0; n < n1; ++n, ++it) {
@@ -1349,7 +1357,7 @@ convt_l4w_ts_kernel(const __grid_constant__ CUtensorMap tmap_x, const L4wArgs ar
             }
             __syncwarp();
         }
-    } else if (warp == 1) {
+    } else if (warp == 6) {
         // ===== x producer: [128 pixels x 32 ci] per tile, two tiles per image =====
         const uint32_t x_ring = smem_u32(xring);
         for (int ti = 0; ti < ntiles; ++ti) {
@@ -1367,7 +1375,7 @@ convt_l4w_ts_kernel(const __grid_constant__ CUtensorMap tmap_x, const L4wArgs ar
         for (int ti = 0; ti < ntiles; ++ti) {
             const bool chain_start = (ti % L4W_CHAIN) == 0;
             const int acc = part & 1;
-            if (chain_start && part >= 2) {                                    // the epilogue has drained this buffer's previous chain
+            if (chain_start && part >= 2) {                                    // this buffer's previous chain has been drained
                 mbar_wait(tempty + acc, ((part >> 1) - 1) & 1);
                 tc_fence_after_sync();
             }
@@ -1392,117 +1400,59 @@ convt_l4w_ts_kernel(const __grid_constant__ CUtensorMap tmap_x, const L4wArgs ar
             umma_commit_elect(x_empty + s);
             if (((ti + 1) % L4W_CHAIN) == 0 || ti + 1 == ntiles) { umma_commit_elect(tfull + acc); ++part; }
         }
-    } else if (warp < 11) {
-        // ===== converters: build the pre-activation gradient image, split x, transpose g into tensor memory =====
-        const int ctid = threadIdx.x - 96, wset = (warp - 3) >> 2, quarter = warp & 3;
+    } else if (is_conv) {
+        // ===== converters: build the pre-activation gradient image, transpose g into tensor memory; set 0 drains the chains =====
+        const int quarter = warp & 3, wset = warp >> 2;
         const int r = quarter * RPQ + lane;                                    // row of the lowered gradient owned by this lane
         const bool live = lane < RPQ && r < ROWS;
         const int tap = live ? r / COUT : 0, co = live ? r % COUT : 0, ky = tap >> 2, kx = tap & 3;
         const uint32_t g_lane = smem_u32(gs) + (uint32_t)((co * PLANE + ky * L4W_GP + kx) * 4);
-        const uint32_t t_lane = tmem_base + ((uint32_t)(quarter * 32) << 16) + 256;
-        float bsum[COUT];
-#pragma unroll
-        for (int c = 0; c < COUT; ++c) bsum[c] = 0.f;
-        int gb = 0, pending = -1;
-        for (int n = n0, it = 0; n < n1; ++n, ++it) {
-            const int buf = it % L4W_NGB;
-            asm volatile("bar.sync 1, 256;" ::: "memory");                   // every read of the previous image's gs is done
-            mbar_wait(graw_full + buf, (it / L4W_NGB) & 1);
-            {
-                const float4* g4 = reinterpret_cast<const float4*>(graw + buf * 2 * IMG);
-                const float4* y4 = reinterpret_cast<const float4*>(graw + buf * 2 * IMG + IMG);
-                for (int i = ctid; i < IMG / 4 && !(ar.dbg & 64); i += TS_NCONV) {
-                    const int e = 4 * i, xx = e & 31, yy = (e >> 5) & 31, c = e >> 10;
-                    float4 v = g4[i];
-                    if (ar.y) {
-                        const float4 yv = y4[i];
-                        v.x *= l4w_dact(yv.x, ar.act); v.y *= l4w_dact(yv.y, ar.act); v.z *= l4w_dact(yv.z, ar.act); v.w *= l4w_dact(yv.w, ar.act);
-                    }
-                    float* d = gs + c * PLANE + (yy + 1) * L4W_GP + xx + 1;
-                    d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
-                    const float sv = (v.x + v.y) + (v.z + v.w);
-#pragma unroll
-                    for (int cc = 0; cc < COUT; ++cc) bsum[cc] += (cc == c) ? sv : 0.f;
-                }
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(graw_empty + buf);
-            asm volatile("bar.sync 1, 256;" ::: "memory");                   // gs of this image is complete
-            for (int h = 0; h < 2; ++h) {
-#pragma unroll 1
-                for (int b = 0; b < 2; ++b, ++gb) {
-                    float f[2][16];
-#pragma unroll
-                    for (int a2 = 0; a2 < 2; ++a2) {
-                        const int kb = 4 * b + 2 * a2 + wset, irow = 8 * h + kb;               // row i of the 16x16 grid
-                        const uint32_t base = g_lane + (uint32_t)(2 * irow * L4W_GP * 4);
-#pragma unroll
-                        for (int k = 0; k < 16; ++k) {
-                            if (live && !(ar.dbg & 2)) asm volatile("ld.shared.f32 %0, [%1];" : "=f"(f[a2][k]) : "r"(base + (uint32_t)(8 * k)));
-                            else f[a2][k] = 0.f;
-                        }
-                    }
-                    if (pending >= 0) {
-                        tmem_st_wait();
-                        tc_fence_before_sync();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(a_full + (pending & 3));
-                    }
-                    if (gb >= 4) mbar_wait(done + (gb & 3), ((gb >> 2) - 1) & 1);
-                    tc_fence_after_sync();
-#pragma unroll
-                    for (int a2 = 0; a2 < 2; ++a2) {
-                        const int at = 2 * a2 + wset;
-                        uint32_t hm[16];
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hm[j]) : "f"(f[a2][2 * j + 1]), "f"(f[a2][2 * j]));
-                            const float r0 = f[a2][2 * j] - __uint_as_float(hm[j] << 16);
-                            const float r1 = f[a2][2 * j + 1] - __uint_as_float(hm[j] & 0xffff0000u);
-                            asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hm[8 + j]) : "f"(r1), "f"(r0));
-                        }
-                        const uint32_t ta = t_lane + ((4 * gb + at) & (TW_A_SLOTS - 1)) * 16;
-                        tmem_st_32x8(ta, hm);
-                        tmem_st_32x8(ta + 8, hm + 8);
-                    }
-                    pending = gb;
-                }
-            }
-        }
-        if (pending >= 0) {
-            tmem_st_wait();
-            tc_fence_before_sync();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(a_full + (pending & 3));
-        }
-        // bias partials of the 256 converter threads -> shared memory (the g staging area is free now)
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-#pragma unroll
-        for (int c = 0; c < COUT; ++c) graw[c * TS_NCONV + ctid] = bsum[c];
-    } else {
-        // ===== epilogue: chains are drained into registers; one partial per CTA at the end =====
-        const int quarter = warp & 3, r = quarter * RPQ + lane;
-        const bool live = lane < RPQ && r < ROWS;
-        float accr[32];
+        const uint32_t t_lane = tmem_base + ((uint32_t)(quarter * 32) << 16);
+        float accr[32];                                                        // set 0: this row's weight gradient over all chains
 #pragma unroll
         for (int j = 0; j < 32; ++j) accr[j] = 0.f;
-        // these warps also split every landed x tile in place (one row per thread) and hand it to the tensor core
-        const uint32_t x_ring = smem_u32(xring);
-        const int xrow = quarter * 32 + lane;
-        int part = 0;
-        for (int ti = 0; ti < ntiles; ++ti) {
-            const int s = ti % L4W_NXS, ph = (ti / L4W_NXS) & 1;
-            mbar_wait(x_full + s, ph);
-            if (!(ar.dbg & 4)) ts_split_row(x_ring + s * 16384 + xrow * 128, xrow & 7);
-            fence_proxy_async_smem();
+        int gb = 0, part = 0;
+        for (int n = n0, it = 0; n < n1; ++n, ++it) {
+            mbar_wait(gs_full + (it & 1), (it >> 1) & 1);
+            const uint32_t g_img = g_lane + (uint32_t)((it & 1) * GSZ * 4);
+#pragma unroll 1
+            for (int b4 = 0; b4 < 4; ++b4, ++gb) {                          // batch = 4 k-blocks (one per set) of tile b4 / 2
+                const int irow = 4 * b4 + wset;                              // row i of the 16x16 grid = this set's k-block
+                const uint32_t base = g_img + (uint32_t)(2 * irow * L4W_GP * 4);
+                float f[16];
+#pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    if (live && !(ar.dbg & 2)) asm volatile("ld.shared.f32 %0, [%1];" : "=f"(f[k]) : "r"(base + (uint32_t)(8 * k)));
+                    else f[k] = 0.f;
+                }
+                if (gb >= 4) mbar_wait(done + (gb & 3), ((gb >> 2) - 1) & 1);
+                tc_fence_after_sync();
+                uint32_t hm[16];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hm[j]) : "f"(f[2 * j + 1]), "f"(f[2 * j]));
+                    const float r0 = f[2 * j] - __uint_as_float(hm[j] << 16);
+                    const float r1 = f[2 * j + 1] - __uint_as_float(hm[j] & 0xffff0000u);
+                    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hm[8 + j]) : "f"(r1), "f"(r0));
+                }
+                const uint32_t ta = t_lane + 256 + ((4 * gb + wset) & (TW_A_SLOTS - 1)) * 16;
+                tmem_st_32x8(ta, hm);
+                tmem_st_32x8(ta + 8, hm + 8);
+                tmem_st_wait();
+                tc_fence_before_sync();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(a_full + (gb & 3));
+            }
             __syncwarp();
-            if (lane == 0) mbar_arrive(x_ready + s);
-            if (((ti + 1) % L4W_CHAIN) == 0 || ti + 1 == ntiles) {
+            if (lane == 0) mbar_arrive(gs_empty + (it & 1));                  // the last reads of this image are in registers
+            // chain ends after this image's second tile?  set 0 drains it (the MMAs of the chain complete a little later)
+            const int ti_last = 2 * it + 1;
+            if (wset == 0 && (((ti_last + 1) % L4W_CHAIN) == 0 || ti_last + 1 == ntiles)) {
                 const int acc = part & 1;
                 mbar_wait_relaxed(tfull + acc, (part >> 1) & 1);
                 tc_fence_after_sync();
                 float v[32];
-                tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * 32), v);
+                tmem_ld_32x32(t_lane + (uint32_t)(acc * 32), v);
 #pragma unroll
                 for (int j = 0; j < 32; ++j) accr[j] += v[j];
                 tc_fence_before_sync();
@@ -1511,19 +1461,68 @@ convt_l4w_ts_kernel(const __grid_constant__ CUtensorMap tmap_x, const L4wArgs ar
                 ++part;
             }
         }
-        if (live) {
-            const int tap = r / COUT, co = r % COUT;
+        if (wset == 0 && live) {
             float* out = ar.part + (long)blockIdx.x * (TOT + COUT);
 #pragma unroll
             for (int ci = 0; ci < 32; ++ci) out[(ci * COUT + co) * 16 + tap] = accr[ci];
         }
+    } else if (warp == 7 || warp == 10 || warp == 11 || warp == 14) {
+        // ===== builders: g * act'(y) of the NEXT image into its zero-bordered buffer (+ bias sums), x tiles split in place =====
+        const uint32_t x_ring = smem_u32(xring);
+        const int sidx = ((warp == 7 ? 0 : warp == 10 ? 1 : warp == 11 ? 2 : 3) << 5) + lane;
+        float bsum[COUT];
+#pragma unroll
+        for (int c = 0; c < COUT; ++c) bsum[c] = 0.f;
+        auto build = [&](int it) {
+            const int buf = it % L4W_NGB;
+            mbar_wait(gs_empty + (it & 1), ((it >> 1) & 1) ^ 1);              // the converters have read image it - 2
+            mbar_wait(graw_full + buf, (it / L4W_NGB) & 1);
+            const float4* g4 = reinterpret_cast<const float4*>(graw + buf * 2 * IMG);
+            const float4* y4 = reinterpret_cast<const float4*>(graw + buf * 2 * IMG + IMG);
+            float* gd = gs + (it & 1) * GSZ;
+            for (int i = sidx; i < IMG / 4 && !(ar.dbg & 64); i += 128) {
+                const int e = 4 * i, xx = e & 31, yy = (e >> 5) & 31, c = e >> 10;
+                float4 v = g4[i];
+                if (ar.y) {
+                    const float4 yv = y4[i];
+                    v.x *= l4w_dact(yv.x, ar.act); v.y *= l4w_dact(yv.y, ar.act); v.z *= l4w_dact(yv.z, ar.act); v.w *= l4w_dact(yv.w, ar.act);
+                }
+                float* d = gd + c * PLANE + (yy + 1) * L4W_GP + xx + 1;
+                d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+                const float sv = (v.x + v.y) + (v.z + v.w);
+#pragma unroll
+                for (int cc = 0; cc < COUT; ++cc) bsum[cc] += (cc == c) ? sv : 0.f;
+            }
+            __syncwarp();
+            if (lane == 0) { mbar_arrive(gs_full + (it & 1)); mbar_arrive(graw_empty + buf); }
+        };
+        if (n0 < n1) build(0);
+        for (int n = n0, it = 0; n < n1; ++n, ++it) {
+            for (int h = 0; h < 2; ++h) {
+                const int ti = 2 * it + h, s = ti % L4W_NXS, ph = (ti / L4W_NXS) & 1;
+                mbar_wait(x_full + s, ph);
+                if (!(ar.dbg & 4)) ts_split_row(x_ring + s * 16384 + sidx * 128, sidx & 7);
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(x_ready + s);
+            }
+            if (n + 1 < n1) build(it + 1);
+        }
+        // bias partials of the 128 builder threads -> shared memory (the g staging area is free once EVERY builder warp has
+        // read the last image)
+        asm volatile("bar.sync 2, 128;" ::: "memory");
+#pragma unroll
+        for (int c = 0; c < COUT; ++c) graw[c * 128 + sidx] = bsum[c];
     }
     tc_fence_before_sync();
     __syncthreads();
     if (warp == 2) tmem_dealloc(tmem_base, 512);
+    if (n0 >= n1 && threadIdx.x < TOT) {                                       // a CTA without images still owns a partial
+        for (int i = threadIdx.x; i < TOT; i += TW_THREADS) ar.part[(long)blockIdx.x * (TOT + COUT) + i] = 0.f;
+    }
     if (threadIdx.x < COUT) {                                                  // bias: fixed order over the converter threads
         float s = 0.f;
-        for (int i = 0; i < TS_NCONV; ++i) s += graw[threadIdx.x * TS_NCONV + i];
+        for (int i = 0; i < 128; ++i) s += graw[threadIdx.x * 128 + i];
         ar.part[(long)blockIdx.x * (TOT + COUT) + TOT + threadIdx.x] = s;
     }
 }
@@ -1543,7 +1542,7 @@ int mmvae_convt_l4_wgrad_ts(const float* x, const float* g, const float* y_act, 
     L4wArgs ar{};
     ar.g = g; ar.y = y_act; ar.part = part; ar.n_img = N; ar.act = act; ar.imgs_per_cta = (N + P - 1) / P;
     ar.dbg = mmvae_tc_dbg_bits();
-    const int smem = 1024 + L4W_NXS * 16384 + L4W_NGB * 2 * COUT * 1024 * 4 + ((COUT * 34 * L4W_GP + 3) & ~3) * 4 + 512;
+    const int smem = 1024 + L4W_NXS * 16384 + L4W_NGB * 2 * COUT * 1024 * 4 + 2 * ((COUT * 34 * L4W_GP + 3) & ~3) * 4 + 512;
     static bool attr_done = false;
     auto kern = convt_l4w_ts_kernel<COUT>;
     if (!attr_done) {
