@@ -57,7 +57,7 @@ KERNEL_OF = {
     "mmvae_gemm[skinny]": "gemm_skinny_kernel", "mmvae_gemm[small]": "gemm_small_kernel",
     "mmvae_convt_tc_fwd": "convt_fwd9_kernel", "mmvae_convt_tc_dgrad": "gemm_tc_kernel(dgrad)", "mmvae_convt_tc_wgrad": "gemm_tc_kernel(wgrad)",
     "mmvae_convt_small_fwd": "convt_l4_fwd_tc_kernel", "mmvae_convt_small_dgrad": "convt_l4_dgrad_tc_kernel",
-    "mmvae_convt_small_wgrad": "convt_small_wgrad_kernel", "mmvae_loglik_fwd": "loglik_fwd_kernel", "mmvae_loglik_bwd": "loglik_bwd_kernel",
+    "mmvae_convt_small_wgrad": "convt_l4w_ts_kernel", "mmvae_loglik_fwd": "loglik_fwd_kernel", "mmvae_loglik_bwd": "loglik_bwd_kernel",
 }
 
 
