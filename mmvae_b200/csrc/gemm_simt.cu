@@ -217,9 +217,55 @@ splitk_reduce_kernel(const float* __restrict__ ws, const float* __restrict__ bia
     }
 }
 
+// Small outputs with many partials (the weight gradient of the encoder's first convolution: 32 x 48 outputs, K = 32768): the
+// kernel above would put all S partials of an element on one thread of a handful of blocks (44 us measured).  Here a block
+// owns 32 float4 of the output and its 8 warps take the partials z = w, w + 8, ... (coalesced 512-byte rows); the eight sums are
+// added in warp order through shared memory -- a fixed association, so still deterministic.
+__global__ void __launch_bounds__(256)
+splitk_reduce_small_kernel(const float* __restrict__ ws, const float* __restrict__ bias, float* __restrict__ C, long MN, int N,
+                           int S, int act) {
+    __shared__ float4 red[8][32];
+    const long MN4 = MN >> 2;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const long i = (long)blockIdx.x * 32 + lane;
+    const float4* w4 = reinterpret_cast<const float4*>(ws);
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < MN4) {
+        int z = w;
+        for (; z + 24 < S; z += 32) {
+            const float4 v0 = __ldcs(w4 + (long)z * MN4 + i), v1 = __ldcs(w4 + (long)(z + 8) * MN4 + i);
+            const float4 v2 = __ldcs(w4 + (long)(z + 16) * MN4 + i), v3 = __ldcs(w4 + (long)(z + 24) * MN4 + i);
+            s.x += v0.x; s.y += v0.y; s.z += v0.z; s.w += v0.w;
+            s.x += v1.x; s.y += v1.y; s.z += v1.z; s.w += v1.w;
+            s.x += v2.x; s.y += v2.y; s.z += v2.z; s.w += v2.w;
+            s.x += v3.x; s.y += v3.y; s.z += v3.z; s.w += v3.w;
+        }
+        for (; z < S; z += 8) {
+            const float4 v = __ldcs(w4 + (long)z * MN4 + i);
+            s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
+    }
+    red[w][lane] = s;
+    __syncthreads();
+    if (w == 0 && i < MN4) {
+        float4 t = red[0][lane];
+#pragma unroll
+        for (int j = 1; j < 8; ++j) { const float4 v = red[j][lane]; t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w; }
+        if (bias) {
+            const int n = (int)((i * 4) % N);
+            t.x += bias[n]; t.y += bias[n + 1]; t.z += bias[n + 2]; t.w += bias[n + 3];
+        }
+        reinterpret_cast<float4*>(C)[i] = make_float4(apply_act(t.x, act), apply_act(t.y, act), apply_act(t.z, act), apply_act(t.w, act));
+    }
+}
+
 static void splitk_reduce_launch(const float* ws, const float* bias, float* C, long MN, int N, int S, int act, cudaStream_t st) {
     const bool vec = (N % 4 == 0) && ((((uintptr_t)ws | (uintptr_t)C) & 15) == 0);
     const long work = vec ? MN / 4 : MN;
+    if (vec && S >= 16 && work <= 32L * MMVAE_NUM_SMS * 2) {
+        splitk_reduce_small_kernel<<<(int)((work + 31) / 32), 256, 0, st>>>(ws, bias, C, MN, N, S, act);
+        return;
+    }
     const int grid = (int)min((long)MMVAE_NUM_SMS * 8, (work + 255) / 256);
     if (vec) splitk_reduce_kernel<true><<<grid, 256, 0, st>>>(ws, bias, C, MN, N, S, act);
     else splitk_reduce_kernel<false><<<grid, 256, 0, st>>>(ws, bias, C, MN, N, S, act);
