@@ -132,7 +132,9 @@ static int launch_fwd(const float* recon, const float* x, float* lp, float* lp_l
     const double row_const = (LIK == MMVAE_LIK_NORMAL) ? -(double)D * (double)MMVAE_LOG_SQRT_2PI
                            : (LIK == MMVAE_LIK_LAPLACE) ? -(double)D * (double)MMVAE_LOG2 : 0.0;
     const int D4 = D / 4;
-    if (D4 <= 512) {
+    // one warp per row keeps 4 x 128-bit loads per thread in flight and needs no block barrier; one block per row only pays when
+    // there are too few rows to fill the machine with warps (measured at R = 7680, D = 3072: 27 us per block-row, see below)
+    if (D4 <= 512 || (long)R >= 8L * MMVAE_NUM_SMS) {
         const int rpb = LL_THREADS / 32;
         loglik_fwd_kernel<LIK, 32><<<ceil_div_i(R, rpb), LL_THREADS, 0, st>>>(
             (const float4*)recon, (const float4*)x, lp, lp_lo, R, B, D4, x_div, c, row_const);
