@@ -355,15 +355,20 @@ gemm_skinny_kernel(const float* __restrict__ X, const float* __restrict__ W, con
     const int rows = min(SK_ROWS, R - r0);
 #pragma unroll 2
     for (int r = 0; r < rows; ++r) {
-        float4 a = b4;
+        // packed fp32 FMAs (FFMA2: two columns per instruction, same IEEE result per lane): the loop is issue-bound otherwise
+        float2 a01 = make_float2(b4.x, b4.y), a23 = make_float2(b4.z, b4.w);
 #pragma unroll
         for (int k = 0; k < KMAX; k += 4) {
             const float4 xv = *reinterpret_cast<const float4*>(&xs[r][k]);          // same address in every lane: broadcast
-            a.x = fmaf(xv.x, w[k].x, a.x); a.y = fmaf(xv.x, w[k].y, a.y); a.z = fmaf(xv.x, w[k].z, a.z); a.w = fmaf(xv.x, w[k].w, a.w);
-            a.x = fmaf(xv.y, w[k + 1].x, a.x); a.y = fmaf(xv.y, w[k + 1].y, a.y); a.z = fmaf(xv.y, w[k + 1].z, a.z); a.w = fmaf(xv.y, w[k + 1].w, a.w);
-            a.x = fmaf(xv.z, w[k + 2].x, a.x); a.y = fmaf(xv.z, w[k + 2].y, a.y); a.z = fmaf(xv.z, w[k + 2].z, a.z); a.w = fmaf(xv.z, w[k + 2].w, a.w);
-            a.x = fmaf(xv.w, w[k + 3].x, a.x); a.y = fmaf(xv.w, w[k + 3].y, a.y); a.z = fmaf(xv.w, w[k + 3].z, a.z); a.w = fmaf(xv.w, w[k + 3].w, a.w);
+            const float xk[4] = {xv.x, xv.y, xv.z, xv.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float2 xx = make_float2(xk[q], xk[q]);
+                a01 = __ffma2_rn(xx, make_float2(w[k + q].x, w[k + q].y), a01);
+                a23 = __ffma2_rn(xx, make_float2(w[k + q].z, w[k + q].w), a23);
+            }
         }
+        float4 a = make_float4(a01.x, a01.y, a23.x, a23.y);
         a.x = apply_act(a.x, act); a.y = apply_act(a.y, act); a.z = apply_act(a.z, act); a.w = apply_act(a.w, act);
         __stcs(reinterpret_cast<float4*>(Y + (long)(r0 + r) * N + n), a);
     }
