@@ -22,7 +22,7 @@ moe_logw_fwd_kernel(const float* __restrict__ z, const float* __restrict__ mu, c
                     const float* __restrict__ pz_loc, const float* __restrict__ pz_scale, float* __restrict__ lw,
                     float* __restrict__ wt, float* __restrict__ loss_per, int M, int K, int B, int L, int dist,
                     int mode) {
-    extern __shared__ double smd[];               // red[32], lw[P] (fp64), then floats: mu[M*L], std[M*L], ploc[L], pscale[L]
+    extern __shared__ double smd[];               // red[32], lw[P] (fp64), then floats: mu[M*L], std[M*L], ploc[L], pscale[L], z[P*L]
     const int P = M * K;
     double* red = smd;
     double* s_lw = smd + 32;
@@ -30,7 +30,12 @@ moe_logw_fwd_kernel(const float* __restrict__ z, const float* __restrict__ mu, c
     float* s_std = s_mu + M * L;
     float* s_pl = s_std + M * L;
     float* s_ps = s_pl + L;
-    const int b = blockIdx.x;
+    float* s_z = s_ps + L;                        // the block's P latent rows: every load of the block is in flight at once
+    const int b = blockIdx.x;                     // (a thread walking its own row paid one L2 round trip per element)
+    for (int i = threadIdx.x; i < P * L; i += blockDim.x) {
+        const int p = i / L, l = i - p * L;
+        s_z[i] = z[((long)p * B + b) * L + l];
+    }
     for (int i = threadIdx.x; i < M * L; i += blockDim.x) {
         const int e = i / L, l = i - e * L;
         s_mu[i] = mu[((long)e * B + b) * L + l];
@@ -41,7 +46,7 @@ moe_logw_fwd_kernel(const float* __restrict__ z, const float* __restrict__ mu, c
     const double log_M = log((double)M);
     for (int p = threadIdx.x; p < P; p += blockDim.x) {
         const int r = p / K, k = p - r * K;
-        const float* zr = z + (((long)r * K + k) * B + b) * L;
+        const float* zr = s_z + p * L;
         double lpz = 0.0, lq[MOE_MAX_M];
 #pragma unroll
         for (int e = 0; e < MOE_MAX_M; ++e) lq[e] = 0.0;
@@ -111,7 +116,7 @@ __global__ void moe_loss_reduce_kernel(float* __restrict__ loss, const float* __
     if (threadIdx.x == 0) loss[0] = (float)s;
 }
 
-// backward.  dynamic smem: mu[M*L], std[M*L], ploc[L], pscale[L], cpi[P*M]
+// backward.  dynamic smem: mu[M*L], std[M*L], ploc[L], pscale[L], cpi[P*M], z[P*L]
 __global__ void __launch_bounds__(MOE_THREADS)
 moe_logw_bwd_kernel(const float* __restrict__ gloss, const float* __restrict__ z, const float* __restrict__ mu,
                     const float* __restrict__ stdv, const float* __restrict__ wt, const float* __restrict__ pz_loc,
@@ -126,7 +131,12 @@ moe_logw_bwd_kernel(const float* __restrict__ gloss, const float* __restrict__ z
     float* s_cpi = s_ps + L;                      // [P][M]: c_p * pi_e
     const int b = blockIdx.x;
     const int P = M * K;
+    float* s_z = s_cpi + P * M;                   // the block's P latent rows (see the forward kernel)
     const float g = gloss[0];
+    for (int i = threadIdx.x; i < P * L; i += blockDim.x) {
+        const int p = i / L, l = i - p * L;
+        s_z[i] = z[((long)p * B + b) * L + l];
+    }
     for (int i = threadIdx.x; i < M * L; i += blockDim.x) {
         const int e = i / L, l = i - e * L;
         s_mu[i] = mu[((long)e * B + b) * L + l];
@@ -142,7 +152,7 @@ moe_logw_bwd_kernel(const float* __restrict__ gloss, const float* __restrict__ z
 #pragma unroll
         for (int e = 0; e < MOE_MAX_M; ++e) lq[e] = 0.f;
         for (int l = 0; l < L; ++l) {
-            const float zz = z[zo + l];
+            const float zz = s_z[p * L + l];
 #pragma unroll
             for (int e = 0; e < MOE_MAX_M; ++e)
                 if (e < M) lq[e] += lat_logprob(dist, zz, s_mu[e * L + l], s_std[e * L + l]);
@@ -157,7 +167,7 @@ moe_logw_bwd_kernel(const float* __restrict__ gloss, const float* __restrict__ z
 #pragma unroll
         for (int e = 0; e < MOE_MAX_M; ++e) if (e < M) { lq[e] *= inv; s_cpi[p * M + e] = c * lq[e]; }
         for (int l = 0; l < L; ++l) {
-            const float zz = z[zo + l];
+            const float zz = s_z[p * L + l];
             float d = lat_dlogprob_dz(dist, zz, s_pl[l], s_ps[l]);
 #pragma unroll
             for (int e = 0; e < MOE_MAX_M; ++e)
@@ -175,8 +185,7 @@ moe_logw_bwd_kernel(const float* __restrict__ gloss, const float* __restrict__ z
         if (!dreg) {
             const float m_ = s_mu[i], s_ = s_std[i];
             for (int p = 0; p < P; ++p) {
-                const int r = p / K, k = p - r * K;
-                const float zz = z[(((long)r * K + k) * B + b) * L + l];
+                const float zz = s_z[p * L + l];
                 const float w = s_cpi[p * M + e];
                 am += w * lat_dlogprob_dz(dist, zz, m_, s_);        // -(-d/dz) : lw has -lqmix, d/dmu = -d/dz
                 as -= w * lat_dlogprob_dscale(dist, zz, m_, s_);
@@ -194,7 +203,7 @@ extern "C" int mmvae_moe_logw_fwd(const float* z, const float* mu, const float* 
     MMVAE_REQUIRE(M >= 1 && M <= MOE_MAX_M && K > 0 && B > 0 && L > 0, "moe_logw_fwd: bad sizes M=%d K=%d B=%d L=%d", M, K, B, L);
     MMVAE_REQUIRE(dist == 0 || dist == 1, "moe_logw_fwd: bad dist");
     MMVAE_REQUIRE(mode >= 0 && mode <= 3, "moe_logw_fwd: bad mode %d", mode);
-    const size_t smem = ((size_t)32 + (size_t)M * K) * sizeof(double) + ((size_t)2 * M * L + 2 * L) * sizeof(float);
+    const size_t smem = ((size_t)32 + (size_t)M * K) * sizeof(double) + ((size_t)2 * M * L + 2 * L + (size_t)M * K * L) * sizeof(float);
     MMVAE_REQUIRE(smem <= 200 * 1024, "moe_logw_fwd: M*K (+ M*L) too large for shared memory");
     cudaStream_t st = (cudaStream_t)stream;
     if (smem > 48 * 1024) {
@@ -217,7 +226,7 @@ extern "C" int mmvae_moe_logw_bwd(const float* grad_loss, const float* z, const 
                   "moe_logw_bwd: null pointer");
     MMVAE_REQUIRE(M >= 1 && M <= MOE_MAX_M && K > 0 && B > 0 && L > 0, "moe_logw_bwd: bad sizes");
     MMVAE_REQUIRE(mode >= 0 && mode <= 3, "moe_logw_bwd: bad mode %d", mode);
-    const size_t smem = ((size_t)2 * M * L + 2 * L + (size_t)M * K * M) * sizeof(float);
+    const size_t smem = ((size_t)2 * M * L + 2 * L + (size_t)M * K * M + (size_t)M * K * L) * sizeof(float);
     MMVAE_REQUIRE(smem <= 200 * 1024, "moe_logw_bwd: M*K*M too large for shared memory");
     cudaStream_t st = (cudaStream_t)stream;
     if (smem > 48 * 1024) {
