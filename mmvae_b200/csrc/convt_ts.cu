@@ -83,9 +83,7 @@ __device__ __forceinline__ void ts_split_row(uint32_t row_addr, int sw) {
     uint32_t hp[16], mp[16];
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
-        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hp[j]) : "f"(f[2 * j + 1]), "f"(f[2 * j]));
-        const float r0 = f[2 * j] - __uint_as_float(hp[j] << 16), r1 = f[2 * j + 1] - __uint_as_float(hp[j] & 0xffff0000u);
-        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(mp[j]) : "f"(r1), "f"(r0));
+        bf16_split_pair(f[2 * j], f[2 * j + 1], hp[j], mp[j]);
     }
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
@@ -387,11 +385,7 @@ convt_ts_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                                                      "=f"(f[4 * c + 3]) : "r"(addr + ((uint32_t)((4 * half + c) ^ sw) << 4)));
 #pragma unroll
                                     for (int j = 0; j < 8; ++j) {
-                                        uint32_t hp;
-                                        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hp) : "f"(f[2 * j + 1]), "f"(f[2 * j]));
-                                        const float r0 = f[2 * j] - __uint_as_float(hp << 16), r1 = f[2 * j + 1] - __uint_as_float(hp & 0xffff0000u);
-                                        v[wi][j] = hp;
-                                        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(v[wi][8 + j]) : "f"(r1), "f"(r0));
+                                        bf16_split_pair(f[2 * j], f[2 * j + 1], v[wi][j], v[wi][8 + j]);
                                     }
                                     if (ar.dbg & 4) {
 #pragma unroll
@@ -1039,10 +1033,7 @@ convt_ts_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_c
                             uint32_t hm[16];
 #pragma unroll
                             for (int j = 0; j < 8; ++j) {
-                                asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hm[j]) : "f"(f[a2][2 * j + 1]), "f"(f[a2][2 * j]));
-                                const float r0 = f[a2][2 * j] - __uint_as_float(hm[j] << 16);
-                                const float r1 = f[a2][2 * j + 1] - __uint_as_float(hm[j] & 0xffff0000u);
-                                asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hm[8 + j]) : "f"(r1), "f"(r0));
+                                bf16_split_pair(f[a2][2 * j], f[a2][2 * j + 1], hm[j], hm[8 + j]);
                             }
                             const uint32_t ta = t_lane + ((4 * gb + at) & (TW_A_SLOTS - 1)) * 16;
                             tmem_st_32x8(ta, hm);
@@ -1430,10 +1421,7 @@ convt_l4w_ts_kernel(const __grid_constant__ CUtensorMap tmap_x, const L4wArgs ar
                 uint32_t hm[16];
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
-                    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hm[j]) : "f"(f[2 * j + 1]), "f"(f[2 * j]));
-                    const float r0 = f[2 * j] - __uint_as_float(hm[j] << 16);
-                    const float r1 = f[2 * j + 1] - __uint_as_float(hm[j] & 0xffff0000u);
-                    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hm[8 + j]) : "f"(r1), "f"(r0));
+                    bf16_split_pair(f[2 * j], f[2 * j + 1], hm[j], hm[8 + j]);
                 }
                 const uint32_t ta = t_lane + 256 + ((4 * gb + wset) & (TW_A_SLOTS - 1)) * 16;
                 tmem_st_32x8(ta, hm);
