@@ -22,7 +22,7 @@
 #include "common.cuh"
 #include "sm100_ptx.cuh"
 
-#define L4_THREADS 320
+#define L4_THREADS 448                  // warps 0 producer, 1 issuer, 2-5 converter, 6-9 epilogue (scatter), 10-13 finalize
 #define L4_STAGES 4
 #define L4_NACC 4
 #define L4_TILE (128 * 32 * 4)          // one A tile: 128 pixels x 32 channels fp32 = 16 KB
@@ -154,68 +154,8 @@ convt_l4_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float* 
             umma_commit_elect(tfull + acc);
         }
     } else if (warp < 6) {
-        // ===== converter: lo tile beside the landed tile; these warps also FINALIZE the images the epilogue warps have
-        // scattered (bias + activation + NCHW store + re-zero), one image behind, so that the scatter of image n+1
-        // overlaps the store of image n (two smem images; img_full / img_empty hand them over) =====
+        // ===== converter: lo tile beside the landed tile =====
         const int tq = threadIdx.x - 64;
-        __shared__ double ll_red[2][4];
-        float bv[COUT];
-#pragma unroll
-        for (int c = 0; c < COUT; ++c) bv[c] = bias ? __ldg(bias + c) : 0.f;
-        auto finalize = [&](int n) {
-            float* out = out0 + (n & 1) * OUT_SMEM;
-            mbar_wait(img_full + (n & 1), (n >> 1) & 1);
-            if (!(dbg & 2)) {
-                const int img = blockIdx.x + n * gridDim.x;
-                // the smem rows are shifted by one column (position = ox + 1): thread (row, j) reads the aligned float4
-                // at positions 4j..4j+3 = columns 4j-1..4j+2 and takes column 4j+3 from its right neighbour's first
-                // element (the lane above; position 32 for the last float4 of a row) -> aligned 128-bit global stores
-                float4* dst = reinterpret_cast<float4*>(y + (long)img * OUT_FLOATS);
-                const float4* xr = ll.lp ? reinterpret_cast<const float4*>(ll.x + (long)((img / ll.x_div) % ll.B) * OUT_FLOATS) : nullptr;
-                float part = 0.f;                              // this thread's 24 pixel terms (fp32, as the reference's)
-                float4 xv[OUT_FLOATS / 4 / 128];
-                if (ll.lp) {                                   // all data loads in flight before the first use
-#pragma unroll
-                    for (int i = 0; i < OUT_FLOATS / 4 / 128; ++i) xv[i] = __ldg(xr + tq + i * 128);
-                }
-#pragma unroll
-                for (int i = 0; i < OUT_FLOATS / 4 / 128; ++i) {
-                    const int q = tq + i * 128;                // float4 of the NCHW image: 256 per channel -> channel = i >> 1
-                    const int row = q >> 3, j = q & 7;
-                    float4* src = reinterpret_cast<float4*>(out + row * L4_PITCH + 4 * j);
-                    const float4 m = *src;
-                    float nx = __shfl_down_sync(0xffffffffu, m.x, 1);
-                    if (j == 7) nx = out[row * L4_PITCH + 32];
-                    const float b = bv[i >> 1];
-                    float4 o;
-                    o.x = l4_act_fast(m.y + b, act); o.y = l4_act_fast(m.z + b, act);
-                    o.z = l4_act_fast(m.w + b, act); o.w = l4_act_fast(nx + b, act);
-                    if (ll.lp) {
-                        const float d0 = xv[i].x - o.x, d1 = xv[i].y - o.y, d2 = xv[i].z - o.z, d3 = xv[i].w - o.w;
-                        if (ll.lik == MMVAE_LIK_NORMAL) part += -0.5f * ((d0 * d0 + d1 * d1) + (d2 * d2 + d3 * d3));
-                        else part += -((fabsf(d0) + fabsf(d1)) + (fabsf(d2) + fabsf(d3)));
-                    } else {
-                        __stcs(dst + q, o);
-                    }
-                    *src = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (j == 7) out[row * L4_PITCH + 32] = 0.f;
-                }
-                if (ll.lp) {                                   // 128 partial sums of 24 terms -> fp64 total (ll_red alternates per image)
-                    const float ws = warp_sum(part);
-                    if (lane == 0) ll_red[n & 1][warp - 2] = (double)ws;
-                    asm volatile("bar.sync 3, 128;" ::: "memory");
-                    if (tq == 0) {
-                        const double* r = ll_red[n & 1];
-                        const double v = (double)ll.scale * (((r[0] + r[1]) + (r[2] + r[3])) + ll.row_const);
-                        const float hi = (float)v;
-                        ll.lp[img] = hi;
-                        if (ll.lp_lo) ll.lp_lo[img] = (float)(v - (double)hi);
-                    }
-                }
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(img_empty + (n & 1));
-        };
         for (int it = 0; it < my_tiles; ++it) {
             const int s = it % L4_STAGES;
             mbar_wait(full + s, (it / L4_STAGES) & 1);
@@ -231,10 +171,8 @@ convt_l4_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float* 
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(conv + s);
-            if ((it & 1) && it >= 3) finalize((it >> 1) - 1);   // one image behind the conversion
         }
-        if (my_imgs > 0) finalize(my_imgs - 1);
-    } else {
+    } else if (warp < 10) {
         // ===== epilogue: TMEM lane = input pixel; its 16*COUT values are added into the smem image of its output =====
         const int lane_base = (warp & 3) * 32, e = (warp - 6) * 32 + lane;
         const int p = lane_base + lane;                     // pixel of the tile
@@ -318,6 +256,70 @@ convt_l4_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const float* 
             }
             if (half && e == 0) mbar_arrive(img_full + (n & 1));   // every pixel of image n has been scattered
         }
+    } else {
+        // ===== finalize: the images the epilogue warps have scattered (bias + activation + NCHW store + re-zero), on their
+        // own four warps so that neither the conversion of the next tiles nor the scatter of image n+1 waits for the
+        // store of image n (two smem images; img_full / img_empty hand them over) =====
+        const int tq = threadIdx.x - 320;
+        __shared__ double ll_red[2][4];
+        float bv[COUT];
+#pragma unroll
+        for (int c = 0; c < COUT; ++c) bv[c] = bias ? __ldg(bias + c) : 0.f;
+        auto finalize = [&](int n) {
+            float* out = out0 + (n & 1) * OUT_SMEM;
+            mbar_wait(img_full + (n & 1), (n >> 1) & 1);
+            if (!(dbg & 2)) {
+                const int img = blockIdx.x + n * gridDim.x;
+                // the smem rows are shifted by one column (position = ox + 1): thread (row, j) reads the aligned float4
+                // at positions 4j..4j+3 = columns 4j-1..4j+2 and takes column 4j+3 from its right neighbour's first
+                // element (the lane above; position 32 for the last float4 of a row) -> aligned 128-bit global stores
+                float4* dst = reinterpret_cast<float4*>(y + (long)img * OUT_FLOATS);
+                const float4* xr = ll.lp ? reinterpret_cast<const float4*>(ll.x + (long)((img / ll.x_div) % ll.B) * OUT_FLOATS) : nullptr;
+                float part = 0.f;                              // this thread's 24 pixel terms (fp32, as the reference's)
+                float4 xv[OUT_FLOATS / 4 / 128];
+                if (ll.lp) {                                   // all data loads in flight before the first use
+#pragma unroll
+                    for (int i = 0; i < OUT_FLOATS / 4 / 128; ++i) xv[i] = __ldg(xr + tq + i * 128);
+                }
+#pragma unroll
+                for (int i = 0; i < OUT_FLOATS / 4 / 128; ++i) {
+                    const int q = tq + i * 128;                // float4 of the NCHW image: 256 per channel -> channel = i >> 1
+                    const int row = q >> 3, j = q & 7;
+                    float4* src = reinterpret_cast<float4*>(out + row * L4_PITCH + 4 * j);
+                    const float4 m = *src;
+                    float nx = __shfl_down_sync(0xffffffffu, m.x, 1);
+                    if (j == 7) nx = out[row * L4_PITCH + 32];
+                    const float b = bv[i >> 1];
+                    float4 o;
+                    o.x = l4_act_fast(m.y + b, act); o.y = l4_act_fast(m.z + b, act);
+                    o.z = l4_act_fast(m.w + b, act); o.w = l4_act_fast(nx + b, act);
+                    if (ll.lp) {
+                        const float d0 = xv[i].x - o.x, d1 = xv[i].y - o.y, d2 = xv[i].z - o.z, d3 = xv[i].w - o.w;
+                        if (ll.lik == MMVAE_LIK_NORMAL) part += -0.5f * ((d0 * d0 + d1 * d1) + (d2 * d2 + d3 * d3));
+                        else part += -((fabsf(d0) + fabsf(d1)) + (fabsf(d2) + fabsf(d3)));
+                    } else {
+                        __stcs(dst + q, o);
+                    }
+                    *src = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (j == 7) out[row * L4_PITCH + 32] = 0.f;
+                }
+                if (ll.lp) {                                   // 128 partial sums of 24 terms -> fp64 total (ll_red alternates per image)
+                    const float ws = warp_sum(part);
+                    if (lane == 0) ll_red[n & 1][warp - 10] = (double)ws;
+                    asm volatile("bar.sync 3, 128;" ::: "memory");
+                    if (tq == 0) {
+                        const double* r = ll_red[n & 1];
+                        const double v = (double)ll.scale * (((r[0] + r[1]) + (r[2] + r[3])) + ll.row_const);
+                        const float hi = (float)v;
+                        ll.lp[img] = hi;
+                        if (ll.lp_lo) ll.lp_lo[img] = (float)(v - (double)hi);
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(img_empty + (n & 1));
+        };
+        for (int n = 0; n < my_imgs; ++n) finalize(n);
     }
     tc_fence_before_sync();
     __syncthreads();
