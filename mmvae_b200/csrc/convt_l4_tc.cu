@@ -9,12 +9,12 @@
 // x 3 passes (3xTF32) = 12 UMMAs of 32 + N/4 clocks.  The col block never leaves the SM: each epilogue thread owns one
 // input pixel (one TMEM lane) and adds its 16*COUT values into the output image held in shared memory
 // (y[co, 2iy-1+ky, 2ix-1+kx]) in four barrier-separated tap phases (fixed summation order: deterministic); after the
-// two tiles of an image the four epilogue warps add the bias, apply the activation and stream the finished NCHW image
-// out with coalesced 128-bit stores.
+// two tiles of an image four finalize warps add the bias, apply the activation, stream the finished NCHW image out with
+// coalesced 128-bit stores and zero the buffer again, while the epilogue warps scatter the next image into a second one.
 //
-// Warp roles (320 threads, one persistent CTA per SM): warp 0 TMA producer, warp 1 UMMA issuer, warps 2-5 hi/lo
+// Warp roles (448 threads, one persistent CTA per SM): warp 0 TMA producer, warp 1 UMMA issuer, warps 2-5 hi/lo
 // converter (the landed fp32 tile is the tf32 "hi" operand by truncation; lo = rn_tf32(x - trunc_tf32(x)) is written
-// beside it), warps 6-9 epilogue.  The weights (hi and lo, 16*COUT rows x 32) are split once per CTA and written in the
+// beside it), warps 6-9 epilogue (scatter), warps 10-13 finalize.  The weights (hi and lo, 16*COUT rows x 32) are split once per CTA and written in the
 // 128-byte-swizzled K-major layout by ordinary stores.  TMEM: 4 accumulator pairs (big = hi*hi, small = lo*hi + hi*lo)
 // of 2 x 64 columns.
 #include <cuda.h>
